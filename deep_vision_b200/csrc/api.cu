@@ -1,0 +1,44 @@
+// api.cu — ctx lifecycle for libdvb200.so.  No CPU fallback: dvb_create fails without a CUDA device.
+#include "common.cuh"
+
+extern "C" int32_t dvb_version(void) { return 100; }
+
+extern "C" int32_t dvb_create(int32_t device, dvb_ctx** out) {
+    if (!out) return DVB_E_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) { cudaGetLastError(); return DVB_E_CUDA; }
+    if (cudaSetDevice(device) != cudaSuccess) return DVB_E_CUDA;
+    dvb_ctx* c = new dvb_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) {
+        c->num_sm = prop.multiProcessorCount;
+        c->smem_optin = prop.sharedMemPerBlockOptin;
+    }
+    for (int i = 0; i < DVB_LEASES; i++) {
+        if (cudaStreamCreateWithFlags(&c->leases[i].stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreate(&c->leases[i].ev0) != cudaSuccess || cudaEventCreate(&c->leases[i].ev1) != cudaSuccess) {
+            dvb_destroy(c); return DVB_E_CUDA;
+        }
+    }
+    *out = c;
+    return DVB_OK;
+}
+
+extern "C" void dvb_destroy(dvb_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    for (int i = 0; i < DVB_LEASES; i++) {
+        if (c->leases[i].stream) { cudaStreamSynchronize(c->leases[i].stream); cudaStreamDestroy(c->leases[i].stream); }
+        if (c->leases[i].ev0) cudaEventDestroy(c->leases[i].ev0);
+        if (c->leases[i].ev1) cudaEventDestroy(c->leases[i].ev1);
+        if (c->leases[i].arena.base) cudaFree(c->leases[i].arena.base);
+    }
+    delete c;
+}
+
+extern "C" const char* dvb_last_error(dvb_ctx* c) { return c ? c->err : "null ctx"; }
+extern "C" int64_t dvb_launch_count(dvb_ctx* c) { return c ? c->launches.load() : 0; }
+extern "C" void dvb_set_timing(dvb_ctx* c, int32_t enabled) { if (c) c->timing.store(enabled ? 1 : 0); }
+extern "C" float dvb_last_kernel_ms(dvb_ctx* c) { return c ? c->last_ms : 0.f; }

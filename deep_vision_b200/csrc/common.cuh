@@ -1,0 +1,101 @@
+// common.cuh — ctx, stream/workspace leases and error plumbing for libdvb200.so (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include <string>
+#include <vector>
+#include <atomic>
+#include <thread>
+#include <algorithm>
+#include "../../include/dvb200.h"
+
+#define DVB_NUM_SM_FALLBACK 148
+#define DVB_LEASES 4
+
+struct dvb_arena {
+    uint8_t* base = nullptr;
+    size_t cap = 0, used = 0;
+};
+
+struct dvb_lease {
+    cudaStream_t stream = nullptr;
+    dvb_arena arena;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool busy = false;
+};
+
+struct dvb_ctx {
+    int device = 0;
+    int num_sm = DVB_NUM_SM_FALLBACK;
+    size_t smem_optin = 0;
+    std::mutex mu;
+    dvb_lease leases[DVB_LEASES];
+    std::atomic<int64_t> launches{0};
+    std::atomic<int> timing{0};
+    float last_ms = 0.f;
+    // per-thread error text would need TLS keyed by ctx; one buffer per ctx guarded by mu is enough here
+    char err[512] = {0};
+};
+
+static inline void dvb_set_err(dvb_ctx* ctx, const char* fmt, const char* a = "", const char* b = "") {
+    if (!ctx) return;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    snprintf(ctx->err, sizeof(ctx->err), fmt, a, b);
+}
+
+#define DVB_CUDA(ctx, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
+    dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e__), #expr); return DVB_E_CUDA; } } while (0)
+
+// RAII lease of a stream + workspace arena
+struct dvb_scope {
+    dvb_ctx* ctx; dvb_lease* l = nullptr;
+    explicit dvb_scope(dvb_ctx* c) : ctx(c) {
+        for (;;) {
+            {
+                std::lock_guard<std::mutex> g(ctx->mu);
+                for (int i = 0; i < DVB_LEASES; i++) if (!ctx->leases[i].busy) { l = &ctx->leases[i]; l->busy = true; break; }
+            }
+            if (l) break;
+            std::this_thread::yield();
+        }
+        l->arena.used = 0;
+        cudaSetDevice(ctx->device);
+    }
+    ~dvb_scope() { std::lock_guard<std::mutex> g(ctx->mu); l->busy = false; }
+    cudaStream_t stream() const { return l->stream; }
+    // reserve total workspace up front (grows the arena if needed; invalidates earlier allocs)
+    int32_t reserve(size_t bytes) {
+        bytes = (bytes + 255) & ~size_t(255);
+        if (bytes <= l->arena.cap) return DVB_OK;
+        cudaStreamSynchronize(l->stream);
+        if (l->arena.base) cudaFree(l->arena.base);
+        l->arena.base = nullptr; l->arena.cap = 0;
+        size_t want = bytes + (bytes >> 2);
+        if (cudaMalloc(&l->arena.base, want) != cudaSuccess) {
+            if (cudaMalloc(&l->arena.base, bytes) != cudaSuccess) { cudaGetLastError(); dvb_set_err(ctx, "out of device memory%s%s"); return DVB_E_NOMEM; }
+            want = bytes;
+        }
+        l->arena.cap = want;
+        return DVB_OK;
+    }
+    template <typename T> T* alloc(size_t n) {
+        size_t bytes = (n * sizeof(T) + 255) & ~size_t(255);
+        if (l->arena.used + bytes > l->arena.cap) return nullptr;
+        T* p = reinterpret_cast<T*>(l->arena.base + l->arena.used);
+        l->arena.used += bytes;
+        return p;
+    }
+};
+
+static inline size_t dvb_pad(size_t bytes) { return (bytes + 255 + 64) & ~size_t(255); }
+
+// Stage a caller array: HOST -> async copy into `dst` (device); DEVICE -> use in place.
+template <typename T>
+static inline const T* dvb_in(int mem, const T* src, T* dst, size_t n, cudaStream_t s, cudaError_t* err) {
+    if (mem == DVB_MEM_DEVICE) return src;
+    if (n) { cudaError_t e = cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, s); if (e != cudaSuccess) *err = e; }
+    return dst;
+}

@@ -1,0 +1,316 @@
+"""Claim -> fact weak evidence binding on the GPU (rows a1/a2 of SURVEY.md §8).
+
+Host-side mirror of the reference interface:
+  * `_tokenize_similarity_text_v3(text)`            web/server.py:24722
+  * `infer_weak_evidence_refs_v3(field, item, evidence_pack, min_score)`   web/server.py:24780
+plus the batch form `bind_batch` that the drop-in and the bulk paths use.
+
+What runs where: the O(claims x facts x text) work — decode, lower, tokenise, set overlap,
+fp64 score, first-max argmax — is ONE CUDA kernel (csrc/bind.cu) reached through the C-ABI
+`dvb_bind_claims`.  The host only does what the reference does once per claim outside the
+fact loop: gate checks, joining the claim's text fields, the preferred-dimension lookup and
+the threshold arithmetic (web/server.py:24787-24811, 24848-24859).  There is no CPU scorer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import re
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from .packing import pack_texts, ptr
+
+_QID = re.compile(r"Q\d+")
+
+CLAIM_TEXT_FIELDS = {
+    "risks": ("risk", "impact", "mitigation"),
+    "actions": ("action", "owner", "timeline", "metric"),
+    "open_questions": ("question", "reason", "impact", "suggested_follow_up"),
+}
+
+
+@dataclass
+class WeakBindingConfig:
+    """Reference knobs (web/server.py:977-979, 990); read at call time, never baked into kernels."""
+    enabled: bool = True
+    min_score: float = 0.46
+    unknown_ratio_trigger: float = 0.65
+
+
+DEFAULT_CONFIG = WeakBindingConfig()
+
+
+def _as_float(value: Any, default: float = 0.0) -> float:      # web/server.py:22860
+    try:
+        return float(value)
+    except Exception:
+        return default
+
+
+def _text(value: Any) -> str:
+    return str(value or "")
+
+
+# ----------------------------------------------------------------------------- host control logic
+
+def infer_item_dimension_key(field: str, item: Any, evidence_pack: Any) -> str:
+    """Preferred dimension of a claim (web/server.py:24735-24777): explicit `dimension` if it is a
+    coverage key, else the coverage key whose vocabulary (key, name, missing aspects) hits the
+    claim's lower-cased text most often; first best wins."""
+    if not isinstance(item, dict) or not isinstance(evidence_pack, dict):
+        return ""
+    coverage = evidence_pack.get("dimension_coverage", {})
+    if not isinstance(coverage, dict):
+        return ""
+    explicit = _text(item.get("dimension", "")).strip()
+    if explicit in coverage:
+        return explicit
+    corpus = " ".join(_text(item.get(k, "")) for k in
+                      ("title", "description", "risk", "action", "question", "reason", "impact")).lower()
+    if not corpus:
+        return ""
+    winner, winner_hits = "", 0
+    for key, meta in coverage.items():
+        if not isinstance(meta, dict):
+            continue
+        aspects = meta.get("missing_aspects", [])
+        vocab = [key, _text(meta.get("name", ""))] + (list(aspects) if isinstance(aspects, list) else [])
+        hits = 0
+        for word in vocab:
+            needle = _text(word).strip().lower()
+            if needle and needle in corpus:
+                hits += 1
+        if hits > winner_hits:
+            winner, winner_hits = key, hits
+    return winner
+
+
+def is_evidence_sparse(evidence_pack: Any, config: WeakBindingConfig = DEFAULT_CONFIG) -> bool:
+    """web/server.py:24102-24112"""
+    if not isinstance(evidence_pack, dict):
+        return False
+    facts = evidence_pack.get("facts", [])
+    unknowns = evidence_pack.get("unknowns", [])
+    snapshot = evidence_pack.get("quality_snapshot", {}) or {}
+    n_facts = len(facts) if isinstance(facts, list) else 0
+    n_unknown = len(unknowns) if isinstance(unknowns, list) else 0
+    ratio = (n_unknown / n_facts) if n_facts > 0 else 0.0
+    avg_q = _as_float(snapshot.get("average_quality_score", 0.0), 0.0)
+    return ratio >= config.unknown_ratio_trigger or avg_q <= 0.32
+
+
+def action_strategy_flags(evidence_pack: Any, config: WeakBindingConfig = DEFAULT_CONFIG) -> Tuple[bool, int]:
+    """(prefer_open_questions, min_actions) of web/server.py:24115-24190 — the two fields the
+    binding threshold reads (24851-24854)."""
+    if not isinstance(evidence_pack, dict):
+        return False, 2
+    facts = evidence_pack.get("facts", [])
+    blindspots = evidence_pack.get("blindspots", [])
+    unknowns = evidence_pack.get("unknowns", [])
+    snapshot = evidence_pack.get("quality_snapshot", {}) or {}
+    n_facts = len(facts) if isinstance(facts, list) else 0
+    n_blind = len(blindspots) if isinstance(blindspots, list) else 0
+    n_unknown = len(unknowns) if isinstance(unknowns, list) else 0
+    unknown_ratio = (n_unknown / n_facts) if n_facts > 0 else 0.0
+    avg_q = max(0.0, min(1.0, _as_float(snapshot.get("average_quality_score", 0.0), 0.0)))
+    total_formal = max(0, int(snapshot.get("total_formal_questions", 0) or 0))
+    modes = snapshot.get("answer_mode_distribution", {})
+    intents = snapshot.get("evidence_intent_distribution", {})
+    modes = modes if isinstance(modes, dict) else {}
+    intents = intents if isinstance(intents, dict) else {}
+    pick_only = (max(0, int(modes.get("pick_only", 0) or 0)) / total_formal) if total_formal > 0 else 0.0
+    low_intent = (max(0, int(intents.get("low", 0) or 0)) / total_formal) if total_formal > 0 else 0.0
+    low_signal = total_formal > 0 and (pick_only >= 0.55 or low_intent >= 0.55)
+    min_actions = 3 if n_facts >= 10 else 2
+    prefer_open = bool(is_evidence_sparse(evidence_pack, config) or n_blind >= 8 or low_signal)
+    if n_facts <= 3 and n_blind >= 8 and (unknown_ratio >= 0.25 or avg_q <= 0.58 or low_signal):
+        min_actions, prefer_open = 1, True
+    elif n_facts <= 6 and (n_blind >= 6 or unknown_ratio >= 0.40 or avg_q <= 0.42 or low_signal):
+        min_actions, prefer_open = min(min_actions, 2), True
+    return prefer_open, int(min_actions)
+
+
+def binding_threshold(field: str, min_score: Any, preferred_dimension: str, evidence_pack: dict,
+                      config: WeakBindingConfig = DEFAULT_CONFIG) -> float:
+    """web/server.py:24848-24859 (same additions in the same order)."""
+    threshold = float(min_score or config.min_score)
+    if field == "actions":
+        prefer_open, min_actions = action_strategy_flags(evidence_pack, config)
+        threshold += 0.04
+        if prefer_open:
+            threshold += 0.02
+        if int(min_actions or 2) <= 1:
+            threshold += 0.04
+    if preferred_dimension:
+        threshold -= 0.03
+    avg_q = _as_float((evidence_pack.get("quality_snapshot", {}) or {}).get("average_quality_score", 0.0), 0.0)
+    if avg_q <= 0.30:
+        threshold += 0.02
+    return max(0.25, min(threshold, 0.92))
+
+
+# ----------------------------------------------------------------------------- packing of sessions
+
+class _Session:
+    """Facts of one evidence_pack in device order (only facts whose q_id matches Q\\d+, 24817-24819)."""
+
+    __slots__ = ("qids", "texts", "quality", "dims", "hard", "dim_ids")
+
+    def __init__(self, evidence_pack: dict):
+        self.qids: List[str] = []
+        self.texts: List[str] = []
+        self.quality: List[float] = []
+        self.dims: List[int] = []
+        self.hard: List[int] = []
+        self.dim_ids: Dict[str, int] = {}
+        facts = evidence_pack.get("facts", [])
+        for fact in facts if isinstance(facts, list) else []:
+            if not isinstance(fact, dict):
+                continue
+            qid = _text(fact.get("q_id", "")).upper().strip()
+            if not _QID.fullmatch(qid):
+                continue
+            dim = _text(fact.get("dimension", ""))
+            self.qids.append(qid)
+            self.texts.append(" ".join((_text(fact.get("question", "")), _text(fact.get("answer", "")),
+                                        _text(fact.get("dimension_name", "")), dim)))
+            self.quality.append(max(0.0, min(1.0, _as_float(fact.get("quality_score", 0.0), 0.0))))
+            self.dims.append(self.dim_ids.setdefault(dim, len(self.dim_ids)))
+            self.hard.append(1 if bool(fact.get("hard_triggered", False)) else 0)
+
+
+def bind_packed(ctx: "_lib.Context", claim_utf8, claim_off, fact_utf8, fact_off, sess_claim_off, sess_fact_off,
+                fact_quality, fact_dim, fact_hard, claim_pref_dim, claim_threshold, *, want_lens: bool = False,
+                max_claim_group_bytes: int = 0):
+    """Thin call of dvb_bind_claims on host numpy arrays (end-to-end path: H2D, kernel, D2H)."""
+    n_sessions = len(sess_claim_off) - 1
+    n_claims, n_facts = int(sess_claim_off[-1]), int(sess_fact_off[-1])
+    best = np.full(max(n_claims, 1), -1, np.int32)
+    score = np.zeros(max(n_claims, 1), np.float64)
+    bound = np.zeros(max(n_claims, 1), np.uint8)
+    lc = np.zeros(max(n_claims, 1), np.int32) if want_lens else None
+    lf = np.zeros(max(n_facts, 1), np.int32) if want_lens else None
+    rc = ctx.lib.dvb_bind_claims(ctx.handle, _lib.MEM_HOST, ptr(claim_utf8), ptr(claim_off), ptr(fact_utf8), ptr(fact_off),
+                                 ptr(sess_claim_off), ptr(sess_fact_off), n_sessions,
+                                 ptr(fact_quality), ptr(fact_dim), ptr(fact_hard), ptr(claim_pref_dim), ptr(claim_threshold),
+                                 ptr(best), ptr(score), ptr(bound), ptr(lc) if want_lens else None,
+                                 ptr(lf) if want_lens else None, int(max_claim_group_bytes))
+    ctx.check(rc, "dvb_bind_claims")
+    out = {"best_fact": best[:n_claims], "best_score": score[:n_claims], "bound": bound[:n_claims]}
+    if want_lens:
+        out["len_claim"] = lc[:n_claims]
+        out["len_fact"] = lf[:n_facts]
+    return out
+
+
+def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakBindingConfig = DEFAULT_CONFIG,
+               ctx: Optional["_lib.Context"] = None, dimension_resolver=None) -> List[dict]:
+    """Batch form of infer_weak_evidence_refs_v3: one kernel launch for all (field, item, pack, min_score).
+    Requests that share an evidence_pack object share one device session."""
+    results: List[Optional[dict]] = [None] * len(requests)
+    resolver = dimension_resolver or infer_item_dimension_key
+    sessions: Dict[int, Tuple[_Session, List[Tuple[int, str, int, float]]]] = {}
+    order: List[int] = []
+    for i, (field, item, pack, min_score) in enumerate(requests):
+        empty = {"refs": [], "score": 0.0}
+        if not config.enabled or field not in CLAIM_TEXT_FIELDS or not isinstance(item, dict) or not isinstance(pack, dict):
+            results[i] = empty
+            continue
+        facts = pack.get("facts", [])
+        if not isinstance(facts, list) or not facts:
+            results[i] = empty
+            continue
+        key = id(pack)
+        if key not in sessions:
+            sessions[key] = (_Session(pack), [])
+            order.append(key)
+        sess, claims = sessions[key]
+        claim_text = " ".join(_text(item.get(k, "")) for k in CLAIM_TEXT_FIELDS[field])
+        preferred = resolver(field, item, pack)
+        pref_id = -1
+        if preferred:
+            pref_id = sess.dim_ids.get(preferred, 1 << 30)       # a dimension no fact carries never matches
+        threshold = binding_threshold(field, min_score, preferred, pack, config)
+        claims.append((i, claim_text, pref_id, threshold))
+    order = [k for k in order if sessions[k][1] and sessions[k][0].texts]
+    for k, (sess, claims) in sessions.items():
+        if not sess.texts:
+            for (i, _t, _p, _th) in claims:
+                results[i] = {"refs": [], "score": 0.0}
+    if order:
+        ctx = ctx or _lib.Context.get()
+        claim_texts, fact_texts, sco, sfo = [], [], [0], [0]
+        fq, fd, fh, cp, ct = [], [], [], [], []
+        for k in order:
+            sess, claims = sessions[k]
+            claim_texts.extend(t for (_i, t, _p, _th) in claims)
+            cp.extend(p for (_i, _t, p, _th) in claims)
+            ct.extend(th for (_i, _t, _p, th) in claims)
+            fact_texts.extend(sess.texts)
+            fq.extend(sess.quality)
+            fd.extend(sess.dims)
+            fh.extend(sess.hard)
+            sco.append(len(claim_texts))
+            sfo.append(len(fact_texts))
+        cu, co = pack_texts(claim_texts)
+        fu, fo = pack_texts(fact_texts)
+        out = bind_packed(ctx, cu, co, fu, fo, np.asarray(sco, np.int64), np.asarray(sfo, np.int64),
+                          np.asarray(fq, np.float64), np.asarray(fd, np.int32), np.asarray(fh, np.uint8),
+                          np.asarray(cp, np.int32), np.asarray(ct, np.float64))
+        pos = 0
+        for k in order:
+            sess, claims = sessions[k]
+            for (i, _t, _p, _th) in claims:
+                bf = int(out["best_fact"][pos])
+                if bf < 0:
+                    results[i] = {"refs": [], "score": 0.0}
+                else:
+                    sc = round(float(out["best_score"][pos]), 3)
+                    results[i] = {"refs": [sess.qids[bf]] if out["bound"][pos] else [], "score": sc}
+                pos += 1
+    return [r if r is not None else {"refs": [], "score": 0.0} for r in results]
+
+
+def infer_weak_evidence_refs_v3(field: str, item: dict, evidence_pack: dict, min_score: Any = None, *,
+                                config: WeakBindingConfig = DEFAULT_CONFIG, ctx=None, dimension_resolver=None) -> dict:
+    """Drop-in for web/server.py:24780.  Never raises for the inputs the reference accepts."""
+    if min_score is None:
+        min_score = config.min_score
+    return bind_batch([(field, item, evidence_pack, min_score)], config=config, ctx=ctx,
+                      dimension_resolver=dimension_resolver)[0]
+
+
+# ----------------------------------------------------------------------------- a1: token keys
+
+def tokenize_similarity_keys(texts: Sequence[str], ctx=None) -> List[np.ndarray]:
+    """Sorted distinct 64-bit token keys per text (key spec: include/dvb200.h)."""
+    ctx = ctx or _lib.Context.get()
+    data, off = pack_texts(texts)
+    n = len(texts)
+    cap = int(off[-1]) // 2 + n + 1
+    keys = np.zeros(cap, np.uint64)
+    ooff = np.zeros(n + 1, np.int64)
+    rc = ctx.lib.dvb_tokenize_v3(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, ptr(keys), cap, ptr(ooff))
+    ctx.check(rc, "dvb_tokenize_v3")
+    return [keys[ooff[i]:ooff[i + 1]].copy() for i in range(n)]
+
+
+def decode_token_key(key: int) -> Optional[str]:
+    """Inverse of the injective key classes (tags 0 and 1); None for hashed long tokens."""
+    key = int(key)
+    tag = key >> 62
+    if tag == 0:
+        chars = [(key >> s) & 0x7FFF for s in (45, 30, 15, 0)]
+        return "".join(chr(c - 1 + 0x4E00) for c in chars if c)
+    if tag == 1:
+        out = []
+        for i in range(10):
+            c = (key >> (6 * (9 - i))) & 0x3F
+            if not c:
+                break
+            out.append(chr(ord("a") + c - 1) if c <= 26 else (chr(ord("0") + c - 27) if c <= 36 else "_"))
+        return "".join(out)
+    return None

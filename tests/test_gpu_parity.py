@@ -1,0 +1,76 @@
+"""GPU parity (B200): CUDA path through the C-ABI vs the CPU oracle and the golden fixtures."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_a1_keys_golden(gpu_ctx, oracle, golden):
+    from deep_vision_b200 import evidence
+    cases = golden("a1_tokenize.json")
+    texts = [c["text"] for c in cases]
+    got = evidence.tokenize_similarity_keys(texts, ctx=gpu_ctx)
+    for c, keys in zip(cases, got):
+        want = sorted(oracle.token_key(t) for t in c["tokens"])
+        assert keys.tolist() == want, repr(c["text"][:40])
+        # injective classes decode back to the reference's token strings
+        for k in keys.tolist():
+            s = evidence.decode_token_key(k)
+            if s is not None:
+                assert s in c["tokens"]
+
+
+def test_a1_keys_synthetic_and_ragged(gpu_ctx, oracle):
+    from deep_vision_b200 import evidence, synth
+    data, off = synth.make_texts(300, 171, seed=7)
+    raw = data.tobytes()
+    texts = [raw[off[i]:off[i + 1]].decode("utf-8") for i in range(300)]
+    texts += ["", "a", texts[0] * 9, "x" * 5000, "中" * 4000, texts[1][:5], "ab " * 3000]
+    got = evidence.tokenize_similarity_keys(texts, ctx=gpu_ctx)
+    for t, keys in zip(texts, got):
+        assert keys.tolist() == oracle.tokenize_v3_keys(t).tolist(), repr(t[:30])
+
+
+def test_a2_golden_cases(gpu_ctx, golden):
+    from deep_vision_b200 import evidence
+    g = golden("a2_bind.json")
+    reqs = [(c["field"], c["item"], g["packs"][c["pack"]] if isinstance(c["pack"], str) else c["pack"], c["min_score"])
+            for c in g["cases"]]
+    got = evidence.bind_batch(reqs, ctx=gpu_ctx)
+    for c, r in zip(g["cases"], got):
+        assert r == c["result"], c["name"]
+    # single-call form
+    c = g["cases"][0]
+    assert evidence.infer_weak_evidence_refs_v3(c["field"], c["item"], c["pack"], c["min_score"], ctx=gpu_ctx) == c["result"]
+
+
+@pytest.mark.parametrize("n_sessions,turns,claims", [(64, 40, 24), (5, 70, 40), (3, 1, 1), (40, 7, 33)])
+def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
+    from deep_vision_b200 import evidence, synth
+    c = synth.make_sessions(n_sessions, turns=turns, claims_per_session=claims, seed=11 + n_sessions)
+    args = (c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
+            c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
+    got = evidence.bind_packed(gpu_ctx, *args, want_lens=True)
+    ref = oracle.bind_claims(None, None, c.sess_claim_off, c.sess_fact_off, c.fact_quality, c.fact_dim, c.fact_hard,
+                             c.claim_pref_dim, c.claim_threshold, packed=(c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off))
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))   # bit-exact fp64
+    assert np.array_equal(got["bound"], ref["bound"])
+    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
+    assert np.array_equal(got["len_fact"], np.minimum(ref["len_fact"], 18))
+    # hint path gives the same answer
+    got2 = evidence.bind_packed(gpu_ctx, *args, max_claim_group_bytes=c.max_claim_group_bytes)
+    assert np.array_equal(got2["best_fact"], ref["best_fact"])
+
+
+def test_a2_large_claim_table_global_fallback(gpu_ctx, oracle):
+    """claims of one session too large for the shared-memory table -> global-memory table path"""
+    from deep_vision_b200 import evidence, synth
+    c = synth.make_sessions(2, turns=6, claims_per_session=30, claim_chars=4000, seed=5)
+    args = (c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
+            c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
+    got = evidence.bind_packed(gpu_ctx, *args)
+    ref = oracle.bind_claims(None, None, c.sess_claim_off, c.sess_fact_off, c.fact_quality, c.fact_dim, c.fact_hard,
+                             c.claim_pref_dim, c.claim_threshold, packed=(c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off))
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
