@@ -26,6 +26,7 @@ _SIGS = {
     "dvb_launch_count": (C.c_int64, [_vp]),
     "dvb_set_timing": (None, [_vp, C.c_int32]),
     "dvb_last_kernel_ms": (C.c_float, [_vp]),
+    "dvb_set_stream": (None, [_vp, _vp]),
     "dvb_tokenize_v3": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, C.c_int64, _vp]),
     "dvb_bind_claims": (C.c_int32, [_vp, C.c_int32] + [_vp] * 6 + [C.c_int64] + [_vp] * 10 + [C.c_int64]),
 }
@@ -102,6 +103,9 @@ class Context:
     @property
     def last_kernel_ms(self) -> float:
         return float(self.lib.dvb_last_kernel_ms(self.handle))
+
+    def set_stream(self, stream_ptr):
+        self.lib.dvb_set_stream(self.handle, stream_ptr)
 
     def close(self):
         if self.handle:

@@ -42,3 +42,4 @@ extern "C" const char* dvb_last_error(dvb_ctx* c) { return c ? c->err : "null ct
 extern "C" int64_t dvb_launch_count(dvb_ctx* c) { return c ? c->launches.load() : 0; }
 extern "C" void dvb_set_timing(dvb_ctx* c, int32_t enabled) { if (c) c->timing.store(enabled ? 1 : 0); }
 extern "C" float dvb_last_kernel_ms(dvb_ctx* c) { return c ? c->last_ms : 0.f; }
+extern "C" void dvb_set_stream(dvb_ctx* c, void* stream) { if (c) c->user_stream.store(stream); }

@@ -35,6 +35,7 @@ struct dvb_ctx {
     dvb_lease leases[DVB_LEASES];
     std::atomic<int64_t> launches{0};
     std::atomic<int> timing{0};
+    std::atomic<void*> user_stream{nullptr};   // dvb_set_stream: run every call on the caller's stream
     float last_ms = 0.f;
     // per-thread error text would need TLS keyed by ctx; one buffer per ctx guarded by mu is enough here
     char err[512] = {0};
@@ -65,12 +66,12 @@ struct dvb_scope {
         cudaSetDevice(ctx->device);
     }
     ~dvb_scope() { std::lock_guard<std::mutex> g(ctx->mu); l->busy = false; }
-    cudaStream_t stream() const { return l->stream; }
+    cudaStream_t stream() const { void* u = ctx->user_stream.load(); return u ? (cudaStream_t)u : l->stream; }
     // reserve total workspace up front (grows the arena if needed; invalidates earlier allocs)
     int32_t reserve(size_t bytes) {
         bytes = (bytes + 255) & ~size_t(255);
         if (bytes <= l->arena.cap) return DVB_OK;
-        cudaStreamSynchronize(l->stream);
+        cudaStreamSynchronize(stream());
         if (l->arena.base) cudaFree(l->arena.base);
         l->arena.base = nullptr; l->arena.cap = 0;
         size_t want = bytes + (bytes >> 2);

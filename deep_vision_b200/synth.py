@@ -25,12 +25,16 @@ def _zipf_cdf(n: int) -> np.ndarray:
 
 
 _CDF = _zipf_cdf(ALPHABET)
+_LUT_BITS = 22
+# inverse-CDF lookup table: rank for each of 2^22 equally spaced quantiles (exact Zipf up to 2^-22)
+_LUT = np.minimum(np.searchsorted(_CDF, (np.arange(1 << _LUT_BITS) + 0.5) / (1 << _LUT_BITS), side="right"),
+                  ALPHABET - 1).astype(np.uint32)
 
 
 def code_points(rng: np.random.Generator, n: int) -> np.ndarray:
     """n code points of synthetic text (uint32)."""
-    cp = (0x4E00 + np.searchsorted(_CDF, rng.random(n), side="right")).astype(np.uint32)
-    np.minimum(cp, 0x4E00 + ALPHABET - 1, out=cp)
+    cp = _LUT[rng.integers(0, 1 << _LUT_BITS, size=n, dtype=np.uint32)]
+    cp += np.uint32(0x4E00)
     pos = np.arange(16, n, 17)
     cp[pos] = PUNCT[rng.integers(0, 4, size=len(pos))]
     # ASCII words / numbers
@@ -51,20 +55,24 @@ def code_points(rng: np.random.Generator, n: int) -> np.ndarray:
 
 
 def utf8_encode(cp: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
-    """Vectorised UTF-8 encoding of BMP code points. -> (bytes uint8, byte offset of each cp [n+1])"""
+    """Vectorised UTF-8 encoding of BMP code points. -> (bytes uint8 + 64 pad, byte offset of each cp [n+1])"""
     cp = cp.astype(np.uint32, copy=False)
-    nb = np.where(cp < 0x80, 1, np.where(cp < 0x800, 2, 3)).astype(np.int64)
-    off = np.zeros(len(cp) + 1, dtype=np.int64)
+    n = len(cp)
+    nb = np.ones(n, dtype=np.int8)
+    nb[cp >= 0x80] = 2
+    nb[cp >= 0x800] = 3
+    off = np.zeros(n + 1, dtype=np.int64)
     np.cumsum(nb, out=off[1:])
+    planes = np.empty((n, 3), dtype=np.uint8)
+    planes[:, 0] = np.where(nb == 3, 0xE0 | (cp >> 12), np.where(nb == 2, 0xC0 | (cp >> 6), cp))
+    planes[:, 1] = np.where(nb == 3, 0x80 | ((cp >> 6) & 0x3F), 0x80 | (cp & 0x3F))
+    planes[:, 2] = 0x80 | (cp & 0x3F)
+    valid = np.empty((n, 3), dtype=bool)
+    valid[:, 0] = True
+    valid[:, 1] = nb >= 2
+    valid[:, 2] = nb == 3
     out = np.zeros(int(off[-1]) + 64, dtype=np.uint8)
-    o = off[:-1]
-    m1, m2, m3 = nb == 1, nb == 2, nb == 3
-    out[o[m1]] = cp[m1]
-    out[o[m2]] = 0xC0 | (cp[m2] >> 6)
-    out[o[m2] + 1] = 0x80 | (cp[m2] & 0x3F)
-    out[o[m3]] = 0xE0 | (cp[m3] >> 12)
-    out[o[m3] + 1] = 0x80 | ((cp[m3] >> 6) & 0x3F)
-    out[o[m3] + 2] = 0x80 | (cp[m3] & 0x3F)
+    out[:int(off[-1])] = planes[valid]
     return out, off
 
 

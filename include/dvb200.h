@@ -58,6 +58,9 @@ int64_t     dvb_launch_count(dvb_ctx* ctx);
  * events on the launching stream (0 if timing was not enabled with dvb_set_timing). */
 void        dvb_set_timing(dvb_ctx* ctx, int32_t enabled);
 float       dvb_last_kernel_ms(dvb_ctx* ctx);
+/* run all subsequent calls on the caller's CUDA stream (a cudaStream_t; NULL restores the internal
+ * per-call streams).  Lets the caller bracket calls with its own CUDA events. */
+void        dvb_set_stream(dvb_ctx* ctx, void* stream);
 
 /* ---- a1  replaces: _tokenize_similarity_text_v3(text) -> set[str]   web/server.py:24722-24732
  * For each text: the sorted distinct token keys.  out_keys is CSR by out_off[n+1] (int64).

@@ -66,7 +66,7 @@ def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
 def test_a2_large_claim_table_global_fallback(gpu_ctx, oracle):
     """claims of one session too large for the shared-memory table -> global-memory table path"""
     from deep_vision_b200 import evidence, synth
-    c = synth.make_sessions(2, turns=6, claims_per_session=30, claim_chars=4000, seed=5)
+    c = synth.make_sessions(2, turns=6, claims_per_session=30, claim_chars=4000, copy_frac=0.05, seed=5)
     args = (c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
             c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
     got = evidence.bind_packed(gpu_ctx, *args)
