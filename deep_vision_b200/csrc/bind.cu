@@ -2,22 +2,29 @@
 // replaces: the scoring loop of infer_weak_evidence_refs_v3 (reference web/server.py:24813-24864)
 //
 // One CTA per session (persistent grid, sessions strided).  Per group of <=32 claims:
-//   phase C  warps tokenise the claims into a shared-memory open-addressing table
-//            key -> bitmask of claims containing the token; len(A) counted on first insert.
-//   phase F  per batch of <=64 facts: warps stream facts (coalesced 16-byte loads, text.cuh),
-//            probe each token; a per-entry 64-bit `seen` mask makes the count a SET overlap;
-//            a 64-slot per-warp set gives min(len(B), 18) exactly.
-//   phase S  fp64 scores in the reference's operation order (no FMA contraction), strict '>'
-//            scanning facts in index order (first maximum wins).
+//   phase C  warps tokenise the claims (text.cuh) and insert every token key into an exact
+//            open-addressing table  key -> bitmask of claims  that lives in an L2-resident
+//            per-CTA global workspace; two shared-memory bitmap filters (bigram ids, token keys)
+//            record which keys exist.  len(A) is counted on first insert.
+//   phase F  warps stream facts with coalesced 16-byte loads; a fact token is looked up in the
+//            table only if it passes the filter (~1 % false positives), 32 survivors at a time;
+//            hits set a bit in a per-warp bitmap over table slots, which makes the overlap a SET
+//            overlap; a 64-slot per-warp set gives min(len(B), 18) exactly.
+//            At the end of each fact, lane c scores claim c in fp64 in the reference's operation
+//            order (no FMA contraction) and keeps its running best under the total order
+//            (score desc, fact index asc)  ==  the reference's strict '>' scan in index order.
+//   phase R  per-claim reduction of the warps' bests, outputs.
 // No intermediate key arrays ever reach HBM: algorithmic traffic = claim + fact bytes in, 16 B/claim out.
 #include "common.cuh"
 #include "text.cuh"
 
 #define BIND_WARPS 8
 #define BIND_THREADS (BIND_WARPS * 32)
-#define BIND_CLAIMS 32      // claims per group (bits of cmask)
-#define BIND_FACTS 64       // facts per batch (bits of seen)
-#define BIND_WSET 64        // per-warp distinct-token set slots (>= 17 + 32)
+#define BIND_CLAIMS 32          // claims per group (bits of cmask)
+#define BIND_WSET 64            // per-warp distinct-token set slots (>= 17 + 32)
+#define BIND_FB_BITS 16         // bigram filter: 2^16 bits = 8 KB
+#define BIND_FT_BITS 13         // token filter: 2^13 bits = 1 KB
+#define BIND_QCAP 64
 
 struct BindParams {
     const uint8_t* claim_utf8; const int64_t* claim_off; const uint8_t* fact_utf8; const int64_t* fact_off;
@@ -26,7 +33,8 @@ struct BindParams {
     const int32_t* claim_pref_dim; const double* claim_threshold;
     int32_t* best_fact; double* best_score; uint8_t* bound; int32_t* len_claim; int32_t* len_fact;
     uint32_t cap;                         // table capacity (power of two)
-    unsigned long long* gtable;           // global-memory tables (per CTA) when the table does not fit smem, else null
+    unsigned long long* gtable;           // per CTA: cap keys (u64) then cap cmasks (u32)
+    uint32_t* ghit;                       // per-warp hit bitmaps in global memory when cap/32 words do not fit smem, else null
 };
 
 __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {
@@ -34,25 +42,32 @@ __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {
     x ^= x >> 16; x *= 0x9E3779B1u; x ^= x >> 15;
     return x;
 }
+__device__ __forceinline__ uint32_t bind_fb_index(uint32_t bigram_id) { return (bigram_id * 0x9E3779B1u) >> (32 - BIND_FB_BITS); }
+__device__ __forceinline__ uint32_t bind_ft_index(uint64_t key) { return (uint32_t)(key >> 24) & ((1u << BIND_FT_BITS) - 1u); }
 
-struct BindShared {       // fixed part; tables follow in dynamic smem
-    dv_warp_window win[BIND_WARPS];
+struct BindShared {       // fixed part; per-warp hit bitmaps follow in dynamic smem
+    dv_warp_buf wbuf[BIND_WARPS];
+    unsigned long long ktab[DV_KTAB];
+    unsigned long long queue[BIND_WARPS][BIND_QCAP];
     unsigned long long wset[BIND_WARPS][BIND_WSET];
+    uint32_t fb[1u << (BIND_FB_BITS - 5)];
+    uint32_t ft[1u << (BIND_FT_BITS - 5)];
+    uint32_t ov[BIND_WARPS][BIND_CLAIMS];
+    double rbest[BIND_WARPS][BIND_CLAIMS];
+    int ridx[BIND_WARPS][BIND_CLAIMS];
     int wcnt[BIND_WARPS];
-    uint32_t ov[BIND_FACTS * BIND_CLAIMS];
     int lenA[BIND_CLAIMS];
-    int lenB[BIND_FACTS];
     int next_item;
 };
 
+// ---- claims: insert every token, set filter bits
 struct EmitClaim {
-    unsigned long long* tkeys; uint32_t* tcmask; uint32_t mask; int* lenA; int c;
+    unsigned long long* tkeys; uint32_t* tcmask; uint32_t mask; uint32_t* fb; uint32_t* ft; int* lenA; int c;
     __device__ __forceinline__ void restart() {}
-    __device__ __forceinline__ void operator()(bool v, uint64_t key) {
-        if (!v) return;
+    __device__ __forceinline__ void insert(uint64_t key) {
         uint32_t slot = bind_hash(key) & mask;
         for (;;) {
-            unsigned long long prev = atomicCAS(&tkeys[slot], 0ULL, (unsigned long long)key);
+            const unsigned long long prev = atomicCAS(&tkeys[slot], 0ULL, (unsigned long long)key);
             if (prev == 0ULL || prev == key) break;
             slot = (slot + 1) & mask;
         }
@@ -60,43 +75,82 @@ struct EmitClaim {
         const uint32_t old = atomicOr(&tcmask[slot], bit);
         if (!(old & bit)) atomicAdd(&lenA[c], 1);
     }
+    __device__ __forceinline__ void bigram(bool v, uint32_t id) {
+        if (!v) return;
+        const uint32_t h = bind_fb_index(id);
+        atomicOr(&fb[h >> 5], 1u << (h & 31));
+        insert((uint64_t)id);
+    }
+    __device__ __forceinline__ void token(bool v, uint64_t key) {
+        if (!v) return;
+        const uint32_t h = bind_ft_index(key);
+        atomicOr(&ft[h >> 5], 1u << (h & 31));
+        insert(key);
+    }
 };
 
+// ---- facts: filter, queue survivors, probe 32 at a time, mark hit slots
 struct EmitFact {
-    const unsigned long long* tkeys; const uint32_t* tcmask; unsigned long long* tseen; uint32_t mask;
-    uint32_t* ov_row; int fl; unsigned long long* wset; int* wcnt; bool full;
+    const unsigned long long* tkeys; uint32_t mask; const uint32_t* fb; const uint32_t* ft;
+    unsigned long long* queue; uint32_t* hit; unsigned long long* wset; int* wcnt;
+    int qn; bool full; int lane;
     __device__ __forceinline__ void restart() {}
-    __device__ __forceinline__ void operator()(bool v, uint64_t key) {
-        const uint32_t h = bind_hash(key);
-        if (!full) {                                             // distinct count up to 18 (warp-uniform branch)
-            if (v) {
-                uint32_t s = (h >> 20) & (BIND_WSET - 1);
-                for (;;) {
-                    unsigned long long prev = atomicCAS(&wset[s], 0ULL, (unsigned long long)key);
-                    if (prev == 0ULL) { atomicAdd(wcnt, 1); break; }
-                    if (prev == key) break;
-                    s = (s + 1) & (BIND_WSET - 1);
-                }
+    __device__ __forceinline__ void count_distinct(bool v, uint64_t key) {       // until 18 distinct tokens were seen
+        if (v) {
+            uint32_t s = (bind_hash(key) >> 20) & (BIND_WSET - 1);
+            for (;;) {
+                const unsigned long long prev = atomicCAS(&wset[s], 0ULL, (unsigned long long)key);
+                if (prev == 0ULL) { atomicAdd(wcnt, 1); break; }
+                if (prev == key) break;
+                s = (s + 1) & (BIND_WSET - 1);
             }
-            __syncwarp();
-            full = (*(volatile int*)wcnt >= 18);
         }
+        __syncwarp();
+        full = (*(volatile int*)wcnt >= 18);
+    }
+    __device__ __forceinline__ void probe(bool v, uint64_t key) {
         if (!v) return;
-        uint32_t slot = h & mask;
+        uint32_t slot = bind_hash(key) & mask;
         for (;;) {
-            const unsigned long long k = tkeys[slot];
-            if (k == key) {
-                const unsigned long long bit = 1ULL << fl;
-                const unsigned long long old = atomicOr(&tseen[slot], bit);
-                if (!(old & bit)) {
-                    uint32_t cm = tcmask[slot];
-                    while (cm) { const int c = __ffs(cm) - 1; cm &= cm - 1; atomicAdd(&ov_row[c], 1u); }
-                }
-                return;
-            }
+            const unsigned long long k = __ldcg(&tkeys[slot]);     // table is written by L2 atomics: bypass L1
+            if (k == key) { atomicOr(&hit[slot >> 5], 1u << (slot & 31)); return; }
             if (k == 0ULL) return;
             slot = (slot + 1) & mask;
         }
+    }
+    __device__ __forceinline__ void push(bool v, uint64_t key) {
+        const uint32_t m = __ballot_sync(0xffffffffu, v);
+        if (!m) return;
+        if (v) queue[qn + __popc(m & ((1u << lane) - 1u))] = key;
+        qn += __popc(m);
+        __syncwarp();
+        if (qn >= 32) {
+            probe(true, queue[lane]);
+            __syncwarp();
+            const unsigned long long rest = (lane + 32 < qn) ? queue[lane + 32] : 0ULL;
+            __syncwarp();
+            queue[lane] = rest;
+            qn -= 32;
+            __syncwarp();
+        }
+    }
+    __device__ __forceinline__ void flush() {
+        __syncwarp();
+        probe(lane < qn, lane < qn ? queue[lane] : 0ULL);
+        qn = 0;
+        __syncwarp();
+    }
+    __device__ __forceinline__ void bigram(bool v, uint32_t id) {
+        if (!full) count_distinct(v, (uint64_t)id);
+        const uint32_t h = bind_fb_index(id);
+        const bool pass = v && ((fb[h >> 5] >> (h & 31)) & 1u);
+        push(pass, (uint64_t)id);
+    }
+    __device__ __forceinline__ void token(bool v, uint64_t key) {
+        if (!full) count_distinct(v, key);
+        const uint32_t h = bind_ft_index(key);
+        const bool pass = v && ((ft[h >> 5] >> (h & 31)) & 1u);
+        push(pass, key);
     }
 };
 
@@ -104,25 +158,26 @@ extern __shared__ __align__(16) unsigned char bind_smem[];
 
 __global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
     BindShared& sh = *reinterpret_cast<BindShared*>(bind_smem);
-    unsigned long long* tkeys; unsigned long long* tseen; uint32_t* tcmask;
-    if (p.gtable) {
-        unsigned long long* base = p.gtable + (size_t)blockIdx.x * ((size_t)p.cap * 2 + (size_t)p.cap / 2);
-        tkeys = base; tseen = base + p.cap; tcmask = reinterpret_cast<uint32_t*>(base + 2 * (size_t)p.cap);
-    } else {
-        unsigned long long* base = reinterpret_cast<unsigned long long*>(bind_smem + ((sizeof(BindShared) + 15) & ~size_t(15)));
-        tkeys = base; tseen = base + p.cap; tcmask = reinterpret_cast<uint32_t*>(base + 2 * (size_t)p.cap);
-    }
-    double* scores = reinterpret_cast<double*>(tseen);          // aliases `seen` during phase S (cap >= 2048 entries)
-    const uint32_t mask = p.cap - 1;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t hit_words = p.cap >> 5;
+    unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * ((size_t)p.cap + (size_t)p.cap / 2);
+    uint32_t* tcmask = reinterpret_cast<uint32_t*>(tkeys + p.cap);
+    uint32_t* hit = p.ghit ? p.ghit + ((size_t)blockIdx.x * BIND_WARPS + warp) * hit_words
+                           : reinterpret_cast<uint32_t*>(bind_smem + ((sizeof(BindShared) + 15) & ~size_t(15))) + (size_t)warp * hit_words;
+    const uint32_t mask = p.cap - 1;
+    dv_fill_ktab(sh.ktab);
+    for (uint32_t i = lane; i < hit_words; i += 32) hit[i] = 0u;
+    __syncthreads();
 
     for (int64_t s = blockIdx.x; s < p.n_sessions; s += gridDim.x) {
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
         const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
         for (int64_t cg = c0; cg < c1; cg += BIND_CLAIMS) {
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
-            // ---- clear table
+            // ---- clear table + filters
             for (uint32_t i = tid; i < p.cap; i += BIND_THREADS) { tkeys[i] = 0ULL; tcmask[i] = 0u; }
+            for (uint32_t i = tid; i < (1u << (BIND_FB_BITS - 5)); i += BIND_THREADS) sh.fb[i] = 0u;
+            for (uint32_t i = tid; i < (1u << (BIND_FT_BITS - 5)); i += BIND_THREADS) sh.ft[i] = 0u;
             if (tid < BIND_CLAIMS) sh.lenA[tid] = 0;
             if (tid == 0) sh.next_item = 0;
             __syncthreads();
@@ -133,72 +188,74 @@ __global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
                 c = __shfl_sync(0xffffffffu, c, 0);
                 if (c >= ncg) break;
                 const int64_t b = p.claim_off[cg + c], e = p.claim_off[cg + c + 1];
-                EmitClaim emit{ tkeys, tcmask, mask, sh.lenA, c };
-                dv_tokenize_v3_warp(p.claim_utf8 + b, (int32_t)(e - b), &sh.win[warp], emit);
+                EmitClaim emit{ tkeys, tcmask, mask, sh.fb, sh.ft, sh.lenA, c };
+                dv_tokenize_v3_warp(p.claim_utf8 + b, (int32_t)(e - b), &sh.wbuf[warp], sh.ktab, emit);
             }
             __syncthreads();
-            double best = 0.0; int best_f = -1;                 // thread c (< ncg) owns claim c
-            // ---- fact batches
-            for (int64_t fb = f0; fb < f1; fb += BIND_FACTS) {
-                const int nfb = (int)min((int64_t)BIND_FACTS, f1 - fb);
-                for (uint32_t i = tid; i < p.cap; i += BIND_THREADS) tseen[i] = 0ULL;
-                for (int i = tid; i < BIND_FACTS * BIND_CLAIMS; i += BIND_THREADS) sh.ov[i] = 0u;
-                if (tid == 0) sh.next_item = 0;
-                __syncthreads();
-                // ---- phase F
-                for (;;) {
-                    int fl = 0;
-                    if (lane == 0) fl = atomicAdd(&sh.next_item, 1);
-                    fl = __shfl_sync(0xffffffffu, fl, 0);
-                    if (fl >= nfb) break;
-                    sh.wset[warp][lane] = 0ULL; sh.wset[warp][lane + 32] = 0ULL;
-                    if (lane == 0) sh.wcnt[warp] = 0;
-                    __syncwarp();
-                    const int64_t b = p.fact_off[fb + fl], e = p.fact_off[fb + fl + 1];
-                    EmitFact emit{ tkeys, tcmask, tseen, mask, &sh.ov[fl * BIND_CLAIMS], fl, sh.wset[warp], &sh.wcnt[warp], false };
-                    dv_tokenize_v3_warp(p.fact_utf8 + b, (int32_t)(e - b), &sh.win[warp], emit);
-                    __syncwarp();
-                    if (lane == 0) {
-                        const int n = min(sh.wcnt[warp], 18);
-                        sh.lenB[fl] = n;
-                        if (p.len_fact && cg == c0) p.len_fact[fb + fl] = n;
+            if (tid == 0) sh.next_item = 0;
+            __syncthreads();
+            // ---- phase F
+            double best = -1.0; int best_f = 0x7fffffff;          // lane c (< ncg) tracks claim c
+            const int la = lane < ncg ? sh.lenA[lane] : 0;
+            const int da = max(3, min(la, 14));
+            const int pref = lane < ncg ? p.claim_pref_dim[cg + lane] : -1;
+            for (;;) {
+                int f = 0;
+                if (lane == 0) f = atomicAdd(&sh.next_item, 1);
+                f = __shfl_sync(0xffffffffu, f, 0);
+                if ((int64_t)f >= f1 - f0) break;
+                sh.wset[warp][lane] = 0ULL; sh.wset[warp][lane + 32] = 0ULL;
+                sh.ov[warp][lane] = 0u;
+                if (lane == 0) sh.wcnt[warp] = 0;
+                __syncwarp();
+                const int64_t b = p.fact_off[f0 + f], e = p.fact_off[f0 + f + 1];
+                EmitFact emit{ tkeys, mask, sh.fb, sh.ft, sh.queue[warp], hit, sh.wset[warp], &sh.wcnt[warp], 0, false, lane };
+                dv_tokenize_v3_warp(p.fact_utf8 + b, (int32_t)(e - b), &sh.wbuf[warp], sh.ktab, emit);
+                emit.flush();
+                // hit bitmap -> per-claim overlap counts; clear as we go
+                for (uint32_t wd = lane; wd < hit_words; wd += 32) {
+                    uint32_t bits = *(volatile uint32_t*)&hit[wd];
+                    if (bits) {
+                        hit[wd] = 0u;
+                        while (bits) {
+                            const uint32_t slot = wd * 32 + (__ffs(bits) - 1); bits &= bits - 1;
+                            uint32_t cm = __ldcg(&tcmask[slot]);
+                            while (cm) { const int c = __ffs(cm) - 1; cm &= cm - 1; atomicAdd(&sh.ov[warp][c], 1u); }
+                        }
                     }
                 }
-                __syncthreads();
-                // ---- phase S: scores for (fact, claim) pairs of this batch
-                for (int i = tid; i < nfb * BIND_CLAIMS; i += BIND_THREADS) {
-                    const int fl = i / BIND_CLAIMS, c = i % BIND_CLAIMS;
-                    double sc = -1.0;
-                    const uint32_t ov = sh.ov[i];
-                    if (c < ncg && ov > 0u) {
-                        const int la = sh.lenA[c], lb = sh.lenB[fl];
-                        const int da = max(3, min(la, 14)), db = max(4, min(lb, 18));
-                        const double coverage = __ddiv_rn((double)ov, (double)da);
-                        const double precision = __ddiv_rn((double)ov, (double)db);
-                        double q = p.fact_quality[fb + fl];
-                        q = q > 0.0 ? (q < 1.0 ? q : 1.0) : 0.0;
-                        const int pref = p.claim_pref_dim[cg + c];
-                        const double dimb = (pref >= 0 && p.fact_dim[fb + fl] == pref) ? 0.12 : 0.0;
-                        const double hardb = p.fact_hard[fb + fl] ? 0.04 : 0.0;
-                        sc = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(0.62, coverage), __dmul_rn(0.18, precision)),
-                                                           __dmul_rn(0.16, q)), dimb), hardb);
-                    }
-                    scores[i] = sc;
+                __syncwarp();
+                const int lb = min(sh.wcnt[warp], 18);
+                if (lane == 0 && p.len_fact && cg == c0) p.len_fact[f0 + f] = lb;
+                const uint32_t ov = sh.ov[warp][lane];
+                if (lane < ncg && ov > 0u) {
+                    const int db = max(4, min(lb, 18));
+                    const double coverage = __ddiv_rn((double)ov, (double)da);
+                    const double precision = __ddiv_rn((double)ov, (double)db);
+                    double q = p.fact_quality[f0 + f];
+                    q = q > 0.0 ? (q < 1.0 ? q : 1.0) : 0.0;
+                    const double dimb = (pref >= 0 && p.fact_dim[f0 + f] == pref) ? 0.12 : 0.0;
+                    const double hardb = p.fact_hard[f0 + f] ? 0.04 : 0.0;
+                    const double sc = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(0.62, coverage), __dmul_rn(0.18, precision)),
+                                                                     __dmul_rn(0.16, q)), dimb), hardb);
+                    if (sc > best || (sc == best && f < best_f)) { best = sc; best_f = f; }
                 }
-                __syncthreads();
-                if (tid < ncg) {
-                    for (int fl = 0; fl < nfb; fl++) {
-                        const double sc = scores[fl * BIND_CLAIMS + tid];
-                        if (sc >= 0.0 && (best_f < 0 || sc > best)) { best = sc; best_f = (int)(fb - f0) + fl; }
-                    }
-                }
-                __syncthreads();
+                __syncwarp();
             }
+            sh.rbest[warp][lane] = best; sh.ridx[warp][lane] = best_f;
+            __syncthreads();
+            // ---- phase R
             if (tid < ncg) {
+                double b = -1.0; int bf = 0x7fffffff;
+                for (int w = 0; w < BIND_WARPS; w++) {
+                    const double sc = sh.rbest[w][tid]; const int fi = sh.ridx[w][tid];
+                    if (sc > b || (sc == b && fi < bf)) { b = sc; bf = fi; }
+                }
                 const int64_t c = cg + tid;
-                p.best_fact[c] = best_f;
-                p.best_score[c] = best_f >= 0 ? best : 0.0;
-                p.bound[c] = (best_f >= 0 && !(__dadd_rn(best, 1e-9) < p.claim_threshold[c])) ? 1 : 0;
+                const bool any = b >= 0.0;
+                p.best_fact[c] = any ? bf : -1;
+                p.best_score[c] = any ? b : 0.0;
+                p.bound[c] = (any && !(__dadd_rn(b, 1e-9) < p.claim_threshold[c])) ? 1 : 0;
                 if (p.len_claim) p.len_claim[c] = min(sh.lenA[tid], 14);
             }
             __syncthreads();
@@ -207,10 +264,10 @@ __global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
 }
 
 static inline uint32_t bind_table_cap(int64_t max_group_bytes) {
-    // distinct tokens of a text <= 0.45 * bytes + 1 (bigrams + pieces of a CJK run); load factor <= 2/3
-    int64_t bound = (max_group_bytes * 9) / 20 + BIND_CLAIMS + 1;
-    int64_t want = bound + bound / 2;
-    uint32_t cap = 2048; while ((int64_t)cap < want) cap <<= 1;
+    // distinct tokens of a text <= bytes/3 + 1 (<= one token per CJK char, <= one per 3 ASCII bytes); load factor <= 1/2
+    int64_t bound = max_group_bytes / 3 + BIND_CLAIMS + 1;
+    int64_t want = bound * 2;
+    uint32_t cap = 1024; while ((int64_t)cap < want) cap <<= 1;
     return cap;
 }
 
@@ -261,8 +318,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     }
     const uint32_t cap = bind_table_cap(max_claim_group_bytes);
     const size_t fixed = (sizeof(BindShared) + 15) & ~size_t(15);
-    size_t smem = fixed + (size_t)cap * 20;
-    bool use_global = smem > ctx->smem_optin;
+    const size_t hit_bytes = (size_t)BIND_WARPS * (cap >> 5) * 4;
+    size_t smem = fixed + hit_bytes;
+    const bool use_global = hit_bytes > 16384;          // huge claim groups: hit bitmaps move to global memory
     if (use_global) smem = fixed;
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1;
@@ -276,7 +334,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
               + 2 * dvb_pad(8 * (size_t)(n_sessions + 1)) + dvb_pad(8 * (size_t)n_facts) + dvb_pad(4 * (size_t)n_facts) + dvb_pad((size_t)n_facts)
               + dvb_pad(4 * (size_t)n_claims) * 3 + dvb_pad(8 * (size_t)n_claims) * 2 + dvb_pad((size_t)n_claims) + dvb_pad(4 * (size_t)n_facts);
     }
-    if (use_global) need += dvb_pad((size_t)grid * (size_t)cap * 20);
+    need += dvb_pad((size_t)grid * (size_t)cap * 12);
+    if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.n_sessions = n_sessions; p.cap = cap;
@@ -317,7 +376,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         p.best_fact = out_best_fact; p.best_score = out_best_score; p.bound = out_bound; p.len_claim = out_len_claim; p.len_fact = out_len_fact;
     }
     if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
-    if (use_global) { p.gtable = sc.alloc<unsigned long long>(((size_t)grid * (size_t)cap * 20 + 7) / 8); if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
+    p.gtable = sc.alloc<unsigned long long>(((size_t)grid * (size_t)cap * 12 + 7) / 8);
+    if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+    if (use_global) { p.ghit = sc.alloc<uint32_t>((size_t)grid * hit_bytes / 4); if (!p.ghit) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
     const bool timing = ctx->timing.load() != 0;
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, st));
     k_bind_claims<<<grid, BIND_THREADS, smem, st>>>(p);

@@ -7,25 +7,30 @@
 struct EmitToGlobal {
     unsigned long long* out; int32_t cap; int32_t n; int lane;
     __device__ __forceinline__ void restart() { n = 0; }
-    __device__ __forceinline__ void operator()(bool v, uint64_t key) {
+    __device__ __forceinline__ void push(bool v, uint64_t key) {
         const uint32_t m = __ballot_sync(0xffffffffu, v);
         if (!m) return;
         const int r = __popc(m & ((1u << lane) - 1u));
         if (v && n + r < cap) out[n + r] = key;
         n += __popc(m);
     }
+    __device__ __forceinline__ void bigram(bool v, uint32_t id) { push(v, (uint64_t)id); }
+    __device__ __forceinline__ void token(bool v, uint64_t key) { push(v, key); }
 };
 
 // one warp per text; raw keys (with duplicates) go to scratch[seg_off[t] .. ), count to raw_cnt[t]
 __global__ void __launch_bounds__(256) k_emit_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n_texts,
                                                     const int64_t* __restrict__ seg_off, unsigned long long* __restrict__ scratch,
                                                     int32_t* __restrict__ raw_cnt) {
-    __shared__ dv_warp_window win[8];
+    __shared__ dv_warp_buf wbuf[8];
+    __shared__ unsigned long long ktab[DV_KTAB];
+    dv_fill_ktab(ktab);
+    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int64_t t = (int64_t)blockIdx.x * 8 + warp; t < n_texts; t += (int64_t)gridDim.x * 8) {
         const int64_t b = off[t], e = off[t + 1];
         EmitToGlobal emit{ scratch + seg_off[t], (int32_t)(seg_off[t + 1] - seg_off[t]), 0, lane };
-        dv_tokenize_v3_warp(utf8 + b, (int32_t)(e - b), &win[warp], emit);
+        dv_tokenize_v3_warp(utf8 + b, (int32_t)(e - b), &wbuf[warp], ktab, emit);
         if (lane == 0) raw_cnt[t] = emit.n < emit.cap ? emit.n : emit.cap;
         __syncwarp();
     }

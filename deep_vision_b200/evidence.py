@@ -299,18 +299,8 @@ def tokenize_similarity_keys(texts: Sequence[str], ctx=None) -> List[np.ndarray]
 
 
 def decode_token_key(key: int) -> Optional[str]:
-    """Inverse of the injective key classes (tags 0 and 1); None for hashed long tokens."""
+    """Inverse of the injective key class (tag 0: CJK bigram); None for hashed tokens."""
     key = int(key)
-    tag = key >> 62
-    if tag == 0:
-        chars = [(key >> s) & 0x7FFF for s in (45, 30, 15, 0)]
-        return "".join(chr(c - 1 + 0x4E00) for c in chars if c)
-    if tag == 1:
-        out = []
-        for i in range(10):
-            c = (key >> (6 * (9 - i))) & 0x3F
-            if not c:
-                break
-            out.append(chr(ord("a") + c - 1) if c <= 26 else (chr(ord("0") + c - 27) if c <= 36 else "_"))
-        return "".join(out)
+    if key >> 62 == 0:
+        return chr(((key >> 15) & 0x7FFF) - 1 + 0x4E00) + chr((key & 0x7FFF) - 1 + 0x4E00)
     return None

@@ -21,13 +21,14 @@
  *  - there is NO CPU fallback: without a CUDA device dvb_create fails.
  *
  * Token key (64-bit), produced by dvb_tokenize_v3 and used inside dvb_bind_claims:
- *   symbols are the lowered code points of class ASCII [a-z0-9_] or CJK [U+4E00..U+9FFF]
- *   tag 0 (bits 63:62): CJK token, 2..4 chars : (cp-0x4E00+1) packed 15 bits each, first char
- *                        highest, zero padded (injective; a bigram is a 2-char token)
- *   tag 1: ASCII token, <=10 chars : code a-z 1..26, 0-9 27..36, _ 37, 6 bits each, first char
- *                        highest, zero padded (injective)
- *   tag 2: ASCII token, >10 chars  : hash62 (FNV-1a over code points, length, fmix64)
- *   tag 3: CJK token, 5..12 chars  : hash62
+ *   symbols are the lowered code points of class ASCII [a-z0-9_] or CJK [U+4E00..U+9FFF];
+ *   code(sym) = cp-0x4E00+1 (CJK, 1..20992) or a-z 1..26, 0-9 27..36, _ 37 (ASCII)
+ *   tag 0 (bits 63:62): CJK bigram           : (code0 << 15) | code1              (injective)
+ *   tag 1: ASCII token (len >= 2)            : (1<<62) | (M >> 2)
+ *   tag 3: CJK piece (3..12 chars)           : (3<<62) | (M >> 2)
+ *   M = sum_d code_d * K(d) + len * K_LEN mod 2^64, K(d) = splitmix64(d+1)|1, K_LEN = splitmix64(0x4C454E)|1
+ *   (multilinear hashing: any two distinct tokens collide with probability 2^-62; the oracle
+ *   compares token STRINGS, so a collision would surface as a parity failure, not silently)
  */
 #ifndef DVB200_H
 #define DVB200_H

@@ -129,38 +129,33 @@ static void scan_tokens_v3(const uint32_t* low, int64_t n, tok_cb cb, void* ctx)
 
 /* -------------------------------------------------------------- token keys */
 
-static uint64_t hash62(const uint32_t* sym, int32_t len) {
-    uint64_t h = 0xcbf29ce484222325ULL;
-    for (int32_t i = 0; i < len; i++) { h ^= (uint64_t)sym[i]; h *= 0x100000001b3ULL; }
-    h ^= (uint64_t)len; h *= 0x100000001b3ULL;
-    h ^= h >> 33; h *= 0xff51afd7ed558ccdULL; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL; h ^= h >> 33;
-    return h & 0x3FFFFFFFFFFFFFFFULL;
+static uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
 }
 static inline uint32_t ascii_code(uint32_t c) {        /* a-z 1..26, 0-9 27..36, _ 37 */
     if (c >= 'a' && c <= 'z') return c - 'a' + 1;
     if (c >= '0' && c <= '9') return c - '0' + 27;
     return 37;
 }
-/* Token key spec (include/dvb200.h):
- *  tag 0: CJK token, len 2..4  : (cp-0x4E00+1) packed 15 bits each, first char highest, zero padded
- *  tag 1: ASCII token, len<=10 : code 1..37 packed 6 bits each, first char highest, zero padded
- *  tag 2: ASCII token, len>10  : hash62 over the code points
- *  tag 3: CJK token, len 5..12 : hash62 over the code points                */
+/* Token key spec (include/dvb200.h), restated:
+ *  code(sym) = cp-0x4E00+1 for CJK, 1..37 for ASCII [a-z0-9_]
+ *  tag 0: CJK bigram                : (code0 << 15) | code1                      (injective)
+ *  tag 1: ASCII token, len >= 2     : (1<<62) | (M >> 2)
+ *  tag 3: CJK piece, len 3..12      : (3<<62) | (M >> 2)
+ *  M = sum_d code_d * K(d) + len * K_LEN  (mod 2^64),  K(d) = splitmix64(d+1)|1  (multilinear hash) */
 uint64_t dvo_token_key(const uint32_t* tok, int32_t len) {
-    if (is_cjk(tok[0])) {
-        if (len <= 4) {
-            uint64_t k = 0;
-            for (int i = 0; i < 4; i++) k = (k << 15) | (i < len ? (uint64_t)(tok[i] - 0x4E00 + 1) : 0);
-            return k;
-        }
-        return (3ULL << 62) | hash62(tok, len);
+    int cjk = is_cjk(tok[0]);
+    if (cjk && len == 2) return ((uint64_t)(tok[0] - 0x4E00 + 1) << 15) | (uint64_t)(tok[1] - 0x4E00 + 1);
+    uint64_t m = 0;
+    for (int32_t d = 0; d < len; d++) {
+        uint64_t code = cjk ? (uint64_t)(tok[d] - 0x4E00 + 1) : (uint64_t)ascii_code(tok[d]);
+        m += code * (splitmix64((uint64_t)d + 1) | 1ULL);
     }
-    if (len <= 10) {
-        uint64_t k = 0;
-        for (int i = 0; i < 10; i++) k = (k << 6) | (i < len ? (uint64_t)ascii_code(tok[i]) : 0);
-        return (1ULL << 62) | k;
-    }
-    return (2ULL << 62) | hash62(tok, len);
+    m += (uint64_t)len * (splitmix64(0x4C454EULL) | 1ULL);
+    return ((cjk ? 3ULL : 1ULL) << 62) | (m >> 2);
 }
 
 /* ------------------------------------------- content-exact token interning */
