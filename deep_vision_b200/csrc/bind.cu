@@ -43,7 +43,7 @@ __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {
     return x;
 }
 __device__ __forceinline__ uint32_t bind_fb_index(uint32_t bigram_id) { return (bigram_id * 0x9E3779B1u) >> (32 - BIND_FB_BITS); }
-__device__ __forceinline__ uint32_t bind_ft_index(uint64_t key) { return (uint32_t)(key >> 24) & ((1u << BIND_FT_BITS) - 1u); }
+__device__ __forceinline__ uint32_t bind_ft_index(uint32_t sig) { return sig >> (32 - BIND_FT_BITS); }
 
 struct BindShared {       // fixed part; per-warp hit bitmaps follow in dynamic smem
     dv_warp_buf wbuf[BIND_WARPS];
@@ -81,9 +81,10 @@ struct EmitClaim {
         atomicOr(&fb[h >> 5], 1u << (h & 31));
         insert((uint64_t)id);
     }
-    __device__ __forceinline__ void token(bool v, uint64_t key) {
+    __device__ __forceinline__ bool need_token(uint32_t) const { return true; }
+    __device__ __forceinline__ void token(bool v, uint64_t key, uint32_t sig) {
         if (!v) return;
-        const uint32_t h = bind_ft_index(key);
+        const uint32_t h = bind_ft_index(sig);
         atomicOr(&ft[h >> 5], 1u << (h & 31));
         insert(key);
     }
@@ -146,11 +147,11 @@ struct EmitFact {
         const bool pass = v && ((fb[h >> 5] >> (h & 31)) & 1u);
         push(pass, (uint64_t)id);
     }
-    __device__ __forceinline__ void token(bool v, uint64_t key) {
+    __device__ __forceinline__ bool ft_pass(uint32_t sig) const { const uint32_t h = bind_ft_index(sig); return (ft[h >> 5] >> (h & 31)) & 1u; }
+    __device__ __forceinline__ bool need_token(uint32_t sig) const { return !full || ft_pass(sig); }
+    __device__ __forceinline__ void token(bool v, uint64_t key, uint32_t sig) {
         if (!full) count_distinct(v, key);
-        const uint32_t h = bind_ft_index(key);
-        const bool pass = v && ((ft[h >> 5] >> (h & 31)) & 1u);
-        push(pass, key);
+        push(v && ft_pass(sig), key);
     }
 };
 

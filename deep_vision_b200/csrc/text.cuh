@@ -5,31 +5,35 @@
 //   each piece (len>=2) and all bigrams inside a piece are tokens.
 //
 // One warp streams one text.
-//   pass A  coalesced 16-byte loads (512 B per iteration); each lane classifies its 16 bytes in
-//           registers (look-behind through the neighbour lane's last word) and the warp compacts
-//           the resulting SYMBOLS (u16: 0 = separator, 1..20992 = CJK code, 0x8000|code = ASCII)
-//           into a dense shared-memory buffer with one prefix sum.
+//   pass A  coalesced 16-byte loads (512 B per iteration).  Each lane finds the bytes at which a
+//           symbol is produced with SWAR bit tricks on its four words (ASCII bytes, 2-/4-byte
+//           leads = separators, third byte of a 3-byte char), then decodes one symbol per set bit
+//           from a conflict-free shared-memory copy of its bytes; one warp prefix sum compacts
+//           the SYMBOLS (u16: 0 = separator, 1..20992 = CJK code, 0x8000|code = ASCII) densely.
 //   pass B  32 symbols per step, one per lane: run starts by ballot/clz, position inside the
-//           12-char piece, exact bigram ids, and the multilinear token hash
-//               M = sum_d code_d * K(d)      (K(d) = splitmix64(d+1)|1)
-//           of every piece / ASCII run by ONE segmented 64-bit warp scan whose carry crosses
-//           steps and tiles — no per-lane loops, no look-behind beyond one symbol.
-// Tokens are emitted at their last symbol: emit.bigram(valid, id30) / emit.token(valid, key64),
-// both called warp-convergently.
+//           12-char piece, exact bigram ids; piece / ASCII-run tokens are detected at their last
+//           symbol and their 64-bit multilinear key  M = sum_d code_d * K(d)  is computed (a short
+//           loop over the symbol history) only for tokens the consumer asks for — every token
+//           of a claim, but only filter survivors of a fact.
+// Tokens are emitted warp-convergently: emit.bigram(valid, id30), emit.token(valid, key64, sig).
 //
-// Texts containing a byte that may lower-case INTO the ASCII class from outside it
-// (U+0130 -> 'i'+U+0307, U+212A -> 'k'; conservatively: any 0xC4 lead or E2 84 xx) restart on
-// the exact serial path dv_tokenize_serial().
+// Restart on the exact serial path dv_tokenize_serial() when the text contains
+//   * a byte that may lower-case INTO the ASCII class from outside it (U+0130 -> 'i'+U+0307,
+//     U+212A -> 'k'; detected as lead 0xC4 / bytes E2 84), or
+//   * a needed ASCII token longer than the 64-symbol history.
 #pragma once
 #include <stdint.h>
 
 #define DV_SYM_ASCII 0x8000u
 #define DV_TILE   512                    // bytes staged per iteration (32 lanes x 16 B)
-#define DV_SYMCAP (DV_TILE + 40)         // history + pending + new symbols + terminator, padded
+#define DV_HIST   64                     // processed symbols kept for key loops (max fast-path token length)
+#define DV_SYMCAP (DV_HIST + DV_TILE + 8) // history + held-back + new symbols + terminator, padded
 
 struct __align__(16) dv_warp_buf {
+    uint32_t raw[32 * 5];                // per lane: [previous word, 4 data words]; stride 5 words = conflict-free
     uint16_t sym[DV_SYMCAP];
     unsigned long long queue[32];        // serial-path key queue
+    uint32_t qsig[32];                   // serial-path token signatures
     uint32_t qkind;                      // bit i: queue[i] is a bigram id
 };
 
@@ -62,36 +66,8 @@ __device__ __forceinline__ uint32_t dv_ascii_sym(uint32_t b) {          // b < 0
 __device__ __forceinline__ bool dv_is_cjk_sym(uint32_t s) { return s - 1u < 20992u; }
 __device__ __forceinline__ bool dv_is_ascii_sym(uint32_t s) { return s >= DV_SYM_ASCII; }
 
-#define DV_NOSYM 0xFFFFu
-// Symbols ENDING at each of the 16 bytes of one lane (DV_NOSYM where no char ends), packed 2 per word.
-// prev = the word preceding the 16 bytes.  Returns the number of symbols.
-__device__ __forceinline__ int dv_symbolize16(uint4 w, uint32_t prev, uint32_t packed[8], bool& exotic) {
-    const uint32_t words[5] = { prev, w.x, w.y, w.z, w.w };
-    int cnt = 0;
-#pragma unroll
-    for (int t = 0; t < 16; t++) {
-        const int q = 4 + t;
-        const uint32_t b  = (words[q >> 2] >> ((q & 3) * 8)) & 0xFFu;
-        const uint32_t p1 = (words[(q - 1) >> 2] >> (((q - 1) & 3) * 8)) & 0xFFu;
-        const uint32_t p2 = (words[(q - 2) >> 2] >> (((q - 2) & 3) * 8)) & 0xFFu;
-        uint32_t s;
-        if (b < 0x80u) s = dv_ascii_sym(b);
-        else if (b < 0xC0u) {                                           // continuation byte
-            if (p1 >= 0xC0u) s = (p1 < 0xE0u) ? 0u : DV_NOSYM;          // end of a 2-byte char / middle of a longer one
-            else if (p1 >= 0x80u) {
-                if (p2 >= 0xE0u) {
-                    if (p2 < 0xF0u) {                                   // end of a 3-byte char
-                        const uint32_t code = (((p2 & 0x0Fu) << 12) | ((p1 & 0x3Fu) << 6) | (b & 0x3Fu)) - 0x4E00u;
-                        s = code < 20992u ? code + 1u : 0u;
-                    } else s = DV_NOSYM;                                // third byte of a 4-byte char
-                } else s = 0u;                                          // end of a 4-byte char (or invalid)
-            } else s = 0u;                                              // invalid: continuation after ASCII
-            if (p1 == 0xE2u && b == 0x84u) exotic = true;
-        } else { s = DV_NOSYM; if (b == 0xC4u) exotic = true; }         // lead byte
-        cnt += (s != DV_NOSYM);
-        if (t & 1) packed[t >> 1] |= s << 16; else packed[t >> 1] = s;
-    }
-    return cnt;
+__device__ __forceinline__ uint32_t dv_token_sig(uint32_t prev_sym, uint32_t last_sym, uint32_t len) {
+    return (prev_sym * 0x9E3779B1u) ^ (last_sym * 0x85EBCA6Bu) ^ (len * 0xC2B2AE35u);   // filter signature (top bits used)
 }
 
 // ---------------------------------------------------------------- exact serial path
@@ -103,6 +79,7 @@ __device__ void dv_tokenize_serial(const uint8_t* text, int32_t n, dv_warp_buf* 
     int32_t i = 0;
     int qn = 0; uint32_t qkind = 0;
     int cls = 0, alen = 0, plen = 0; uint64_t asum = 0, psum = 0; uint32_t prev_code = 0;      // lane-0 state
+    uint32_t s_prev = 0, s_last = 0;                                                            // last two symbols (for signatures)
     bool done = false;
     while (!done) {
         if (lane == 0) {
@@ -124,26 +101,27 @@ __device__ void dv_tokenize_serial(const uint8_t* text, int32_t n, dv_warp_buf* 
                     else if (cp == 0x0130u) { scls = 1; code = 9; brk_after = true; }      // -> 'i' + U+0307
                 }
                 if (cls == 1 && scls != 1) {                                               // ASCII run closes
-                    if (alen >= 2) wb->queue[qn++] = dv_token_key(asum, alen, false);
+                    if (alen >= 2) { wb->qsig[qn] = dv_token_sig(s_prev, s_last, alen); wb->queue[qn++] = dv_token_key(asum, alen, false); }
                     alen = 0; asum = 0;
                 }
                 if (cls == 2 && scls != 2) {                                               // CJK run closes
-                    if (plen >= 3) wb->queue[qn++] = dv_token_key(psum, plen, true);
+                    if (plen >= 3) { wb->qsig[qn] = dv_token_sig(s_prev, s_last, plen); wb->queue[qn++] = dv_token_key(psum, plen, true); }
                     plen = 0; psum = 0;
                 }
                 cls = scls;
                 if (done) break;
                 if (scls == 1) {
                     asum += (uint64_t)code * dv_kpos(alen, ktab); alen++;
+                    s_prev = s_last; s_last = DV_SYM_ASCII | code;
                     if (brk_after) {
-                        if (alen >= 2) wb->queue[qn++] = dv_token_key(asum, alen, false);
+                        if (alen >= 2) { wb->qsig[qn] = dv_token_sig(s_prev, s_last, alen); wb->queue[qn++] = dv_token_key(asum, alen, false); }
                         alen = 0; asum = 0; cls = 0;
                     }
                 } else if (scls == 2) {
-                    if (plen == 12) { wb->queue[qn++] = dv_token_key(psum, 12, true); plen = 0; psum = 0; }
+                    if (plen == 12) { wb->qsig[qn] = dv_token_sig(s_prev, s_last, 12); wb->queue[qn++] = dv_token_key(psum, 12, true); plen = 0; psum = 0; }
                     if (plen >= 1) { qkind |= 1u << qn; wb->queue[qn++] = ((uint64_t)prev_code << 15) | code; }
                     psum += (uint64_t)code * dv_kpos(plen, ktab); plen++;
-                    prev_code = code;
+                    prev_code = code; s_prev = s_last; s_last = code;
                 }
             }
         }
@@ -154,84 +132,96 @@ __device__ void dv_tokenize_serial(const uint8_t* text, int32_t n, dv_warp_buf* 
         const uint64_t key = lane < qn ? wb->queue[lane] : 0ULL;
         const bool is_bg = (qkind >> lane) & 1u;
         emit.bigram(lane < qn && is_bg, (uint32_t)key);
-        emit.token(lane < qn && !is_bg, key);
+        emit.token(lane < qn && !is_bg, key, lane < qn ? wb->qsig[lane] : 0u);
         __syncwarp();
     }
 }
 
 // ---------------------------------------------------------------- parallel fast path
-// Returns true (warp-uniform) if an exotic byte was met: the routine then stops at once and the
-// caller restarts the text on the serial path.  Detection happens in pass A of the tile holding
-// the byte, i.e. before any token it could influence is emitted (a token's last symbol and its
-// one-symbol look-ahead lie at most 4 bytes apart and a tile's last symbol is held back), so
-// everything emitted up to that point is a correct prefix; consumers are idempotent or reset
-// via emit.restart().
+// Returns true (warp-uniform) if the text must restart on the serial path.  Exotic bytes are
+// detected in pass A of the tile holding them, i.e. before any token they could influence is
+// emitted (a token's last symbol and its one-symbol look-ahead lie at most 4 bytes apart and a
+// tile's last symbol is held back), so everything emitted up to that point is a correct prefix;
+// consumers are idempotent or reset via emit.restart().
 template <class Emit>
 __device__ bool dv_tokenize_fast(const uint8_t* text, int32_t n, dv_warp_buf* wb, const unsigned long long* ktab, Emit& emit) {
     const int lane = threadIdx.x & 31;
     const int32_t a = (int32_t)((uintptr_t)text & 15u);
-    uint16_t* B = wb->sym;                         // B[0] = last processed symbol, B[1..] = pending symbols
-    if (lane == 0) B[0] = 0;
+    uint16_t* B = wb->sym;                         // B[0..H) processed history, B[H..] pending symbols
+    uint32_t* R = wb->raw + lane * 5;
+    const uint8_t* Rb = reinterpret_cast<const uint8_t*>(R);
+    B[lane] = 0; B[lane + 32] = 0;
     int pending = 0;
     uint32_t carry_word = 0;
-    int32_t gbase = 0;                             // global symbol index of B[1]
+    int32_t gbase = 0;                             // global symbol index of B[H]
     int32_t cstart = 0, astart = 0;                // global index of the most recent CJK / ASCII run start
-    uint64_t scarry = 0;                           // scan value at the last processed symbol
     __syncwarp();
     for (int32_t tile = -a; tile < n; tile += DV_TILE) {
-        // ---- pass A: load, classify, compact
+        // ---- pass A: load, find symbol positions (SWAR), decode, compact
         const int32_t pos = tile + lane * 16;
         uint4 w = make_uint4(0, 0, 0, 0);
+        uint32_t inmask = 0;                                           // bit t: byte t of this lane is inside the text
         if (pos < n && pos + 16 > 0) {
             w = *reinterpret_cast<const uint4*>(text + pos);
-            if (pos < 0 || pos + 16 > n) {                             // mask bytes outside the text
-                uint32_t ws[4] = { w.x, w.y, w.z, w.w };
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    uint32_t m = 0;
-#pragma unroll
-                    for (int bb = 0; bb < 4; bb++) { const int32_t q = pos + k * 4 + bb; if (q >= 0 && q < n) m |= 0xFFu << (bb * 8); }
-                    ws[k] &= m;
-                }
-                w = make_uint4(ws[0], ws[1], ws[2], ws[3]);
-            }
+            const int lo = pos < 0 ? -pos : 0, hi = (n - pos) < 16 ? (n - pos) : 16;
+            inmask = (0xFFFFu >> (16 - hi)) & (0xFFFFu << lo);
         }
         uint32_t prev = __shfl_up_sync(0xffffffffu, w.w, 1);
         if (lane == 0) prev = carry_word;
         carry_word = __shfl_sync(0xffffffffu, w.w, 31);
-        bool ex = false;
-        uint32_t packed[8];
-        int cnt = dv_symbolize16(w, prev, packed, ex);
-        if (__any_sync(0xffffffffu, ex)) return true;
-        // bytes outside the text were zeroed -> they produced separator symbols; drop them
-        if (pos < 0 || pos + 16 > n) {
-            cnt = 0;
+        R[0] = prev; R[1] = w.x; R[2] = w.y; R[3] = w.z; R[4] = w.w;
+        // per byte, flag in bit 7:  H = non-ASCII, b6/b5/b4 = next bits of the byte
+        uint32_t m16 = 0;
+        {
+            const uint32_t ws[5] = { prev, w.x, w.y, w.z, w.w };
+            uint32_t l3_prev;
+            {
+                const uint32_t x = ws[0], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
+                l3_prev = Hh & b6 & b5 & ~b4;
+            }
 #pragma unroll
-            for (int t = 0; t < 16; t++) {
-                const int32_t q = pos + t;
-                const uint32_t s = (packed[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-                if (q < 0 || q >= n) { if (t & 1) packed[t >> 1] |= 0xFFFF0000u; else packed[t >> 1] |= 0xFFFFu; }
-                else cnt += (s != DV_NOSYM);
+            for (int k = 1; k < 5; k++) {
+                const uint32_t x = ws[k], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
+                const uint32_t lead = Hh & b6, cont = Hh & ~b6;
+                const uint32_t l3 = lead & b5 & ~b4;
+                const uint32_t l24 = lead & ~(b5 & ~b4);                                  // 2-byte or 4-byte lead: separator at the lead
+                const uint32_t l3s = (l3 << 16) | (l3_prev >> 16);                       // lead3 two bytes earlier
+                const uint32_t ends = (~x & 0x80808080u) | l24 | (cont & l3s);
+                m16 |= ((((ends >> 7) * 0x00204081u) >> 21) & 0xFu) << ((k - 1) * 4);    // gather bits 0,8,16,24 -> 4 bits
+                l3_prev = l3;
             }
         }
+        m16 &= inmask;
+        const int cnt = __popc(m16);
         int incl = cnt;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += y; }
         const int total = __shfl_sync(0xffffffffu, incl, 31);
-        int widx = 1 + pending + incl - cnt;
-#pragma unroll
-        for (int t = 0; t < 16; t++) {
-            const uint32_t s = (packed[t >> 1] >> ((t & 1) * 16)) & 0xFFFFu;
-            if (s != DV_NOSYM) B[widx++] = (uint16_t)s;
+        int widx = DV_HIST + pending + incl - cnt;
+        bool ex = false;
+        __syncwarp();
+        while (m16) {
+            const int t = __ffs(m16) - 1; m16 &= m16 - 1;
+            const int ao = t + 1;                                       // byte offset of byte t-3 inside the lane's 20-byte block
+            const uint32_t lo = R[ao >> 2], hi2 = R[(ao >> 2) + 1];
+            const uint32_t x = __funnelshift_r(lo, hi2, (ao & 3) * 8);   // bytes t-3..t, byte t on top
+            const uint32_t b = x >> 24, p1 = (x >> 16) & 0xFFu, p2 = (x >> 8) & 0xFFu;
+            const uint32_t code = (((p2 & 0x0Fu) << 12) | ((p1 & 0x3Fu) << 6) | (b & 0x3Fu)) - 0x4E00u;
+            uint32_t s = (b < 0x80u) ? dv_ascii_sym(b) : ((b < 0xC0u && code < 20992u) ? code + 1u : 0u);
+            ex |= (b == 0xC4u) | (b < 0xC0u && b >= 0x80u && p2 == 0xE2u && p1 == 0x84u);
+            B[widx++] = (uint16_t)s;
         }
+        (void)Rb;
+        if (__any_sync(0xffffffffu, ex)) return true;
         const bool last = (tile + DV_TILE >= n);
         const int m = pending + total;
         int m_proc = m;
-        if (last) { if (lane == 0) B[1 + m] = 0; } else m_proc = m > 0 ? m - 1 : 0;
+        if (last) { if (lane == 0) B[DV_HIST + m] = 0; } else m_proc = m > 0 ? m - 1 : 0;
         __syncwarp();
         // ---- pass B: 32 symbols per step
+        bool too_long = false;
         for (int s0 = 0; s0 < m_proc; s0 += 32) {
-            const int i = 1 + s0 + lane;
+            const int i = DV_HIST + s0 + lane;
             const bool act = s0 + lane < m_proc;
             const uint32_t sv = act ? B[i] : 0u;
             const uint32_t sm1 = act ? B[i - 1] : 0u;
@@ -249,35 +239,41 @@ __device__ bool dv_tokenize_fast(const uint8_t* text, int32_t n, dv_warp_buf* wb
             if (as_mask) astart = step_g + (31 - __clz(as_mask));
             const uint32_t d = isC ? (uint32_t)(gi - my_cs) : (uint32_t)(gi - my_as);
             const uint32_t dist = isC ? d % 12u : (isA ? d : 0u);     // distance to the token's first symbol
-            // multilinear contribution + segmented inclusive scan (segments = pieces / ASCII runs)
-            uint64_t v = 0;
-            if (isC || isA) v = (uint64_t)(sv & 0x7FFFu) * dv_kpos(dist, ktab);
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) {
-                const uint64_t y = __shfl_up_sync(0xffffffffu, v, off);
-                if (lane >= off && dist >= (uint32_t)off) v += y;
-            }
-            if (dist > (uint32_t)lane) v += scarry;                    // token began before this step
-            const int nact = min(32, m_proc - s0);
-            scarry = __shfl_sync(0xffffffffu, v, nact - 1);
-            // tokens ending here
             const bool bg = prevC && dist != 0u;
-            const uint32_t bg_id = (sm1 << 15) | sv;
+            emit.bigram(bg, (sm1 << 15) | sv);
             const bool tk = isC ? ((dist == 11u || !nextC) && dist >= 2u) : (isA && !nextA && dist >= 1u);
-            const uint64_t key = dv_token_key(v, dist + 1u, isC);
-            emit.bigram(bg, bg_id);
-            emit.token(tk, key);
-        }
-        // ---- slide: keep the last processed symbol and the held-back one
-        __syncwarp();
-        if (!last && m > 0) {
-            if (lane == 0) {
-                const uint16_t h0 = m_proc >= 1 ? B[m_proc] : B[0];
-                const uint16_t h1 = B[m];
-                B[0] = h0; B[1] = h1;
+            const uint32_t len = dist + 1u;
+            const uint32_t sig = dv_token_sig(sm1, sv, len);
+            const bool need = tk && emit.need_token(sig);
+            uint64_t key = 0;
+            if (__any_sync(0xffffffffu, need)) {
+                if (need) {
+                    if (len > DV_HIST) too_long = true;
+                    else {
+                        uint64_t mm = 0;
+                        const uint16_t* tp = B + (i - (int)dist);
+                        for (uint32_t q = 0; q < len; q++) mm += (uint64_t)(tp[q] & 0x7FFFu) * ktab[q];
+                        key = dv_token_key(mm, len, isC);
+                    }
+                }
+                if (__any_sync(0xffffffffu, too_long)) return true;
+                emit.token(need, key, sig);
             }
-            pending = 1;
-        } else pending = last ? 0 : pending;
+        }
+        // ---- slide: keep the last DV_HIST processed symbols and the held-back one
+        __syncwarp();
+        {
+            const int keep = DV_HIST + ((!last && m > 0) ? 1 : 0);
+            uint16_t t0 = 0, t1 = 0, t2 = 0;
+            if (lane < keep) t0 = B[m_proc + lane];
+            if (lane + 32 < keep) t1 = B[m_proc + lane + 32];
+            if (lane + 64 < keep) t2 = B[m_proc + lane + 64];
+            __syncwarp();
+            if (lane < keep) B[lane] = t0;
+            if (lane + 32 < keep) B[lane + 32] = t1;
+            if (lane + 64 < keep) B[lane + 64] = t2;
+            pending = keep - DV_HIST;
+        }
         gbase += m_proc;
         __syncwarp();
     }

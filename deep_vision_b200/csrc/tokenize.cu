@@ -15,7 +15,8 @@ struct EmitToGlobal {
         n += __popc(m);
     }
     __device__ __forceinline__ void bigram(bool v, uint32_t id) { push(v, (uint64_t)id); }
-    __device__ __forceinline__ void token(bool v, uint64_t key) { push(v, key); }
+    __device__ __forceinline__ bool need_token(uint32_t) const { return true; }
+    __device__ __forceinline__ void token(bool v, uint64_t key, uint32_t) { push(v, key); }
 };
 
 // one warp per text; raw keys (with duplicates) go to scratch[seg_off[t] .. ), count to raw_cnt[t]
