@@ -28,6 +28,10 @@ _SIGS = {
     "dvb_last_kernel_ms": (C.c_float, [_vp]),
     "dvb_set_stream": (None, [_vp, _vp]),
     "dvb_tokenize_v3": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, C.c_int64, _vp]),
+    "dvb_symbolize": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp]),
+    "dvb_chunk_scores": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, C.c_int32, _vp, C.c_int32, _vp]),
+    "dvb_topk": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),
+    "dvb_chunk_build": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, C.c_int32, _vp] + [_vp] * 7),
     "dvb_bind_claims": (C.c_int32, [_vp, C.c_int32] + [_vp] * 6 + [C.c_int64] + [_vp] * 10 + [C.c_int64]),
 }
 

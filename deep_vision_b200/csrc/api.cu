@@ -34,6 +34,7 @@ extern "C" void dvb_destroy(dvb_ctx* c) {
         if (c->leases[i].ev0) cudaEventDestroy(c->leases[i].ev0);
         if (c->leases[i].ev1) cudaEventDestroy(c->leases[i].ev1);
         if (c->leases[i].arena.base) cudaFree(c->leases[i].arena.base);
+        for (void* b : c->leases[i].overflow) cudaFree(b);
     }
     delete c;
 }

@@ -23,6 +23,8 @@ struct dvb_arena {
 struct dvb_lease {
     cudaStream_t stream = nullptr;
     dvb_arena arena;
+    std::vector<void*> overflow;         // extra blocks of the previous call (arena was too small)
+    size_t high_water = 0;               // bytes the previous calls needed in total
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool busy = false;
 };
@@ -62,9 +64,15 @@ struct dvb_scope {
             if (l) break;
             std::this_thread::yield();
         }
-        l->arena.used = 0;
         cudaSetDevice(ctx->device);
+        // the previous call on this lease synchronised its stream before returning
+        for (void* b : l->overflow) cudaFree(b);
+        l->overflow.clear();
+        l->arena.used = 0;
+        call_bytes = 0;
+        if (l->high_water > l->arena.cap) reserve(l->high_water);
     }
+    size_t call_bytes = 0;
     ~dvb_scope() { std::lock_guard<std::mutex> g(ctx->mu); l->busy = false; }
     cudaStream_t stream() const { void* u = ctx->user_stream.load(); return u ? (cudaStream_t)u : l->stream; }
     // reserve total workspace up front (grows the arena if needed; invalidates earlier allocs)
@@ -83,11 +91,18 @@ struct dvb_scope {
         return DVB_OK;
     }
     template <typename T> T* alloc(size_t n) {
-        size_t bytes = (n * sizeof(T) + 255) & ~size_t(255);
-        if (l->arena.used + bytes > l->arena.cap) return nullptr;
-        T* p = reinterpret_cast<T*>(l->arena.base + l->arena.used);
-        l->arena.used += bytes;
-        return p;
+        size_t bytes = (n * sizeof(T) + 255 + 64) & ~size_t(255);
+        call_bytes += bytes;
+        if (call_bytes > l->high_water) l->high_water = call_bytes;
+        if (l->arena.used + bytes <= l->arena.cap) {
+            T* p = reinterpret_cast<T*>(l->arena.base + l->arena.used);
+            l->arena.used += bytes;
+            return p;
+        }
+        void* b = nullptr;                                       // arena too small this time: one-off block,
+        if (cudaMalloc(&b, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }   // the arena grows on the next call
+        l->overflow.push_back(b);
+        return reinterpret_cast<T*>(b);
     }
 };
 
@@ -100,3 +115,39 @@ static inline const T* dvb_in(int mem, const T* src, T* dst, size_t n, cudaStrea
     if (n) { cudaError_t e = cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, s); if (e != cudaSuccess) *err = e; }
     return dst;
 }
+
+// Host/device staging of call arguments.  HOST: inputs are copied to fresh workspace, outputs are
+// produced in workspace and copied back by finish().  DEVICE: caller pointers are used in place.
+struct dvb_io {
+    dvb_scope& sc; int mem; cudaStream_t st; cudaError_t err = cudaSuccess; bool oom = false;
+    struct Out { void* host; void* dev; size_t bytes; };
+    std::vector<Out> outs;
+    dvb_io(dvb_scope& s, int m) : sc(s), mem(m), st(s.stream()) {}
+    template <typename T> const T* in(const T* p, size_t n) {
+        if (mem == DVB_MEM_DEVICE || !p) return p;
+        T* d = sc.alloc<T>(n ? n : 1);
+        if (!d) { oom = true; return nullptr; }
+        if (n) { cudaError_t e = cudaMemcpyAsync(d, p, n * sizeof(T), cudaMemcpyHostToDevice, st); if (e != cudaSuccess) err = e; }
+        return d;
+    }
+    template <typename T> T* out(T* p, size_t n) {
+        if (mem == DVB_MEM_DEVICE || !p) return p;
+        T* d = sc.alloc<T>(n ? n : 1);
+        if (!d) { oom = true; return nullptr; }
+        outs.push_back({ p, d, n * sizeof(T) });
+        return d;
+    }
+    template <typename T> T* tmp(size_t n) { T* d = sc.alloc<T>(n ? n : 1); if (!d) oom = true; return d; }
+    int32_t check(dvb_ctx* ctx) {
+        if (oom) { dvb_set_err(ctx, "out of device memory%s%s"); return DVB_E_NOMEM; }
+        if (err != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s while staging arguments%s", cudaGetErrorString(err)); return DVB_E_CUDA; }
+        return DVB_OK;
+    }
+    int32_t finish(dvb_ctx* ctx) {
+        cudaError_t e = cudaGetLastError();
+        for (auto& o : outs) if (o.bytes && e == cudaSuccess) e = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s at finish%s", cudaGetErrorString(e)); return DVB_E_CUDA; }
+        return DVB_OK;
+    }
+};

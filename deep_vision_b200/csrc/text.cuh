@@ -70,6 +70,58 @@ __device__ __forceinline__ uint32_t dv_token_sig(uint32_t prev_sym, uint32_t las
     return (prev_sym * 0x9E3779B1u) ^ (last_sym * 0x85EBCA6Bu) ^ (len * 0xC2B2AE35u);   // filter signature (top bits used)
 }
 
+// ---- pass A building blocks (shared by the tokenizer and the symboliser in chunk.cu)
+// Load this lane's 16 bytes of the tile, stash [prev word, 4 words] in R, return the 16-bit mask of
+// bytes at which a symbol is produced: ASCII bytes, 2-/4-byte leads (separator at the lead) and the
+// third byte of 3-byte chars.  Bytes outside [0, n) never produce symbols.
+__device__ __forceinline__ uint32_t dv_tile_masks(const uint8_t* text, int32_t n, int32_t tile, int lane,
+                                                  uint32_t& carry_word, uint32_t* R) {
+    const int32_t pos = tile + lane * 16;
+    uint4 w = make_uint4(0, 0, 0, 0);
+    uint32_t inmask = 0;
+    if (pos < n && pos + 16 > 0) {
+        w = *reinterpret_cast<const uint4*>(text + pos);
+        const int lo = pos < 0 ? -pos : 0, hi = (n - pos) < 16 ? (n - pos) : 16;
+        inmask = (0xFFFFu >> (16 - hi)) & (0xFFFFu << lo);
+    }
+    uint32_t prev = __shfl_up_sync(0xffffffffu, w.w, 1);
+    if (lane == 0) prev = carry_word;
+    carry_word = __shfl_sync(0xffffffffu, w.w, 31);
+    R[0] = prev; R[1] = w.x; R[2] = w.y; R[3] = w.z; R[4] = w.w;
+    uint32_t m16 = 0;
+    const uint32_t ws[5] = { prev, w.x, w.y, w.z, w.w };
+    uint32_t l3_prev;
+    {
+        const uint32_t x = ws[0], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
+        l3_prev = Hh & b6 & b5 & ~b4;
+    }
+#pragma unroll
+    for (int k = 1; k < 5; k++) {
+        const uint32_t x = ws[k], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
+        const uint32_t lead = Hh & b6, cont = Hh & ~b6;
+        const uint32_t l3 = lead & b5 & ~b4;
+        const uint32_t l24 = lead & ~(b5 & ~b4);                                  // 2-byte or 4-byte lead: separator at the lead
+        const uint32_t l3s = (l3 << 16) | (l3_prev >> 16);                       // lead3 two bytes earlier
+        const uint32_t ends = (~x & 0x80808080u) | l24 | (cont & l3s);
+        m16 |= ((((ends >> 7) * 0x00204081u) >> 21) & 0xFu) << ((k - 1) * 4);    // gather bits 0,8,16,24 -> 4 bits
+        l3_prev = l3;
+    }
+    return m16 & inmask;
+}
+// Symbol produced at byte t (a set bit of dv_tile_masks) of this lane.  `c4` is set for a 0xC4 lead
+// (U+0100..U+013F: U+0130 lower-cases to 'i' + U+0307, which needs the serial path).
+__device__ __forceinline__ uint32_t dv_decode_sym(const uint32_t* R, int t, bool& c4) {
+    const int ao = t + 1;                                               // offset of byte t-3 in the lane's 20-byte block
+    const uint32_t x = __funnelshift_r(R[ao >> 2], R[(ao >> 2) + 1], (ao & 3) * 8);   // bytes t-3..t, byte t on top
+    const uint32_t b = x >> 24, p1 = (x >> 16) & 0xFFu, p2 = (x >> 8) & 0xFFu;
+    const uint32_t code = (((p2 & 0x0Fu) << 12) | ((p1 & 0x3Fu) << 6) | (b & 0x3Fu)) - 0x4E00u;
+    c4 |= (b == 0xC4u);
+    if (b < 0x80u) return dv_ascii_sym(b);
+    if (b >= 0xC0u) return 0u;                                          // 2-/4-byte lead
+    if (code < 20992u) return code + 1u;                                // CJK
+    return ((x >> 8) == 0x00AA84E2u) ? (DV_SYM_ASCII | 11u) : 0u;       // U+212A KELVIN SIGN lower-cases to 'k'
+}
+
 // ---------------------------------------------------------------- exact serial path
 // Lane 0 walks the text; keys are queued and emitted by the whole warp.  Handles every
 // code point exactly (U+0130 -> 'i' + separator, U+212A -> 'k').
@@ -149,7 +201,6 @@ __device__ bool dv_tokenize_fast(const uint8_t* text, int32_t n, dv_warp_buf* wb
     const int32_t a = (int32_t)((uintptr_t)text & 15u);
     uint16_t* B = wb->sym;                         // B[0..H) processed history, B[H..] pending symbols
     uint32_t* R = wb->raw + lane * 5;
-    const uint8_t* Rb = reinterpret_cast<const uint8_t*>(R);
     B[lane] = 0; B[lane + 32] = 0;
     int pending = 0;
     uint32_t carry_word = 0;
@@ -158,40 +209,7 @@ __device__ bool dv_tokenize_fast(const uint8_t* text, int32_t n, dv_warp_buf* wb
     __syncwarp();
     for (int32_t tile = -a; tile < n; tile += DV_TILE) {
         // ---- pass A: load, find symbol positions (SWAR), decode, compact
-        const int32_t pos = tile + lane * 16;
-        uint4 w = make_uint4(0, 0, 0, 0);
-        uint32_t inmask = 0;                                           // bit t: byte t of this lane is inside the text
-        if (pos < n && pos + 16 > 0) {
-            w = *reinterpret_cast<const uint4*>(text + pos);
-            const int lo = pos < 0 ? -pos : 0, hi = (n - pos) < 16 ? (n - pos) : 16;
-            inmask = (0xFFFFu >> (16 - hi)) & (0xFFFFu << lo);
-        }
-        uint32_t prev = __shfl_up_sync(0xffffffffu, w.w, 1);
-        if (lane == 0) prev = carry_word;
-        carry_word = __shfl_sync(0xffffffffu, w.w, 31);
-        R[0] = prev; R[1] = w.x; R[2] = w.y; R[3] = w.z; R[4] = w.w;
-        // per byte, flag in bit 7:  H = non-ASCII, b6/b5/b4 = next bits of the byte
-        uint32_t m16 = 0;
-        {
-            const uint32_t ws[5] = { prev, w.x, w.y, w.z, w.w };
-            uint32_t l3_prev;
-            {
-                const uint32_t x = ws[0], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
-                l3_prev = Hh & b6 & b5 & ~b4;
-            }
-#pragma unroll
-            for (int k = 1; k < 5; k++) {
-                const uint32_t x = ws[k], Hh = x & 0x80808080u, b6 = (x << 1) & 0x80808080u, b5 = (x << 2) & 0x80808080u, b4 = (x << 3) & 0x80808080u;
-                const uint32_t lead = Hh & b6, cont = Hh & ~b6;
-                const uint32_t l3 = lead & b5 & ~b4;
-                const uint32_t l24 = lead & ~(b5 & ~b4);                                  // 2-byte or 4-byte lead: separator at the lead
-                const uint32_t l3s = (l3 << 16) | (l3_prev >> 16);                       // lead3 two bytes earlier
-                const uint32_t ends = (~x & 0x80808080u) | l24 | (cont & l3s);
-                m16 |= ((((ends >> 7) * 0x00204081u) >> 21) & 0xFu) << ((k - 1) * 4);    // gather bits 0,8,16,24 -> 4 bits
-                l3_prev = l3;
-            }
-        }
-        m16 &= inmask;
+        uint32_t m16 = dv_tile_masks(text, n, tile, lane, carry_word, R);
         const int cnt = __popc(m16);
         int incl = cnt;
 #pragma unroll
@@ -199,19 +217,10 @@ __device__ bool dv_tokenize_fast(const uint8_t* text, int32_t n, dv_warp_buf* wb
         const int total = __shfl_sync(0xffffffffu, incl, 31);
         int widx = DV_HIST + pending + incl - cnt;
         bool ex = false;
-        __syncwarp();
         while (m16) {
             const int t = __ffs(m16) - 1; m16 &= m16 - 1;
-            const int ao = t + 1;                                       // byte offset of byte t-3 inside the lane's 20-byte block
-            const uint32_t lo = R[ao >> 2], hi2 = R[(ao >> 2) + 1];
-            const uint32_t x = __funnelshift_r(lo, hi2, (ao & 3) * 8);   // bytes t-3..t, byte t on top
-            const uint32_t b = x >> 24, p1 = (x >> 16) & 0xFFu, p2 = (x >> 8) & 0xFFu;
-            const uint32_t code = (((p2 & 0x0Fu) << 12) | ((p1 & 0x3Fu) << 6) | (b & 0x3Fu)) - 0x4E00u;
-            uint32_t s = (b < 0x80u) ? dv_ascii_sym(b) : ((b < 0xC0u && code < 20992u) ? code + 1u : 0u);
-            ex |= (b == 0xC4u) | (b < 0xC0u && b >= 0x80u && p2 == 0xE2u && p1 == 0x84u);
-            B[widx++] = (uint16_t)s;
+            B[widx++] = (uint16_t)dv_decode_sym(R, t, ex);
         }
-        (void)Rb;
         if (__any_sync(0xffffffffu, ex)) return true;
         const bool last = (tile + DV_TILE >= n);
         const int m = pending + total;

@@ -1,0 +1,292 @@
+"""Uploaded-document chunking and top-k chunk recall (rows a4-a7 of SURVEY.md §8).
+
+Host-side mirror of the reference interface (web/server.py):
+  * `_build_reference_material_chunks(content)`                         31932
+  * `_tokenize_reference_material_query(query_text)`                    32037
+  * `select_reference_material_context(doc, *, query_text, max_chars, chunk_limit)`   32054
+plus the batch primitives `chunk_scores` / `topk` they are built on.
+
+On the GPU: the code-point index + window walk of the chunker (dvb_chunk_build), decode + lower +
+non-overlapping substring counting (dvb_chunk_scores) and the top-k (dvb_topk).  On the host: what
+the reference does once per call around those loops — query term extraction (a <=300-char string),
+dict / prefix-string assembly and the `chunks.json` manifest I/O.
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import re
+from dataclasses import dataclass
+from pathlib import Path
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from .packing import encode, pack_texts, ptr
+
+_TERM = re.compile(r"[a-z0-9_]{2,}|[一-鿿]{2,}")
+_WS = re.compile(r"\s+")
+
+
+@dataclass
+class ReferenceMaterialConfig:
+    """web/server.py:31882-31889 and :858 (read at call time)."""
+    chunk_size: int = 1800
+    chunk_overlap: int = 160
+    context_chunk_limit: int = 4
+    inline_chunk_preview_limit: int = 120
+    preview_limit: int = 300
+    max_doc_length: int = 2000
+
+    def normalized(self) -> "ReferenceMaterialConfig":
+        size = max(800, int(self.chunk_size))
+        overlap = max(0, int(self.chunk_overlap))
+        if overlap >= size:
+            overlap = max(0, size // 10)
+        return ReferenceMaterialConfig(size, overlap, max(1, int(self.context_chunk_limit)),
+                                       max(20, int(self.inline_chunk_preview_limit)), self.preview_limit, self.max_doc_length)
+
+
+DEFAULT_CONFIG = ReferenceMaterialConfig()
+
+
+# ----------------------------------------------------------------------------- a6 (host, per query)
+
+def _tokenize_reference_material_query(query_text: str) -> List[str]:
+    """web/server.py:32037-32051: ordered distinct terms; pure-CJK terms of >= 6 chars also
+    contribute their 4-grams, then their 3-grams; at most 80 terms."""
+    lowered = str(query_text or "").lower()
+    terms: List[str] = []
+    seen = set()
+
+    def add(t: str):
+        if t and t not in seen:
+            seen.add(t)
+            terms.append(t)
+
+    for term in _TERM.findall(lowered):
+        add(term)
+        if len(term) >= 6 and "一" <= term[0] <= "鿿":
+            for size in (4, 3):
+                for i in range(len(term) - size + 1):
+                    add(term[i:i + size])
+    return terms[:80]
+
+
+def terms_to_symbols(queries_terms: Sequence[Sequence[str]]) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """Terms -> the kernels' symbol alphabet (include/dvb200.h): (term_sym u16, term_off i32, query_term_off i32)."""
+    syms: List[int] = []
+    toff = [0]
+    qoff = [0]
+    for terms in queries_terms:
+        for t in terms:
+            for ch in t:
+                o = ord(ch)
+                if 0x4E00 <= o <= 0x9FFF:
+                    syms.append(o - 0x4E00 + 1)
+                elif "a" <= ch <= "z":
+                    syms.append(0x8000 | (o - 97 + 1))
+                elif "0" <= ch <= "9":
+                    syms.append(0x8000 | (o - 48 + 27))
+                elif ch == "_":
+                    syms.append(0x8000 | 37)
+                else:
+                    raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
+            toff.append(len(syms))
+        qoff.append(len(toff) - 1)
+    return (np.asarray(syms if syms else [0], np.uint16), np.asarray(toff, np.int32), np.asarray(qoff, np.int32))
+
+
+# ----------------------------------------------------------------------------- GPU primitives
+
+def chunk_scores(chunk_texts: Sequence[str], queries_terms: Sequence[Sequence[str]], ctx=None, packed=None) -> np.ndarray:
+    """score[q, c] = sum_t lower(chunk_c).count(term_t)   (web/server.py:32075-32076)."""
+    ctx = ctx or _lib.Context.get()
+    data, off = packed if packed is not None else pack_texts(chunk_texts)
+    n = len(off) - 1
+    tsym, toff, qoff = terms_to_symbols(queries_terms)
+    nq = len(queries_terms)
+    out = np.zeros(max(nq * n, 1), np.int32)
+    if n and nq:
+        rc = ctx.lib.dvb_chunk_scores(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, ptr(tsym), ptr(toff), len(toff) - 1,
+                                      ptr(qoff), nq, ptr(out))
+        ctx.check(rc, "dvb_chunk_scores")
+    return out[:nq * n].reshape(nq, n)
+
+
+def topk(score: np.ndarray, k: int, index: Optional[np.ndarray] = None, index_base: int = 0, ctx=None):
+    """Per row of `score`: (idx[k], score[k], n_valid) under (score desc, index asc), positives only."""
+    ctx = ctx or _lib.Context.get()
+    score = np.ascontiguousarray(np.atleast_2d(score), np.int32)
+    nq, n = score.shape
+    idx = np.ascontiguousarray(np.atleast_2d(index), np.int64) if index is not None else None
+    oi = np.full((nq, k), -1, np.int64)
+    os_ = np.zeros((nq, k), np.int32)
+    on = np.zeros(nq, np.int32)
+    rc = ctx.lib.dvb_topk(ctx.handle, _lib.MEM_HOST, ptr(score) if n else None, ptr(idx) if idx is not None else None, n, nq,
+                          int(index_base), int(k), ptr(oi), ptr(os_), ptr(on))
+    ctx.check(rc, "dvb_topk")
+    return oi, os_, on
+
+
+def symbolize(texts: Sequence[str], ctx=None) -> List[np.ndarray]:
+    ctx = ctx or _lib.Context.get()
+    data, off = pack_texts(texts)
+    n = len(texts)
+    sym = np.zeros(int(off[-1]) + 8, np.uint16)
+    cnt = np.zeros(max(n, 1), np.int32)
+    if n:
+        rc = ctx.lib.dvb_symbolize(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, ptr(sym), ptr(cnt))
+        ctx.check(rc, "dvb_symbolize")
+    return [sym[off[i]:off[i] + cnt[i]].copy() for i in range(n)]
+
+
+def chunk_spans(contents: Sequence[str], chunk_size: int, overlap: int, ctx=None):
+    """dvb_chunk_build on a batch of documents -> per document a list of
+    (start, end, tstart, tend, tbyte0, tbyte1) and the encoded bytes of each document."""
+    ctx = ctx or _lib.Context.get()
+    data, off = pack_texts(contents)
+    n = len(contents)
+    third = max(0, chunk_size // 3)
+    step = max(1, min(chunk_size, max(200, chunk_size // 2) + 1) - min(overlap, third))
+    caps = (off[1:] - off[:-1]) // step + 2
+    cap_off = np.zeros(n + 1, np.int64)
+    np.cumsum(caps, out=cap_off[1:])
+    cap = int(cap_off[-1])
+    count = np.zeros(max(n, 1), np.int32)
+    arrs32 = [np.zeros(max(cap, 1), np.int32) for _ in range(4)]
+    arrs64 = [np.zeros(max(cap, 1), np.int64) for _ in range(2)]
+    if n:
+        rc = ctx.lib.dvb_chunk_build(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, int(chunk_size), int(overlap), ptr(cap_off),
+                                     ptr(count), *[ptr(a) for a in arrs32], *[ptr(a) for a in arrs64])
+        ctx.check(rc, "dvb_chunk_build")
+    out = []
+    for d in range(n):
+        c = int(count[d])
+        if c > caps[d]:
+            raise _lib.DvbError("dvb_chunk_build: capacity bound violated")
+        s = int(cap_off[d])
+        out.append(list(zip(*[a[s:s + c].tolist() for a in arrs32 + arrs64])))
+    return out, data, off
+
+
+# ----------------------------------------------------------------------------- reference-shaped API
+
+def _compact_preview(content: str, limit: int) -> str:
+    """web/server.py:31892-31896"""
+    text = _WS.sub(" ", str(content or "")).strip()
+    if len(text) <= limit:
+        return text
+    return text[: max(0, limit - 3)].rstrip() + "..."
+
+
+def _build_reference_material_chunks(content: str, *, config: ReferenceMaterialConfig = DEFAULT_CONFIG, ctx=None) -> List[dict]:
+    """Drop-in for web/server.py:31932: list of {chunk_id, index, start, end, text, preview}."""
+    text = str(content or "")
+    if not text:
+        return []
+    cfg = config.normalized()
+    overlap = min(cfg.chunk_overlap, max(0, cfg.chunk_size // 3))
+    spans, data, off = chunk_spans([text], cfg.chunk_size, overlap, ctx=ctx)
+    raw = data[: int(off[1])].tobytes()
+    chunks = []
+    for (start, end, _ts, _te, b0, b1) in spans[0]:
+        chunk_text = raw[b0:b1].decode("utf-8", "surrogatepass")
+        chunks.append({
+            "chunk_id": f"chunk-{len(chunks) + 1:04d}",
+            "index": len(chunks),
+            "start": start,
+            "end": end,
+            "text": chunk_text,
+            "preview": _compact_preview(chunk_text, cfg.inline_chunk_preview_limit),
+        })
+    return chunks
+
+
+def build_chunk_manifest(*, doc_id: str, filename: str, content: str, ext: str,
+                         config: ReferenceMaterialConfig = DEFAULT_CONFIG, ctx=None) -> dict:
+    """The `chunks.json` payload of save_reference_material_fulltext_artifacts (web/server.py:31990-31999)."""
+    text = str(content or "")
+    cfg = config.normalized()
+    return {
+        "version": 1, "doc_id": doc_id, "name": filename, "type": ext,
+        "content_sha256": hashlib.sha256(text.encode("utf-8")).hexdigest(),
+        "chunk_size": cfg.chunk_size, "chunk_overlap": cfg.chunk_overlap,
+        "chunks": _build_reference_material_chunks(text, config=config, ctx=ctx),
+    }
+
+
+def load_chunks_from_manifest(path) -> List[dict]:
+    """web/server.py:32020-32034 (path already resolved by the caller); I/O errors -> []."""
+    try:
+        payload = json.loads(Path(path).read_text(encoding="utf-8"))
+    except Exception:
+        return []
+    chunks = payload.get("chunks", []) if isinstance(payload, dict) else []
+    return [c for c in chunks if isinstance(c, dict) and str(c.get("text") or "").strip()]
+
+
+def select_reference_material_context(doc: dict, *, query_text: str = "", max_chars: int = 0, chunk_limit: int = 0,
+                                      chunk_loader: Optional[Callable[[dict], List[dict]]] = None,
+                                      config: ReferenceMaterialConfig = DEFAULT_CONFIG, ctx=None) -> Tuple[str, dict]:
+    """Drop-in for web/server.py:32054.  `chunk_loader` is the reference's load_reference_material_chunks."""
+    cfg = config.normalized()
+    chunks = chunk_loader(doc) if chunk_loader is not None else []
+    limit = max(1, int(max_chars or cfg.max_doc_length))
+    if not chunks:
+        content = str((doc or {}).get("content") or "")
+        return content[:limit], {"mode": "stored_content", "selected_chunks": [], "chunk_count": 0}
+
+    terms = _tokenize_reference_material_query(query_text)
+    max_chunks = max(1, int(chunk_limit or cfg.context_chunk_limit))
+    selected: List[dict] = []
+    picked = []
+    if terms:
+        texts = [str(c.get("text") or "") for c in chunks]
+        scores = chunk_scores(texts, [terms], ctx=ctx)[0]
+        order_index = np.asarray([int(c.get("index", 0) or 0) for c in chunks], np.int64)
+        pos = np.arange(len(chunks), dtype=np.int64)
+        if np.array_equal(order_index, pos):
+            k = min(max_chunks, 32)
+            idx, _sc, n_valid = topk(scores, k, ctx=ctx)
+            picked = idx[0][: int(n_valid[0])].tolist()
+            if max_chunks > 32 and int(n_valid[0]) == 32:
+                picked = None                        # rare: more than 32 chunks requested -> generic path below
+        else:
+            picked = None
+        if picked is None:                           # chunk["index"] is not the list position, or k > 32:
+            ranked = sorted((i for i in range(len(chunks)) if scores[i] > 0), key=lambda i: (-int(scores[i]), int(order_index[i]), i))
+            picked = ranked[:max_chunks]
+    if picked:
+        selected = [chunks[i] for i in picked]
+        selected.sort(key=lambda item: int(item.get("index", 0) or 0))
+    else:
+        candidates = [0]
+        if len(chunks) > 2:
+            candidates.append(len(chunks) // 2)
+        if len(chunks) > 1:
+            candidates.append(len(chunks) - 1)
+        for i in candidates:
+            if chunks[i] not in selected:
+                selected.append(chunks[i])
+            if len(selected) >= max_chunks:
+                break
+
+    parts, used, meta_sel = [], 0, []
+    for chunk in selected:
+        text = str(chunk.get("text") or "").strip()
+        if not text:
+            continue
+        prefix = f"[片段 {int(chunk.get('index', 0) or 0) + 1}/{len(chunks)}]\n"
+        available = limit - used - len(prefix)
+        if available <= 0:
+            break
+        clipped = text[:available]
+        parts.append(prefix + clipped)
+        used += len(prefix) + len(clipped)
+        meta_sel.append({"chunk_id": chunk.get("chunk_id"), "index": chunk.get("index"), "start": chunk.get("start"), "end": chunk.get("end")})
+        if used >= limit:
+            break
+    return "\n\n".join(parts).strip(), {"mode": "chunk_selection", "selected_chunks": meta_sel, "chunk_count": len(chunks),
+                                       "query_terms": terms[:12]}

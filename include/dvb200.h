@@ -95,6 +95,43 @@ int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
                         int32_t* out_len_claim, int32_t* out_len_fact,
                         int64_t max_claim_group_bytes);
 
+/* ---- a7  replaces: scoring loop + top-k of select_reference_material_context   web/server.py:32073-32087
+ * Symbols: the lowered text as uint16 per character: 0 = separator (anything that is not a token
+ * character), 1..20992 = CJK U+4E00+code-1, 0x8000|code = ASCII [a-z0-9_] (code a-z 1..26, 0-9 27..36, _ 37).
+ * U+0130 yields 'i' + separator, U+212A yields 'k' (CPython str.lower()).  Query terms (web/server.py:32039)
+ * contain only token characters, so lowered.count(term) == non-overlapping substring count on symbols. */
+
+/* text t -> out_sym[off[t]-off[0] .. +out_cnt[t])   (out_sym needs off[n]-off[0] entries) */
+int32_t dvb_symbolize(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_texts,
+                      uint16_t* out_sym, int32_t* out_cnt);
+
+/* out_score[q*n_chunks + c] = sum over the terms of query q of count(term in lower(chunk c)).
+ * Terms are symbol strings: term t = term_sym[term_off[t] .. term_off[t+1]); query q owns terms
+ * [query_term_off[q], query_term_off[q+1]).  Exact scan; intended for API-sized inputs. */
+int32_t dvb_chunk_scores(dvb_ctx* ctx, int32_t mem, const uint8_t* chunk_utf8, const int64_t* chunk_off, int64_t n_chunks,
+                         const uint16_t* term_sym, const int32_t* term_off, int32_t n_terms,
+                         const int32_t* query_term_off, int32_t nq, int32_t* out_score);
+
+/* Per query: the k (<= 32) best candidates with score > 0 under (score desc, index asc) ==
+ * sorted(positive, key=(-score, index))[:k].  score is [nq][n]; idx is [nq][n] explicit indices or NULL
+ * (index = index_base + position).  Also merges candidate lists (per shard / per GPU after the
+ * all-gather): pass the gathered lists as score/idx.  out_idx/out_score are [nq][k] (idx -1 / score 0 =
+ * empty), out_n[q] = number of valid entries. */
+int32_t dvb_topk(dvb_ctx* ctx, int32_t mem, const int32_t* score, const int64_t* idx, int64_t n, int32_t nq,
+                 int64_t index_base, int32_t k, int64_t* out_idx, int32_t* out_score, int32_t* out_n);
+
+/* ---- a4  replaces: _build_reference_material_chunks(content)   web/server.py:31932-31970
+ * Per document d the chunks are written at [cap_off[d], cap_off[d] + out_count[d]) of the output arrays
+ * (cap_off[n_docs+1]: caller-chosen capacities; a document of B bytes never yields more than
+ * B / max(1, min(size, max(200,size/2)+1) - min(overlap,size/3)) + 2 chunks).  start/end/tstart/tend are CODE-POINT
+ * indices: chunk["start"], chunk["end"], and chunk["text"] == content[tstart:tend] (== content[start:end].strip());
+ * tbyte0/tbyte1 are the byte offsets of tstart/tend inside the document.  Chunks whose stripped text is
+ * empty are skipped (web/server.py:31952), so `index` is the position in the output. */
+int32_t dvb_chunk_build(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_docs,
+                        int32_t chunk_size, int32_t overlap, const int64_t* cap_off,
+                        int32_t* out_count, int32_t* out_start, int32_t* out_end, int32_t* out_tstart, int32_t* out_tend,
+                        int64_t* out_tbyte0, int64_t* out_tbyte1);
+
 #ifdef __cplusplus
 }
 #endif
