@@ -36,6 +36,7 @@ extern "C" void dvb_destroy(dvb_ctx* c) {
         if (c->leases[i].arena.base) cudaFree(c->leases[i].arena.base);
         for (void* b : c->leases[i].overflow) cudaFree(b);
     }
+    for (int i = 0; i < 6; i++) if (c->unicode_dev[i]) cudaFree(c->unicode_dev[i]);
     delete c;
 }
 

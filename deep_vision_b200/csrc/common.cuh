@@ -39,6 +39,8 @@ struct dvb_ctx {
     std::atomic<int> timing{0};
     std::atomic<void*> user_stream{nullptr};   // dvb_set_stream: run every call on the caller's stream
     float last_ms = 0.f;
+    std::mutex unicode_mu;
+    void* unicode_dev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // CPython case tables (gate.cu)
     // per-thread error text would need TLS keyed by ctx; one buffer per ctx guarded by mu is enough here
     char err[512] = {0};
 };

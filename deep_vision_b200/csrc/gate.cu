@@ -1,0 +1,494 @@
+// gate.cu — question-similarity gate and solution-signature Jaccard.
+// replaces: normalize_interview_question_text / question_token_set / is_similar_interview_question /
+//           find_similar_interview_question_log      (reference web/server.py:20462-20501)
+//           _solution_signature_ngrams / _solution_jaccard_similarity   (web/server.py:36798-36813)
+//
+//  k_question_keys  one thread per question: decode, strip, full CPython lower() (table from
+//                   include/dv_unicode_tables.h, final-sigma rule included), the ordered synonym
+//                   replaces, punctuation/whitespace removal, the stop-word replaces in the CALLER's
+//                   order, then the sorted distinct bigram keys over ALL code points.
+//  history index    (key, history id) pairs radix-sorted by key (sort.cuh): the postings of a bigram
+//                   are one contiguous, id-ordered range.
+//  k_gate_match     one CTA per candidate: postings of its bigrams are accumulated into packed 16-bit
+//                   shared-memory counters (one per history question), then one pass over the counters
+//                   evaluates  inter / max(1, |L|+|R|-inter) >= threshold  in fp64 exactly as the
+//                   reference and keeps the LARGEST matching history index (reversed(logs) scan).
+#include "common.cuh"
+#include "sort.cuh"
+#include "../../include/dv_unicode_tables.h"
+
+struct GateUnicode {            // device copies of the CPython tables
+    const uint32_t* lower_src; const uint32_t* lower_dst;      // [N], [N][3]
+    const uint32_t* cased_lo; const uint32_t* cased_hi; const uint32_t* cign_lo; const uint32_t* cign_hi;
+    int n_lower, n_cased, n_cign;
+};
+struct GateTablesDev {          // synonym / stop-word tables as code-point CSR, caller order
+    const uint32_t* syn_src; const int32_t* syn_src_off; const uint32_t* syn_dst; const int32_t* syn_dst_off; int32_t n_syn;
+    const uint32_t* stop; const int32_t* stop_off; int32_t n_stop;
+};
+
+__device__ __forceinline__ bool gate_in_ranges(uint32_t cp, const uint32_t* lo, const uint32_t* hi, int n) {
+    int a = 0, b = n - 1;
+    while (a <= b) { const int m = (a + b) >> 1; if (cp < lo[m]) b = m - 1; else if (cp > hi[m]) a = m + 1; else return true; }
+    return false;
+}
+__device__ __forceinline__ bool gate_is_space(uint32_t c) {
+    return (c - 9u < 5u) || (c - 0x1Cu < 5u) || c == 0x85u || c == 0xA0u || c == 0x1680u || (c - 0x2000u < 11u) ||
+           c == 0x2028u || c == 0x2029u || c == 0x202Fu || c == 0x205Fu || c == 0x3000u;
+}
+__device__ __forceinline__ bool gate_is_punct(uint32_t c) {          // web/server.py:20466 character class besides \s
+    switch (c) {
+        case 0xFF0C: case 0x3002: case 0xFF1F: case 0xFF01: case 0x3001: case 0xFF1B: case 0xFF1A:
+        case ',': case '.': case '?': case '!': case ';': case ':': case 0xFF08: case 0xFF09: case '(': case ')':
+        case 0x3010: case 0x3011: case '[': case ']': case '"': case '\'': case 0x201C: case 0x201D: case 0x2018: case 0x2019:
+            return true;
+        default: return false;
+    }
+}
+// CPython str.lower() of in[0..n) -> out; returns new length (<= n + #U+0130)
+__device__ int64_t gate_lower(const uint32_t* in, int64_t n, uint32_t* out, const GateUnicode& U) {
+    int64_t k = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const uint32_t cp = in[i];
+        if (cp < 0x80u) { out[k++] = (cp - 'A' < 26u) ? cp + 32u : cp; continue; }
+        if (cp >= 0x3000u && cp < 0xA000u) { out[k++] = cp; continue; }         // CJK block: nothing is cased
+        if (cp == 0x3A3u) {                                                      // Final_Sigma context
+            int64_t j; uint32_t c = 0;
+            for (j = i - 1; j >= 0; j--) { c = in[j]; if (!gate_in_ranges(c, U.cign_lo, U.cign_hi, U.n_cign)) break; }
+            bool fin = (j >= 0 && gate_in_ranges(c, U.cased_lo, U.cased_hi, U.n_cased));
+            if (fin) {
+                for (j = i + 1; j < n; j++) { c = in[j]; if (!gate_in_ranges(c, U.cign_lo, U.cign_hi, U.n_cign)) break; }
+                fin = (j == n || !gate_in_ranges(c, U.cased_lo, U.cased_hi, U.n_cased));
+            }
+            out[k++] = fin ? 0x3C2u : 0x3C3u;
+            continue;
+        }
+        int a = 0, b = U.n_lower - 1, hit = -1;
+        while (a <= b) { const int m = (a + b) >> 1; const uint32_t s = U.lower_src[m]; if (cp < s) b = m - 1; else if (cp > s) a = m + 1; else { hit = m; break; } }
+        if (hit < 0) { out[k++] = cp; continue; }
+        for (int t = 0; t < 3; t++) { const uint32_t dcp = U.lower_dst[hit * 3 + t]; if (!dcp) break; out[k++] = dcp; }
+    }
+    return k;
+}
+// str.replace(src, dst): left-to-right, non-overlapping
+__device__ int64_t gate_replace(const uint32_t* in, int64_t n, const uint32_t* src, int32_t ns, const uint32_t* dst, int32_t nd, uint32_t* out) {
+    if (ns <= 0) { for (int64_t i = 0; i < n; i++) out[i] = in[i]; return n; }
+    int64_t i = 0, k = 0;
+    while (i < n) {
+        bool m = (i + ns <= n) && in[i] == src[0];
+        for (int32_t j = 1; m && j < ns; j++) m = in[i + j] == src[j];
+        if (m) { for (int32_t j = 0; j < nd; j++) out[k++] = dst[j]; i += ns; }
+        else out[k++] = in[i++];
+    }
+    return k;
+}
+__device__ void gate_heapsort(unsigned long long* a, int64_t n) {
+    for (int64_t start = n / 2 - 1; start >= 0; start--) {
+        int64_t root = start;
+        for (;;) { int64_t c = 2 * root + 1; if (c >= n) break; if (c + 1 < n && a[c] < a[c + 1]) c++; if (a[root] >= a[c]) break; const unsigned long long t = a[root]; a[root] = a[c]; a[c] = t; root = c; }
+    }
+    for (int64_t end = n - 1; end > 0; end--) {
+        const unsigned long long t0 = a[0]; a[0] = a[end]; a[end] = t0;
+        int64_t root = 0;
+        for (;;) { int64_t c = 2 * root + 1; if (c >= end) break; if (c + 1 < end && a[c] < a[c + 1]) c++; if (a[root] >= a[c]) break; const unsigned long long t = a[root]; a[root] = a[c]; a[c] = t; root = c; }
+    }
+}
+
+// one thread per question.  Scratch: two code-point buffers of cap_off[s+1]-cap_off[s] entries each;
+// keys of question s are written at keys[cap_off[s] ...], their count to key_cnt[s]; the normalised text
+// (optional) to norm[cap_off[s] ...] / norm_len[s].
+__global__ void __launch_bounds__(128) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
+                                                        const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
+                                                        GateUnicode U, GateTablesDev T,
+                                                        unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
+                                                        uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t* t = utf8 + off[s];
+        const int64_t nb = off[s + 1] - off[s];
+        uint32_t* a = bufA + cap_off[s]; uint32_t* b = bufB + cap_off[s];
+        // decode
+        int64_t m = 0;
+        for (int64_t i = 0; i < nb;) {
+            uint32_t c = t[i], cp; int len;
+            if (c < 0x80u) { cp = c; len = 1; } else if (c < 0xE0u) { cp = c & 0x1Fu; len = 2; } else if (c < 0xF0u) { cp = c & 0x0Fu; len = 3; } else { cp = c & 0x07u; len = 4; }
+            for (int j = 1; j < len && i + j < nb; j++) cp = (cp << 6) | (t[i + j] & 0x3Fu);
+            i += len; a[m++] = cp;
+        }
+        // strip().lower()
+        int64_t lo = 0, hi = m;
+        while (lo < hi && gate_is_space(a[lo])) lo++;
+        while (hi > lo && gate_is_space(a[hi - 1])) hi--;
+        m = gate_lower(a + lo, hi - lo, b, U);
+        uint32_t* cur = b; uint32_t* oth = a;
+        for (int32_t y = 0; y < T.n_syn; y++) {
+            m = gate_replace(cur, m, T.syn_src + T.syn_src_off[y], T.syn_src_off[y + 1] - T.syn_src_off[y],
+                             T.syn_dst + T.syn_dst_off[y], T.syn_dst_off[y + 1] - T.syn_dst_off[y], oth);
+            uint32_t* tmp = cur; cur = oth; oth = tmp;
+        }
+        { int64_t k = 0; for (int64_t i = 0; i < m; i++) { const uint32_t c = cur[i]; if (!gate_is_space(c) && !gate_is_punct(c)) cur[k++] = c; } m = k; }
+        for (int32_t y = 0; y < T.n_stop; y++) {
+            m = gate_replace(cur, m, T.stop + T.stop_off[y], T.stop_off[y + 1] - T.stop_off[y], nullptr, 0, oth);
+            uint32_t* tmp = cur; cur = oth; oth = tmp;
+        }
+        if (norm) { for (int64_t i = 0; i < m; i++) norm[cap_off[s] + i] = cur[i]; norm_len[s] = (int32_t)m; }
+        // bigram keys, sorted distinct
+        unsigned long long* ks = keys + cap_off[s];
+        int64_t nk = 0;
+        if (m == 1) { ks[0] = (1ULL << 42) | cur[0]; nk = 1; }
+        else if (m > 1) {
+            for (int64_t i = 0; i + 1 < m; i++) ks[i] = ((unsigned long long)cur[i] << 21) | cur[i + 1];
+            nk = m - 1;
+            gate_heapsort(ks, nk);
+            int64_t u = 1; for (int64_t i = 1; i < nk; i++) if (ks[i] != ks[u - 1]) ks[u++] = ks[i];
+            nk = u;
+        }
+        key_cnt[s] = (int32_t)nk;
+    }
+}
+
+// (key, hid) pairs of the history questions, compacted at pair_off[h]
+__global__ void k_gate_pairs(const unsigned long long* __restrict__ keys, const int64_t* __restrict__ cap_off, const int32_t* __restrict__ key_cnt,
+                             const int64_t* __restrict__ pair_off, int64_t n_hist, unsigned long long* __restrict__ pk, uint32_t* __restrict__ pv) {
+    for (int64_t h = blockIdx.x; h < n_hist; h += gridDim.x) {
+        const int32_t c = key_cnt[h];
+        for (int32_t i = threadIdx.x; i < c; i += blockDim.x) { pk[pair_off[h] + i] = keys[cap_off[h] + i]; pv[pair_off[h] + i] = (uint32_t)h; }
+    }
+}
+
+#define GATE_THREADS 256
+extern __shared__ uint32_t gate_acc[];
+__global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long long* __restrict__ ckeys, const int64_t* __restrict__ ccap_off,
+                                                              const int32_t* __restrict__ ccnt, int64_t n_cand,
+                                                              const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
+                                                              const int32_t* __restrict__ hcnt, int64_t n_hist, int32_t tile_h, double thr,
+                                                              int64_t* __restrict__ out) {
+    __shared__ long long s_best;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int acc_words = (tile_h + 1) >> 1;
+    for (int i = threadIdx.x; i < acc_words; i += GATE_THREADS) gate_acc[i] = 0u;
+    __syncthreads();
+    for (int64_t c = blockIdx.x; c < n_cand; c += gridDim.x) {
+        const int32_t L = ccnt[c];
+        const unsigned long long* ck = ckeys + ccap_off[c];
+        if (threadIdx.x == 0) s_best = -1;
+        __syncthreads();
+        if (L > 0) {
+            for (int64_t h0 = 0; h0 < n_hist; h0 += tile_h) {
+                const int64_t h1 = min(n_hist, h0 + (int64_t)tile_h);
+                for (int32_t j = warp; j < L; j += GATE_THREADS / 32) {
+                    const unsigned long long key = ck[j];
+                    int64_t a = 0, b = n_pairs;                                   // lower_bound of (key, h0)
+                    while (a < b) { const int64_t m = (a + b) >> 1; const unsigned long long k = pk[m]; if (k < key || (k == key && (int64_t)pv[m] < h0)) a = m + 1; else b = m; }
+                    for (int64_t p = a + lane; p < n_pairs; p += 32) {
+                        if (pk[p] != key) break;
+                        const int64_t h = pv[p];
+                        if (h >= h1) break;
+                        const uint32_t r = (uint32_t)(h - h0);
+                        atomicAdd(&gate_acc[r >> 1], 1u << ((r & 1u) * 16));
+                    }
+                }
+                __syncthreads();
+                long long best = -1;
+                for (int i = threadIdx.x; i < acc_words; i += GATE_THREADS) {
+                    const uint32_t w = gate_acc[i];
+                    if (w) {
+                        gate_acc[i] = 0u;
+#pragma unroll
+                        for (int e = 0; e < 2; e++) {
+                            const int32_t inter = (int32_t)((w >> (16 * e)) & 0xFFFFu);
+                            const int64_t h = h0 + 2 * (int64_t)i + e;
+                            if (inter > 0 && h < h1) {
+                                int32_t un = L + hcnt[h] - inter; if (un < 1) un = 1;
+                                if (__ddiv_rn((double)inter, (double)un) >= thr) best = h > best ? h : best;
+                            }
+                        }
+                    }
+                }
+                for (int s = 16; s > 0; s >>= 1) { const long long o = __shfl_xor_sync(0xffffffffu, best, s); best = o > best ? o : best; }
+                if (lane == 0 && best >= 0) atomicMax(&s_best, best);
+                __syncthreads();
+            }
+        }
+        if (threadIdx.x == 0) out[c] = s_best;
+        __syncthreads();
+    }
+}
+
+// exclusive scan of int32 counts into int64 offsets (single CTA)
+static __global__ void __launch_bounds__(1024) k_gate_scan_counts(const int32_t* __restrict__ cnt, int64_t* __restrict__ off, int64_t n) {
+    __shared__ long long warp_tot[32];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        long long v = i < n ? cnt[i] : 0, x = v;
+        for (int d = 1; d < 32; d <<= 1) { long long y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        long long before = carry;
+        for (int w = 0; w < warp; w++) before += warp_tot[w];
+        if (i < n) off[i] = before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) off[n] = carry;
+}
+
+// ------------------------------------------------------------------ host side
+static int32_t gate_unicode(dvb_ctx* ctx, GateUnicode* U) {
+    std::lock_guard<std::mutex> g(ctx->unicode_mu);
+    if (!ctx->unicode_dev[0]) {
+        std::vector<uint32_t> dst((size_t)DV_LOWER_N * 3);
+        for (int i = 0; i < DV_LOWER_N; i++) for (int t = 0; t < 3; t++) dst[(size_t)i * 3 + t] = dv_lower_dst[i][t];
+        const void* src[6] = { dv_lower_src, dst.data(), dv_cased_lo, dv_cased_hi, dv_cign_lo, dv_cign_hi };
+        const size_t bytes[6] = { sizeof(dv_lower_src), dst.size() * 4, sizeof(dv_cased_lo), sizeof(dv_cased_hi), sizeof(dv_cign_lo), sizeof(dv_cign_hi) };
+        void* dev[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+        for (int i = 0; i < 6; i++) {
+            if (cudaMalloc(&dev[i], bytes[i]) != cudaSuccess || cudaMemcpy(dev[i], src[i], bytes[i], cudaMemcpyHostToDevice) != cudaSuccess) {
+                for (int j = 0; j <= i; j++) if (dev[j]) cudaFree(dev[j]);
+                cudaGetLastError();
+                return DVB_E_CUDA;
+            }
+        }
+        for (int i = 5; i >= 0; i--) ctx->unicode_dev[i] = dev[i];
+    }
+    U->lower_src = (const uint32_t*)ctx->unicode_dev[0]; U->lower_dst = (const uint32_t*)ctx->unicode_dev[1];
+    U->cased_lo = (const uint32_t*)ctx->unicode_dev[2]; U->cased_hi = (const uint32_t*)ctx->unicode_dev[3];
+    U->cign_lo = (const uint32_t*)ctx->unicode_dev[4]; U->cign_hi = (const uint32_t*)ctx->unicode_dev[5];
+    U->n_lower = DV_LOWER_N; U->n_cased = DV_CASED_RANGES_N; U->n_cign = DV_CIGN_RANGES_N;
+    return DVB_OK;
+}
+
+struct GateHostTables {
+    std::vector<int32_t> sso, sdo, sto;       // host copies of the offset arrays
+    int64_t growth = 1;
+};
+// stages the tables and computes the worst-case growth factor of the synonym replaces
+static int32_t gate_tables(dvb_ctx* ctx, dvb_io& io, const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst,
+                           const int32_t* syn_dst_off, int32_t n_syn, const uint32_t* stop, const int32_t* stop_off, int32_t n_stop,
+                           GateTablesDev* T, GateHostTables* H) {
+    if (n_syn < 0 || n_stop < 0 || (n_syn > 0 && (!syn_src || !syn_src_off || !syn_dst || !syn_dst_off)) || (n_stop > 0 && (!stop || !stop_off))) {
+        dvb_set_err(ctx, "gate tables: invalid argument%s%s"); return DVB_E_INVALID; }
+    H->sso.assign((size_t)n_syn + 1, 0); H->sdo.assign((size_t)n_syn + 1, 0); H->sto.assign((size_t)n_stop + 1, 0);
+    if (io.mem == DVB_MEM_HOST) {
+        if (n_syn) { memcpy(H->sso.data(), syn_src_off, 4 * (size_t)(n_syn + 1)); memcpy(H->sdo.data(), syn_dst_off, 4 * (size_t)(n_syn + 1)); }
+        if (n_stop) memcpy(H->sto.data(), stop_off, 4 * (size_t)(n_stop + 1));
+    } else {
+        if (n_syn) { DVB_CUDA(ctx, cudaMemcpyAsync(H->sso.data(), syn_src_off, 4 * (size_t)(n_syn + 1), cudaMemcpyDeviceToHost, io.st));
+                     DVB_CUDA(ctx, cudaMemcpyAsync(H->sdo.data(), syn_dst_off, 4 * (size_t)(n_syn + 1), cudaMemcpyDeviceToHost, io.st)); }
+        if (n_stop) DVB_CUDA(ctx, cudaMemcpyAsync(H->sto.data(), stop_off, 4 * (size_t)(n_stop + 1), cudaMemcpyDeviceToHost, io.st));
+        DVB_CUDA(ctx, cudaStreamSynchronize(io.st));
+    }
+    H->growth = 1;
+    for (int32_t y = 0; y < n_syn; y++) {
+        const int32_t ns = H->sso[y + 1] - H->sso[y], nd = H->sdo[y + 1] - H->sdo[y];
+        if (ns > 0 && nd > ns) { H->growth *= (nd + ns - 1) / ns; if (H->growth > 64) { dvb_set_err(ctx, "gate tables: synonym growth too large%s%s"); return DVB_E_INVALID; } }
+    }
+    T->n_syn = n_syn; T->n_stop = n_stop;
+    T->syn_src = io.in(syn_src, (size_t)H->sso[n_syn]); T->syn_src_off = io.in(syn_src_off, (size_t)n_syn + 1);
+    T->syn_dst = io.in(syn_dst, (size_t)H->sdo[n_syn]); T->syn_dst_off = io.in(syn_dst_off, (size_t)n_syn + 1);
+    T->stop = io.in(stop, (size_t)H->sto[n_stop]); T->stop_off = io.in(stop_off, (size_t)n_stop + 1);
+    return DVB_OK;
+}
+
+// capacity offsets (entries) per string: (bytes + 2) * growth
+static int32_t gate_caps(dvb_ctx* ctx, dvb_io& io, const int64_t* off, int64_t n, int64_t growth, std::vector<int64_t>* hoff, std::vector<int64_t>* cap) {
+    hoff->resize((size_t)n + 1);
+    if (io.mem == DVB_MEM_HOST) memcpy(hoff->data(), off, 8 * (size_t)(n + 1));
+    else { DVB_CUDA(ctx, cudaMemcpyAsync(hoff->data(), off, 8 * (size_t)(n + 1), cudaMemcpyDeviceToHost, io.st)); DVB_CUDA(ctx, cudaStreamSynchronize(io.st)); }
+    cap->resize((size_t)n + 1);
+    (*cap)[0] = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const int64_t nb = (*hoff)[i + 1] - (*hoff)[i];
+        if (nb < 0 || nb > 60000) { dvb_set_err(ctx, "question gate: a question is limited to 60000 bytes%s%s"); return DVB_E_INVALID; }
+        (*cap)[i + 1] = (*cap)[i] + (nb + 2) * growth;
+    }
+    return DVB_OK;
+}
+
+extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n,
+                                      const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst, const int32_t* syn_dst_off, int32_t n_syn,
+                                      const uint32_t* stop, const int32_t* stop_off, int32_t n_stop,
+                                      int64_t* out_cap_off, uint64_t* out_keys, int32_t* out_key_cnt, uint32_t* out_norm, int32_t* out_norm_len, int64_t out_cap) {
+    if (!ctx || n < 0 || !off || !out_cap_off || !out_keys || !out_key_cnt) { dvb_set_err(ctx, "dvb_question_keys: invalid argument%s%s"); return DVB_E_INVALID; }
+    if (n == 0) return DVB_OK;
+    dvb_scope sc(ctx); dvb_io io(sc, mem);
+    GateUnicode U; int32_t rc = gate_unicode(ctx, &U); if (rc) { dvb_set_err(ctx, "cannot upload unicode tables%s%s"); return rc; }
+    GateTablesDev T; GateHostTables H;
+    rc = gate_tables(ctx, io, syn_src, syn_src_off, syn_dst, syn_dst_off, n_syn, stop, stop_off, n_stop, &T, &H); if (rc) return rc;
+    std::vector<int64_t> hoff, cap;
+    rc = gate_caps(ctx, io, off, n, H.growth, &hoff, &cap); if (rc) return rc;
+    if (cap[n] > out_cap) { dvb_set_err(ctx, "dvb_question_keys: out_cap too small%s%s"); return DVB_E_CAPACITY; }
+    const int64_t total = hoff[n] - hoff[0];
+    const uint8_t* d_utf8 = mem == DVB_MEM_HOST ? io.in(utf8 + hoff[0], (size_t)total + 16) - hoff[0] : utf8;
+    const int64_t* d_off = io.in(off, (size_t)n + 1);
+    int64_t* d_cap = io.tmp<int64_t>((size_t)n + 1);
+    uint32_t* bufA = io.tmp<uint32_t>((size_t)cap[n] + 1); uint32_t* bufB = io.tmp<uint32_t>((size_t)cap[n] + 1);
+    unsigned long long* d_keys = (unsigned long long*)io.out(out_keys, (size_t)cap[n]);
+    int32_t* d_cnt = io.out(out_key_cnt, (size_t)n);
+    uint32_t* d_norm = out_norm ? io.out(out_norm, (size_t)cap[n]) : nullptr;
+    int32_t* d_nl = out_norm ? io.out(out_norm_len, (size_t)n) : nullptr;
+    rc = io.check(ctx); if (rc) return rc;
+    DVB_CUDA(ctx, cudaMemcpyAsync(d_cap, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
+    if (mem == DVB_MEM_HOST) memcpy(out_cap_off, cap.data(), 8 * (size_t)(n + 1));
+    else DVB_CUDA(ctx, cudaMemcpyAsync(out_cap_off, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
+    const int grid = (int)std::min<int64_t>((n + 127) / 128, (int64_t)ctx->num_sm * 16);
+    k_question_keys<<<grid, 128, 0, io.st>>>(d_utf8, d_off, n, d_cap, bufA, bufB, U, T, d_keys, d_cnt, d_norm, d_nl);
+    ctx->launches += 1;
+    return io.finish(ctx);          // synchronises: `cap` stays alive until here
+}
+
+extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* cand_utf8, const int64_t* cand_off, int64_t n_cand,
+                                      const uint8_t* hist_utf8, const int64_t* hist_off, int64_t n_hist,
+                                      const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst, const int32_t* syn_dst_off, int32_t n_syn,
+                                      const uint32_t* stop, const int32_t* stop_off, int32_t n_stop,
+                                      double threshold, int64_t* out_match) {
+    if (!ctx || n_cand < 0 || n_hist < 0 || !cand_off || !out_match || (n_hist > 0 && !hist_off)) { dvb_set_err(ctx, "dvb_question_gate: invalid argument%s%s"); return DVB_E_INVALID; }
+    if (n_cand == 0) return DVB_OK;
+    dvb_scope sc(ctx); dvb_io io(sc, mem);
+    int64_t* d_out = io.out(out_match, (size_t)n_cand);
+    if (n_hist == 0) {
+        int32_t rc0 = io.check(ctx); if (rc0) return rc0;
+        DVB_CUDA(ctx, cudaMemsetAsync(d_out, 0xFF, 8 * (size_t)n_cand, io.st));
+        return io.finish(ctx);
+    }
+    GateUnicode U; int32_t rc = gate_unicode(ctx, &U); if (rc) { dvb_set_err(ctx, "cannot upload unicode tables%s%s"); return rc; }
+    GateTablesDev T; GateHostTables H;
+    rc = gate_tables(ctx, io, syn_src, syn_src_off, syn_dst, syn_dst_off, n_syn, stop, stop_off, n_stop, &T, &H); if (rc) return rc;
+    std::vector<int64_t> coff, ccap, hoff, hcap;
+    rc = gate_caps(ctx, io, cand_off, n_cand, H.growth, &coff, &ccap); if (rc) return rc;
+    rc = gate_caps(ctx, io, hist_off, n_hist, H.growth, &hoff, &hcap); if (rc) return rc;
+    const int64_t ctotal = coff[n_cand] - coff[0], htotal = hoff[n_hist] - hoff[0];
+    const uint8_t* d_cu = mem == DVB_MEM_HOST ? io.in(cand_utf8 + coff[0], (size_t)ctotal + 16) - coff[0] : cand_utf8;
+    const uint8_t* d_hu = mem == DVB_MEM_HOST ? io.in(hist_utf8 + hoff[0], (size_t)htotal + 16) - hoff[0] : hist_utf8;
+    const int64_t* d_co = io.in(cand_off, (size_t)n_cand + 1); const int64_t* d_ho = io.in(hist_off, (size_t)n_hist + 1);
+    int64_t* d_ccap = io.tmp<int64_t>((size_t)n_cand + 1); int64_t* d_hcap = io.tmp<int64_t>((size_t)n_hist + 1);
+    const int64_t bufn = std::max(ccap[n_cand], hcap[n_hist]) + 1;
+    uint32_t* bufA = io.tmp<uint32_t>((size_t)bufn); uint32_t* bufB = io.tmp<uint32_t>((size_t)bufn);
+    unsigned long long* d_ck = io.tmp<unsigned long long>((size_t)ccap[n_cand] + 1); int32_t* d_cc = io.tmp<int32_t>((size_t)n_cand);
+    unsigned long long* d_hk = io.tmp<unsigned long long>((size_t)hcap[n_hist] + 1); int32_t* d_hc = io.tmp<int32_t>((size_t)n_hist);
+    int64_t* d_poff = io.tmp<int64_t>((size_t)n_hist + 1);
+    rc = io.check(ctx); if (rc) return rc;
+    DVB_CUDA(ctx, cudaMemcpyAsync(d_ccap, ccap.data(), 8 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, io.st));
+    DVB_CUDA(ctx, cudaMemcpyAsync(d_hcap, hcap.data(), 8 * (size_t)(n_hist + 1), cudaMemcpyHostToDevice, io.st));
+    const int gh = (int)std::min<int64_t>((n_hist + 127) / 128, (int64_t)ctx->num_sm * 16);
+    k_question_keys<<<gh, 128, 0, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
+    const int gc = (int)std::min<int64_t>((n_cand + 127) / 128, (int64_t)ctx->num_sm * 16);
+    k_question_keys<<<gc, 128, 0, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
+    k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
+    int64_t n_pairs = 0;
+    DVB_CUDA(ctx, cudaMemcpyAsync(&n_pairs, d_poff + n_hist, 8, cudaMemcpyDeviceToHost, io.st));
+    DVB_CUDA(ctx, cudaStreamSynchronize(io.st));
+    ctx->launches += 3;
+    if (n_pairs >= 0x7FFFFFFFLL) { dvb_set_err(ctx, "dvb_question_gate: history too large%s%s"); return DVB_E_CAPACITY; }
+    unsigned long long* pk = io.tmp<unsigned long long>((size_t)n_pairs + 1); unsigned long long* pk2 = io.tmp<unsigned long long>((size_t)n_pairs + 1);
+    uint32_t* pv = io.tmp<uint32_t>((size_t)n_pairs + 1); uint32_t* pv2 = io.tmp<uint32_t>((size_t)n_pairs + 1);
+    uint32_t* hist = io.tmp<uint32_t>((size_t)(256 * ((n_pairs + RS_TILE - 1) / RS_TILE + 1) + 256));
+    rc = io.check(ctx); if (rc) return rc;
+    if (n_pairs > 0) {
+        k_gate_pairs<<<(int)std::min<int64_t>(n_hist, (int64_t)ctx->num_sm * 8), 128, 0, io.st>>>(d_hk, d_hcap, d_hc, d_poff, n_hist, pk, pv);
+        ctx->launches += 1;
+        int64_t l = 0;
+        const int which = dv_radix_sort_pairs(pk, pv, pk2, pv2, n_pairs, 0, 48, hist, io.st, &l);   // keys use 43 bits
+        ctx->launches += l;
+        if (which) { pk = pk2; pv = pv2; }
+    }
+    const int32_t tile_h = (int32_t)std::min<int64_t>(n_hist, 96 * 1024);
+    const size_t smem = (size_t)((tile_h + 1) / 2) * 4;
+    DVB_CUDA(ctx, cudaFuncSetAttribute(k_gate_match, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gate_match, GATE_THREADS, smem));
+    const int grid = (int)std::min<int64_t>(n_cand, (int64_t)ctx->num_sm * std::max(1, occ));
+    const bool timing = ctx->timing.load() != 0;
+    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
+    k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out);
+    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
+    ctx->launches += 1;
+    rc = io.finish(ctx);
+    if (rc == DVB_OK && timing) { float ms = 0.f; cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1); ctx->last_ms = ms; }
+    return rc;
+}
+
+// ================================================================== a10: solution signature Jaccard
+// One thread per (left, right) pair of ALREADY clean_solution_text()'d strings (tiny volume: <= 8 pairs
+// per report).  lower(), drop everything but [0-9a-z] and CJK, n-gram set (n <= 4; a text of <= n
+// characters is its own single token), |L&R| and |L|R|.
+__device__ int32_t sol_grams(const uint8_t* t, int64_t nb, int32_t n, unsigned long long* keys) {
+    // 15-bit symbols: CJK 1..20992, [a-z0-9] 20993..21028; U+212A -> 'k', U+0130 -> 'i' (its U+0307 is dropped)
+    int32_t m = 0;
+    uint16_t* sym = reinterpret_cast<uint16_t*>(keys);            // symbols overlay the front of the key buffer
+    for (int64_t i = 0; i < nb;) {
+        uint32_t c = t[i], cp; int len;
+        if (c < 0x80u) { cp = c; len = 1; } else if (c < 0xE0u) { cp = c & 0x1Fu; len = 2; } else if (c < 0xF0u) { cp = c & 0x0Fu; len = 3; } else { cp = c & 0x07u; len = 4; }
+        for (int j = 1; j < len && i + j < nb; j++) cp = (cp << 6) | (t[i + j] & 0x3Fu);
+        i += len;
+        uint32_t s = 0;
+        if (cp < 0x80u) { const uint32_t l = cp | 0x20u; if (l - 'a' < 26u) s = 20992u + (l - 'a' + 1u); else if (cp - '0' < 10u) s = 20992u + (cp - '0' + 27u); }
+        else if (cp - 0x4E00u < 20992u) s = cp - 0x4E00u + 1u;
+        else if (cp == 0x212Au) s = 20992u + 11u;
+        else if (cp == 0x0130u) s = 20992u + 9u;
+        if (s) sym[m++] = (uint16_t)s;                             // 2 B written per >= 1 B read: never overtakes the reader? (sym is a
+    }                                                              // different buffer from t, so there is no hazard at all)
+    if (m == 0) return 0;
+    if (m <= n) {                                                  // a text of <= n characters is its own single token
+        unsigned long long k = 0; for (int32_t j = 0; j < m; j++) k = (k << 15) | sym[j];
+        keys[0] = m < n ? (((unsigned long long)m << 60) | k) : k;
+        return 1;
+    }
+    const int32_t ng = m - n + 1;
+    // keys[i] (8 B) overlays symbols 4i..4i+3.  Going from the back, n-gram i' < i needs symbols <= i+2 < 4i (i >= 1).
+    for (int32_t i = ng - 1; i >= 0; i--) {
+        unsigned long long k = 0; for (int32_t j = 0; j < n; j++) k = (k << 15) | sym[i + j];
+        keys[i] = k;
+    }
+    gate_heapsort(keys, ng);
+    int32_t u = 1; for (int32_t i = 1; i < ng; i++) if (keys[i] != keys[u - 1]) keys[u++] = keys[i];
+    return u;
+}
+
+__global__ void k_solution_jaccard(const uint8_t* __restrict__ lu, const int64_t* __restrict__ lo, const uint8_t* __restrict__ ru, const int64_t* __restrict__ ro,
+                                   int64_t n_pairs, int32_t ngram, const int64_t* __restrict__ cap_off, unsigned long long* __restrict__ bufL,
+                                   unsigned long long* __restrict__ bufR, int32_t* __restrict__ out_inter, int32_t* __restrict__ out_union,
+                                   int32_t* __restrict__ out_nl, int32_t* __restrict__ out_nr) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pairs; p += (int64_t)gridDim.x * blockDim.x) {
+        unsigned long long* kl = bufL + cap_off[p]; unsigned long long* kr = bufR + cap_off[p];
+        const int32_t a = sol_grams(lu + lo[p], lo[p + 1] - lo[p], ngram, kl);
+        const int32_t b = sol_grams(ru + ro[p], ro[p + 1] - ro[p], ngram, kr);
+        int32_t i = 0, j = 0, c = 0;
+        while (i < a && j < b) { if (kl[i] < kr[j]) i++; else if (kl[i] > kr[j]) j++; else { c++; i++; j++; } }
+        out_inter[p] = c; out_union[p] = a + b - c; out_nl[p] = a; out_nr[p] = b;
+    }
+}
+
+extern "C" int32_t dvb_solution_jaccard(dvb_ctx* ctx, int32_t mem, const uint8_t* left_utf8, const int64_t* left_off,
+                                         const uint8_t* right_utf8, const int64_t* right_off, int64_t n_pairs, int32_t ngram,
+                                         int32_t* out_inter, int32_t* out_union, int32_t* out_nleft, int32_t* out_nright) {
+    if (!ctx || n_pairs < 0 || !left_off || !right_off || ngram < 1 || ngram > 4 || !out_inter || !out_union || !out_nleft || !out_nright) {
+        dvb_set_err(ctx, "dvb_solution_jaccard: invalid argument (1 <= ngram <= 4)%s%s"); return DVB_E_INVALID; }
+    if (n_pairs == 0) return DVB_OK;
+    dvb_scope sc(ctx); dvb_io io(sc, mem);
+    std::vector<int64_t> lo((size_t)n_pairs + 1), ro((size_t)n_pairs + 1), cap((size_t)n_pairs + 1);
+    if (mem == DVB_MEM_HOST) { memcpy(lo.data(), left_off, 8 * (size_t)(n_pairs + 1)); memcpy(ro.data(), right_off, 8 * (size_t)(n_pairs + 1)); }
+    else {
+        DVB_CUDA(ctx, cudaMemcpyAsync(lo.data(), left_off, 8 * (size_t)(n_pairs + 1), cudaMemcpyDeviceToHost, io.st));
+        DVB_CUDA(ctx, cudaMemcpyAsync(ro.data(), right_off, 8 * (size_t)(n_pairs + 1), cudaMemcpyDeviceToHost, io.st));
+        DVB_CUDA(ctx, cudaStreamSynchronize(io.st));
+    }
+    cap[0] = 0;
+    for (int64_t p = 0; p < n_pairs; p++) cap[p + 1] = cap[p] + std::max(lo[p + 1] - lo[p], ro[p + 1] - ro[p]) + 2;
+    const uint8_t* d_lu = mem == DVB_MEM_HOST ? io.in(left_utf8 + lo[0], (size_t)(lo[n_pairs] - lo[0]) + 16) - lo[0] : left_utf8;
+    const uint8_t* d_ru = mem == DVB_MEM_HOST ? io.in(right_utf8 + ro[0], (size_t)(ro[n_pairs] - ro[0]) + 16) - ro[0] : right_utf8;
+    const int64_t* d_lo = io.in(left_off, (size_t)n_pairs + 1); const int64_t* d_ro = io.in(right_off, (size_t)n_pairs + 1);
+    int64_t* d_cap = io.tmp<int64_t>((size_t)n_pairs + 1);
+    unsigned long long* bl = io.tmp<unsigned long long>((size_t)cap[n_pairs] + 1); unsigned long long* br = io.tmp<unsigned long long>((size_t)cap[n_pairs] + 1);
+    int32_t* d_i = io.out(out_inter, (size_t)n_pairs); int32_t* d_u = io.out(out_union, (size_t)n_pairs);
+    int32_t* d_nl = io.out(out_nleft, (size_t)n_pairs); int32_t* d_nr = io.out(out_nright, (size_t)n_pairs);
+    int32_t rc = io.check(ctx); if (rc) return rc;
+    DVB_CUDA(ctx, cudaMemcpyAsync(d_cap, cap.data(), 8 * (size_t)(n_pairs + 1), cudaMemcpyHostToDevice, io.st));
+    k_solution_jaccard<<<(int)std::min<int64_t>((n_pairs + 63) / 64, 1024), 64, 0, io.st>>>(d_lu, d_lo, d_ru, d_ro, n_pairs, ngram, d_cap, bl, br, d_i, d_u, d_nl, d_nr);
+    ctx->launches += 1;
+    return io.finish(ctx);
+}

@@ -132,6 +132,37 @@ int32_t dvb_chunk_build(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const in
                         int32_t* out_count, int32_t* out_start, int32_t* out_end, int32_t* out_tstart, int32_t* out_tend,
                         int64_t* out_tbyte0, int64_t* out_tbyte1);
 
+/* ---- a8/a9  replaces: normalize_interview_question_text / question_token_set /
+ *                        is_similar_interview_question / find_similar_interview_question_log   web/server.py:20462-20501
+ * Synonym and stop-word tables are code-point CSR arrays IN THE CALLER'S ITERATION ORDER (the reference
+ * iterates a dict and a set: web/server.py:20464, 20467 — the set order depends on PYTHONHASHSEED, so the
+ * caller passes list(QUESTION_SIMILARITY_STOPWORDS) of its own process).  Empty synonym sources are skipped.
+ * Bigram key: (cp0 << 21) | cp1 over ALL code points of the normalised text; a 1-char text is (1<<42)|cp. */
+
+/* Sorted distinct bigram keys of each question at out_keys[out_cap_off[i] .. + out_key_cnt[i]); optionally the
+ * normalised text (code points) at out_norm[out_cap_off[i] .. + out_norm_len[i]).  out_cap >= sum (bytes_i+2)*G,
+ * G = worst-case growth of the synonym replaces (1 for the reference's tables). */
+int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n,
+                          const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst, const int32_t* syn_dst_off, int32_t n_syn,
+                          const uint32_t* stop, const int32_t* stop_off, int32_t n_stop,
+                          int64_t* out_cap_off, uint64_t* out_keys, int32_t* out_key_cnt, uint32_t* out_norm, int32_t* out_norm_len, int64_t out_cap);
+
+/* out_match[c] = the LARGEST history index h with  |L&R| / max(1, |L|R|) >= threshold  (fp64, as the reference),
+ * L = token set of history[h], R = token set of candidate c; -1 if none (empty sets never match). */
+int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* cand_utf8, const int64_t* cand_off, int64_t n_cand,
+                          const uint8_t* hist_utf8, const int64_t* hist_off, int64_t n_hist,
+                          const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst, const int32_t* syn_dst_off, int32_t n_syn,
+                          const uint32_t* stop, const int32_t* stop_off, int32_t n_stop,
+                          double threshold, int64_t* out_match);
+
+/* ---- a10  replaces: _solution_signature_ngrams / _solution_jaccard_similarity   web/server.py:36798-36813
+ * Inputs are pairs of ALREADY clean_solution_text()'d strings.  Per pair: |L&R|, |L|R|, |L|, |R| of the
+ * n-gram sets (1 <= ngram <= 4) over lower(text) restricted to [0-9a-z] and CJK; the caller rounds
+ * inter / max(1, union) to 3 places (0.0 if either set is empty). */
+int32_t dvb_solution_jaccard(dvb_ctx* ctx, int32_t mem, const uint8_t* left_utf8, const int64_t* left_off,
+                             const uint8_t* right_utf8, const int64_t* right_off, int64_t n_pairs, int32_t ngram,
+                             int32_t* out_inter, int32_t* out_union, int32_t* out_nleft, int32_t* out_nright);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,77 @@
+"""Rows a8-a10: question-similarity gate and solution Jaccard."""
+import numpy as np
+import pytest
+
+
+def test_default_tables_match_reference_constants(golden):
+    from deep_vision_b200 import question_similarity as qs
+    g = golden("a8_a9_gate.json")
+    assert [list(x) for x in qs.DEFAULT_SYNONYMS] == g["synonyms"]
+    assert sorted(qs.DEFAULT_STOPWORDS) == sorted(g["stopwords"])
+
+
+def test_clean_solution_text_host(golden):
+    from deep_vision_b200 import question_similarity as qs
+    for case in golden("a10_solution_jaccard.json"):
+        assert qs.clean_solution_text(case["left"]) == case["left_clean"]
+        assert qs.clean_solution_text(case["right"]) == case["right_clean"]
+
+
+@pytest.mark.gpu
+def test_gpu_gate_golden(gpu_ctx, golden):
+    from deep_vision_b200 import question_similarity as qs
+    g = golden("a8_a9_gate.json")
+    gate = qs.QuestionGate([tuple(x) for x in g["synonyms"]], g["stopwords"], ctx=gpu_ctx)
+    texts = [q for q, _ in g["normalized"]]
+    keys, norms = gate.keys(texts, want_norm=True)
+    for (q, want), got in zip(g["normalized"], norms):
+        assert got == want, repr(q)
+    for q, toks in g["token_sets"]:
+        assert sorted(gate.question_token_set(q)) == toks
+    assert gate.match(g["candidates"], g["history"], g["threshold"]).tolist() == g["match"]
+    for a, b, want in g["pairs"]:
+        assert gate.is_similar_interview_question(a, b) is want
+    # reference known-answer test (tests/test_question_fast_strategy.py:1854-1872)
+    assert gate.is_similar_interview_question("当前最核心的业务痛点是什么？", "目前最大的业务问题主要是什么？")
+    assert gate.is_similar_interview_question("当前最让你们头疼的痛点是什么？", "当前最影响推进的痛点是什么？")
+    assert not gate.is_similar_interview_question("当前最核心的业务痛点是什么？", "需要对接哪些外部系统？")
+    logs = [{"question": h, "i": i} for i, h in enumerate(g["history"])]
+    for c, m in list(zip(g["candidates"], g["match"]))[:40]:
+        r = gate.find_similar_interview_question_log(logs, c, g["threshold"])
+        assert (r is None and (m < 0 or not c.strip())) or (r is logs[m])
+
+
+@pytest.mark.gpu
+def test_gpu_gate_vs_oracle_random(gpu_ctx, oracle):
+    from deep_vision_b200 import question_similarity as qs
+    rng = np.random.default_rng(9)
+    words = ["当前", "目前", "主要", "最", "核心", "请", "你", "们", "痛点", "诉求", "最关键", "最大的", "头疼", "影响推进", "业务", "系统", "方案",
+             "A", "b", "？", " ", "，", "的", "一", "个", "下", "是什么", "哪些", "方面", "对接", "外部", "流程", "İ", "ΑΣ", "Σ", "　", "ǅ", "😀"]
+    def mk(n):
+        return ["".join(rng.choice(words, size=int(rng.integers(0, 14)))) for _ in range(n)]
+    hist, cands = mk(700), mk(900)
+    cands[:100] = [h + "？" for h in hist[:100]]
+    stop = list(reversed(qs.DEFAULT_STOPWORDS))
+    gate = qs.QuestionGate(qs.DEFAULT_SYNONYMS + [("系统", "平台系统"), ("", "x")], stop, ctx=gpu_ctx)       # growth > 1, empty source
+    og = oracle.Gate(gate.synonyms, stop)
+    keys, norms = gate.keys(cands, want_norm=True)
+    for c, k, nm in zip(cands, keys, norms):
+        assert nm == og.normalize(c), repr(c)
+        assert k.tolist() == og.keys(c).tolist()
+    for thr in (0.62, 0.3, 1.0, 0.0):
+        assert gate.match(cands, hist, thr).tolist() == og.gate(cands, hist, thr).tolist()
+    assert gate.match(cands[:5], [], 0.62).tolist() == [-1] * 5
+
+
+@pytest.mark.gpu
+def test_gpu_solution_jaccard_golden(gpu_ctx, golden, oracle):
+    from deep_vision_b200 import question_similarity as qs
+    cases = golden("a10_solution_jaccard.json")
+    for case in cases:
+        assert qs._solution_jaccard_similarity(case["left"], case["right"], ctx=gpu_ctx) == case["similarity"]
+    pairs = [(c["left_clean"], c["right_clean"]) for c in cases]
+    for n in (1, 2, 3, 4):
+        inter, union, nl, nr = qs.solution_jaccard_counts(pairs, n, ctx=gpu_ctx)
+        for (l, r), i, u in zip(pairs, inter, union):
+            _j, oi, ou = oracle.solution_jaccard(l, r, n)
+            assert (int(i), int(u)) == (oi, ou), (l, r, n)
