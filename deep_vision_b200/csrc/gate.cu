@@ -166,13 +166,26 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int acc_words = (tile_h + 1) >> 1;
     for (int i = threadIdx.x; i < acc_words; i += GATE_THREADS) gate_acc[i] = 0u;
+    // threshold <= 0: pairs with NO shared bigram also satisfy 0/union >= threshold (web/server.py:20490-20491), and they
+    // never show up in the postings, so the answer is simply the last history entry with a non-empty token set.
+    __shared__ long long s_last_nonempty;
+    if (0.0 >= thr) {
+        if (threadIdx.x == 0) s_last_nonempty = -1;
+        __syncthreads();
+        long long ln = -1;
+        for (int64_t h = threadIdx.x; h < n_hist; h += GATE_THREADS) if (hcnt[h] > 0) ln = h;
+        for (int s = 16; s > 0; s >>= 1) { const long long o = __shfl_xor_sync(0xffffffffu, ln, s); ln = o > ln ? o : ln; }
+        if (lane == 0 && ln >= 0) atomicMax(&s_last_nonempty, ln);
+    }
     __syncthreads();
     for (int64_t c = blockIdx.x; c < n_cand; c += gridDim.x) {
         const int32_t L = ccnt[c];
         const unsigned long long* ck = ckeys + ccap_off[c];
         if (threadIdx.x == 0) s_best = -1;
         __syncthreads();
-        if (L > 0) {
+        if (L > 0 && 0.0 >= thr) {
+            if (threadIdx.x == 0) s_best = s_last_nonempty;
+        } else if (L > 0) {
             for (int64_t h0 = 0; h0 < n_hist; h0 += tile_h) {
                 const int64_t h1 = min(n_hist, h0 + (int64_t)tile_h);
                 for (int32_t j = warp; j < L; j += GATE_THREADS / 32) {
