@@ -12,7 +12,7 @@ import threading
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "libdvb200.so"
+LIB_PATH = Path(os.environ.get("DVB_LIB", HERE / "libdvb200.so"))   # DVB_LIB: A/B-test another build of the same ABI
 
 DVB_OK, DVB_E_INVALID, DVB_E_CAPACITY, DVB_E_CUDA, DVB_E_NOMEM = 0, -1, -2, -3, -4
 MEM_HOST, MEM_DEVICE = 0, 1
