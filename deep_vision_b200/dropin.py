@@ -1,0 +1,136 @@
+"""install(server_module): rebind the reference's hot-path names on a loaded `web.server` module.
+
+The reference has no FFI; callers resolve these functions by bare name at call time and `server.py` re-pushes
+its globals into `report_generation_runtime.py` on every entry (web/server.py:25927-26023), so assigning the
+attributes is the whole integration — the reference's own tests patch functions the same way
+(tests/test_security_regression.py:4211-4219).  Every knob is read from the module AT CALL TIME
+(web/server.py:977-979, 990, 31882-31889, 858, 20429-20459, 35839-35845); nothing is baked into kernels.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, Optional
+
+from . import evidence, question_similarity as qs, reference_material as rm
+
+_SAVED: Dict[int, Dict[str, Any]] = {}
+_MISSING = object()
+
+HOT_NAMES = (
+    "_tokenize_similarity_text_v3", "infer_weak_evidence_refs_v3",
+    "_build_reference_material_chunks", "_tokenize_reference_material_query", "select_reference_material_context",
+    "normalize_interview_question_text", "question_token_set", "is_similar_interview_question",
+    "find_similar_interview_question_log", "_solution_jaccard_similarity",
+    "evaluate_answer_depth", "evaluate_answer_quality", "classify_answer_evidence_class_v3",
+    "backfill_session_interview_log_evidence_annotations",
+)
+
+
+def _weak_cfg(mod) -> evidence.WeakBindingConfig:
+    return evidence.WeakBindingConfig(
+        enabled=bool(getattr(mod, "REPORT_V3_WEAK_BINDING_ENABLED", True)),
+        min_score=float(getattr(mod, "REPORT_V3_WEAK_BINDING_MIN_SCORE", 0.46)),
+        unknown_ratio_trigger=float(getattr(mod, "REPORT_V3_UNKNOWN_RATIO_TRIGGER", 0.65)))
+
+
+def _rm_cfg(mod) -> rm.ReferenceMaterialConfig:
+    d = rm.DEFAULT_CONFIG
+    return rm.ReferenceMaterialConfig(
+        chunk_size=int(getattr(mod, "REFERENCE_MATERIAL_CHUNK_SIZE", d.chunk_size)),
+        chunk_overlap=int(getattr(mod, "REFERENCE_MATERIAL_CHUNK_OVERLAP", d.chunk_overlap)),
+        context_chunk_limit=int(getattr(mod, "REFERENCE_MATERIAL_CONTEXT_CHUNK_LIMIT", d.context_chunk_limit)),
+        inline_chunk_preview_limit=int(getattr(mod, "REFERENCE_MATERIAL_INLINE_CHUNK_PREVIEW_LIMIT", d.inline_chunk_preview_limit)),
+        preview_limit=int(getattr(mod, "REFERENCE_MATERIAL_PREVIEW_LIMIT", d.preview_limit)),
+        max_doc_length=int(getattr(mod, "MAX_DOC_LENGTH", d.max_doc_length)))
+
+
+def _gate(mod, ctx) -> qs.QuestionGate:
+    """Synonym dict and stop-word SET in the live process's iteration order (the set order is PYTHONHASHSEED dependent)."""
+    syn = getattr(mod, "QUESTION_SIMILARITY_SYNONYMS", None)
+    stop = getattr(mod, "QUESTION_SIMILARITY_STOPWORDS", None)
+    key = (id(syn), id(stop))
+    cached = getattr(mod, "_dvb200_gate_cache", None)
+    if cached is not None and cached[0] == key:
+        return cached[1]
+    gate = qs.QuestionGate(list(syn.items()) if isinstance(syn, dict) else None,
+                           list(stop) if stop is not None else None, ctx=ctx)
+    try:
+        setattr(mod, "_dvb200_gate_cache", (key, gate))
+    except Exception:
+        pass
+    return gate
+
+
+def build_bindings(mod, ctx=None) -> Dict[str, Any]:
+    """The replacement callables, keyed by the reference name (signatures of SURVEY.md §8b)."""
+
+    def _tokenize_similarity_text_v3(text):
+        return evidence._tokenize_similarity_text_v3(text, ctx=ctx)
+
+    def infer_weak_evidence_refs_v3(field, item, evidence_pack, min_score=None):
+        cfg = _weak_cfg(mod)
+        try:
+            return evidence.infer_weak_evidence_refs_v3(field, item, evidence_pack, cfg.min_score if min_score is None else min_score,
+                                                        config=cfg, ctx=ctx)
+        except evidence._lib.DvbError:
+            raise
+        except Exception:
+            return {"refs": [], "score": 0.0}
+
+    def _build_reference_material_chunks(content):
+        return rm._build_reference_material_chunks(content, config=_rm_cfg(mod), ctx=ctx)
+
+    def _tokenize_reference_material_query(query_text):
+        return rm._tokenize_reference_material_query(query_text)
+
+    def select_reference_material_context(doc, *, query_text="", max_chars=0, chunk_limit=0):
+        loader = getattr(mod, "load_reference_material_chunks", None)
+        return rm.select_reference_material_context(doc, query_text=query_text, max_chars=max_chars, chunk_limit=chunk_limit,
+                                                    chunk_loader=loader, config=_rm_cfg(mod), ctx=ctx)
+
+    def normalize_interview_question_text(text):
+        return _gate(mod, ctx).normalize_interview_question_text(text)
+
+    def question_token_set(text):
+        return _gate(mod, ctx).question_token_set(text)
+
+    def is_similar_interview_question(left, right, threshold=0.62):
+        return _gate(mod, ctx).is_similar_interview_question(left, right, threshold)
+
+    def find_similar_interview_question_log(logs, question, threshold=0.62):
+        return _gate(mod, ctx).find_similar_interview_question_log(logs, question, threshold)
+
+    def _solution_jaccard_similarity(left, right):
+        return qs._solution_jaccard_similarity(left, right, int(getattr(mod, "SOLUTION_SIMILARITY_NGRAM_SIZE", 2)), ctx=ctx)
+
+    bindings = dict(locals())
+    for k in ("mod", "ctx"):
+        bindings.pop(k, None)
+    try:                                             # a11-a13 (annotation path); present once annotations.py is built
+        from . import annotations
+        bindings.update(annotations.build_bindings(mod, ctx))
+    except ImportError:
+        pass
+    return {k: v for k, v in bindings.items() if k in HOT_NAMES}
+
+
+def install(server_module, ctx=None, names: Optional[tuple] = None) -> Dict[str, Any]:
+    """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent."""
+    bindings = build_bindings(server_module, ctx)
+    saved = _SAVED.setdefault(id(server_module), {})
+    done = {}
+    for name, fn in bindings.items():
+        if names is not None and name not in names:
+            continue
+        current = getattr(server_module, name, _MISSING)
+        if current is _MISSING:
+            continue                                  # no-op for anything the module does not define
+        if name not in saved:
+            saved[name] = current
+        setattr(server_module, name, fn)
+        done[name] = fn
+    return done
+
+
+def uninstall(server_module) -> None:
+    for name, fn in _SAVED.pop(id(server_module), {}).items():
+        setattr(server_module, name, fn)

@@ -304,3 +304,39 @@ def decode_token_key(key: int) -> Optional[str]:
     if key >> 62 == 0:
         return chr(((key >> 15) & 0x7FFF) - 1 + 0x4E00) + chr((key & 0x7FFF) - 1 + 0x4E00)
     return None
+
+
+def _tokenize_similarity_text_v3(text: Any, ctx=None) -> set:
+    """Drop-in for web/server.py:24722: the token STRINGS.  Decode, CPython lower() and character classes come from
+    the GPU symboliser (`dvb_symbolize`); the host only slices runs of the resulting symbol stream into the reference's
+    tokens (ASCII runs of >= 2 chars; CJK runs cut greedily into <= 12-char pieces, each piece and its bigrams)."""
+    from .reference_material import symbolize
+    source = str(text or "")
+    if not source.strip():
+        return set()
+    sym = symbolize([source], ctx=ctx)[0]
+    tokens: set = set()
+    i, n = 0, len(sym)
+    while i < n:
+        s = int(sym[i])
+        if s == 0:
+            i += 1
+            continue
+        ascii_cls = s >= 0x8000
+        j = i
+        while j < n and int(sym[j]) != 0 and (int(sym[j]) >= 0x8000) == ascii_cls:
+            j += 1
+        if ascii_cls:
+            if j - i >= 2:
+                tokens.add("".join("_abcdefghijklmnopqrstuvwxyz0123456789_"[(int(c) & 0x7FFF)] if (int(c) & 0x7FFF) <= 36
+                                   else "_" for c in sym[i:j]))
+        else:
+            run = "".join(chr(int(c) - 1 + 0x4E00) for c in sym[i:j])
+            for p in range(0, len(run), 12):
+                piece = run[p:p + 12]
+                if len(piece) >= 2:
+                    tokens.add(piece)
+                    for q in range(len(piece) - 1):
+                        tokens.add(piece[q:q + 2])
+        i = j
+    return tokens
