@@ -1,0 +1,582 @@
+"""Per-turn evidence annotation and the bulk re-index path (rows a11-a14 of SURVEY.md §8).
+
+Host-side mirror of the reference interface (web/server.py unless noted):
+  * `evaluate_answer_depth(question, answer, dimension, options=None, ...)`          21221
+  * `evaluate_answer_quality(eval_result, answer, is_follow_up, follow_up_round)`    20370
+  * `classify_answer_evidence_class_v3(signals, quality_score, evidence_intent)`     22552
+  * `backfill_session_interview_log_evidence_annotations(session, *, refresh_quality=True, overwrite_contract=False)`  21469
+  * `backfill_session_files(session_files, *, apply_changes=False, backup_dir=None, server_module=None)`
+                                                             scripts/migrate_session_evidence_annotations.py:64
+
+What runs where: every string scan of those functions — ~100 `keyword in text` tests, the exact-match lists,
+`any(c.isdigit())`, `len(text.strip())`, `option in answer` — is done for ALL turns of ALL sessions of a batch by two
+CUDA kernels (`dvb_text_features`, `dvb_contains`; csrc/annotate.cu).  The host then runs the reference's small
+decision tree per turn over the resulting bit masks, in the reference's fp64 operation order (sum() left to right),
+because the contract inference is sequential per session (it counts the PRIOR formal questions of the same dimension,
+web/server.py:21432).  There is no CPU text scanner here.
+"""
+from __future__ import annotations
+
+import copy
+import json
+import shutil
+from dataclasses import dataclass, field
+from pathlib import Path
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from .packing import pack_texts, ptr
+
+# ----------------------------------------------------------------------------- the reference's literals, as pattern groups
+RICH_OPTION_CAUSE_KEYWORDS = ("导致", "影响", "因为", "所以", "瓶颈", "阻塞", "误拦截", "投诉", "风险", "失败", "延迟")       # 20304
+RICH_OPTION_CONTEXT_KEYWORDS = ("高峰期", "夜间", "白天", "审批", "接口", "流程", "场景", "订单", "工单", "客户", "用户")    # 20307
+RICH_OPTION_ROLE_KEYWORDS = ("客服", "销售", "运营", "风控", "研发", "产品", "实施", "财务", "法务", "商家")               # 20310
+RICH_OPTION_PROCESS_KEYWORDS = ("流转", "复核", "上线", "对接", "集成", "回访", "分配", "排查", "协作", "审核")            # 20313
+VAGUE_INDICATORS = ("看情况", "不一定", "可能", "或许", "大概", "差不多", "到时候", "再说", "还没想好", "不确定", "看具体", "根据情况",
+                    "待定", "以后再说", "暂时不清楚", "目前还不好说", "都可以", "都行", "随便", "无所谓", "一般", "不太了解", "没想过",
+                    "不知道", "说不好", "很难说")                                                                          # 21271-21280
+GENERIC_ANSWERS = ("好的", "是的", "可以", "没问题", "需要", "应该要", "对", "嗯", "行", "同意", "没有", "不需要")          # 21286-21289
+INFORMATIVE_TOKENS = ("（", ")", "：", ":", "如", "例如", "比如", "因为")                                                  # 21299
+CONTRADICTION_PAIRS = (("需要", "不需要"), ("可以", "不可以"), ("支持", "不支持"), ("已经", "还没"), ("有", "没有"), ("必须", "可选"))  # 21322-21329
+SCENARIO_KEYWORDS = ("比如", "例如", "当", "如果", "场景", "案例")                                                          # 20387
+OPTION_PUNCT_TOKENS = ("（", ")", "：", ":", "/", "-", "，")                                                              # 20343
+DIMENSION_UNIT_TOKENS = ("分钟", "小时", "天", "周", "月", "成本", "预算", "上线")                                           # 20357
+QUESTION_RICH_MARKERS = ("原因", "场景", "影响", "频次", "角色", "流程", "瓶颈")                                             # 20355
+QUESTION_EVIDENCE_MARKERS = ("原因", "为什么", "场景", "影响", "频次", "角色", "流程", "主要是因为", "哪种情况")               # 21441-21443
+
+G_VAGUE, G_INFORMATIVE, G_SEMICOLON = 0, 1, 2
+G_CONTRA_L, G_CONTRA_R = 3, 9                     # six bits each
+G_SCENARIO, G_GENERIC, G_OPT_PUNCT = 15, 16, 17
+G_CAUSE, G_CONTEXT, G_ROLE, G_PROCESS, G_UNITS = 18, 19, 20, 21, 22
+G_Q_RICH, G_Q_EVIDENCE = 24, 25
+
+DIMENSION_FOLLOW_UP_SENSITIVITY = {"customer_needs": 0.8, "business_process": 0.6, "tech_constraints": 0.5,
+                                   "project_constraints": 0.4}                                                           # 19013
+HARD_FOLLOW_UP_SIGNALS = {"vague_expression", "generic_answer", "contradiction_detected"}                                # 19249
+QUESTION_ANSWER_MODES = {"pick_only", "pick_with_reason"}                                                                # 19624
+QUESTION_EVIDENCE_INTENTS = {"low", "medium", "high"}
+
+
+def _pattern_table():
+    groups: List[Tuple[int, Sequence[str], int]] = [
+        (G_VAGUE, VAGUE_INDICATORS, 0), (G_INFORMATIVE, INFORMATIVE_TOKENS, 0), (G_SEMICOLON, ("；",), 0),
+        (G_SCENARIO, SCENARIO_KEYWORDS, 0), (G_GENERIC, GENERIC_ANSWERS, 1), (G_OPT_PUNCT, OPTION_PUNCT_TOKENS, 0),
+        (G_CAUSE, RICH_OPTION_CAUSE_KEYWORDS, 0), (G_CONTEXT, RICH_OPTION_CONTEXT_KEYWORDS, 0), (G_ROLE, RICH_OPTION_ROLE_KEYWORDS, 0),
+        (G_PROCESS, RICH_OPTION_PROCESS_KEYWORDS, 0), (G_UNITS, DIMENSION_UNIT_TOKENS, 0),
+        (G_Q_RICH, QUESTION_RICH_MARKERS, 0), (G_Q_EVIDENCE, QUESTION_EVIDENCE_MARKERS, 0)]
+    for i, (left, right) in enumerate(CONTRADICTION_PAIRS):
+        groups.append((G_CONTRA_L + i, (left,), 0))
+        groups.append((G_CONTRA_R + i, (right,), 0))
+    blobs, grp, whole = [], [], []
+    for g, pats, w in groups:
+        for p in pats:
+            blobs.append(p.encode("utf-8")); grp.append(g); whole.append(w)
+    off = np.zeros(len(blobs) + 1, np.int32)
+    off[1:] = np.cumsum([len(b) for b in blobs])
+    return (np.frombuffer(b"".join(blobs) + b"\0" * 16, np.uint8).copy(), off, np.asarray(grp, np.uint8), np.asarray(whole, np.uint8))
+
+
+_PATTERNS = _pattern_table()
+
+
+# ----------------------------------------------------------------------------- GPU feature extraction
+def text_features(texts: Sequence[str], ctx=None):
+    """(mask u64[n], stripped length i32[n], flags u8[n]) for each text; flags bit 0 = has a str.isdigit() char."""
+    ctx = ctx or _lib.Context.get()
+    n = len(texts)
+    mask = np.zeros(max(n, 1), np.uint64); length = np.zeros(max(n, 1), np.int32); flags = np.zeros(max(n, 1), np.uint8)
+    if n:
+        data, off = pack_texts(texts)
+        pb, po, pg, pw = _PATTERNS
+        rc = ctx.lib.dvb_text_features(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, ptr(pb), ptr(po), ptr(pg), ptr(pw), len(pg),
+                                       ptr(mask), ptr(length), ptr(flags), None, None)
+        ctx.check(rc, "dvb_text_features")
+    return mask[:n], length[:n], flags[:n]
+
+
+def contains(haystacks: Sequence[str], needles: Sequence[str], needle_hay: Sequence[int], ctx=None) -> np.ndarray:
+    """bits per needle: 1 = needle in hay.strip(); 2 = needle.strip() (non-empty) in hay.strip(); 4 = stripped texts equal."""
+    ctx = ctx or _lib.Context.get()
+    nn = len(needles)
+    out = np.zeros(max(nn, 1), np.uint8)
+    if nn:
+        hu, ho = pack_texts(haystacks)
+        nu, no = pack_texts(needles)
+        nh = np.asarray(needle_hay, np.int32)
+        rc = ctx.lib.dvb_contains(ctx.handle, _lib.MEM_HOST, ptr(hu), ptr(ho), len(haystacks), ptr(nu), ptr(no), ptr(nh), nn, ptr(out))
+        ctx.check(rc, "dvb_contains")
+    return out[:nn]
+
+
+@dataclass
+class OptionFeatures:
+    is_str: bool
+    length: int = 0            # len(str(option or "").strip())
+    mask: int = 0
+    has_digit: bool = False
+    raw_in_answer: bool = False      # option in answer.strip()              (web/server.py:21321)
+    strip_in_answer: bool = False    # option.strip() in answer.strip()      (20327)
+    equals_answer: bool = False      # option.strip() == answer.strip()      (20326)
+
+
+@dataclass
+class TurnFeatures:
+    q_mask: int = 0
+    a_mask: int = 0
+    a_len: int = 0
+    a_digit: bool = False
+    options: List[OptionFeatures] = field(default_factory=list)
+
+
+def _bit(mask: int, g: int) -> bool:
+    return bool((mask >> g) & 1)
+
+
+def extract_turn_features(turns: Sequence[Tuple[str, str, Sequence[Any]]], ctx=None) -> List[TurnFeatures]:
+    """turns: (question, answer, options).  Two kernel launches for the whole batch."""
+    texts: List[str] = []
+    needles: List[str] = []
+    needle_hay: List[int] = []
+    layout = []
+    for ti, (question, answer, options) in enumerate(turns):
+        q, a = str(question or ""), str(answer)
+        base = len(texts)
+        texts.extend((q, a))
+        opt_texts = []
+        for opt in (options or []):
+            is_str = isinstance(opt, str)
+            t = opt if is_str else str(opt or "")
+            opt_texts.append((is_str, t))
+            texts.append(t)
+            needles.append(t)
+            needle_hay.append(ti)
+        layout.append((base, opt_texts))
+    mask, length, flags = text_features(texts, ctx=ctx)
+    bits = contains([str(t[1]) for t in turns], needles, needle_hay, ctx=ctx) if needles else np.zeros(0, np.uint8)
+    out: List[TurnFeatures] = []
+    nd = 0
+    for (base, opt_texts), (_q, answer, _o) in zip(layout, turns):
+        tf = TurnFeatures(q_mask=int(mask[base]), a_mask=int(mask[base + 1]), a_len=int(length[base + 1]),
+                          a_digit=bool(flags[base + 1] & 1))
+        for j, (is_str, t) in enumerate(opt_texts):
+            k = base + 2 + j
+            b = int(bits[nd]); nd += 1
+            tf.options.append(OptionFeatures(is_str=is_str, length=int(length[k]), mask=int(mask[k]), has_digit=bool(flags[k] & 1),
+                                             raw_in_answer=bool(b & 1), strip_in_answer=bool(b & 2), equals_answer=bool(b & 4)))
+        out.append(tf)
+    return out
+
+
+# ----------------------------------------------------------------------------- decision logic over the features
+def normalize_question_answer_mode(answer_mode: Any, fallback: str = "pick_only") -> str:                # 19629
+    normalized = str(answer_mode or "").strip().lower()
+    if normalized in QUESTION_ANSWER_MODES:
+        return normalized
+    fb = str(fallback or "").strip().lower()
+    return fb if fb in QUESTION_ANSWER_MODES else "pick_only"
+
+
+def normalize_question_evidence_intent(evidence_intent: Any, fallback: str = "low") -> str:               # 19639
+    normalized = str(evidence_intent or "").strip().lower()
+    if normalized in QUESTION_EVIDENCE_INTENTS:
+        return normalized
+    fb = str(fallback or "").strip().lower()
+    return fb if fb in QUESTION_EVIDENCE_INTENTS else "low"
+
+
+def _rich_option(tf: TurnFeatures, dimension: Any) -> Tuple[bool, bool]:
+    """(_score_rich_option_answer(...)["is_rich_option"], ["exact_option"])   web/server.py:20318-20367"""
+    cands = [o for o in tf.options if o.length > 0]                 # option_list: stripped, non-empty
+    if tf.a_len == 0 or not cands:
+        return False, False
+    exact = any(o.equals_answer for o in cands)
+    matched = [o for o in cands if o.strip_in_answer]
+    if not exact and not matched:
+        return False, False
+    if exact:                                                        # primary option == the stripped answer itself
+        p_len, p_mask, p_digit = tf.a_len, tf.a_mask, tf.a_digit
+    else:
+        best = matched[0]
+        for o in matched[1:]:                                        # max(..., key=len): first of the longest
+            if o.length > best.length:
+                best = o
+        p_len, p_mask, p_digit = best.length, best.mask, best.has_digit
+    score = 0
+    score += 1 if exact else 0
+    score += 1 if p_len >= 10 else 0
+    score += 1 if p_len >= 16 else 0
+    for g in (G_OPT_PUNCT, G_CAUSE, G_CONTEXT, G_ROLE, G_PROCESS):
+        score += 1 if _bit(p_mask, g) else 0
+    score += 1 if p_digit else 0
+    score += 1 if _bit(tf.q_mask, G_Q_RICH) else 0
+    if str(dimension or "").strip().lower() in {"tech_constraints", "project_constraints"} and _bit(p_mask, G_UNITS):
+        score += 1
+    return bool(score >= 4 or (exact and score >= 3 and p_len >= 12)), exact
+
+
+_FOLLOW_UP_REASONS = {                                                                                   # 21406-21414
+    "too_short": "回答过于简短，需要补充具体细节",
+    "vague_expression": "回答包含模糊表述，需要明确具体要求",
+    "generic_answer": "回答过于笼统，需要深入了解具体需求",
+    "option_only": "当前答案方向明确，但仍需补一个关键依据以支撑后续结论",
+    "no_quantification": "缺少量化指标，需要明确具体数据要求",
+    "single_selection": "只选择了单一选项，需要了解是否还有其他需求",
+    "contradiction_detected": "回答中存在前后冲突，需要澄清真实约束",
+}
+_SIGNAL_WEIGHTS = {"too_short": 0.4, "vague_expression": 0.5, "generic_answer": 0.8, "option_only": 0.3, "no_quantification": 0.2,
+                   "single_selection": 0.2, "contradiction_detected": 0.6}
+_NEGATIVE_PENALTY = {"too_short": 0.2, "vague_expression": 0.25, "generic_answer": 0.3, "option_only": 0.2, "no_quantification": 0.1,
+                     "single_selection": 0.1, "contradiction_detected": 0.25}
+
+
+def depth_from_features(tf: TurnFeatures, dimension: Any, options: Any, is_follow_up: bool = False, multi_select: bool = False,
+                        answer_mode: Any = "", requires_rationale: bool = False, evidence_intent: Any = "",
+                        sensitivity_table: Optional[dict] = None, hard_signals: Optional[Iterable[str]] = None) -> dict:
+    """evaluate_answer_depth (web/server.py:21221-21401) with every string test replaced by a feature bit."""
+    table = DIMENSION_FOLLOW_UP_SENSITIVITY if sensitivity_table is None else sensitivity_table
+    hard = HARD_FOLLOW_UP_SIGNALS if hard_signals is None else hard_signals
+    signals: List[str] = []
+    answer_len = tf.a_len
+    sensitivity = table.get(dimension, 0.5)
+    mode = normalize_question_answer_mode(answer_mode, fallback="pick_with_reason" if requires_rationale else "pick_only")
+    needs_rationale = bool(requires_rationale or mode == "pick_with_reason")
+    intent = normalize_question_evidence_intent(evidence_intent, fallback="high" if needs_rationale else "low")
+    pick_only = mode == "pick_only" and not needs_rationale
+    rich, exact = _rich_option(tf, dimension)
+
+    short_threshold = int(20 + sensitivity * 20)
+    if options:
+        short_threshold = min(short_threshold, (10 if multi_select else 6) if pick_only else (18 if multi_select else 12))
+    if answer_len < short_threshold and not rich:
+        signals.append("too_short")
+    if _bit(tf.a_mask, G_VAGUE):
+        signals.append("vague_expression")
+    if _bit(tf.a_mask, G_GENERIC):
+        signals.append("generic_answer")
+    if options:
+        informative = answer_len >= 10 or rich or _bit(tf.a_mask, G_INFORMATIVE)
+        if not pick_only and exact and answer_len < 16 and not informative:
+            signals.append("option_only")
+        if rich:
+            signals.append("rich_option_answer")
+    has_numbers = tf.a_digit
+    if dimension in ("tech_constraints", "project_constraints") and not has_numbers and answer_len < 60:
+        signals.append("no_quantification")
+    if multi_select and options and not _bit(tf.a_mask, G_SEMICOLON) and len(options) >= 3 and not rich:
+        selected = 0
+        for o in tf.options:
+            if not o.is_str:
+                raise TypeError("'in <string>' requires string as left operand")      # what `opt in answer` raises in the reference
+            selected += 1 if o.raw_in_answer else 0
+        if selected <= 1 and answer_len < 30:
+            signals.append("single_selection")
+    if any(_bit(tf.a_mask, G_CONTRA_L + i) and _bit(tf.a_mask, G_CONTRA_R + i) for i in range(len(CONTRADICTION_PAIRS))):
+        signals.append("contradiction_detected")
+
+    sufficient: List[str] = []
+    if answer_len > 80:
+        sufficient.append("detailed_answer")
+    if _bit(tf.a_mask, G_SEMICOLON) and answer_len > 40:
+        sufficient.append("multi_point_answer")
+    if has_numbers and answer_len > 30:
+        sufficient.append("quantified_answer")
+    if rich:
+        sufficient.append("rich_option_answer")
+
+    follow_up_score = sum(_SIGNAL_WEIGHTS.get(s, 0.1) for s in signals)
+    follow_up_score *= sensitivity
+    sufficient_weights = {"detailed_answer": 0.5, "multi_point_answer": 0.3, "quantified_answer": 0.2,
+                          "rich_option_answer": 0.25 if intent == "high" else 0.18}
+    follow_up_score -= sum(sufficient_weights.get(s, 0) for s in sufficient)
+    hard_triggered = any(s in hard for s in signals)
+
+    reasons = [_FOLLOW_UP_REASONS.get(s, "") for s in signals if s in _FOLLOW_UP_REASONS]
+    reason = reasons[0] if reasons else "需要进一步了解详细需求"
+    if follow_up_score >= 0.4:
+        needs, suggest = True, False
+    elif follow_up_score >= 0.15 and not sufficient:
+        needs, suggest = False, True
+    else:
+        needs, suggest, reason = False, False, None
+    return {"needs_follow_up": needs, "suggest_ai_eval": suggest, "reason": reason, "signals": signals,
+            "hard_triggered": hard_triggered, "has_numbers": has_numbers, "follow_up_score": round(follow_up_score, 2)}
+
+
+def quality_from_features(eval_result: dict, a_len: int, a_mask: int, is_follow_up: Any, follow_up_round: Any) -> dict:
+    """evaluate_answer_quality (web/server.py:20370-20426); a_len = len(answer.strip()), a_mask from the answer text."""
+    signals = eval_result.get("signals", [])
+    hard_triggered = eval_result.get("hard_triggered", False)
+    quality_score = 0.5
+    if a_len >= 120:
+        quality_score += 0.2
+    elif a_len >= 80:
+        quality_score += 0.1
+    if eval_result.get("has_numbers"):
+        quality_score += 0.1
+    if _bit(a_mask, G_SCENARIO):
+        quality_score += 0.1
+    if "rich_option_answer" in signals:
+        quality_score += 0.12
+    quality_score -= sum(_NEGATIVE_PENALTY.get(signal, 0.05) for signal in signals)
+    if is_follow_up and follow_up_round >= 1 and not hard_triggered:
+        quality_score += 0.05
+    quality_score = max(0.0, min(1.0, quality_score))
+    quality_signals: List[str] = []
+    if quality_score >= 0.75:
+        quality_signals.append("high_quality")
+    if eval_result.get("has_numbers"):
+        quality_signals.append("quantified")
+    if a_len >= 80:
+        quality_signals.append("detailed")
+    if "rich_option_answer" in signals:
+        quality_signals.append("rich_option")
+    for signal in signals:
+        if signal not in quality_signals:
+            quality_signals.append(signal)
+    return {"quality_score": round(quality_score, 2), "quality_signals": quality_signals, "hard_triggered": bool(hard_triggered)}
+
+
+def classify_answer_evidence_class_v3(signals: Any, quality_score: Any, evidence_intent: Any) -> str:     # 22552 (no text work)
+    normalized = {str(item or "").strip().lower() for item in (signals or []) if str(item or "").strip()}
+    intent = normalize_question_evidence_intent(evidence_intent, fallback="low")
+    try:
+        q = float(quality_score)
+    except Exception:
+        q = 0.0
+    q = max(0.0, min(1.0, q))
+    if "rich_option_answer" in normalized:
+        return "rich_option"
+    if normalized & {"vague_expression", "generic_answer", "contradiction_detected"}:
+        return "pending_follow_up" if intent in {"medium", "high"} else "weak_inferred"
+    if normalized & {"too_short", "option_only", "no_quantification", "single_selection"}:
+        return "pending_follow_up" if intent == "high" else "weak_inferred"
+    if q < 0.35 and intent in {"medium", "high"}:
+        return "weak_inferred"
+    return "explicit"
+
+
+# ----------------------------------------------------------------------------- reference-shaped single calls
+def evaluate_answer_depth(question: str, answer: str, dimension: str, options: list = None, is_follow_up: bool = False,
+                          multi_select: bool = False, answer_mode: str = "", requires_rationale: bool = False,
+                          evidence_intent: str = "", *, ctx=None, sensitivity_table=None, hard_signals=None) -> dict:
+    """Drop-in for web/server.py:21221 (a batch of one turn)."""
+    answer.strip                                   # the reference calls answer.strip(): non-str answers raise AttributeError
+    tf = extract_turn_features([(question, answer, options)], ctx=ctx)[0]
+    return depth_from_features(tf, dimension, options, is_follow_up, multi_select, answer_mode, requires_rationale, evidence_intent,
+                               sensitivity_table, hard_signals)
+
+
+def evaluate_answer_quality(eval_result: dict, answer: str, is_follow_up: bool, follow_up_round: int, *, ctx=None) -> dict:
+    """Drop-in for web/server.py:20370."""
+    mask, length, _flags = text_features([str(answer or "")], ctx=ctx)
+    return quality_from_features(eval_result, int(length[0]), int(mask[0]), is_follow_up, follow_up_round)
+
+
+def build_question_capture_contract(*, should_follow_up: bool, hard_triggered: bool, missing_aspects: Optional[list] = None,
+                                    formal_questions_count: int = 0, dimension: str = "") -> dict:       # 19669 (no text work)
+    missing_count = len(list(missing_aspects or []))
+    normalized_dimension = str(dimension or "").strip().lower()
+    if should_follow_up or hard_triggered or missing_count > 0:
+        return {"answer_mode": "pick_with_reason", "requires_rationale": True, "evidence_intent": "high"}
+    if formal_questions_count >= 2 or normalized_dimension in {"tech_constraints", "project_constraints"}:
+        return {"answer_mode": "pick_with_reason", "requires_rationale": True, "evidence_intent": "medium"}
+    return {"answer_mode": "pick_only", "requires_rationale": False, "evidence_intent": "low"}
+
+
+def _contract_from_features(log: dict, prior_dim_logs: list, tf: TurnFeatures) -> dict:
+    """_infer_legacy_log_capture_contract (web/server.py:21419-21466) over the feature bits."""
+    dimension = str(log.get("dimension", "") or "").strip()
+    is_follow_up = bool(log.get("is_follow_up", False) or int(log.get("follow_up_round", 0) or 0) > 0)
+    hard_triggered = bool(log.get("hard_triggered", False))
+    formal = len([item for item in (prior_dim_logs or []) if not item.get("is_follow_up", False)])
+    contract = build_question_capture_contract(should_follow_up=is_follow_up, hard_triggered=hard_triggered, missing_aspects=[],
+                                               formal_questions_count=formal, dimension=dimension)
+    asks_for_evidence = _bit(tf.q_mask, G_Q_EVIDENCE)
+    marker_bits = (1 << G_CAUSE) | (1 << G_CONTEXT) | (1 << G_ROLE) | (1 << G_PROCESS)
+    options_are_rich = any(o.length >= 10 and (o.mask & marker_bits) for o in tf.options)
+    if asks_for_evidence or options_are_rich:
+        contract["answer_mode"] = "pick_with_reason"
+        contract["requires_rationale"] = True
+        current = normalize_question_evidence_intent(contract.get("evidence_intent", ""), fallback="low")
+        if is_follow_up or asks_for_evidence:
+            contract["evidence_intent"] = "high"
+        elif current == "low":
+            contract["evidence_intent"] = "medium"
+    return {"answer_mode": normalize_question_answer_mode(contract.get("answer_mode", ""), fallback="pick_only"),
+            "requires_rationale": bool(contract.get("requires_rationale", False)),
+            "evidence_intent": normalize_question_evidence_intent(contract.get("evidence_intent", ""), fallback="low")}
+
+
+# ----------------------------------------------------------------------------- a12: backfill (bulk re-index body)
+_SNAPSHOT_KEYS = ("answer_mode", "requires_rationale", "evidence_intent", "follow_up_signals", "quality_score", "quality_signals",
+                  "hard_triggered", "needs_follow_up", "answer_evidence_class")
+_ZERO = {"changed": False, "logs_total": 0, "logs_updated": 0, "field_updates": {}}
+
+
+def _log_texts(log: dict) -> Tuple[str, str, list]:
+    options = log.get("options", []) if isinstance(log.get("options", []), list) else []
+    return str(log.get("question", "") or ""), str(log.get("answer", "") or ""), options
+
+
+def _backfill_one(session: dict, feats: List[TurnFeatures], refresh_quality: bool, overwrite_contract: bool,
+                  sensitivity_table=None, hard_signals=None) -> dict:
+    interview_log = session.get("interview_log", [])
+    changed, logs_updated, field_updates, dim_history = False, 0, {}, {}
+    it = iter(feats)
+    for log in interview_log:
+        if not isinstance(log, dict):
+            continue
+        tf = next(it)
+        dimension = str(log.get("dimension", "") or "").strip()
+        prior = dim_history.setdefault(dimension, [])
+        inferred = _contract_from_features(log, prior, tf)
+        raw_mode = str(log.get("answer_mode", "") or "").strip().lower()
+        raw_intent = str(log.get("evidence_intent", "") or "").strip().lower()
+        current_mode = normalize_question_answer_mode(raw_mode, fallback=inferred["answer_mode"])
+        explicit = raw_mode in QUESTION_ANSWER_MODES and raw_intent in QUESTION_EVIDENCE_INTENTS
+        answer_mode = current_mode if (explicit and not overwrite_contract) else inferred["answer_mode"]
+        requires_rationale = bool(log.get("requires_rationale", False) or answer_mode == "pick_with_reason")
+        if overwrite_contract or not explicit:
+            requires_rationale = bool(inferred["requires_rationale"] or answer_mode == "pick_with_reason")
+        evidence_intent = normalize_question_evidence_intent(
+            log.get("evidence_intent", "") if (explicit and not overwrite_contract) else inferred["evidence_intent"],
+            fallback="high" if requires_rationale else ("medium" if answer_mode == "pick_with_reason" else "low"))
+        before = {k: (copy.deepcopy(log.get(k)) if k in ("follow_up_signals", "quality_signals") else log.get(k)) for k in _SNAPSHOT_KEYS}
+        log["answer_mode"] = answer_mode
+        log["requires_rationale"] = requires_rationale
+        log["evidence_intent"] = evidence_intent
+        _q, _a, options = _log_texts(log)
+        eval_result = depth_from_features(tf, dimension, options, bool(log.get("is_follow_up", False)),
+                                          bool(log.get("question_multi_select", log.get("multi_select", False))),
+                                          answer_mode, requires_rationale, evidence_intent, sensitivity_table, hard_signals)
+        quality = quality_from_features(eval_result, tf.a_len, tf.a_mask, bool(log.get("is_follow_up", False)),
+                                        int(log.get("follow_up_round", 0) or 0))
+        evidence_class = classify_answer_evidence_class_v3(eval_result.get("signals", []), quality.get("quality_score", 0.0), evidence_intent)
+        if refresh_quality or "follow_up_signals" not in log:
+            log["follow_up_signals"] = list(eval_result.get("signals", []) or [])
+            log["needs_follow_up"] = bool(eval_result.get("needs_follow_up", False))
+        if refresh_quality or "quality_score" not in log:
+            log["quality_score"] = quality.get("quality_score", 0.0)
+            log["quality_signals"] = list(quality.get("quality_signals", []) or [])
+            log["hard_triggered"] = bool(quality.get("hard_triggered", False))
+        log["answer_evidence_class"] = evidence_class
+        after = {k: log.get(k) for k in _SNAPSHOT_KEYS}
+        if before != after:
+            changed = True
+            logs_updated += 1
+            for key, value in after.items():
+                if before.get(key) != value:
+                    field_updates[key] = field_updates.get(key, 0) + 1
+        prior.append(log)
+    return {"changed": changed, "logs_total": len([log for log in interview_log if isinstance(log, dict)]),
+            "logs_updated": logs_updated, "field_updates": field_updates}
+
+
+def backfill_sessions(sessions: Sequence[Any], *, refresh_quality: bool = True, overwrite_contract: bool = False, ctx=None,
+                      sensitivity_table=None, hard_signals=None) -> List[dict]:
+    """Batch form: the text features of every turn of every session come from two kernel launches; sessions are then
+    finished one after the other (each session dict is mutated in place, like the reference)."""
+    turns, spans = [], []
+    for session in sessions:
+        logs = session.get("interview_log", []) if isinstance(session, dict) else None
+        if not isinstance(logs, list):
+            spans.append(None)
+            continue
+        start = len(turns)
+        turns.extend(_log_texts(log) for log in logs if isinstance(log, dict))
+        spans.append((start, len(turns)))
+    feats = extract_turn_features(turns, ctx=ctx) if turns else []
+    out = []
+    for session, span in zip(sessions, spans):
+        if span is None:
+            out.append(dict(_ZERO, field_updates={}))
+        else:
+            out.append(_backfill_one(session, feats[span[0]:span[1]], refresh_quality, overwrite_contract, sensitivity_table, hard_signals))
+    return out
+
+
+def backfill_session_interview_log_evidence_annotations(session: dict, *, refresh_quality: bool = True, overwrite_contract: bool = False,
+                                                        ctx=None) -> dict:
+    """Drop-in for web/server.py:21469 (mutates session["interview_log"][i] in place, returns the summary)."""
+    return backfill_sessions([session], refresh_quality=refresh_quality, overwrite_contract=overwrite_contract, ctx=ctx)[0]
+
+
+# ----------------------------------------------------------------------------- a14: the bulk re-index script body
+def get_utc_now() -> str:
+    from datetime import datetime, timezone
+    return datetime.now(timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
+
+
+def backfill_session_files(session_files: Iterable[Path], *, apply_changes: bool = False, backup_dir: Optional[Path] = None,
+                           server_module=None, batch_sessions: int = 2048, ctx=None, shard: Optional[Tuple[int, int]] = None) -> dict:
+    """scripts/migrate_session_evidence_annotations.py:64-114 with the per-file calls batched (`batch_sessions` files per
+    pair of kernel launches).  `server_module` only supplies get_utc_now() for the write-back stamp.  `shard=(rank, world)`
+    processes a contiguous block of the file list (multi-GPU: sessions are independent; summaries add up)."""
+    files = [Path(f) for f in session_files]
+    if shard is not None:
+        from .parallel import shard_range
+        lo, hi = shard_range(len(files), shard[0], shard[1])
+        files = files[lo:hi]
+    summary = {"sessions_total": 0, "sessions_changed": 0, "logs_total": 0, "logs_updated": 0, "field_updates": {}, "changed_sessions": []}
+    now = getattr(server_module, "get_utc_now", None) or get_utc_now
+    for b0 in range(0, len(files), max(1, int(batch_sessions))):
+        batch = files[b0:b0 + max(1, int(batch_sessions))]
+        datas = [json.loads(f.read_text(encoding="utf-8")) for f in batch]
+        results = backfill_sessions(datas, refresh_quality=True, overwrite_contract=False, ctx=ctx)
+        for session_file, session_data, result in zip(batch, datas, results):
+            summary["sessions_total"] += 1
+            summary["logs_total"] += int(result.get("logs_total", 0) or 0)
+            summary["logs_updated"] += int(result.get("logs_updated", 0) or 0)
+            for name, count in (result.get("field_updates", {}) or {}).items():
+                summary["field_updates"][name] = summary["field_updates"].get(name, 0) + int(count or 0)
+            if result.get("changed"):
+                summary["sessions_changed"] += 1
+                summary["changed_sessions"].append({
+                    "session_id": session_data.get("session_id", session_file.stem) if isinstance(session_data, dict) else session_file.stem,
+                    "topic": session_data.get("topic", ""), "logs_updated": int(result.get("logs_updated", 0) or 0),
+                    "field_updates": dict(result.get("field_updates", {}) or {})})
+                if apply_changes:
+                    if backup_dir is not None:
+                        shutil.copy2(session_file, Path(backup_dir) / session_file.name)
+                    session_data["updated_at"] = now()
+                    session_file.write_text(json.dumps(session_data, ensure_ascii=False, indent=2), encoding="utf-8")
+    return summary
+
+
+def merge_summaries(parts: Sequence[dict]) -> dict:
+    """Sum per-rank summaries of backfill_session_files (counters add; changed_sessions concatenate in rank order)."""
+    out = {"sessions_total": 0, "sessions_changed": 0, "logs_total": 0, "logs_updated": 0, "field_updates": {}, "changed_sessions": []}
+    for p in parts:
+        for k in ("sessions_total", "sessions_changed", "logs_total", "logs_updated"):
+            out[k] += int(p.get(k, 0))
+        for name, count in p.get("field_updates", {}).items():
+            out["field_updates"][name] = out["field_updates"].get(name, 0) + int(count)
+        out["changed_sessions"].extend(p.get("changed_sessions", []))
+    return out
+
+
+def build_bindings(mod, ctx=None) -> Dict[str, Any]:
+    """Replacement callables for dropin.install(); DIMENSION_FOLLOW_UP_SENSITIVITY / HARD_FOLLOW_UP_SIGNALS are read from
+    the server module at call time."""
+    def _tables():
+        return getattr(mod, "DIMENSION_FOLLOW_UP_SENSITIVITY", None), getattr(mod, "HARD_FOLLOW_UP_SIGNALS", None)
+
+    def _depth(question, answer, dimension, options=None, is_follow_up=False, multi_select=False, answer_mode="",
+               requires_rationale=False, evidence_intent=""):
+        st, hs = _tables()
+        return evaluate_answer_depth(question, answer, dimension, options, is_follow_up, multi_select, answer_mode, requires_rationale,
+                                     evidence_intent, ctx=ctx, sensitivity_table=st, hard_signals=hs)
+
+    def _quality(eval_result, answer, is_follow_up, follow_up_round):
+        return evaluate_answer_quality(eval_result, answer, is_follow_up, follow_up_round, ctx=ctx)
+
+    def _backfill(session, *, refresh_quality=True, overwrite_contract=False):
+        st, hs = _tables()
+        return backfill_sessions([session], refresh_quality=refresh_quality, overwrite_contract=overwrite_contract, ctx=ctx,
+                                 sensitivity_table=st, hard_signals=hs)[0]
+
+    return {"evaluate_answer_depth": _depth, "evaluate_answer_quality": _quality,
+            "classify_answer_evidence_class_v3": classify_answer_evidence_class_v3,
+            "backfill_session_interview_log_evidence_annotations": _backfill}

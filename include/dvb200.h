@@ -163,6 +163,25 @@ int32_t dvb_solution_jaccard(dvb_ctx* ctx, int32_t mem, const uint8_t* left_utf8
                              const uint8_t* right_utf8, const int64_t* right_off, int64_t n_pairs, int32_t ngram,
                              int32_t* out_inter, int32_t* out_union, int32_t* out_nleft, int32_t* out_nright);
 
+/* ---- a11-a13  replaces the string scans of: evaluate_answer_depth (web/server.py:21221-21401), _score_rich_option_answer
+ *               (20318-20367), evaluate_answer_quality (20370-20426), _infer_legacy_log_capture_contract (21419-21466)
+ * Per text: [b0, b1) = byte bounds of Python's text.strip(); out_len = len(text.strip()) in code points;
+ * out_flags bit 0 = any(c.isdigit() for c in text.strip()), bit 1 = stripped text non-empty;
+ * out_mask bit g = some pattern of group g (0..63) occurs in the stripped text as a substring, or — for patterns with
+ * pat_whole != 0 — equals the stripped text.  Patterns (UTF-8, 1..255 bytes each, CSR by int32 pat_off[n_pat+1]) are the
+ * reference's literal keyword lists; the pattern arrays are ALWAYS host pointers (they are tiny), whatever `mem` says.
+ * out_b0 / out_b1 may both be NULL. */
+int32_t dvb_text_features(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_texts,
+                          const uint8_t* pat_utf8, const int32_t* pat_off, const uint8_t* pat_group, const uint8_t* pat_whole, int32_t n_pat,
+                          uint64_t* out_mask, int32_t* out_len, uint8_t* out_flags, int32_t* out_b0, int32_t* out_b1);
+
+/* Needle j is searched in haystack needle_hay[j] (`option in answer`, web/server.py:20326-20327, 21321).  out_bits[j]:
+ * bit 0 = needle (raw) in haystack.strip()  ("" is contained in everything, as in Python);
+ * bit 1 = needle.strip() non-empty and in haystack.strip();  bit 2 = needle.strip() == haystack.strip() != "". */
+int32_t dvb_contains(dvb_ctx* ctx, int32_t mem, const uint8_t* hay_utf8, const int64_t* hay_off, int64_t n_hay,
+                     const uint8_t* needle_utf8, const int64_t* needle_off, const int32_t* needle_hay, int64_t n_needles,
+                     uint8_t* out_bits);
+
 #ifdef __cplusplus
 }
 #endif

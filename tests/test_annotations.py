@@ -1,0 +1,169 @@
+"""a11-a14: per-turn evidence annotation + bulk re-index.  Golden vectors come from the REAL reference functions
+(tools/make_golden_annot.py); the CPU suite pins the oracle and the host decision logic, the GPU suite the kernels."""
+import copy
+import json
+import random
+
+import numpy as np
+import pytest
+
+
+@pytest.fixture(scope="module")
+def gold(golden):
+    return golden("a11_a13_annotations.json")
+
+
+def test_oracle_backfill_matches_reference(gold):
+    from oracle import dv_annot
+    for case in gold["backfill"]:
+        work = copy.deepcopy(case["input"])
+        summary = dv_annot.backfill(work, case["refresh_quality"], case["overwrite_contract"])
+        assert summary == case["summary"]
+        assert (work.get("interview_log") if isinstance(work, dict) else None) == case["logs_after"]
+
+
+def test_oracle_depth_quality_class_match_reference(gold):
+    from oracle import dv_annot
+    for c in gold["depth"]:
+        ev = dv_annot.answer_depth(**c["kwargs"])
+        assert ev == c["depth"], c["kwargs"]
+        ql = dv_annot.answer_quality(ev, c["kwargs"]["answer"], c["kwargs"]["is_follow_up"], c["follow_up_round"])
+        assert ql == c["quality"]
+        assert dv_annot.evidence_class(ev["signals"], ql["quality_score"], c["kwargs"]["evidence_intent"]) == c["class"]
+
+
+# ---- plain-Python stand-ins for the two kernels (tests only): they let the CPU suite check the HOST decision tree
+def py_text_features(texts, ctx=None):
+    from deep_vision_b200 import annotations as an
+    pb, po, pg, pw = an._PATTERNS
+    pats = [(bytes(pb[po[i]:po[i + 1]]).decode("utf-8"), int(pg[i]), int(pw[i])) for i in range(len(pg))]
+    mask = np.zeros(len(texts), np.uint64); length = np.zeros(len(texts), np.int32); flags = np.zeros(len(texts), np.uint8)
+    for i, t in enumerate(texts):
+        s = t.strip()
+        m = 0
+        for p, g, w in pats:
+            if (s == p) if w else (p in s):
+                m |= 1 << g
+        mask[i] = m; length[i] = len(s); flags[i] = (1 if any(c.isdigit() for c in s) else 0) | (2 if s else 0)
+    return mask, length, flags
+
+
+def py_contains(haystacks, needles, needle_hay, ctx=None):
+    out = np.zeros(len(needles), np.uint8)
+    for j, (nd, h) in enumerate(zip(needles, needle_hay)):
+        hay, s = haystacks[h].strip(), nd.strip()
+        out[j] = (1 if nd in hay else 0) | (2 if s and s in hay else 0) | (4 if s and s == hay else 0)
+    return out
+
+
+def _check_product_against_golden(an, gold, ctx=None):
+    for case in gold["backfill"]:
+        work = copy.deepcopy(case["input"])
+        summary = an.backfill_session_interview_log_evidence_annotations(work, refresh_quality=case["refresh_quality"],
+                                                                         overwrite_contract=case["overwrite_contract"], ctx=ctx)
+        assert summary == case["summary"]
+        assert (work.get("interview_log") if isinstance(work, dict) else None) == case["logs_after"]
+    # the batch form gives the same per-session results with two launches in total
+    inputs = [copy.deepcopy(c["input"]) for c in gold["backfill"] if c["refresh_quality"]]
+    want = [c for c in gold["backfill"] if c["refresh_quality"]]
+    got = an.backfill_sessions(inputs, ctx=ctx)
+    assert got == [c["summary"] for c in want]
+    for c in gold["depth"]:
+        ev = an.evaluate_answer_depth(**c["kwargs"], ctx=ctx)
+        assert ev == c["depth"], c["kwargs"]
+        ql = an.evaluate_answer_quality(ev, c["kwargs"]["answer"], c["kwargs"]["is_follow_up"], c["follow_up_round"], ctx=ctx)
+        assert ql == c["quality"]
+        assert an.classify_answer_evidence_class_v3(ev["signals"], ql["quality_score"], c["kwargs"]["evidence_intent"]) == c["class"]
+
+
+def test_host_decision_logic_with_standin_features(gold, monkeypatch):
+    from deep_vision_b200 import annotations as an
+    monkeypatch.setattr(an, "text_features", py_text_features)
+    monkeypatch.setattr(an, "contains", py_contains)
+    _check_product_against_golden(an, gold)
+
+
+def test_script_body_dry_run_apply_and_shards(tmp_path, gold, monkeypatch):
+    """scripts/migrate_session_evidence_annotations.py:64-114 semantics (summary schema, dry run, --apply + backup)."""
+    from deep_vision_b200 import annotations as an
+    monkeypatch.setattr(an, "text_features", py_text_features)
+    monkeypatch.setattr(an, "contains", py_contains)
+    sess_dir, bak = tmp_path / "sessions", tmp_path / "bak"
+    sess_dir.mkdir(); bak.mkdir()
+    cases = [c for c in gold["backfill"] if c["refresh_quality"] and isinstance(c["input"].get("interview_log"), list)][:12]
+    files = []
+    for c in cases:
+        f = sess_dir / (c["input"]["session_id"] + ".json")
+        f.write_text(json.dumps(c["input"], ensure_ascii=False), encoding="utf-8")
+        files.append(f)
+    files.sort()
+    by_id = {c["input"]["session_id"]: c for c in cases}
+    dry = an.backfill_session_files(files, batch_sessions=5)
+    assert dry["sessions_total"] == len(files)
+    assert dry["logs_total"] == sum(c["summary"]["logs_total"] for c in cases)
+    assert dry["logs_updated"] == sum(c["summary"]["logs_updated"] for c in cases)
+    assert dry["sessions_changed"] == sum(1 for c in cases if c["summary"]["changed"])
+    assert [e["session_id"] for e in dry["changed_sessions"]] == [f.stem for f in files if by_id[f.stem]["summary"]["changed"]]
+    assert json.loads(files[0].read_text(encoding="utf-8")) == by_id[files[0].stem]["input"]          # dry run: untouched
+    parts = [an.backfill_session_files(files, shard=(r, 3)) for r in range(3)]                        # 3 "ranks"
+    assert an.merge_summaries(parts) == dry
+
+    class FakeServer:
+        @staticmethod
+        def get_utc_now():
+            return "2026-01-01T00:00:00Z"
+    applied = an.backfill_session_files(files, apply_changes=True, backup_dir=bak, server_module=FakeServer)
+    assert applied == dry
+    for f in files:
+        c = by_id[f.stem]
+        data = json.loads(f.read_text(encoding="utf-8"))
+        if c["summary"]["changed"]:
+            assert data["updated_at"] == "2026-01-01T00:00:00Z" and data["interview_log"] == c["logs_after"]
+            assert json.loads((bak / f.name).read_text(encoding="utf-8")) == c["input"]
+        else:
+            assert data == c["input"] and not (bak / f.name).exists()
+
+
+# ----------------------------------------------------------------------------- GPU
+ADVERSARIAL = ["", " ", "　\n好的\t", "好的", "好的吧", "x²", "٣ items", "𝟘", "no digits here", "a", " 可选 必须 ", "😀需要不需要",
+               "（a)：b:c/d-e，f", "如", "当 如果", "abc" * 50 + "；" + "影响" * 30, " x ", "É１２", "﻿可以"]
+
+
+@pytest.mark.gpu
+def test_gpu_text_features_and_contains_vs_python(gpu_ctx):
+    from deep_vision_b200 import annotations as an
+    m, ln, fl = an.text_features(ADVERSARIAL, ctx=gpu_ctx)
+    wm, wl, wf = py_text_features(ADVERSARIAL)
+    assert ln.tolist() == wl.tolist() and fl.tolist() == wf.tolist()
+    assert m.tolist() == wm.tolist()
+    hays = ADVERSARIAL
+    needles, nh = [], []
+    rng = random.Random(3)
+    for h, hay in enumerate(hays):
+        for nd in ("", " ", "好的", " 好的 ", hay, hay.strip(), hay[1:4], "需要", "x", "\n"):
+            needles.append(nd); nh.append(h)
+    got = an.contains(hays, needles, nh, ctx=gpu_ctx)
+    assert got.tolist() == py_contains(hays, needles, nh).tolist()
+
+
+@pytest.mark.gpu
+def test_gpu_annotations_golden(gpu_ctx, gold):
+    from deep_vision_b200 import annotations as an
+    _check_product_against_golden(an, gold, ctx=gpu_ctx)
+
+
+@pytest.mark.gpu
+def test_gpu_backfill_vs_oracle_random(gpu_ctx):
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parents[1] / "tools"))
+    from make_golden_annot import make_log
+    from deep_vision_b200 import annotations as an
+    from oracle import dv_annot
+    rng = random.Random(77)
+    sessions = [{"session_id": "r%d" % s, "interview_log": [make_log(rng) for _ in range(rng.randint(0, 30))]} for s in range(300)]
+    ref = copy.deepcopy(sessions)
+    want = [dv_annot.backfill(s) for s in ref]
+    got = an.backfill_sessions(sessions, ctx=gpu_ctx)
+    assert got == want
+    assert sessions == ref
