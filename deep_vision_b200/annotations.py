@@ -44,13 +44,14 @@ SCENARIO_KEYWORDS = ("比如", "例如", "当", "如果", "场景", "案例")   
 OPTION_PUNCT_TOKENS = ("（", ")", "：", ":", "/", "-", "，")                                                              # 20343
 DIMENSION_UNIT_TOKENS = ("分钟", "小时", "天", "周", "月", "成本", "预算", "上线")                                           # 20357
 QUESTION_RICH_MARKERS = ("原因", "场景", "影响", "频次", "角色", "流程", "瓶颈")                                             # 20355
+PACK_VAGUE_TERMS = ("看情况", "不确定", "都可以", "不知道", "可能", "暂时不清楚", "以后再说", "差不多")                                  # 22576
 QUESTION_EVIDENCE_MARKERS = ("原因", "为什么", "场景", "影响", "频次", "角色", "流程", "主要是因为", "哪种情况")               # 21441-21443
 
 G_VAGUE, G_INFORMATIVE, G_SEMICOLON = 0, 1, 2
 G_CONTRA_L, G_CONTRA_R = 3, 9                     # six bits each
 G_SCENARIO, G_GENERIC, G_OPT_PUNCT = 15, 16, 17
 G_CAUSE, G_CONTEXT, G_ROLE, G_PROCESS, G_UNITS = 18, 19, 20, 21, 22
-G_Q_RICH, G_Q_EVIDENCE = 24, 25
+G_Q_RICH, G_Q_EVIDENCE, G_PACK_VAGUE = 24, 25, 26
 
 DIMENSION_FOLLOW_UP_SENSITIVITY = {"customer_needs": 0.8, "business_process": 0.6, "tech_constraints": 0.5,
                                    "project_constraints": 0.4}                                                           # 19013
@@ -65,7 +66,7 @@ def _pattern_table():
         (G_SCENARIO, SCENARIO_KEYWORDS, 0), (G_GENERIC, GENERIC_ANSWERS, 1), (G_OPT_PUNCT, OPTION_PUNCT_TOKENS, 0),
         (G_CAUSE, RICH_OPTION_CAUSE_KEYWORDS, 0), (G_CONTEXT, RICH_OPTION_CONTEXT_KEYWORDS, 0), (G_ROLE, RICH_OPTION_ROLE_KEYWORDS, 0),
         (G_PROCESS, RICH_OPTION_PROCESS_KEYWORDS, 0), (G_UNITS, DIMENSION_UNIT_TOKENS, 0),
-        (G_Q_RICH, QUESTION_RICH_MARKERS, 0), (G_Q_EVIDENCE, QUESTION_EVIDENCE_MARKERS, 0)]
+        (G_Q_RICH, QUESTION_RICH_MARKERS, 0), (G_Q_EVIDENCE, QUESTION_EVIDENCE_MARKERS, 0), (G_PACK_VAGUE, PACK_VAGUE_TERMS, 0)]
     for i, (left, right) in enumerate(CONTRADICTION_PAIRS):
         groups.append((G_CONTRA_L + i, (left,), 0))
         groups.append((G_CONTRA_R + i, (right,), 0))
@@ -557,6 +558,162 @@ def merge_summaries(parts: Sequence[dict]) -> dict:
     return out
 
 
+# ----------------------------------------------------------------------------- a13: evidence pack
+# (pair_id, index into CONTRADICTION_PAIRS, description)   web/server.py:22579-22585
+_PACK_CONTRADICTIONS = (("need", 0, "需求取向冲突"), ("support", 2, "支持立场冲突"), ("available", 4, "资源现状冲突"),
+                        ("must", 5, "约束优先级冲突"), ("ready", 3, "准备状态冲突"))
+
+
+def build_report_evidence_pack(session: dict, *, server_module, ctx=None) -> dict:
+    """Drop-in for web/server.py:22568-22803.  Annotation (a12) and every `term in answer` test run on the GPU; the
+    per-dimension coverage block calls the server module's own helpers (get_dimension_info_for_session,
+    get_interview_mode_config, get_dimension_missing_aspects, resolve_report_template_for_session), which are outside
+    the hot path.  The caller's session is not mutated (deep copy, 22570)."""
+    from datetime import datetime, timezone
+    mod = server_module
+    work = copy.deepcopy(session) if isinstance(session, dict) else {}
+    st, hs = getattr(mod, "DIMENSION_FOLLOW_UP_SENSITIVITY", None), getattr(mod, "HARD_FOLLOW_UP_SIGNALS", None)
+    backfill_sessions([work], refresh_quality=True, overwrite_contract=False, ctx=ctx, sensitivity_table=st, hard_signals=hs)
+    interview_log = work.get("interview_log", [])
+    dim_info = mod.get_dimension_info_for_session(work)
+    mode_config = mod.get_interview_mode_config(work)
+    answers = [str(log.get("answer", "")) for log in interview_log]
+    a_masks = [int(m) for m in text_features(answers, ctx=ctx)[0]] if answers else []
+
+    facts, unknowns, contradictions, blindspots = [], [], [], []
+    state, seen_contra, seen_unknown = {}, set(), set()
+    mode_dist = {m: 0 for m in QUESTION_ANSWER_MODES}
+    intent_dist = {i: 0 for i in QUESTION_EVIDENCE_INTENTS}
+    class_dist = {"explicit": 0, "rich_option": 0, "weak_inferred": 0, "pending_follow_up": 0}
+    for idx, log in enumerate(interview_log, 1):
+        q_id = "Q%d" % idx
+        dim_key = log.get("dimension", "")
+        dim_name = dim_info.get(dim_key, {}).get("name", dim_key or "未分类")
+        answer = answers[idx - 1].strip()
+        a_mask = a_masks[idx - 1]
+        signals = log.get("follow_up_signals") if isinstance(log.get("follow_up_signals"), list) else []
+        try:
+            quality = float(log.get("quality_score", 0) or 0)
+        except Exception:
+            quality = 0.0
+        quality = max(0.0, min(1.0, quality))
+        mode = normalize_question_answer_mode(log.get("answer_mode", ""), fallback="pick_only")
+        needs_why = bool(log.get("requires_rationale", False) or mode == "pick_with_reason")
+        intent = normalize_question_evidence_intent(log.get("evidence_intent", ""),
+                                                    fallback="high" if needs_why else ("medium" if mode == "pick_with_reason" else "low"))
+        mode_dist[mode] = mode_dist.get(mode, 0) + 1
+        intent_dist[intent] = intent_dist.get(intent, 0) + 1
+        klass = classify_answer_evidence_class_v3(signals, quality, intent)
+        class_dist[klass] = class_dist.get(klass, 0) + 1
+        facts.append({
+            "q_id": q_id, "dimension": dim_key, "dimension_name": dim_name, "question": str(log.get("question", "")).strip(),
+            "answer": answer, "is_follow_up": bool(log.get("is_follow_up", False)), "follow_up_round": int(log.get("follow_up_round", 0) or 0),
+            "quality_score": quality,
+            "quality_signals": log.get("quality_signals", []) if isinstance(log.get("quality_signals"), list) else [],
+            "follow_up_signals": signals, "hard_triggered": bool(log.get("hard_triggered", False)), "answer_mode": mode,
+            "requires_rationale": needs_why, "evidence_intent": intent, "answer_evidence_class": klass})
+
+        reasons = []
+        if klass != "rich_option" and any(sig in ("vague_expression", "generic_answer") for sig in signals):
+            reasons.append("命中模糊回答信号")
+        if _bit(a_mask, G_PACK_VAGUE):
+            reasons.append("回答存在模糊表述")
+        if klass != "rich_option" and 0 < quality < 0.45:
+            reasons.append("回答质量偏低")
+        if reasons:
+            ordered = sorted(set(reasons))
+            ukey = q_id + ":" + "|".join(ordered)
+            if ukey not in seen_unknown:
+                seen_unknown.add(ukey)
+                unknowns.append({"q_id": q_id, "dimension": dim_name, "reason": "；".join(ordered), "answer_excerpt": answer[:120]})
+
+        for pair_id, pi, description in _PACK_CONTRADICTIONS:
+            positive, negative = CONTRADICTION_PAIRS[pi]
+            has_pos, has_neg = _bit(a_mask, G_CONTRA_L + pi), _bit(a_mask, G_CONTRA_R + pi)
+            if has_pos and has_neg:
+                key = "self:%s:%s" % (pair_id, q_id)
+                if key not in seen_contra:
+                    seen_contra.add(key)
+                    contradictions.append({"type": "same_answer_conflict", "pair_id": pair_id, "description": description, "dimension": dim_name,
+                                           "evidence_refs": [q_id], "detail": "%s 同时出现「%s」与「%s」" % (q_id, positive, negative)})
+            if not (has_pos or has_neg):
+                continue
+            now_state = "positive" if has_pos else "negative"
+            prev = state.get((dim_key, pair_id))
+            if prev and prev.get("state") != now_state:
+                key = "cross:%s:%s:%s:%s" % (pair_id, prev.get("q_id"), q_id, dim_key)
+                if key not in seen_contra:
+                    seen_contra.add(key)
+                    contradictions.append({"type": "cross_answer_conflict", "pair_id": pair_id, "description": description, "dimension": dim_name,
+                                           "evidence_refs": [prev.get("q_id"), q_id],
+                                           "detail": "%s 与 %s 对「%s/%s」存在冲突" % (prev.get("q_id"), q_id, positive, negative)})
+            state[(dim_key, pair_id)] = {"state": now_state, "q_id": q_id}
+
+    def _q(value):
+        try:
+            return max(0.0, min(1.0, float(value)))
+        except Exception:
+            return 0.0
+
+    dimension_coverage, adjusted_values, count_values = {}, [], []
+    for dim_key, info in dim_info.items():
+        dim_logs = [log for log in interview_log if log.get("dimension") == dim_key]
+        dim_facts = [f for f in facts if f.get("dimension") == dim_key]
+        count_percent = int(session.get("dimensions", {}).get(dim_key, {}).get("coverage", 0) or 0)
+        count_ratio = max(0, min(100, count_percent)) / 100.0
+        missing = mod.get_dimension_missing_aspects(session, dim_key)
+        key_aspects = info.get("key_aspects", []) if isinstance(info.get("key_aspects", []), list) else []
+        if key_aspects:
+            total = len(key_aspects)
+            ratio = max(0.0, min(1.0, (total - min(total, len(missing))) / total))
+            percent = int(round(ratio * 100))
+        else:
+            percent, ratio = count_percent, count_ratio
+        scores = [_q(f.get("quality_score", 0.0)) for f in dim_facts]
+        avg = (sum(scores) / len(scores)) if scores else 0.0
+        adjusted = max(0.0, min(1.0, ratio * (0.35 + 0.65 * avg)))
+        adjusted_values.append(adjusted)
+        count_values.append(count_ratio)
+        blindspots.extend({"dimension": info.get("name", dim_key), "aspect": aspect} for aspect in missing)
+        dimension_coverage[dim_key] = {
+            "name": info.get("name", dim_key), "coverage_percent": max(0, min(100, percent)), "coverage_ratio": round(ratio, 2),
+            "question_count_coverage_percent": max(0, min(100, count_percent)), "question_count_coverage_ratio": round(count_ratio, 2),
+            "quality_adjusted_coverage": round(adjusted, 3), "raw_average_quality_score": round(avg, 3),
+            "formal_count": len([log for log in dim_logs if not log.get("is_follow_up", False)]),
+            "follow_up_count": len([log for log in dim_logs if log.get("is_follow_up", False)]),
+            "minimum_formal": mode_config.get("formal_questions_per_dim", 3),
+            "maximum_formal": mode_config.get("max_formal_questions_per_dim", mode_config.get("formal_questions_per_dim", 3)),
+            "missing_aspects": missing, "key_aspects": key_aspects}
+
+    raw = [_q(f.get("quality_score", 0.0)) for f in facts]
+    positive_only = [x for x in raw if x > 0]
+    average = sum(raw) / len(raw) if raw else 0.0
+    n_follow = len([f for f in facts if f.get("is_follow_up", False)])
+    template = mod.resolve_report_template_for_session(session)
+    report_cfg = (session.get("scenario_config", {}) or {}).get("report", {})
+    if not isinstance(report_cfg, dict):
+        report_cfg = {}
+    schema = {}
+    if template == getattr(mod, "REPORT_TEMPLATE_CUSTOM_V1", object()):
+        schema, _issues = mod.normalize_custom_report_schema(report_cfg.get("schema"), fallback_sections=report_cfg.get("sections"))
+    return {
+        "topic": session.get("topic", "未知主题"),
+        "report_type": session.get("scenario_config", {}).get("report", {}).get("type", "standard"),
+        "report_template": template, "report_schema": schema, "generated_at": datetime.now(timezone.utc).isoformat(),
+        "facts": facts, "contradictions": contradictions, "unknowns": unknowns, "blindspots": blindspots,
+        "dimension_coverage": dimension_coverage,
+        "overall_coverage": round(sum(adjusted_values) / len(adjusted_values) if adjusted_values else 0.0, 3),
+        "question_count_overall_coverage": round(sum(count_values) / len(count_values) if count_values else 0.0, 3),
+        "quality_snapshot": {
+            "average_quality_score": round(average, 3), "raw_average_quality_score": round(average, 3),
+            "positive_only_average_quality_score": round(sum(positive_only) / len(positive_only) if positive_only else 0.0, 3),
+            "hard_triggered_count": len([f for f in facts if f.get("hard_triggered")]), "total_questions": len(facts),
+            "total_formal_questions": len(facts) - n_follow, "total_follow_up_questions": n_follow,
+            "follow_up_ratio": round(n_follow / len(facts), 3) if facts else 0.0,
+            "answer_mode_distribution": mode_dist, "evidence_intent_distribution": intent_dist,
+            "answer_evidence_class_distribution": class_dist}}
+
+
 def build_bindings(mod, ctx=None) -> Dict[str, Any]:
     """Replacement callables for dropin.install(); DIMENSION_FOLLOW_UP_SENSITIVITY / HARD_FOLLOW_UP_SIGNALS are read from
     the server module at call time."""
@@ -577,6 +734,9 @@ def build_bindings(mod, ctx=None) -> Dict[str, Any]:
         return backfill_sessions([session], refresh_quality=refresh_quality, overwrite_contract=overwrite_contract, ctx=ctx,
                                  sensitivity_table=st, hard_signals=hs)[0]
 
-    return {"evaluate_answer_depth": _depth, "evaluate_answer_quality": _quality,
+    def _pack(session):
+        return build_report_evidence_pack(session, server_module=mod, ctx=ctx)
+
+    return {"evaluate_answer_depth": _depth, "evaluate_answer_quality": _quality, "build_report_evidence_pack": _pack,
             "classify_answer_evidence_class_v3": classify_answer_evidence_class_v3,
             "backfill_session_interview_log_evidence_annotations": _backfill}

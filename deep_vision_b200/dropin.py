@@ -21,7 +21,7 @@ HOT_NAMES = (
     "normalize_interview_question_text", "question_token_set", "is_similar_interview_question",
     "find_similar_interview_question_log", "_solution_jaccard_similarity",
     "evaluate_answer_depth", "evaluate_answer_quality", "classify_answer_evidence_class_v3",
-    "backfill_session_interview_log_evidence_annotations",
+    "backfill_session_interview_log_evidence_annotations", "build_report_evidence_pack",
 )
 
 

@@ -76,11 +76,25 @@ def _check_product_against_golden(an, gold, ctx=None):
         assert an.classify_answer_evidence_class_v3(ev["signals"], ql["quality_score"], c["kwargs"]["evidence_intent"]) == c["class"]
 
 
+def _check_packs(an, gold, ctx=None):
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parents[1] / "tools"))
+    from make_golden_annot import PackStubs
+    for c in gold["packs"]:
+        sess = copy.deepcopy(c["input"])
+        pack = an.build_report_evidence_pack(sess, server_module=PackStubs, ctx=ctx)
+        assert sess == c["input"]                                       # the caller's session is not mutated (web/server.py:22570)
+        assert pack.pop("generated_at")
+        assert pack == c["pack"]
+
+
 def test_host_decision_logic_with_standin_features(gold, monkeypatch):
     from deep_vision_b200 import annotations as an
     monkeypatch.setattr(an, "text_features", py_text_features)
     monkeypatch.setattr(an, "contains", py_contains)
     _check_product_against_golden(an, gold)
+    _check_packs(an, gold)
 
 
 def test_script_body_dry_run_apply_and_shards(tmp_path, gold, monkeypatch):
@@ -150,6 +164,7 @@ def test_gpu_text_features_and_contains_vs_python(gpu_ctx):
 def test_gpu_annotations_golden(gpu_ctx, gold):
     from deep_vision_b200 import annotations as an
     _check_product_against_golden(an, gold, ctx=gpu_ctx)
+    _check_packs(an, gold, ctx=gpu_ctx)
 
 
 @pytest.mark.gpu

@@ -66,6 +66,56 @@ def make_log(rng):
     return log
 
 
+# ---- stand-ins for the app-level helpers build_report_evidence_pack calls (the reference's own test stubs the same
+# functions: tests/test_security_regression.py:4215-4219).  Shared by the golden generator and tests/test_annotations.py.
+class PackStubs:
+    REPORT_TEMPLATE_CUSTOM_V1 = "custom_v1"
+    DIMS = {
+        "customer_needs": {"name": "客户需求", "key_aspects": ["核心痛点", "期望价值", "使用场景", "用户角色"]},
+        "business_process": {"name": "业务流程", "key_aspects": ["关键流程", "角色分工"]},
+        "tech_constraints": {"name": "技术约束", "key_aspects": []},
+        "project_constraints": {"name": "项目约束"},
+    }
+
+    @staticmethod
+    def get_dimension_info_for_session(session):
+        return PackStubs.DIMS
+
+    @staticmethod
+    def get_interview_mode_config(session):
+        return {"formal_questions_per_dim": 3, "max_formal_questions_per_dim": 4} if session.get("mode") != "quick" else {"formal_questions_per_dim": 2}
+
+    @staticmethod
+    def get_dimension_missing_aspects(session, dim_key):
+        return list((session.get("missing", {}) or {}).get(dim_key, []))
+
+    @staticmethod
+    def resolve_report_template_for_session(session):
+        return session.get("template", "standard_v1")
+
+    @staticmethod
+    def normalize_custom_report_schema(schema, fallback_sections=None):
+        return ({"sections": list(fallback_sections or []), "schema": schema}, [])
+
+
+def pack_session(rng, s):
+    logs = [make_log(rng) for _ in range(rng.randint(0, 16))]
+    logs = [log for log in logs if isinstance(log.get("options"), list)]
+    for log in logs:
+        if rng.random() < 0.1:
+            log["answer"] = None if rng.random() < 0.5 else 42
+    sess = {"session_id": "p%03d" % s, "topic": "主题%d" % s, "interview_log": logs,
+            "dimensions": {k: {"coverage": rng.choice([0, 35, 70, 100, 140])} for k in list(PackStubs.DIMS)[: rng.randint(0, 4)]},
+            "missing": {"customer_needs": rng.sample(["核心痛点", "期望价值", "使用场景", "用户角色", "其他"], rng.randint(0, 5)),
+                        "business_process": rng.sample(["关键流程", "角色分工"], rng.randint(0, 2))},
+            "scenario_config": {"report": {"type": rng.choice(["standard", "assessment"]), "sections": ["a", "b"], "schema": {"x": 1}}}}
+    if s % 5 == 0:
+        sess["template"] = "custom_v1"
+    if s % 7 == 0:
+        sess["mode"] = "quick"
+    return sess
+
+
 def main():
     ns = ref_loader.load()
     rng = random.Random(20260111)
@@ -97,10 +147,24 @@ def main():
         ql = ns["evaluate_answer_quality"](ev, log["answer"], kw["is_follow_up"], fr)
         cls = ns["classify_answer_evidence_class_v3"](ev["signals"], ql["quality_score"], kw["evidence_intent"])
         depth.append({"kwargs": kw, "follow_up_round": fr, "depth": ev, "quality": ql, "class": cls})
-    out = {"generator": "tools/make_golden_annot.py", "backfill": cases, "depth": depth}
+    from datetime import datetime, timezone
+    ov = {k: getattr(PackStubs, k) for k in ("REPORT_TEMPLATE_CUSTOM_V1", "get_dimension_info_for_session", "get_interview_mode_config",
+                                             "get_dimension_missing_aspects", "resolve_report_template_for_session",
+                                             "normalize_custom_report_schema")}
+    ov.update(datetime=datetime, timezone=timezone)
+    ns2 = ref_loader.load(extra_names=["build_report_evidence_pack"], overrides=ov)
+    packs = []
+    for s in range(40):
+        sess = pack_session(rng, s)
+        before = copy.deepcopy(sess)
+        pack = ns2["build_report_evidence_pack"](sess)
+        assert sess == before
+        pack.pop("generated_at")
+        packs.append({"input": sess, "pack": pack})
+    out = {"generator": "tools/make_golden_annot.py", "backfill": cases, "depth": depth, "packs": packs}
     p = ROOT / "tests" / "golden" / "a11_a13_annotations.json"
-    p.write_text(json.dumps(out, ensure_ascii=False, indent=0), encoding="utf-8")
-    print("wrote", p, p.stat().st_size, "bytes;", len(cases), "backfill cases,", len(depth), "depth cases")
+    p.write_text(json.dumps(out, ensure_ascii=False, separators=(",", ":")), encoding="utf-8")
+    print("wrote", p, p.stat().st_size, "bytes;", len(cases), "backfill cases,", len(depth), "depth cases,", len(packs), "packs")
 
 
 if __name__ == "__main__":
