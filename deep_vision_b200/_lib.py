@@ -39,6 +39,10 @@ _SIGS = {
     "dvb_solution_jaccard": (C.c_int32, [_vp, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp]),
     "dvb_text_features": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
     "dvb_contains": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, C.c_int64, _vp]),
+    "dvb_chunk_index_build": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.POINTER(_vp)]),
+    "dvb_chunk_index_free": (None, [_vp]),
+    "dvb_chunk_index_stats": (C.c_int32, [_vp, _vp]),
+    "dvb_chunk_index_topk": (C.c_int32, [_vp, _vp, C.c_int32, _vp, _vp, C.c_int32, _vp, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),
     "dvb_bind_claims": (C.c_int32, [_vp, C.c_int32] + [_vp] * 6 + [C.c_int64] + [_vp] * 10 + [C.c_int64]),
 }
 

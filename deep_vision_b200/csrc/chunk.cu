@@ -254,6 +254,26 @@ extern "C" int32_t dvb_chunk_scores(dvb_ctx* ctx, int32_t mem, const uint8_t* ch
     return io.finish(ctx);
 }
 
+// host-side launchers shared with index.cu (device pointers, caller's stream)
+void dv_launch_symbolize(dvb_ctx* ctx, cudaStream_t st, const uint8_t* d_utf8, const int64_t* d_off, int64_t n_texts, uint16_t* d_sym, int32_t* d_cnt) {
+    const int grid = (int)std::min<int64_t>((n_texts + 7) / 8, (int64_t)ctx->num_sm * 8);
+    k_symbolize<<<grid, 256, 0, st>>>(d_utf8, d_off, n_texts, d_sym, d_cnt);
+    ctx->launches += 1;
+}
+int64_t dv_topk_splits(dvb_ctx* ctx, int64_t n, int32_t nq) {
+    return std::max<int64_t>(1, std::min<int64_t>((n + 8191) / 8192, std::max<int64_t>(1, (int64_t)ctx->num_sm * 4 / std::max(1, nq))));
+}
+// d_ps / d_pi: nq * n_split * k scratch entries each
+void dv_topk_device(dvb_ctx* ctx, cudaStream_t st, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq, int64_t index_base, int32_t k,
+                    int64_t n_split, int32_t* d_ps, int64_t* d_pi, int64_t* d_oidx, int32_t* d_oscore, int32_t* d_on) {
+    const int64_t per = (n + n_split - 1) / n_split;
+    dim3 g1((unsigned)n_split, (unsigned)std::min(nq, 65535));
+    k_topk_partial<<<g1, TOPK_WARPS * 32, 0, st>>>(d_score, d_idx, n, index_base, k, per > 0 ? per : 1, nq, d_ps, d_pi);
+    const int grid2 = std::min((nq + 7) / 8, ctx->num_sm * 8);
+    k_topk_final<<<grid2, 256, 0, st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_oscore, d_oidx, d_on);
+    ctx->launches += 2;
+}
+
 extern "C" int32_t dvb_topk(dvb_ctx* ctx, int32_t mem, const int32_t* score, const int64_t* idx, int64_t n, int32_t nq,
                              int64_t index_base, int32_t k, int64_t* out_idx, int32_t* out_score, int32_t* out_n) {
     if (!ctx || n < 0 || nq < 0 || k < 1 || k > 32 || !out_idx || !out_score || !out_n || (n > 0 && !score)) { dvb_set_err(ctx, "dvb_topk: invalid argument (1 <= k <= 32)%s%s"); return DVB_E_INVALID; }

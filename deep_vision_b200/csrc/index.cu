@@ -1,0 +1,372 @@
+// index.cu — positional inverted index over chunk symbols + indexed scoring with top-k (kernel stages K2-K4, bulk a7).
+// replaces, at corpus scale (BASELINE configs 3 and 5): the scoring loop and top-k of select_reference_material_context
+//   (reference web/server.py:32073-32087):  score = sum(lowered.count(term) for term in terms);
+//   sorted(positive, key=(-score, index))[:k].   Results are identical to the scan scorer of chunk.cu (exact counts).
+//
+// Build (dvb_chunk_index_build):
+//   K1  symbolise every chunk (chunk.cu k_symbolize: decode, CPython lower(), class map) -> u16 symbols, resident
+//   K2a every adjacent same-class symbol pair (CJK-CJK or ASCII-ASCII) becomes a posting
+//         key = pair id (30 bits), payload = (chunk, position of the pair's first symbol)
+//       emitted chunk by chunk, position by position
+//   K2b stable LSD radix sort by the 30 key bits only (sort.cuh; 4 passes): postings of one key stay ordered by
+//       (chunk, position) because that is the emission order
+//   K2c segmented reduce: run heads of equal keys -> distinct key list + CSR offsets (the postings "document frequency")
+// Query (dvb_chunk_index_topk), per batch of queries with a dense [batch][n_chunks] int32 score tile in HBM:
+//   K3a plan   per term: binary-search every bigram of the term in the key list, keep the RAREST one (offset j)
+//   K3b score  one warp per term walks that posting list 32 entries at a time: candidate start = pos - j, the term is
+//              verified against the resident symbols (exact), matches are counted greedily left to right per chunk
+//              (non-overlapping == str.count) and added to score[query][chunk]
+//   K4   top-k the warp-level top-k of chunk.cu under (score desc, global index asc), positives only
+// Query terms come from the reference's own term extractor (web/server.py:32037-32051): every term is >= 2 symbols
+// of one class, so each term has at least one indexed pair.
+#include "common.cuh"
+#include "sort.cuh"
+
+struct dvb_index {
+    int device = 0;
+    int64_t n_chunks = 0, n_bytes = 0, n_post = 0, n_keys = 0;
+    uint16_t* sym = nullptr;            // symbols of chunk c at sym[sym_off[c] .. + sym_cnt[c])
+    int64_t* sym_off = nullptr;         // [n_chunks + 1] (= byte offsets rebased to 0)
+    int32_t* sym_cnt = nullptr;         // [n_chunks]
+    unsigned long long* pk = nullptr;   // [n_post] chunk << 32 | pair key, sorted by (key, chunk, pos)
+    uint32_t* pv = nullptr;             // [n_post] position
+    uint32_t* ukeys = nullptr;          // [n_keys] distinct pair keys ascending
+    int64_t* uoff = nullptr;            // [n_keys + 1]
+};
+
+__device__ __forceinline__ uint32_t ix_code(uint32_t s) { return s >= 0x8000u ? 20992u + (s & 0x7FFFu) : s; }     // 15-bit symbol code
+__device__ __forceinline__ bool ix_same_class(uint32_t a, uint32_t b) { return a != 0u && b != 0u && ((a ^ b) & 0x8000u) == 0u; }
+__device__ __forceinline__ uint32_t ix_pair_key(uint32_t a, uint32_t b) { return (ix_code(a) << 15) | ix_code(b); }
+
+// ---- K2a: count, then emit postings (one warp per chunk)
+__global__ void __launch_bounds__(256) k_ix_count(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
+                                                   int64_t n_chunks, int32_t* __restrict__ pair_cnt) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_chunks; c += (int64_t)gridDim.x * 8) {
+        const uint16_t* s = sym + sym_off[c]; const int32_t m = sym_cnt[c];
+        int cnt = 0;
+        for (int32_t i = lane; i + 1 < m; i += 32) cnt += ix_same_class(s[i], s[i + 1]) ? 1 : 0;
+        for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+        if (lane == 0) pair_cnt[c] = cnt;
+    }
+}
+__global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
+                                                  int64_t n_chunks, const int64_t* __restrict__ post_off, unsigned long long* __restrict__ pk, uint32_t* __restrict__ pv) {
+    const int lane = threadIdx.x & 31;
+    for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_chunks; c += (int64_t)gridDim.x * 8) {
+        const uint16_t* s = sym + sym_off[c]; const int32_t m = sym_cnt[c];
+        int64_t w = post_off[c];
+        for (int32_t b0 = 0; b0 + 1 < m; b0 += 32) {
+            const int32_t i = b0 + lane;
+            uint32_t a = 0, b = 0;
+            if (i + 1 < m) { a = s[i]; b = s[i + 1]; }
+            const bool v = ix_same_class(a, b);
+            const uint32_t bal = __ballot_sync(0xffffffffu, v);
+            if (v) {
+                const int64_t o = w + __popc(bal & ((1u << lane) - 1u));
+                pk[o] = ((unsigned long long)c << 32) | ix_pair_key(a, b);
+                pv[o] = (uint32_t)i;
+            }
+            w += __popc(bal);
+        }
+    }
+}
+// exclusive scan of int32 counts into int64 offsets (single CTA; n is the number of chunks / blocks)
+static __global__ void __launch_bounds__(1024) k_ix_scan(const int32_t* __restrict__ cnt, int64_t* __restrict__ off, int64_t n) {
+    __shared__ long long warp_tot[32];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t i = base + threadIdx.x;
+        long long v = i < n ? cnt[i] : 0, x = v;
+        for (int d = 1; d < 32; d <<= 1) { long long y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        long long before = carry;
+        for (int w = 0; w < warp; w++) before += warp_tot[w];
+        if (i < n) off[i] = before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) off[n] = carry;
+}
+
+// ---- K2c: run heads of equal keys.  Blocks of IX_HEAD_TILE postings: count heads, scan the block counts, write.
+#define IX_HEAD_TILE 4096
+__global__ void __launch_bounds__(256) k_ix_head_count(const unsigned long long* __restrict__ pk, int64_t n, int32_t* __restrict__ blk_cnt) {
+    __shared__ int s_cnt;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * IX_HEAD_TILE;
+    int c = 0;
+    for (int i = threadIdx.x; i < IX_HEAD_TILE; i += 256) {
+        const int64_t g = base + i;
+        if (g < n && (g == 0 || (uint32_t)pk[g] != (uint32_t)pk[g - 1])) c++;
+    }
+    for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (threadIdx.x == 0) blk_cnt[blockIdx.x] = s_cnt;
+}
+__global__ void __launch_bounds__(256) k_ix_head_write(const unsigned long long* __restrict__ pk, int64_t n, const int64_t* __restrict__ blk_off,
+                                                        uint32_t* __restrict__ ukeys, int64_t* __restrict__ uoff) {
+    __shared__ int s_warp[8];
+    const int64_t base = (int64_t)blockIdx.x * IX_HEAD_TILE;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int64_t w = blk_off[blockIdx.x];
+    for (int i0 = 0; i0 < IX_HEAD_TILE; i0 += 256) {                 // ordered: 256 consecutive postings per step
+        const int64_t g = base + i0 + threadIdx.x;
+        const bool head = g < n && (g == 0 || (uint32_t)pk[g] != (uint32_t)pk[g - 1]);
+        const uint32_t bal = __ballot_sync(0xffffffffu, head);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        int before = 0, total = 0;
+        for (int k = 0; k < 8; k++) { if (k < warp) before += s_warp[k]; total += s_warp[k]; }
+        if (head) {
+            const int64_t o = w + before + __popc(bal & ((1u << lane) - 1u));
+            ukeys[o] = (uint32_t)pk[g]; uoff[o] = g;
+        }
+        w += total;
+        __syncthreads();
+    }
+}
+
+extern "C" void dvb_chunk_index_free(dvb_index* ix);
+
+// ---- K3a: per term, the rarest indexed pair
+__global__ void __launch_bounds__(256) k_ix_plan(const uint16_t* __restrict__ term_sym, const int32_t* __restrict__ term_off, int32_t n_terms,
+                                                  const uint32_t* __restrict__ ukeys, const int64_t* __restrict__ uoff, int64_t n_keys,
+                                                  int64_t* __restrict__ plan_lo, int64_t* __restrict__ plan_hi, int32_t* __restrict__ plan_j, int32_t* __restrict__ err) {
+    for (int32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_terms; t += gridDim.x * blockDim.x) {
+        const uint16_t* ts = term_sym + term_off[t];
+        const int32_t L = term_off[t + 1] - term_off[t];
+        int64_t best_lo = 0, best_hi = 0; int32_t best_j = -1; int64_t best_df = -1;
+        bool usable = false, bad = L < 2;
+        for (int32_t j = 0; j < L; j++) bad |= ts[j] == 0;
+        for (int32_t j = 0; j + 1 < L && !bad; j++) {
+            if (!ix_same_class(ts[j], ts[j + 1])) continue;
+            usable = true;
+            const uint32_t key = ix_pair_key(ts[j], ts[j + 1]);
+            int64_t lo = 0, hi = n_keys;
+            while (lo < hi) { const int64_t m = (lo + hi) >> 1; if (ukeys[m] < key) lo = m + 1; else hi = m; }
+            int64_t a = 0, b = 0;
+            if (lo < n_keys && ukeys[lo] == key) { a = uoff[lo]; b = uoff[lo + 1]; }
+            if (best_df < 0 || b - a < best_df) { best_df = b - a; best_lo = a; best_hi = b; best_j = j; }
+            if (best_df == 0) break;                              // a pair that occurs nowhere: the term occurs nowhere
+        }
+        if (bad || !usable) atomicExch(err, 1);                   // not a term of the reference's extractor
+        plan_lo[t] = best_lo; plan_hi[t] = best_hi; plan_j[t] = best_j < 0 ? 0 : best_j;
+    }
+}
+
+// ---- K3b: one warp per term walks its posting list
+__global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* __restrict__ term_sym, const int32_t* __restrict__ term_off,
+                                                   const int32_t* __restrict__ query_term_off, int32_t q0, int32_t q1,
+                                                   const int64_t* __restrict__ plan_lo, const int64_t* __restrict__ plan_hi, const int32_t* __restrict__ plan_j,
+                                                   int32_t* __restrict__ score /* [q1 - q0][n_chunks] */) {
+    const int lane = threadIdx.x & 31;
+    const int32_t t_begin = query_term_off[q0], t_end = query_term_off[q1];
+    for (int32_t t = t_begin + (int32_t)(blockIdx.x * 8 + (threadIdx.x >> 5)); t < t_end; t += (int32_t)gridDim.x * 8) {
+        int32_t a = q0, b = q1;                                    // query of term t: last q with query_term_off[q] <= t
+        while (b - a > 1) { const int32_t m = (a + b) >> 1; if (query_term_off[m] <= t) a = m; else b = m; }
+        int32_t* row = score + (int64_t)(a - q0) * ix.n_chunks;
+        const uint16_t* ts = term_sym + term_off[t];
+        const int32_t L = term_off[t + 1] - term_off[t], j = plan_j[t];
+        const int64_t lo = plan_lo[t], hi = plan_hi[t];
+        int64_t cur = -1; int32_t cnt = 0, last_end = 0;
+        for (int64_t p0 = lo; p0 < hi; p0 += 32) {
+            const int64_t p = p0 + lane;
+            int64_t chunk = 0; int32_t start = 0; bool match = false;
+            if (p < hi) {
+                chunk = (int64_t)(ix.pk[p] >> 32); start = (int32_t)ix.pv[p] - j;
+                if (start >= 0 && start + L <= ix.sym_cnt[chunk]) {
+                    const uint16_t* s = ix.sym + ix.sym_off[chunk] + start;
+                    match = true;
+                    for (int32_t d = 0; d < L && match; d++) match = s[d] == ts[d];
+                }
+            }
+            uint32_t bal = __ballot_sync(0xffffffffu, match);
+            while (bal) {                                          // greedy, left to right: non-overlapping == str.count
+                const int src = __ffs(bal) - 1; bal &= bal - 1;
+                const int64_t cb = __shfl_sync(0xffffffffu, chunk, src);
+                const int32_t sb = __shfl_sync(0xffffffffu, start, src);
+                if (cb != cur) {
+                    if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);
+                    cur = cb; cnt = 0; last_end = -2147483647;
+                }
+                if (sb >= last_end) { cnt++; last_end = sb + L; }
+            }
+        }
+        if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+#define IX_CUDA(ctx, idx, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
+    dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e__), #expr); dvb_chunk_index_free(idx); cudaGetLastError(); \
+    return e__ == cudaErrorMemoryAllocation ? DVB_E_NOMEM : DVB_E_CUDA; } } while (0)
+
+extern "C" void dvb_chunk_index_free(dvb_index* ix) {
+    if (!ix) return;
+    cudaSetDevice(ix->device);
+    void* ptrs[] = { ix->sym, ix->sym_off, ix->sym_cnt, ix->pk, ix->pv, ix->ukeys, ix->uoff };
+    for (void* p : ptrs) if (p) cudaFree(p);
+    delete ix;
+}
+
+extern "C" int32_t dvb_chunk_index_stats(const dvb_index* ix, int64_t* out6) {
+    if (!ix || !out6) return DVB_E_INVALID;
+    out6[0] = ix->n_chunks; out6[1] = ix->n_bytes; out6[2] = ix->n_post; out6[3] = ix->n_keys;
+    out6[4] = 2 * ix->n_bytes + 12 * ix->n_chunks + 8 + 12 * ix->n_post + 12 * ix->n_keys + 8;       // resident device bytes
+    out6[5] = ix->device;
+    return DVB_OK;
+}
+
+extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_chunks, dvb_index** out) {
+    if (!ctx || !out || n_chunks < 0 || !off || n_chunks >= (1LL << 32)) { dvb_set_err(ctx, "dvb_chunk_index_build: invalid argument%s%s"); return DVB_E_INVALID; }
+    *out = nullptr;
+    dvb_scope sc(ctx);
+    cudaStream_t st = sc.stream();
+    dvb_index* ix = new dvb_index();
+    ix->device = ctx->device; ix->n_chunks = n_chunks;
+    std::vector<int64_t> hoff((size_t)n_chunks + 1);
+    if (mem == DVB_MEM_HOST) memcpy(hoff.data(), off, 8 * (size_t)(n_chunks + 1));
+    else { IX_CUDA(ctx, ix, cudaMemcpyAsync(hoff.data(), off, 8 * (size_t)(n_chunks + 1), cudaMemcpyDeviceToHost, st)); IX_CUDA(ctx, ix, cudaStreamSynchronize(st)); }
+    const int64_t o0 = hoff[0];
+    for (int64_t c = 0; c <= n_chunks; c++) hoff[c] -= o0;
+    for (int64_t c = 0; c < n_chunks; c++) if (hoff[c + 1] < hoff[c] || hoff[c + 1] - hoff[c] > 0x7fffffffLL / 2) {
+        dvb_set_err(ctx, "dvb_chunk_index_build: bad offsets%s%s"); dvb_chunk_index_free(ix); return DVB_E_INVALID; }
+    const int64_t nb = hoff[n_chunks];
+    ix->n_bytes = nb;
+    uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr;
+    unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
+    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFree(p); };
+#define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { drop(); IX_CUDA(ctx, ix, e2__); } } while (0)
+    IX_TRY(cudaMalloc(&ix->sym, 2 * (size_t)nb + 64));
+    IX_TRY(cudaMalloc(&ix->sym_off, 8 * (size_t)(n_chunks + 1)));
+    IX_TRY(cudaMalloc(&ix->sym_cnt, 4 * (size_t)n_chunks + 4));
+    IX_TRY(cudaMemcpyAsync(ix->sym_off, hoff.data(), 8 * (size_t)(n_chunks + 1), cudaMemcpyHostToDevice, st));
+    const bool timing = ctx->timing.load() != 0;
+    if (timing) IX_TRY(cudaEventRecord(sc.l->ev0, st));
+    if (n_chunks > 0) {
+        const uint8_t* d_utf8 = utf8 + o0;
+        if (mem == DVB_MEM_HOST) {
+            IX_TRY(cudaMalloc(&d_text, (size_t)nb + 64));
+            IX_TRY(cudaMemcpyAsync(d_text, utf8 + o0, (size_t)nb, cudaMemcpyHostToDevice, st));
+            d_utf8 = d_text;
+        }
+        // K1: symbols (sym_off doubles as the rebased byte offsets the symboliser reads)
+        dv_launch_symbolize(ctx, st, d_utf8, ix->sym_off, n_chunks, ix->sym, ix->sym_cnt);
+        // K2a: postings
+        IX_TRY(cudaMalloc(&d_pc, 4 * (size_t)n_chunks + 4));
+        IX_TRY(cudaMalloc(&d_po, 8 * (size_t)(n_chunks + 1)));
+        const int grid = (int)std::min<int64_t>((n_chunks + 7) / 8, (int64_t)ctx->num_sm * 16);
+        k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc);
+        k_ix_scan<<<1, 1024, 0, st>>>(d_pc, d_po, n_chunks);
+        int64_t n_post = 0;
+        IX_TRY(cudaMemcpyAsync(&n_post, d_po + n_chunks, 8, cudaMemcpyDeviceToHost, st));
+        IX_TRY(cudaStreamSynchronize(st));
+        ctx->launches += 2;
+        ix->n_post = n_post;
+        if (mem == DVB_MEM_HOST) { cudaFree(d_text); d_text = nullptr; }
+        if (n_post > 0) {
+            const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
+            IX_TRY(cudaMalloc(&ix->pk, 8 * (size_t)n_post)); IX_TRY(cudaMalloc(&ix->pv, 4 * (size_t)n_post));
+            IX_TRY(cudaMalloc(&t_pk, 8 * (size_t)n_post)); IX_TRY(cudaMalloc(&t_pv, 4 * (size_t)n_post));
+            IX_TRY(cudaMalloc(&d_hist, 4 * (size_t)(256 * nbk + 256)));
+            k_ix_emit<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_po, ix->pk, ix->pv);
+            ctx->launches += 1;
+            // K2b: stable sort by the 30 key bits (32 = 4 passes of 8)
+            int64_t l = 0;
+            const int which = dv_radix_sort_pairs(ix->pk, ix->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
+            ctx->launches += l;
+            if (which) { std::swap(ix->pk, t_pk); std::swap(ix->pv, t_pv); }
+            // K2c: segment heads
+            const int64_t nhb = (n_post + IX_HEAD_TILE - 1) / IX_HEAD_TILE;
+            IX_TRY(cudaMalloc(&d_bc, 4 * (size_t)nhb + 4)); IX_TRY(cudaMalloc(&d_bo, 8 * (size_t)(nhb + 1)));
+            k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bc);
+            k_ix_scan<<<1, 1024, 0, st>>>(d_bc, d_bo, nhb);
+            int64_t n_keys = 0;
+            IX_TRY(cudaMemcpyAsync(&n_keys, d_bo + nhb, 8, cudaMemcpyDeviceToHost, st));
+            IX_TRY(cudaStreamSynchronize(st));
+            ix->n_keys = n_keys;
+            IX_TRY(cudaMalloc(&ix->ukeys, 4 * (size_t)n_keys + 4)); IX_TRY(cudaMalloc(&ix->uoff, 8 * (size_t)(n_keys + 1)));
+            k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bo, ix->ukeys, ix->uoff);
+            IX_TRY(cudaMemcpyAsync(ix->uoff + n_keys, &n_post, 8, cudaMemcpyHostToDevice, st));
+            ctx->launches += 3;
+        }
+    }
+    if (timing) IX_TRY(cudaEventRecord(sc.l->ev1, st));
+    IX_TRY(cudaStreamSynchronize(st));
+    IX_TRY(cudaGetLastError());
+    if (timing) { float ms = 0.f; cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1); ctx->last_ms = ms; }
+    drop();
+#undef IX_TRY
+    *out = ix;
+    return DVB_OK;
+}
+
+extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32_t mem, const uint16_t* term_sym, const int32_t* term_off, int32_t n_terms,
+                                         const int32_t* query_term_off, int32_t nq, int64_t index_base, int32_t k,
+                                         int64_t* out_idx, int32_t* out_score, int32_t* out_n) {
+    if (!ctx || !ix || nq < 0 || n_terms < 0 || k < 1 || k > 32 || !term_off || !query_term_off || !out_idx || !out_score || !out_n ||
+        ix->device != ctx->device) { dvb_set_err(ctx, "dvb_chunk_index_topk: invalid argument (1 <= k <= 32, index of this device)%s%s"); return DVB_E_INVALID; }
+    if (nq == 0) return DVB_OK;
+    dvb_scope sc(ctx); dvb_io io(sc, mem);
+    const int64_t N = ix->n_chunks;
+    // terms: sizes come from the offsets
+    int32_t n_sym = 0;
+    if (mem == DVB_MEM_HOST) n_sym = term_off[n_terms];
+    else { DVB_CUDA(ctx, cudaMemcpyAsync(&n_sym, term_off + n_terms, 4, cudaMemcpyDeviceToHost, io.st)); DVB_CUDA(ctx, cudaStreamSynchronize(io.st)); }
+    std::vector<int32_t> h_qto((size_t)nq + 1);
+    if (mem == DVB_MEM_HOST) memcpy(h_qto.data(), query_term_off, 4 * (size_t)(nq + 1));
+    else { DVB_CUDA(ctx, cudaMemcpyAsync(h_qto.data(), query_term_off, 4 * (size_t)(nq + 1), cudaMemcpyDeviceToHost, io.st)); DVB_CUDA(ctx, cudaStreamSynchronize(io.st)); }
+    if (h_qto[0] != 0 || h_qto[nq] != n_terms) { dvb_set_err(ctx, "dvb_chunk_index_topk: query_term_off must span the terms%s%s"); return DVB_E_INVALID; }
+    // batch of queries sharing one dense score tile (<= 512 MB)
+    const int64_t budget = 512LL << 20;
+    const int32_t B = (int32_t)std::max<int64_t>(1, std::min<int64_t>(nq, N > 0 ? budget / (4 * N) : nq));
+    const int64_t n_split = dv_topk_splits(ctx, N, B);
+    size_t need = dvb_pad(4 * (size_t)B * (size_t)std::max<int64_t>(N, 1)) + dvb_pad(8 * (size_t)n_terms + 8) * 2 + dvb_pad(4 * (size_t)n_terms + 4)
+                + dvb_pad(4 * (size_t)B * n_split * k) + dvb_pad(8 * (size_t)B * n_split * k) + 4096;
+    if (mem == DVB_MEM_HOST) need += dvb_pad(2 * (size_t)n_sym + 2) + dvb_pad(4 * (size_t)n_terms + 4) + dvb_pad(4 * (size_t)nq + 4)
+                                   + dvb_pad(8 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq);
+    int32_t rc = sc.reserve(need); if (rc) return rc;
+    const uint16_t* d_ts = io.in(term_sym, (size_t)n_sym); const int32_t* d_to = io.in(term_off, (size_t)n_terms + 1);
+    const int32_t* d_qto = io.in(query_term_off, (size_t)nq + 1);
+    int64_t* d_oidx = io.out(out_idx, (size_t)nq * k); int32_t* d_osc = io.out(out_score, (size_t)nq * k); int32_t* d_on = io.out(out_n, (size_t)nq);
+    int64_t* d_lo = io.tmp<int64_t>((size_t)n_terms + 1); int64_t* d_hi = io.tmp<int64_t>((size_t)n_terms + 1); int32_t* d_j = io.tmp<int32_t>((size_t)n_terms + 1);
+    int32_t* d_err = io.tmp<int32_t>(1);
+    int32_t* d_score = io.tmp<int32_t>((size_t)B * (size_t)std::max<int64_t>(N, 1));
+    int32_t* d_ps = io.tmp<int32_t>((size_t)B * n_split * k); int64_t* d_pi = io.tmp<int64_t>((size_t)B * n_split * k);
+    rc = io.check(ctx); if (rc) return rc;
+    DVB_CUDA(ctx, cudaMemsetAsync(d_err, 0, 4, io.st));
+    const bool timing = ctx->timing.load() != 0;
+    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
+    if (n_terms > 0) {
+        k_ix_plan<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_ts, d_to, n_terms, ix->ukeys, ix->uoff, ix->n_keys, d_lo, d_hi, d_j, d_err);
+        ctx->launches += 1;
+    }
+    for (int32_t q0 = 0; q0 < nq; q0 += B) {
+        const int32_t q1 = std::min(nq, q0 + B), nb = q1 - q0;
+        if (N > 0) {
+            DVB_CUDA(ctx, cudaMemsetAsync(d_score, 0, 4 * (size_t)nb * (size_t)N, io.st));
+            const int32_t nt = h_qto[q1] - h_qto[q0];
+            if (nt > 0) {
+                k_ix_score<<<std::min((nt + 7) / 8, ctx->num_sm * 16), 256, 0, io.st>>>(*ix, d_ts, d_to, d_qto, q0, q1, d_lo, d_hi, d_j, d_score);
+                ctx->launches += 1;
+            }
+        }
+        dv_topk_device(ctx, io.st, d_score, nullptr, N, nb, index_base, k, dv_topk_splits(ctx, N, nb), d_ps, d_pi,
+                       d_oidx + (size_t)q0 * k, d_osc + (size_t)q0 * k, d_on + q0);
+    }
+    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
+    int32_t h_err = 0;
+    DVB_CUDA(ctx, cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, io.st));
+    rc = io.finish(ctx);
+    if (rc == DVB_OK && timing) { float ms = 0.f; cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1); ctx->last_ms = ms; }
+    if (rc == DVB_OK && h_err) { dvb_set_err(ctx, "dvb_chunk_index_topk: a term has < 2 symbols, a separator, or no same-class pair%s%s"); return DVB_E_INVALID; }
+    return rc;
+}

@@ -157,3 +157,10 @@ def sharded_gate(gate, candidates: Sequence[str], history: Sequence[str], thresh
     if not gather:
         return local
     return np.concatenate([np.asarray(p, np.int64) for p in gather_objects(local, group)])
+
+
+def sharded_index_topk(index, queries_terms: Sequence[Sequence[str]], k: int, group=None, topk_fn: Optional[Callable] = None):
+    """Config 3/5: every rank holds a ChunkIndex over its contiguous shard (index.index_base = first global chunk index).
+    Local indexed top-k -> one all-gather of nq x k candidates -> merge (dvb_topk).  Identical on every rank."""
+    li, ls, _ln = index.topk(queries_terms, k)
+    return merge_topk(li, ls, k, group=group, ctx=index.ctx, topk_fn=topk_fn)

@@ -290,3 +290,52 @@ def select_reference_material_context(doc: dict, *, query_text: str = "", max_ch
             break
     return "\n\n".join(parts).strip(), {"mode": "chunk_selection", "selected_chunks": meta_sel, "chunk_count": len(chunks),
                                        "query_terms": terms[:12]}
+
+
+# ----------------------------------------------------------------------------- bulk path: resident inverted index (configs 3/5)
+class ChunkIndex:
+    """Device-resident positional inverted index over a chunk corpus (csrc/index.cu).  Same results as
+    chunk_scores() + topk() — exact non-overlapping counts, (score desc, index asc), positives only — for many
+    queries against many chunks.  One index per rank holds that rank's contiguous shard; `index_base` makes the
+    returned indices global so shards merge with parallel.merge_topk()."""
+
+    def __init__(self, chunk_texts: Optional[Sequence[str]] = None, *, packed=None, index_base: int = 0, ctx=None, device_ptrs=None):
+        import ctypes as C
+        self.ctx = ctx or _lib.Context.get()
+        self.index_base = int(index_base)
+        self._h = C.c_void_p()
+        if device_ptrs is not None:                      # (utf8_ptr, off_ptr, n): corpus already resident in HBM
+            up, op, n = device_ptrs
+            rc = self.ctx.lib.dvb_chunk_index_build(self.ctx.handle, _lib.MEM_DEVICE, up, op, int(n), C.byref(self._h))
+        else:
+            data, off = packed if packed is not None else pack_texts(chunk_texts or [])
+            rc = self.ctx.lib.dvb_chunk_index_build(self.ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), len(off) - 1, C.byref(self._h))
+        self.ctx.check(rc, "dvb_chunk_index_build")
+        self.build_ms = self.ctx.last_kernel_ms
+
+    def stats(self) -> dict:
+        out = np.zeros(6, np.int64)
+        self.ctx.check(self.ctx.lib.dvb_chunk_index_stats(self._h, ptr(out)), "dvb_chunk_index_stats")
+        return dict(zip(("n_chunks", "text_bytes", "postings", "pair_keys", "device_bytes", "device"), map(int, out)))
+
+    def topk(self, queries_terms: Sequence[Sequence[str]], k: int):
+        """(idx[nq, k] global indices or -1, score[nq, k], n_valid[nq])"""
+        tsym, toff, qoff = terms_to_symbols(queries_terms)
+        nq = len(queries_terms)
+        oi = np.full((max(nq, 1), k), -1, np.int64); os_ = np.zeros((max(nq, 1), k), np.int32); on = np.zeros(max(nq, 1), np.int32)
+        if nq:
+            rc = self.ctx.lib.dvb_chunk_index_topk(self.ctx.handle, self._h, _lib.MEM_HOST, ptr(tsym), ptr(toff), len(toff) - 1, ptr(qoff), nq,
+                                                   self.index_base, int(k), ptr(oi), ptr(os_), ptr(on))
+            self.ctx.check(rc, "dvb_chunk_index_topk")
+        return oi[:nq], os_[:nq], on[:nq]
+
+    def close(self):
+        if self._h:
+            self.ctx.lib.dvb_chunk_index_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

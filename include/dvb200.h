@@ -182,6 +182,23 @@ int32_t dvb_contains(dvb_ctx* ctx, int32_t mem, const uint8_t* hay_utf8, const i
                      const uint8_t* needle_utf8, const int64_t* needle_off, const int32_t* needle_hay, int64_t n_needles,
                      uint8_t* out_bits);
 
+/* ---- a7 at corpus scale (BASELINE configs 3/5)  replaces: the scoring loop + top-k of select_reference_material_context
+ *      (web/server.py:32073-32087) for many queries over a resident chunk corpus.
+ * dvb_chunk_index_build symbolises the chunks and builds a positional inverted index over adjacent same-class symbol
+ * pairs (radix sort + segmented reduce); the index lives in device memory owned by the returned handle (free it with
+ * dvb_chunk_index_free; the caller's text is not retained).  dvb_chunk_index_topk scores term lists (symbol strings as
+ * for dvb_chunk_scores; every term must be >= 2 symbols of one class, which is what web/server.py:32039-32049 emits)
+ * exactly — non-overlapping substring counts, summed per query — and returns per query the k (<= 32) best chunks with
+ * score > 0 under (score desc, index asc), index = index_base + chunk position (so shards of a corpus can be merged
+ * with dvb_topk).  stats: out6 = { n_chunks, text bytes, postings, distinct pair keys, resident device bytes, device }. */
+typedef struct dvb_index dvb_index;
+int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_chunks, dvb_index** out);
+void    dvb_chunk_index_free(dvb_index* index);
+int32_t dvb_chunk_index_stats(const dvb_index* index, int64_t* out6);
+int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* index, int32_t mem, const uint16_t* term_sym, const int32_t* term_off, int32_t n_terms,
+                             const int32_t* query_term_off, int32_t nq, int64_t index_base, int32_t k,
+                             int64_t* out_idx, int32_t* out_score, int32_t* out_n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,85 @@
+"""Bulk a7 (configs 3/5): the positional inverted index gives the same scores / top-k as the scan scorer and the oracle."""
+import numpy as np
+import pytest
+
+from test_parallel import make_corpus, reference_picks
+
+
+def _ref_topk(chunks, terms, k, base=0):
+    scores = [sum(c.lower().count(t) for t in terms) for c in chunks]
+    ranked = sorted((i for i in range(len(chunks)) if scores[i] > 0), key=lambda i: (-scores[i], i))[:k]
+    return [i + base for i in ranked], [scores[i] for i in ranked]
+
+
+@pytest.mark.gpu
+def test_gpu_index_topk_matches_python_count(gpu_ctx):
+    from deep_vision_b200 import reference_material as rm
+    chunks, queries = make_corpus(n_chunks=777, nq=25, seed=4)
+    chunks += ["aaaa", "AAAAA_aaaa", "abababab x abab", "离线离线离线离线离", "x" * 3000 + "审批" * 700, "", "   ", "İstanbul Kelvin K"]
+    queries += [["aa"], ["abab", "ab"], ["离线离", "离线"], ["审批", "审批审批审批"], ["zzzz"], ["aaaa", "aa", "a_"], ["istanbul", "kelvin"], ["st"]]
+    ix = rm.ChunkIndex(chunks, index_base=1000, ctx=gpu_ctx)
+    st = ix.stats()
+    assert st["n_chunks"] == len(chunks) and st["postings"] > 0 and st["pair_keys"] > 0
+    idx, sc, nv = ix.topk(queries, 8)
+    for q, terms in enumerate(queries):
+        wi, ws = _ref_topk(chunks, terms, 8, base=1000)
+        assert idx[q][: nv[q]].tolist() == wi, (q, terms)
+        assert sc[q][: nv[q]].tolist() == ws
+    # same answer as the scan path
+    full = rm.chunk_scores(chunks, queries, ctx=gpu_ctx)
+    si, ss, sn = rm.topk(full, 8, index_base=1000, ctx=gpu_ctx)
+    assert np.array_equal(si, idx) and np.array_equal(ss, sc) and np.array_equal(sn, nv)
+    ix.close()
+    empty = rm.ChunkIndex([], ctx=gpu_ctx)
+    ei, es, en = empty.topk([["离线"]], 4)
+    assert en.tolist() == [0] and ei.tolist() == [[-1] * 4]
+    with pytest.raises(Exception):
+        ix2 = rm.ChunkIndex(["abc"], ctx=gpu_ctx)
+        import deep_vision_b200.reference_material as m
+        tsym = np.asarray([0x8001], np.uint16)                     # a 1-symbol term is not something the reference emits
+        ix2.ctx.check(ix2.ctx.lib.dvb_chunk_index_topk(ix2.ctx.handle, ix2._h, 0, m.ptr(tsym), m.ptr(np.asarray([0, 1], np.int32)), 1,
+                                                      m.ptr(np.asarray([0, 1], np.int32)), 1, 0, 4, m.ptr(np.zeros(4, np.int64)),
+                                                      m.ptr(np.zeros(4, np.int32)), m.ptr(np.zeros(1, np.int32))), "topk")
+
+
+@pytest.mark.gpu
+def test_gpu_index_shards_merge_to_single_shard_result(gpu_ctx):
+    from deep_vision_b200 import parallel, reference_material as rm
+    chunks, queries = make_corpus(n_chunks=2053, nq=21, seed=8)
+    queries = [q for q in queries]
+    one = rm.ChunkIndex(chunks, ctx=gpu_ctx)
+    wi, ws, wn = one.topk(queries, 8)
+    for world in (2, 4, 8):
+        li, ls = [], []
+        for r in range(world):
+            lo, hi = parallel.shard_range(len(chunks), r, world)
+            ix = rm.ChunkIndex(chunks[lo:hi], index_base=lo, ctx=gpu_ctx)
+            i, s, _n = ix.topk(queries, 8)
+            li.append(i); ls.append(s); ix.close()
+        gi, gs, gn = rm.topk(np.concatenate(ls, axis=1), 8, index=np.concatenate(li, axis=1), ctx=gpu_ctx)
+        assert np.array_equal(gi, wi) and np.array_equal(gs, ws) and np.array_equal(gn, wn)
+
+
+@pytest.mark.gpu
+def test_gpu_index_config3_sample_vs_oracle(gpu_ctx, oracle):
+    """config-3 shaped sample: 20k synthetic 512-char chunks, 300 queries half-copied from chunks, top-8."""
+    from deep_vision_b200 import reference_material as rm, synth
+    n, nq = 20000, 300
+    data, off = synth.make_texts(n, 512, seed=123)
+    raw = data.tobytes()
+    rng = np.random.default_rng(5)
+    queries = []
+    texts = {}
+    for q in range(nq):
+        c = int(rng.integers(0, n))
+        t = texts.setdefault(c, raw[off[c]:off[c + 1]].decode("utf-8"))
+        a = int(rng.integers(0, 480))
+        queries.append(rm._tokenize_reference_material_query(t[a:a + int(rng.integers(15, 30))] + " " + t[5:12]))
+    ix = rm.ChunkIndex(packed=(data, off), ctx=gpu_ctx)
+    idx, sc, nv = ix.topk(queries, 8)
+    for q in range(0, nq, 7):                                      # oracle: exact counts over the whole corpus (C, threaded)
+        s = oracle.chunk_scores(None, queries[q], n_threads=8, packed=(data, off))
+        wi, ws = oracle.topk(s, 8)
+        assert idx[q][: nv[q]].tolist() == wi.tolist() and sc[q][: nv[q]].tolist() == ws.tolist()
+    st = ix.stats()
+    assert st["postings"] > n * 300
