@@ -7,7 +7,7 @@
 //   K1  symbolise every chunk (chunk.cu k_symbolize: decode, CPython lower(), class map) -> u16 symbols, resident
 //   K2a every adjacent same-class symbol pair (CJK-CJK or ASCII-ASCII) becomes a posting
 //         key = pair id (30 bits), payload = (chunk, position of the pair's first symbol)
-//       emitted chunk by chunk, position by position
+//       (+ the symbol that follows the pair, a free trigram filter at query time); emitted chunk by chunk, position by position
 //   K2b stable LSD radix sort by the 30 key bits only (sort.cuh; 4 passes): postings of one key stay ordered by
 //       (chunk, position) because that is the emission order
 //   K2c segmented reduce: run heads of equal keys -> distinct key list + CSR offsets (the postings "document frequency")
@@ -21,6 +21,7 @@
 // of one class, so each term has at least one indexed pair.
 #include "common.cuh"
 #include "sort.cuh"
+#include <stdlib.h>
 
 struct dvb_index {
     int device = 0;
@@ -40,14 +41,14 @@ __device__ __forceinline__ uint32_t ix_pair_key(uint32_t a, uint32_t b) { return
 
 // ---- K2a: count, then emit postings (one warp per chunk)
 __global__ void __launch_bounds__(256) k_ix_count(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
-                                                   int64_t n_chunks, int32_t* __restrict__ pair_cnt) {
+                                                   int64_t n_chunks, int32_t* __restrict__ pair_cnt, int32_t* __restrict__ err) {
     const int lane = threadIdx.x & 31;
     for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_chunks; c += (int64_t)gridDim.x * 8) {
         const uint16_t* s = sym + sym_off[c]; const int32_t m = sym_cnt[c];
         int cnt = 0;
         for (int32_t i = lane; i + 1 < m; i += 32) cnt += ix_same_class(s[i], s[i + 1]) ? 1 : 0;
         for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
-        if (lane == 0) pair_cnt[c] = cnt;
+        if (lane == 0) { pair_cnt[c] = cnt; if (m > 65535) atomicExch(err, 1); }
     }
 }
 __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
@@ -58,14 +59,14 @@ __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sy
         int64_t w = post_off[c];
         for (int32_t b0 = 0; b0 + 1 < m; b0 += 32) {
             const int32_t i = b0 + lane;
-            uint32_t a = 0, b = 0;
-            if (i + 1 < m) { a = s[i]; b = s[i + 1]; }
+            uint32_t a = 0, b = 0, nx = 0;
+            if (i + 1 < m) { a = s[i]; b = s[i + 1]; if (i + 2 < m) nx = s[i + 2]; }
             const bool v = ix_same_class(a, b);
             const uint32_t bal = __ballot_sync(0xffffffffu, v);
             if (v) {
                 const int64_t o = w + __popc(bal & ((1u << lane) - 1u));
                 pk[o] = ((unsigned long long)c << 32) | ix_pair_key(a, b);
-                pv[o] = (uint32_t)i;
+                pv[o] = (uint32_t)i | (nx << 16);                  // position | the symbol AFTER the pair (0 = none / separator)
             }
             w += __popc(bal);
         }
@@ -154,41 +155,67 @@ __global__ void __launch_bounds__(256) k_ix_plan(const uint16_t* __restrict__ te
             while (lo < hi) { const int64_t m = (lo + hi) >> 1; if (ukeys[m] < key) lo = m + 1; else hi = m; }
             int64_t a = 0, b = 0;
             if (lo < n_keys && ukeys[lo] == key) { a = uoff[lo]; b = uoff[lo + 1]; }
-            if (best_df < 0 || b - a < best_df) { best_df = b - a; best_lo = a; best_hi = b; best_j = j; }
-            if (best_df == 0) break;                              // a pair that occurs nowhere: the term occurs nowhere
+            // a pair followed by another term symbol is filtered by the posting's look-ahead symbol (~1/50 survive): weigh it
+            const int64_t cost = (j + 2 < L) ? (b - a + 31) / 32 : (b - a);
+            if (best_df < 0 || cost < best_df) { best_df = cost; best_lo = a; best_hi = b; best_j = j; }
+            if (b == a) break;                                    // a pair that occurs nowhere: the term occurs nowhere
         }
         if (bad || !usable) atomicExch(err, 1);                   // not a term of the reference's extractor
         plan_lo[t] = best_lo; plan_hi[t] = best_hi; plan_j[t] = best_j < 0 ? 0 : best_j;
     }
 }
 
-// ---- K3b: one warp per term walks its posting list
+// ---- K3b: posting lists are cut into work items of <= IX_ITEM postings, one warp each, so that a frequent pair
+// (10^5..10^6 postings) does not serialise on one warp.  An item owns the CHUNKS that start inside its range: it skips the
+// leading postings of a chunk the previous item started, and runs past its end to finish its last chunk (the greedy
+// non-overlapping count is per chunk, so chunks must not be split).
+#define IX_ITEM 2048
+__global__ void __launch_bounds__(256) k_ix_items(const int64_t* __restrict__ plan_lo, const int64_t* __restrict__ plan_hi, int32_t n_terms, int32_t* __restrict__ n_items) {
+    for (int32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_terms; t += gridDim.x * blockDim.x)
+        n_items[t] = (int32_t)((plan_hi[t] - plan_lo[t] + IX_ITEM - 1) / IX_ITEM);
+}
 __global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* __restrict__ term_sym, const int32_t* __restrict__ term_off,
                                                    const int32_t* __restrict__ query_term_off, int32_t q0, int32_t q1,
                                                    const int64_t* __restrict__ plan_lo, const int64_t* __restrict__ plan_hi, const int32_t* __restrict__ plan_j,
-                                                   int32_t* __restrict__ score /* [q1 - q0][n_chunks] */) {
+                                                   const int64_t* __restrict__ item_off, int32_t* __restrict__ score /* [q1 - q0][n_chunks] */) {
     const int lane = threadIdx.x & 31;
     const int32_t t_begin = query_term_off[q0], t_end = query_term_off[q1];
-    for (int32_t t = t_begin + (int32_t)(blockIdx.x * 8 + (threadIdx.x >> 5)); t < t_end; t += (int32_t)gridDim.x * 8) {
+    const int64_t w_begin = item_off[t_begin], w_end = item_off[t_end];
+    for (int64_t w = w_begin + (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < w_end; w += (int64_t)gridDim.x * 8) {
+        int32_t ta = t_begin, tb = t_end;                          // term of item w: last t with item_off[t] <= w
+        while (tb - ta > 1) { const int32_t m = (ta + tb) >> 1; if (item_off[m] <= w) ta = m; else tb = m; }
+        const int32_t t = ta;
         int32_t a = q0, b = q1;                                    // query of term t: last q with query_term_off[q] <= t
         while (b - a > 1) { const int32_t m = (a + b) >> 1; if (query_term_off[m] <= t) a = m; else b = m; }
         int32_t* row = score + (int64_t)(a - q0) * ix.n_chunks;
         const uint16_t* ts = term_sym + term_off[t];
         const int32_t L = term_off[t + 1] - term_off[t], j = plan_j[t];
         const int64_t lo = plan_lo[t], hi = plan_hi[t];
+        const int64_t r_lo = lo + (w - item_off[t]) * IX_ITEM, r_hi = min(hi, r_lo + IX_ITEM);
+        const bool use_next = j + 2 < L;
+        const uint32_t next_sym = use_next ? ts[j + 2] : 0u;
+        const int64_t skip_chunk = r_lo > lo ? (int64_t)(ix.pk[r_lo - 1] >> 32) : -1;      // owned by the previous item
+        const int64_t last_chunk = (int64_t)(ix.pk[r_hi - 1] >> 32);                       // ours to finish
+        if (r_lo > lo && skip_chunk == last_chunk) continue;       // the whole item lies inside a chunk the previous item owns
         int64_t cur = -1; int32_t cnt = 0, last_end = 0;
-        for (int64_t p0 = lo; p0 < hi; p0 += 32) {
+        bool more = true;
+        for (int64_t p0 = r_lo; p0 < hi && more; p0 += 32) {
             const int64_t p = p0 + lane;
-            int64_t chunk = 0; int32_t start = 0; bool match = false;
+            int64_t chunk = -2; int32_t start = 0; bool match = false, beyond = false;
             if (p < hi) {
-                chunk = (int64_t)(ix.pk[p] >> 32); start = (int32_t)ix.pv[p] - j;
-                if (start >= 0 && start + L <= ix.sym_cnt[chunk]) {
+                const uint32_t v = ix.pv[p];
+                chunk = (int64_t)(ix.pk[p] >> 32); start = (int32_t)(v & 0xFFFFu) - j;
+                beyond = p >= r_hi && chunk != last_chunk;          // first posting of a chunk the next item owns
+                if (!beyond && chunk != skip_chunk && (!use_next || (v >> 16) == next_sym) && start >= 0 && start + L <= ix.sym_cnt[chunk]) {
                     const uint16_t* s = ix.sym + ix.sym_off[chunk] + start;
                     match = true;
                     for (int32_t d = 0; d < L && match; d++) match = s[d] == ts[d];
                 }
             }
+            // postings are ordered by chunk: everything after the first `beyond` posting is beyond too
+            const uint32_t bey = __ballot_sync(0xffffffffu, beyond);
             uint32_t bal = __ballot_sync(0xffffffffu, match);
+            if (bey) { bal &= (1u << (__ffs(bey) - 1)) - 1u; more = false; }
             while (bal) {                                          // greedy, left to right: non-overlapping == str.count
                 const int src = __ffs(bal) - 1; bal &= bal - 1;
                 const int64_t cb = __shfl_sync(0xffffffffu, chunk, src);
@@ -264,11 +291,15 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
         IX_TRY(cudaMalloc(&d_pc, 4 * (size_t)n_chunks + 4));
         IX_TRY(cudaMalloc(&d_po, 8 * (size_t)(n_chunks + 1)));
         const int grid = (int)std::min<int64_t>((n_chunks + 7) / 8, (int64_t)ctx->num_sm * 16);
-        k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc);
+        IX_TRY(cudaMemsetAsync(d_po, 0, 8, st));                   // d_po[0] doubles as the error flag until the scan overwrites it
+        k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc, reinterpret_cast<int32_t*>(d_po));
+        int32_t too_long = 0;
+        IX_TRY(cudaMemcpyAsync(&too_long, d_po, 4, cudaMemcpyDeviceToHost, st));
         k_ix_scan<<<1, 1024, 0, st>>>(d_pc, d_po, n_chunks);
         int64_t n_post = 0;
         IX_TRY(cudaMemcpyAsync(&n_post, d_po + n_chunks, 8, cudaMemcpyDeviceToHost, st));
         IX_TRY(cudaStreamSynchronize(st));
+        if (too_long) { drop(); dvb_chunk_index_free(ix); dvb_set_err(ctx, "dvb_chunk_index_build: a chunk has more than 65535 characters%s%s"); return DVB_E_INVALID; }
         ctx->launches += 2;
         ix->n_post = n_post;
         if (mem == DVB_MEM_HOST) { cudaFree(d_text); d_text = nullptr; }
@@ -329,7 +360,7 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     const int64_t budget = 512LL << 20;
     const int32_t B = (int32_t)std::max<int64_t>(1, std::min<int64_t>(nq, N > 0 ? budget / (4 * N) : nq));
     const int64_t n_split = dv_topk_splits(ctx, N, B);
-    size_t need = dvb_pad(4 * (size_t)B * (size_t)std::max<int64_t>(N, 1)) + dvb_pad(8 * (size_t)n_terms + 8) * 2 + dvb_pad(4 * (size_t)n_terms + 4)
+    size_t need = dvb_pad(4 * (size_t)B * (size_t)std::max<int64_t>(N, 1)) + dvb_pad(8 * (size_t)n_terms + 16) * 3 + dvb_pad(4 * (size_t)n_terms + 4) * 2
                 + dvb_pad(4 * (size_t)B * n_split * k) + dvb_pad(8 * (size_t)B * n_split * k) + 4096;
     if (mem == DVB_MEM_HOST) need += dvb_pad(2 * (size_t)n_sym + 2) + dvb_pad(4 * (size_t)n_terms + 4) + dvb_pad(4 * (size_t)nq + 4)
                                    + dvb_pad(8 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq);
@@ -339,6 +370,7 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     int64_t* d_oidx = io.out(out_idx, (size_t)nq * k); int32_t* d_osc = io.out(out_score, (size_t)nq * k); int32_t* d_on = io.out(out_n, (size_t)nq);
     int64_t* d_lo = io.tmp<int64_t>((size_t)n_terms + 1); int64_t* d_hi = io.tmp<int64_t>((size_t)n_terms + 1); int32_t* d_j = io.tmp<int32_t>((size_t)n_terms + 1);
     int32_t* d_err = io.tmp<int32_t>(1);
+    int32_t* d_ni = io.tmp<int32_t>((size_t)n_terms + 1); int64_t* d_io = io.tmp<int64_t>((size_t)n_terms + 2);
     int32_t* d_score = io.tmp<int32_t>((size_t)B * (size_t)std::max<int64_t>(N, 1));
     int32_t* d_ps = io.tmp<int32_t>((size_t)B * n_split * k); int64_t* d_pi = io.tmp<int64_t>((size_t)B * n_split * k);
     rc = io.check(ctx); if (rc) return rc;
@@ -347,7 +379,18 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
     if (n_terms > 0) {
         k_ix_plan<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_ts, d_to, n_terms, ix->ukeys, ix->uoff, ix->n_keys, d_lo, d_hi, d_j, d_err);
-        ctx->launches += 1;
+        k_ix_items<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_lo, d_hi, n_terms, d_ni);
+        k_ix_scan<<<1, 1024, 0, io.st>>>(d_ni, d_io, n_terms);
+        ctx->launches += 3;
+    }
+    if (getenv("DVB_IX_DEBUG") && n_terms > 0) {                  // posting volume the plan will visit (diagnostics only)
+        std::vector<int64_t> lo((size_t)n_terms), hi((size_t)n_terms);
+        cudaMemcpyAsync(lo.data(), d_lo, 8 * (size_t)n_terms, cudaMemcpyDeviceToHost, io.st);
+        cudaMemcpyAsync(hi.data(), d_hi, 8 * (size_t)n_terms, cudaMemcpyDeviceToHost, io.st);
+        cudaStreamSynchronize(io.st);
+        int64_t tot = 0, mx = 0, big = 0;
+        for (int32_t t = 0; t < n_terms; t++) { const int64_t d = hi[t] - lo[t]; tot += d; mx = std::max(mx, d); big += d > 4096; }
+        fprintf(stderr, "[dvb ix] terms %d postings visited %lld max %lld terms>4096 %lld\n", n_terms, (long long)tot, (long long)mx, (long long)big);
     }
     for (int32_t q0 = 0; q0 < nq; q0 += B) {
         const int32_t q1 = std::min(nq, q0 + B), nb = q1 - q0;
@@ -355,7 +398,7 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
             DVB_CUDA(ctx, cudaMemsetAsync(d_score, 0, 4 * (size_t)nb * (size_t)N, io.st));
             const int32_t nt = h_qto[q1] - h_qto[q0];
             if (nt > 0) {
-                k_ix_score<<<std::min((nt + 7) / 8, ctx->num_sm * 16), 256, 0, io.st>>>(*ix, d_ts, d_to, d_qto, q0, q1, d_lo, d_hi, d_j, d_score);
+                k_ix_score<<<ctx->num_sm * 16, 256, 0, io.st>>>(*ix, d_ts, d_to, d_qto, q0, q1, d_lo, d_hi, d_j, d_io, d_score);
                 ctx->launches += 1;
             }
         }

@@ -83,3 +83,21 @@ def test_gpu_index_config3_sample_vs_oracle(gpu_ctx, oracle):
         assert idx[q][: nv[q]].tolist() == wi.tolist() and sc[q][: nv[q]].tolist() == ws.tolist()
     st = ix.stats()
     assert st["postings"] > n * 300
+
+
+@pytest.mark.gpu
+def test_gpu_index_work_items_do_not_split_chunks(gpu_ctx):
+    """Posting lists longer than one work item (2048 postings) with chunks straddling item boundaries and a
+    self-overlapping term: counts must still be per-chunk greedy (str.count)."""
+    from deep_vision_b200 import reference_material as rm
+    rng = np.random.default_rng(12)
+    chunks = []
+    for c in range(600):
+        n = int(rng.integers(1, 400))
+        chunks.append(("ab" * n) + ("x" if c % 3 else "") + ("ab" * int(rng.integers(0, 50))) + "离线" * int(rng.integers(0, 300)))
+    queries = [["abab"], ["ab"], ["ababab", "bab"], ["离线离线离", "线离"], ["abx"]]
+    ix = rm.ChunkIndex(chunks, ctx=gpu_ctx)
+    idx, sc, nv = ix.topk(queries, 32)
+    for q, terms in enumerate(queries):
+        wi, ws = _ref_topk(chunks, terms, 32)
+        assert idx[q][: nv[q]].tolist() == wi and sc[q][: nv[q]].tolist() == ws, terms

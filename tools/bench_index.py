@@ -1,0 +1,85 @@
+#!/usr/bin/env python3
+"""Config-3 style measurement: chunks indexed/s (dvb_chunk_index_build, corpus resident in HBM) and effective
+(query, chunk) pairs/s (dvb_chunk_index_topk), one process per GPU (torchrun for N > 1: contiguous shards + NCCL merge).
+  python tools/bench_index.py --chunks 1000000 --queries 100000 --k 8"""
+import argparse
+import json
+import os
+import sys
+import time
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import numpy as np
+import torch
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--chunks", type=int, default=1000000, help="global chunk count (sharded over ranks)")
+ap.add_argument("--chars", type=int, default=512)
+ap.add_argument("--queries", type=int, default=100000)
+ap.add_argument("--k", type=int, default=8)
+ap.add_argument("--reps", type=int, default=3)
+args = ap.parse_args()
+rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(lr)
+if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+from deep_vision_b200 import _lib, parallel, reference_material as rm, synth
+ctx = _lib.Context.get(lr)
+lo, hi = parallel.shard_range(args.chunks, rank, world)
+t0 = time.time()
+data, off = synth.make_texts(hi - lo, args.chars, seed=synth.SEED + 1000 + rank)
+gen_s = time.time() - t0
+# queries: 30-60 chars, half copied from a chunk of rank 0's shard (same on every rank: generated from seed)
+qdata, qoff = synth.make_texts(args.queries, 45, seed=999)
+qraw = qdata.tobytes()
+rng = np.random.default_rng(7)
+if rank == 0:
+    raw0 = data.tobytes()
+queries = []
+for q in range(args.queries):
+    text = qraw[qoff[q]:qoff[q + 1]].decode("utf-8")
+    if rank == 0 or world == 1:
+        pass
+    queries.append(text)
+if world == 1:
+    raw0 = data.tobytes()
+    for q in range(0, args.queries, 2):
+        c = int(rng.integers(0, hi - lo)); s = raw0[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, args.chars - 24))
+        queries[q] = queries[q][:22] + s[a:a + 22]
+t0 = time.time()
+terms = [rm._tokenize_reference_material_query(t) for t in queries]
+tok_s = time.time() - t0
+d_data = torch.from_numpy(data).cuda(); d_off = torch.from_numpy(off).cuda()
+ctx.set_timing(True)
+build_ms = []
+ix = None
+for _ in range(args.reps):
+    if ix is not None:
+        ix.close()
+    torch.cuda.synchronize()
+    ix = rm.ChunkIndex(device_ptrs=(d_data.data_ptr(), d_off.data_ptr(), hi - lo), index_base=lo, ctx=ctx)
+    build_ms.append(ix.build_ms)
+st = ix.stats()
+tsym, toff, qto = rm.terms_to_symbols(terms)
+oi = np.full((args.queries, args.k), -1, np.int64); os_ = np.zeros((args.queries, args.k), np.int32); on = np.zeros(args.queries, np.int32)
+q_ms = []
+for _ in range(args.reps):
+    rc = ctx.lib.dvb_chunk_index_topk(ctx.handle, ix._h, _lib.MEM_HOST, rm.ptr(tsym), rm.ptr(toff), len(toff) - 1, rm.ptr(qto), args.queries,
+                                      lo, args.k, rm.ptr(oi), rm.ptr(os_), rm.ptr(on))
+    ctx.check(rc, "topk")
+    q_ms.append(ctx.last_kernel_ms)
+t0 = time.time()
+gi, gs, gn = parallel.merge_topk(oi, os_, args.k, ctx=ctx)
+merge_s = time.time() - t0
+algo_build = st["text_bytes"] + 4 * st["postings"]            # UTF-8 in + 4 B per posting
+algo_query = 8 * int(os_.sum()) + 16 * args.k * args.queries   # lower bound from the reported top-k only; see DESIGN.md
+if rank == 0:
+    b, qm = min(build_ms), min(q_ms)
+    print(json.dumps({"world": world, "chunks_per_gpu": hi - lo, "queries": args.queries, "k": args.k, "stats": st,
+                      "build_ms": build_ms, "chunks_indexed_per_s_per_gpu": (hi - lo) / (b / 1e3), "build_GBps_algorithmic": algo_build / b / 1e6,
+                      "query_ms": q_ms, "effective_pairs_per_s_per_gpu": (hi - lo) * args.queries / (qm / 1e3),
+                      "merge_s_host_incl_allgather": merge_s, "n_terms": int(len(toff) - 1), "mean_hits": float(gn.mean()),
+                      "host_gen_s": gen_s, "host_tokenize_s": tok_s}))
+if world > 1:
+    dist.barrier(); dist.destroy_process_group()
