@@ -383,15 +383,6 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
         k_ix_scan<<<1, 1024, 0, io.st>>>(d_ni, d_io, n_terms);
         ctx->launches += 3;
     }
-    if (getenv("DVB_IX_DEBUG") && n_terms > 0) {                  // posting volume the plan will visit (diagnostics only)
-        std::vector<int64_t> lo((size_t)n_terms), hi((size_t)n_terms);
-        cudaMemcpyAsync(lo.data(), d_lo, 8 * (size_t)n_terms, cudaMemcpyDeviceToHost, io.st);
-        cudaMemcpyAsync(hi.data(), d_hi, 8 * (size_t)n_terms, cudaMemcpyDeviceToHost, io.st);
-        cudaStreamSynchronize(io.st);
-        int64_t tot = 0, mx = 0, big = 0;
-        for (int32_t t = 0; t < n_terms; t++) { const int64_t d = hi[t] - lo[t]; tot += d; mx = std::max(mx, d); big += d > 4096; }
-        fprintf(stderr, "[dvb ix] terms %d postings visited %lld max %lld terms>4096 %lld\n", n_terms, (long long)tot, (long long)mx, (long long)big);
-    }
     for (int32_t q0 = 0; q0 < nq; q0 += B) {
         const int32_t q1 = std::min(nq, q0 + B), nb = q1 - q0;
         if (N > 0) {
