@@ -28,7 +28,7 @@
 
 struct BindParams {
     const uint8_t* claim_utf8; const int64_t* claim_off; const uint8_t* fact_utf8; const int64_t* fact_off;
-    const int64_t* sess_claim_off; const int64_t* sess_fact_off; int64_t n_sessions;
+    const int64_t* sess_claim_off; const int64_t* sess_fact_off; int64_t s_begin, s_end;   // session range of this launch
     const double* fact_quality; const int32_t* fact_dim; const uint8_t* fact_hard;
     const int32_t* claim_pref_dim; const double* claim_threshold;
     int32_t* best_fact; double* best_score; uint8_t* bound; int32_t* len_claim; int32_t* len_fact;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
     for (uint32_t i = lane; i < hit_words; i += 32) hit[i] = 0u;
     __syncthreads();
 
-    for (int64_t s = blockIdx.x; s < p.n_sessions; s += gridDim.x) {
+    for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
         const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
         for (int64_t cg = c0; cg < c1; cg += BIND_CLAIMS) {
@@ -339,10 +339,12 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
-    p.n_sessions = n_sessions; p.cap = cap;
+    p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
     cudaError_t cerr = cudaSuccess;
     int32_t *d_best = nullptr, *d_lc = nullptr, *d_lf = nullptr; double* d_score = nullptr; uint8_t* d_bound = nullptr;
     std::vector<int64_t> reb_c, reb_f;
+    const uint8_t *h_cu = nullptr, *h_fu = nullptr; uint8_t *d_cu_w = nullptr, *d_fu_w = nullptr;
+    const int64_t *h_co_rel = nullptr, *h_fo_rel = nullptr;
     if (mem == DVB_MEM_HOST) {
         uint8_t* d_cu = sc.alloc<uint8_t>((size_t)claim_bytes + 64); uint8_t* d_fu = sc.alloc<uint8_t>((size_t)fact_bytes + 64);
         int64_t* d_co = sc.alloc<int64_t>((size_t)n_claims + 1); int64_t* d_fo = sc.alloc<int64_t>((size_t)n_facts + 1);
@@ -356,8 +358,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         const int64_t* co = claim_off; const int64_t* fo = fact_off;
         if (co0 != 0) { reb_c.resize((size_t)n_claims + 1); for (int64_t i = 0; i <= n_claims; i++) reb_c[i] = claim_off[i] - co0; co = reb_c.data(); }
         if (fo0 != 0) { reb_f.resize((size_t)n_facts + 1); for (int64_t i = 0; i <= n_facts; i++) reb_f[i] = fact_off[i] - fo0; fo = reb_f.data(); }
-        p.claim_utf8 = dvb_in(mem, claim_utf8 + co0, d_cu, (size_t)claim_bytes, st, &cerr);
-        p.fact_utf8 = dvb_in(mem, fact_utf8 + fo0, d_fu, (size_t)fact_bytes, st, &cerr);
+        p.claim_utf8 = d_cu; p.fact_utf8 = d_fu;          // text is copied slice by slice below
+        h_cu = claim_utf8 + co0; h_fu = fact_utf8 + fo0; d_cu_w = d_cu; d_fu_w = d_fu; h_co_rel = co; h_fo_rel = fo;
         p.claim_off = dvb_in(mem, co, d_co, (size_t)n_claims + 1, st, &cerr);
         p.fact_off = dvb_in(mem, fo, d_fo, (size_t)n_facts + 1, st, &cerr);
         p.sess_claim_off = dvb_in(mem, sess_claim_off, d_sco, (size_t)n_sessions + 1, st, &cerr);
@@ -381,11 +383,54 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
     if (use_global) { p.ghit = sc.alloc<uint32_t>((size_t)grid * hit_bytes / 4); if (!p.ghit) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
     const bool timing = ctx->timing.load() != 0;
-    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, st));
-    k_bind_claims<<<grid, BIND_THREADS, smem, st>>>(p);
-    if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
-    ctx->launches += 1;
-    DVB_CUDA(ctx, cudaGetLastError());
+    if (mem == DVB_MEM_DEVICE) {
+        if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, st));
+        k_bind_claims<<<grid, BIND_THREADS, smem, st>>>(p);
+        if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
+        ctx->launches += 1;
+        DVB_CUDA(ctx, cudaGetLastError());
+    } else {
+        // Host buffers: cut the sessions into slices of ~1/24 of the fact text (8..64 MB); slice i+1 crosses PCIe on
+        // the copy stream while slice i is scored, so a call costs ~max(H2D, kernel) instead of their sum.
+        const int64_t target = std::min<int64_t>(std::max<int64_t>(fact_bytes / 24, (int64_t)8 << 20), (int64_t)64 << 20);
+        std::vector<int64_t> cuts(1, 0);
+        for (int64_t sidx = 1; sidx < n_sessions; sidx++)
+            if (h_fo_rel[sess_fact_off[sidx]] - h_fo_rel[sess_fact_off[cuts.back()]] >= target) cuts.push_back(sidx);
+        cuts.push_back(n_sessions);
+        const size_t n_slices = cuts.size() - 1;
+        dvb_lease* l = sc.l;
+        cudaStream_t cp = st;                                              // one slice: everything on the call's stream
+        if (n_slices > 1) {
+            if (!l->copy) DVB_CUDA(ctx, cudaStreamCreateWithFlags(&l->copy, cudaStreamNonBlocking));
+            while (l->pipe_ev.size() < n_slices + 1) {
+                cudaEvent_t e; DVB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); l->pipe_ev.push_back(e);
+            }
+            cp = l->copy;
+        }
+        auto run = [&]() -> cudaError_t {
+            cudaError_t e = cudaSuccess;
+            #define BIND_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
+            if (n_slices > 1) { BIND_TRY(cudaEventRecord(l->pipe_ev[0], st)); BIND_TRY(cudaStreamWaitEvent(cp, l->pipe_ev[0], 0)); }
+            if (timing) BIND_TRY(cudaEventRecord(l->ev0, st));
+            for (size_t i = 0; i < n_slices; i++) {
+                const int64_t s0 = cuts[i], s1 = cuts[i + 1];
+                const int64_t cb0 = h_co_rel[sess_claim_off[s0]], cb1 = h_co_rel[sess_claim_off[s1]];
+                const int64_t fb0 = h_fo_rel[sess_fact_off[s0]], fb1 = h_fo_rel[sess_fact_off[s1]];
+                if (cb1 > cb0) BIND_TRY(cudaMemcpyAsync(d_cu_w + cb0, h_cu + cb0, (size_t)(cb1 - cb0), cudaMemcpyHostToDevice, cp));
+                if (fb1 > fb0) BIND_TRY(cudaMemcpyAsync(d_fu_w + fb0, h_fu + fb0, (size_t)(fb1 - fb0), cudaMemcpyHostToDevice, cp));
+                if (n_slices > 1) { BIND_TRY(cudaEventRecord(l->pipe_ev[i + 1], cp)); BIND_TRY(cudaStreamWaitEvent(st, l->pipe_ev[i + 1], 0)); }
+                p.s_begin = s0; p.s_end = s1;
+                k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(p);
+                ctx->launches += 1;
+                BIND_TRY(cudaGetLastError());
+            }
+            if (timing) BIND_TRY(cudaEventRecord(l->ev1, st));
+            #undef BIND_TRY
+            return e;
+        };
+        const cudaError_t pe = run();
+        if (pe != cudaSuccess) { if (n_slices > 1) cudaStreamSynchronize(cp); cudaStreamSynchronize(st); DVB_CUDA(ctx, pe); }
+    }
     if (mem == DVB_MEM_HOST && n_claims) {
         DVB_CUDA(ctx, cudaMemcpyAsync(out_best_fact, d_best, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));
         DVB_CUDA(ctx, cudaMemcpyAsync(out_best_score, d_score, 8 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));

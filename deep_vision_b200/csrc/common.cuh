@@ -26,6 +26,8 @@ struct dvb_lease {
     std::vector<void*> overflow;         // extra blocks of the previous call (arena was too small)
     size_t high_water = 0;               // bytes the previous calls needed in total
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t copy = nullptr;         // H2D stream of pipelined host-buffer calls (created on first use)
+    std::vector<cudaEvent_t> pipe_ev;    // one per in-flight input slice
     bool busy = false;
 };
 

@@ -44,7 +44,8 @@ def test_a2_golden_cases(gpu_ctx, golden):
     assert evidence.infer_weak_evidence_refs_v3(c["field"], c["item"], c["pack"], c["min_score"], ctx=gpu_ctx) == c["result"]
 
 
-@pytest.mark.parametrize("n_sessions,turns,claims", [(64, 40, 24), (5, 70, 40), (3, 1, 1), (40, 7, 33)])
+# (400, 40, 24) = 35 MB of fact text: the host-buffer call runs as >= 4 pipelined slices (H2D overlapped with scoring)
+@pytest.mark.parametrize("n_sessions,turns,claims", [(64, 40, 24), (5, 70, 40), (3, 1, 1), (40, 7, 33), (400, 40, 24)])
 def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
     from deep_vision_b200 import evidence, synth
     c = synth.make_sessions(n_sessions, turns=turns, claims_per_session=claims, seed=11 + n_sessions)
