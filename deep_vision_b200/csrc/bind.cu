@@ -35,6 +35,7 @@ struct BindParams {
     uint32_t cap;                         // table capacity (power of two)
     unsigned long long* gtable;           // per CTA: cap keys (u64) then cap cmasks (u32)
     uint32_t* ghit;                       // per-warp hit bitmaps in global memory when cap/32 words do not fit smem, else null
+    int* overflow;                        // fast kernel: set when a claim group does not fit its tables
 };
 
 __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {
@@ -157,7 +158,7 @@ struct EmitFact {
 
 extern __shared__ __align__(16) unsigned char bind_smem[];
 
-__global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
+__global__ void __launch_bounds__(BIND_THREADS) k_bind_claims_general(BindParams p) {
     BindShared& sh = *reinterpret_cast<BindShared*>(bind_smem);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t hit_words = p.cap >> 5;
@@ -264,6 +265,8 @@ __global__ void __launch_bounds__(BIND_THREADS) k_bind_claims(BindParams p) {
     }
 }
 
+#include "bind6.cuh"
+
 static inline uint32_t bind_table_cap(int64_t max_group_bytes) {
     // distinct tokens of a text <= bytes/3 + 1 (<= one token per CJK char, <= one per 3 ASCII bytes); load factor <= 1/2
     int64_t bound = max_group_bytes / 3 + BIND_CLAIMS + 1;
@@ -323,11 +326,22 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     size_t smem = fixed + hit_bytes;
     const bool use_global = hit_bytes > 16384;          // huge claim groups: hit bitmaps move to global memory
     if (use_global) smem = fixed;
-    DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims_general, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 1;
-    DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bind_claims, BIND_THREADS, smem));
+    DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bind_claims_general, BIND_THREADS, smem));
     if (occ < 1) occ = 1;
     const int grid = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ);
+    // ---- fast kernel (bind6.cuh): bigram table in shared memory, sized from the same bound (load factor <= 1/2)
+    const char* force = getenv("DVB_BIND_KERNEL");
+    const bool fast = cap <= B6_CAPB && !(force && !strcmp(force, "general"));
+    const size_t smem6 = 0;                                  // static shared memory
+    int grid6 = 1;
+    if (fast) {
+        int occ6 = 1;
+        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_bind_claims, BIND_THREADS, smem6));
+        if (occ6 < 1) occ6 = 1;
+        grid6 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ6);
+    }
     // ---- workspace
     size_t need = 8192;
     if (mem == DVB_MEM_HOST) {
@@ -337,6 +351,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     }
     need += dvb_pad((size_t)grid * (size_t)cap * 12);
     if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
+    if (fast) need += dvb_pad((size_t)grid6 * bind6_ws_u64_per_cta() * 8) + dvb_pad(4);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
@@ -382,13 +397,29 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     p.gtable = sc.alloc<unsigned long long>(((size_t)grid * (size_t)cap * 12 + 7) / 8);
     if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
     if (use_global) { p.ghit = sc.alloc<uint32_t>((size_t)grid * hit_bytes / 4); if (!p.ghit) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
+    BindParams p6 = p;
+    int* d_ovf = nullptr; int h_ovf = 0;
+    if (fast) {
+        p6.gtable = sc.alloc<unsigned long long>((size_t)grid6 * bind6_ws_u64_per_cta());
+        d_ovf = sc.alloc<int>(1);
+        if (!p6.gtable || !d_ovf) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        p6.overflow = d_ovf;
+        DVB_CUDA(ctx, cudaMemsetAsync(d_ovf, 0, 4, st));
+    }
+    // one launch over sessions [s0, s1): fast kernel unless the call was routed to the general one
+    auto launch = [&](bool use_fast, int64_t s0, int64_t s1) -> cudaError_t {
+        BindParams q = use_fast ? p6 : p;
+        q.s_begin = s0; q.s_end = s1;
+        if (use_fast) k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid6), BIND_THREADS, smem6, st>>>(q);
+        else k_bind_claims_general<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(q);
+        ctx->launches += 1;
+        return cudaGetLastError();
+    };
     const bool timing = ctx->timing.load() != 0;
     if (mem == DVB_MEM_DEVICE) {
         if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, st));
-        k_bind_claims<<<grid, BIND_THREADS, smem, st>>>(p);
+        DVB_CUDA(ctx, launch(fast, 0, n_sessions));
         if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
-        ctx->launches += 1;
-        DVB_CUDA(ctx, cudaGetLastError());
     } else {
         // Host buffers: cut the sessions into slices of ~1/24 of the fact text (8..64 MB); slice i+1 crosses PCIe on
         // the copy stream while slice i is scored, so a call costs ~max(H2D, kernel) instead of their sum.
@@ -419,10 +450,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
                 if (cb1 > cb0) BIND_TRY(cudaMemcpyAsync(d_cu_w + cb0, h_cu + cb0, (size_t)(cb1 - cb0), cudaMemcpyHostToDevice, cp));
                 if (fb1 > fb0) BIND_TRY(cudaMemcpyAsync(d_fu_w + fb0, h_fu + fb0, (size_t)(fb1 - fb0), cudaMemcpyHostToDevice, cp));
                 if (n_slices > 1) { BIND_TRY(cudaEventRecord(l->pipe_ev[i + 1], cp)); BIND_TRY(cudaStreamWaitEvent(st, l->pipe_ev[i + 1], 0)); }
-                p.s_begin = s0; p.s_end = s1;
-                k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(p);
-                ctx->launches += 1;
-                BIND_TRY(cudaGetLastError());
+                BIND_TRY(launch(fast, s0, s1));
             }
             if (timing) BIND_TRY(cudaEventRecord(l->ev1, st));
             #undef BIND_TRY
@@ -430,6 +458,15 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         };
         const cudaError_t pe = run();
         if (pe != cudaSuccess) { if (n_slices > 1) cudaStreamSynchronize(cp); cudaStreamSynchronize(st); DVB_CUDA(ctx, pe); }
+    }
+    if (fast) {                                             // a claim group that did not fit the fast tables: exact re-run
+        DVB_CUDA(ctx, cudaMemcpyAsync(&h_ovf, d_ovf, 4, cudaMemcpyDeviceToHost, st));
+        DVB_CUDA(ctx, cudaStreamSynchronize(st));
+        if (h_ovf) {
+            if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
+            DVB_CUDA(ctx, launch(false, 0, n_sessions));
+            if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
+        }
     }
     if (mem == DVB_MEM_HOST && n_claims) {
         DVB_CUDA(ctx, cudaMemcpyAsync(out_best_fact, d_best, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));

@@ -125,8 +125,8 @@ __device__ __forceinline__ uint32_t dv_decode_sym(const uint32_t* R, int t, bool
 // ---------------------------------------------------------------- exact serial path
 // Lane 0 walks the text; keys are queued and emitted by the whole warp.  Handles every
 // code point exactly (U+0130 -> 'i' + separator, U+212A -> 'k').
-template <class Emit>
-__device__ void dv_tokenize_serial(const uint8_t* text, int32_t n, dv_warp_buf* wb, const unsigned long long* ktab, Emit& emit) {
+template <class Emit, class WB>
+__device__ void dv_tokenize_serial(const uint8_t* text, int32_t n, WB* wb, const unsigned long long* ktab, Emit& emit) {
     const int lane = threadIdx.x & 31;
     int32_t i = 0;
     int qn = 0; uint32_t qkind = 0;

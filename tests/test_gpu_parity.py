@@ -64,6 +64,45 @@ def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
     assert np.array_equal(got2["best_fact"], ref["best_fact"])
 
 
+def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
+    """DVB_BIND_KERNEL=general routes the call to k_bind_claims_general (the fallback of the fast kernel)."""
+    from deep_vision_b200 import evidence, synth
+    c = synth.make_sessions(48, turns=30, claims_per_session=40, seed=77)
+    args = (c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
+            c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
+    fast = evidence.bind_packed(gpu_ctx, *args, want_lens=True)
+    monkeypatch.setenv("DVB_BIND_KERNEL", "general")
+    gen = evidence.bind_packed(gpu_ctx, *args, want_lens=True)
+    for k in fast:
+        assert np.array_equal(fast[k], gen[k]), k
+    ref = oracle.bind_claims(None, None, c.sess_claim_off, c.sess_fact_off, c.fact_quality, c.fact_dim, c.fact_hard,
+                             c.claim_pref_dim, c.claim_threshold, packed=(c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off))
+    assert np.array_equal(gen["best_fact"], ref["best_fact"])
+    assert np.array_equal(gen["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
+
+
+def test_a2_token_table_overflow_reruns_general(gpu_ctx, oracle):
+    """> 704 distinct ASCII tokens in one claim group: the fast kernel raises `overflow`, the call re-runs exactly."""
+    from deep_vision_b200 import packing
+    import random
+    rng = random.Random(9)
+    abc = "abcdefghijklmnopqrstuvwxyz0123456789_"
+    words = sorted({"".join(rng.choice(abc) for _ in range(3)) for _ in range(3000)})
+    claims = [" ".join(rng.sample(words, 60)) for _ in range(25)]         # ~6 KB, ~1200 distinct tokens: fast path, then overflow
+    facts = [" ".join(rng.sample(words, 300)) + " 中文测试数据" for _ in range(12)]
+    cu, co = packing.pack_texts(claims)
+    fu, fo = packing.pack_texts(facts)
+    sco = np.array([0, len(claims)], np.int64); sfo = np.array([0, len(facts)], np.int64)
+    fq = np.linspace(0.1, 0.9, len(facts)); fd = np.zeros(len(facts), np.int32); fh = np.zeros(len(facts), np.uint8)
+    cp = np.full(len(claims), -1, np.int32); ct = np.full(len(claims), 0.46, np.float64)
+    from deep_vision_b200 import evidence
+    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
+    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
+    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
+
+
 def test_a2_large_claim_table_global_fallback(gpu_ctx, oracle):
     """claims of one session too large for the shared-memory table -> global-memory table path"""
     from deep_vision_b200 import evidence, synth

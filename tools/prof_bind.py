@@ -23,3 +23,4 @@ for _ in range(reps):
                                  c.max_claim_group_bytes)
     ctx.check(rc, "bind")
     print("kernel ms", ctx.last_kernel_ms, "GB/s", c.algorithmic_bytes / ctx.last_kernel_ms / 1e6)
+print("launches", ctx.launches)
