@@ -18,6 +18,11 @@
 #define B6_CAPT 1024            // token-table slots (global workspace)
 #define B6_TOK_LIMIT 704        // inserts stop here; up to 256 racing threads still find a free slot
 #define B6_HW ((B6_CAPB + B6_CAPT) / 32)
+#define B6_FT_BITS 15
+#define B6_SPILL 0x80000000u     // bit 31 of a bucket's last slot: an insert continued into the next bucket
+#ifndef B6_CLAIM_RED
+#define B6_CLAIM_RED 1          // claim marks as fire-and-forget REDs, len(A) through the warp's shared bitmap
+#endif
 #ifndef B6_MIN_CTAS
 #define B6_MIN_CTAS 4
 #endif
@@ -29,7 +34,7 @@ struct Bind6Shared {            // static shared memory: every access is [regist
     unsigned long long ktab[DV_KTAB];
     unsigned long long wset[BIND_WARPS][BIND_WSET];
     double rbest[BIND_WARPS][BIND_CLAIMS];
-    uint32_t ft[1u << (BIND_FT_BITS - 5)];
+    uint32_t ft[1u << (B6_FT_BITS - 5)];
     uint32_t ov[BIND_WARPS][BIND_CLAIMS];
     int ridx[BIND_WARPS][BIND_CLAIMS];
     int wcnt[BIND_WARPS];
@@ -39,20 +44,28 @@ struct Bind6Shared {            // static shared memory: every access is [regist
 };
 __shared__ Bind6Shared b6;
 
-// token filter: 2 probes into 8192 bits (false positives ~0.5 % at 350 tokens per claim group)
-__device__ __forceinline__ uint32_t b6_ft_h2(uint32_t sig) { return (sig * 0x9E3779B1u) >> (32 - BIND_FT_BITS); }
+// token filter: one probe into 2^15 bits (false positives ~1 % at 350 tokens per claim group)
 __device__ __forceinline__ bool b6_ft_pass(uint32_t sig) {
-    const uint32_t h1 = bind_ft_index(sig), h2 = b6_ft_h2(sig);
-    return ((b6.ft[h1 >> 5] >> (h1 & 31)) & (b6.ft[h2 >> 5] >> (h2 & 31)) & 1u) != 0u;
+    const uint32_t h = sig >> (32 - B6_FT_BITS);
+    return ((b6.ft[h >> 5] >> (h & 31)) & 1u) != 0u;
 }
 
 struct Emit6Claim {
-    unsigned long long* tkeys; uint32_t* cmask; int c;
+    unsigned long long* tkeys; uint32_t* cmask; int c; int warp;
     __device__ __forceinline__ void restart() {}
+    // slot -> claim bit in the L2-resident mask (fire-and-forget RED); len(A) counts the claim's DISTINCT slots through
+    // the warp's shared-memory bitmap (one warp tokenises one claim), so no global atomic has to return a value
     __device__ __forceinline__ void mark(uint32_t slot) {
+#if B6_CLAIM_RED
+        atomicOr(&cmask[slot], 1u << c);
+        const uint32_t bit = 1u << (slot & 31);
+        const uint32_t old = atomicOr(&b6.hit[warp][slot >> 5], bit);
+        if (!(old & bit)) atomicAdd(&b6.lenA[c], 1);
+#else
         const uint32_t bit = 1u << c;
         const uint32_t old = atomicOr(&cmask[slot], bit);
         if (!(old & bit)) atomicAdd(&b6.lenA[c], 1);
+#endif
     }
     __device__ __forceinline__ void bigram(bool v, uint32_t id) {
         if (!v) return;
@@ -60,9 +73,10 @@ struct Emit6Claim {
         for (uint32_t tries = 0; tries <= B6_NBM; tries++) {
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const uint32_t prev = atomicCAS(&b6.tab[b * 4u + j], 0u, id);
+                const uint32_t prev = atomicCAS(&b6.tab[b * 4u + j], 0u, id) & 0x7FFFFFFFu;
                 if (prev == 0u || prev == id) { mark(b * 4u + j); return; }
             }
+            atomicOr(&b6.tab[b * 4u + 3u], B6_SPILL);           // all four slots taken: the chain continues in the next bucket
             b = (b + 1u) & B6_NBM;
         }
         b6.ovf = 1;                                             // table sized from a wrong hint
@@ -71,9 +85,8 @@ struct Emit6Claim {
     __device__ __forceinline__ void token(bool v, uint64_t key, uint32_t sig) {
         if (!v) return;
         if (*(volatile int*)&b6.ntok >= B6_TOK_LIMIT) { b6.ovf = 1; return; }
-        const uint32_t h1 = bind_ft_index(sig), h2 = b6_ft_h2(sig);
-        atomicOr(&b6.ft[h1 >> 5], 1u << (h1 & 31));
-        atomicOr(&b6.ft[h2 >> 5], 1u << (h2 & 31));
+        const uint32_t h = sig >> (32 - B6_FT_BITS);
+        atomicOr(&b6.ft[h >> 5], 1u << (h & 31));
         uint32_t slot = bind_hash(key) & (B6_CAPT - 1);
         for (;;) {
             const unsigned long long prev = atomicCAS(&tkeys[slot], 0ULL, (unsigned long long)key);
@@ -88,7 +101,7 @@ struct Emit6Claim {
 struct Emit6Fact {
     const unsigned long long* tkeys; int warp;
     bool full, first; int lane;
-    __device__ __forceinline__ void restart() { first = false; }
+    __device__ __forceinline__ void restart() { first = false; }                 // what was emitted is a correct prefix
     __device__ __forceinline__ void count_distinct(bool v, uint64_t key) {       // until 18 distinct tokens were seen
         if (v) {
             uint32_t s = (bind_hash(key) >> 20) & (BIND_WSET - 1);
@@ -116,9 +129,9 @@ struct Emit6Fact {
             uint32_t b = (id * 0x9E3779B1u) >> B6_BSHIFT;
             for (;;) {
                 const uint4 q = *reinterpret_cast<const uint4*>(&b6.tab[b * 4u]);
-                const uint32_t m = (q.x == id ? 1u : 0u) | (q.y == id ? 2u : 0u) | (q.z == id ? 4u : 0u) | (q.w == id ? 8u : 0u);
+                const uint32_t m = (q.x == id ? 1u : 0u) | (q.y == id ? 2u : 0u) | (q.z == id ? 4u : 0u) | ((q.w & 0x7FFFFFFFu) == id ? 8u : 0u);
                 if (m) { const uint32_t hs = b * 4u + (uint32_t)(__ffs(m) - 1); atomicOr(&b6.hit[warp][hs >> 5], 1u << (hs & 31)); break; }
-                if (q.w == 0u) break;                           // buckets fill in slot order: a free last slot ends the chain
+                if (!(q.w & B6_SPILL)) break;                   // no insert ever spilled out of this bucket: the chain ends here
                 b = (b + 1u) & B6_NBM;
             }
         }
@@ -159,7 +172,7 @@ __global__ void __launch_bounds__(BIND_THREADS, B6_MIN_CTAS) k_bind_claims(BindP
             for (uint32_t i = tid; i < (B6_CAPB >> 2); i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
             for (uint32_t i = tid; i < B6_CAPT; i += BIND_THREADS) tkeys[i] = 0ULL;
             for (uint32_t i = tid; i < B6_CAPB + B6_CAPT; i += BIND_THREADS) cmask[i] = 0u;
-            for (uint32_t i = tid; i < (1u << (BIND_FT_BITS - 5)); i += BIND_THREADS) sh.ft[i] = 0u;
+            for (uint32_t i = tid; i < (1u << (B6_FT_BITS - 5)); i += BIND_THREADS) sh.ft[i] = 0u;
             if (tid < BIND_CLAIMS) sh.lenA[tid] = 0;
             if (tid == 0) { sh.next_item = 0; sh.ntok = 0; sh.ovf = 0; }
             __syncthreads();
@@ -170,8 +183,13 @@ __global__ void __launch_bounds__(BIND_THREADS, B6_MIN_CTAS) k_bind_claims(BindP
                 c = __shfl_sync(0xffffffffu, c, 0);
                 if (c >= ncg) break;
                 const int64_t b = p.claim_off[cg + c], e = p.claim_off[cg + c + 1];
-                Emit6Claim emit{ tkeys, cmask, c };
+                Emit6Claim emit{ tkeys, cmask, c, warp };
                 dv6_tokenize_warp(p.claim_utf8 + b, (int32_t)(e - b), &sh.wbuf[warp], sh.ktab, sh.lut, emit);
+#if B6_CLAIM_RED
+                __syncwarp();
+                for (uint32_t i = lane; i < B6_HW; i += 32) sh.hit[warp][i] = 0u;
+                __syncwarp();
+#endif
             }
             __syncthreads();
             if (tid == 0) { sh.next_item = 0; if (sh.ovf) *p.overflow = 1; }
@@ -181,29 +199,39 @@ __global__ void __launch_bounds__(BIND_THREADS, B6_MIN_CTAS) k_bind_claims(BindP
             const int la = lane < ncg ? sh.lenA[lane] : 0;
             const int da = max(3, min(la, 14));
             const int pref = lane < ncg ? p.claim_pref_dim[cg + lane] : -1;
-            for (;;) {
-                int f = 0;
-                if (lane == 0) f = atomicAdd(&sh.next_item, 1);
-                f = __shfl_sync(0xffffffffu, f, 0);
-                if ((int64_t)f >= f1 - f0) break;
+            const int nf = (int)(f1 - f0);
+            int f = 0;
+            if (lane == 0) f = atomicAdd(&sh.next_item, 1);
+            f = __shfl_sync(0xffffffffu, f, 0);
+            int64_t b = 0, e = 0;
+            if (f < nf) { b = p.fact_off[f0 + f]; e = p.fact_off[f0 + f + 1]; }
+            while (f < nf) {
                 sh.wset[warp][lane] = 0ULL; sh.wset[warp][lane + 32] = 0ULL;
                 sh.ov[warp][lane] = 0u;
                 if (lane == 0) sh.wcnt[warp] = 0;
                 __syncwarp();
-                const int64_t b = p.fact_off[f0 + f], e = p.fact_off[f0 + f + 1];
                 Emit6Fact emit{ tkeys, warp, false, true, lane };
                 dv6_tokenize_warp(p.fact_utf8 + b, (int32_t)(e - b), &sh.wbuf[warp], sh.ktab, sh.lut, emit);
                 __syncwarp();
-                // hit bitmap -> per-claim overlap counts; clear as we go
-                for (uint32_t wd = lane; wd < B6_HW; wd += 32) {
-                    uint32_t bits = sh.hit[warp][wd];
-                    if (bits) {
-                        sh.hit[warp][wd] = 0u;
-                        while (bits) {
-                            const uint32_t slot = wd * 32 + (__ffs(bits) - 1); bits &= bits - 1;
-                            uint32_t cm = __ldcg(&cmask[slot]);
-                            while (cm) { const int c = __ffs(cm) - 1; cm &= cm - 1; atomicAdd(&sh.ov[warp][c], 1u); }
+                const double fq = p.fact_quality[f0 + f];                 // issued here, consumed after the hit scan
+                const int fdim = p.fact_dim[f0 + f];
+                const uint32_t fhard = p.fact_hard[f0 + f];
+                // hit bitmap -> per-claim overlap counts.  One flat loop per lane over its (hit slot, claim) pairs, so
+                // the warp iterates max-over-lanes of the pair count instead of a sum of per-word maxima.
+                {
+                    uint32_t wd = lane, cur = 0u, base = 0u, cm = 0u;
+                    for (;;) {
+                        if (cm == 0u) {
+                            while (cur == 0u && wd < B6_HW) {
+                                cur = sh.hit[warp][wd];
+                                if (cur) sh.hit[warp][wd] = 0u;
+                                base = wd * 32u; wd += 32u;
+                            }
+                            if (cur == 0u) break;
+                            cm = __ldcg(&cmask[base + (__ffs(cur) - 1)]); cur &= cur - 1u;
+                            if (cm == 0u) continue;
                         }
+                        atomicAdd(&sh.ov[warp][__ffs(cm) - 1], 1u); cm &= cm - 1u;
                     }
                 }
                 __syncwarp();
@@ -214,15 +242,17 @@ __global__ void __launch_bounds__(BIND_THREADS, B6_MIN_CTAS) k_bind_claims(BindP
                     const int db = max(4, min(lb, 18));
                     const double coverage = __ddiv_rn((double)ov, (double)da);
                     const double precision = __ddiv_rn((double)ov, (double)db);
-                    double q = p.fact_quality[f0 + f];
-                    q = q > 0.0 ? (q < 1.0 ? q : 1.0) : 0.0;
-                    const double dimb = (pref >= 0 && p.fact_dim[f0 + f] == pref) ? 0.12 : 0.0;
-                    const double hardb = p.fact_hard[f0 + f] ? 0.04 : 0.0;
+                    const double q = fq > 0.0 ? (fq < 1.0 ? fq : 1.0) : 0.0;
+                    const double dimb = (pref >= 0 && fdim == pref) ? 0.12 : 0.0;
+                    const double hardb = fhard ? 0.04 : 0.0;
                     const double sc = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(0.62, coverage), __dmul_rn(0.18, precision)),
                                                                      __dmul_rn(0.16, q)), dimb), hardb);
                     if (sc > best || (sc == best && f < best_f)) { best = sc; best_f = f; }
                 }
                 __syncwarp();
+                if (lane == 0) f = atomicAdd(&sh.next_item, 1);
+                f = __shfl_sync(0xffffffffu, f, 0);
+                if (f < nf) { b = p.fact_off[f0 + f]; e = p.fact_off[f0 + f + 1]; }
             }
             sh.rbest[warp][lane] = best; sh.ridx[warp][lane] = best_f;
             __syncthreads();

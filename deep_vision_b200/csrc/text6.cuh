@@ -45,13 +45,25 @@ __device__ bool dv6_tokenize_fast(const uint8_t* text, int32_t n, dv6_warp_buf* 
     int32_t gbase = 0;                             // global symbol index of B[DV6_HIST]
     int32_t rstart = 0;                            // global index of the most recent run start
     const uint32_t lt = (1u << lane) - 1u;
+    // software pipeline: the loads of tile t+1 are issued before tile t is processed
+    uint2 wn = make_uint2(0u, 0u); uint32_t en = 0u;
+    {
+        const int32_t p0 = -a + lane * 8;
+        if (p0 < n && p0 + 8 > 0) wn = *reinterpret_cast<const uint2*>(text + p0);
+        if (lane == 31 && -a + DV6_TILE < n) en = (uint32_t)text[-a + DV6_TILE];
+    }
     for (int32_t tile = -a; tile < n; tile += DV6_TILE) {
         // ---- stage 1
         const int32_t p0 = tile + lane * 8;
-        uint2 w = make_uint2(0u, 0u);
-        if (p0 < n && p0 + 8 > 0) w = *reinterpret_cast<const uint2*>(text + p0);
+        const uint2 w = wn;
         uint32_t nbw = __shfl_down_sync(0xffffffffu, w.x, 1);
-        if (lane == 31) nbw = (tile + DV6_TILE < n) ? (uint32_t)text[tile + DV6_TILE] : 0u;
+        if (lane == 31) nbw = en;
+        {
+            const int32_t q0 = p0 + DV6_TILE;
+            wn = make_uint2(0u, 0u); en = 0u;
+            if (q0 < n) wn = *reinterpret_cast<const uint2*>(text + q0);
+            if (lane == 31 && tile + 2 * DV6_TILE < n) en = (uint32_t)text[tile + 2 * DV6_TILE];
+        }
         const uint32_t cw = __shfl_sync(0xffffffffu, w.y, 31);
         __syncwarp();                                                   // previous tile's decodes are done
         if (lane == 0) R[1] = carry_word;

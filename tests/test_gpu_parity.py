@@ -64,6 +64,60 @@ def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
     assert np.array_equal(got2["best_fact"], ref["best_fact"])
 
 
+def _adversarial_long_texts():
+    import random
+    rng = random.Random(2024)
+    han = [chr(0x4E00 + rng.randrange(3000)) for _ in range(400)]
+    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
+    def word(n): return "".join(rng.choice("abcdefghijklmnopqrstuvwxyz0123456789_") for _ in range(n))
+    pieces = [lambda: cjk(rng.randint(1, 30)), lambda: cjk(rng.randint(40, 70)), lambda: word(rng.randint(1, 12)),
+              lambda: word(rng.randint(60, 70)), lambda: rng.choice(["，", "。", "\n", " ", "  ", "é", "ß", "😀", "Ω", "…", "Ａ", "ｂ"]),
+              lambda: rng.choice(["İ", "K", "ǅ", "ſ", "ı"]), lambda: cjk(12), lambda: cjk(13), lambda: cjk(24) + word(3), lambda: "A" + cjk(2) + "Z9_"]
+    weights = [30, 2, 14, 1, 30, 1, 4, 4, 4, 4]
+    texts = []
+    for target in [383, 384, 385, 500, 1000, 2030, 2047, 2048, 2049, 2050, 2111, 2112, 2113, 3000, 4096, 4097, 6200, 9000] * 3:
+        t = ""
+        while len(t.encode("utf-8")) < target:
+            t += rng.choices(pieces, weights)[0]()
+        texts.append(t)
+    # exact byte lengths around the tile / chunk boundaries (ASCII filler keeps the byte count exact)
+    for nbytes in (2048, 2048 + 64, 4096, 2048 - 16, 2048 * 2 + 63):
+        t = cjk(300)
+        b = len(t.encode("utf-8"))
+        texts.append(t + " " + "x" * 3 + " " + "y" * (nbytes - b - 5 - 6) + " " + cjk(1) + "ab")
+    texts.append(cjk(2000))                         # one run, far longer than the staged history
+    texts.append((word(5) + " ") * 500)             # ASCII only
+    texts.append(("😀" + cjk(3)) * 300)             # 4-byte characters between short runs
+    return texts, rng, han
+
+
+def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
+    """facts >= 384 bytes take text7.cuh (lane = 64-byte chunk automaton): tile/chunk boundaries, long runs (restart),
+    exotic case mappings (restart), long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
+    from deep_vision_b200 import evidence, packing
+    facts, rng, han = _adversarial_long_texts()
+    claims = []
+    for f in facts[::2]:
+        i = rng.randrange(max(1, len(f) - 60))
+        claims.append(f[i:i + rng.randint(5, 60)])
+    claims += ["".join(rng.choice(han) for _ in range(20)) for _ in range(6)]
+    n_sess = 3
+    cu, co = packing.pack_texts(claims * n_sess)
+    fu, fo = packing.pack_texts(facts * n_sess)
+    sco = np.arange(n_sess + 1, dtype=np.int64) * len(claims)
+    sfo = np.arange(n_sess + 1, dtype=np.int64) * len(facts)
+    nf, nc = len(facts) * n_sess, len(claims) * n_sess
+    fq = np.linspace(0.05, 0.95, nf); fd = (np.arange(nf) % 4).astype(np.int32); fh = (np.arange(nf) % 3 == 0).astype(np.uint8)
+    cp = (np.arange(nc) % 5 - 1).astype(np.int32); ct = np.full(nc, 0.46, np.float64)
+    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
+    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
+    assert np.array_equal(got["len_fact"], np.minimum(ref["len_fact"], 18))
+    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
+    assert np.array_equal(got["bound"], ref["bound"])
+
+
 def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
     """DVB_BIND_KERNEL=general routes the call to k_bind_claims_general (the fallback of the fast kernel)."""
     from deep_vision_b200 import evidence, synth
