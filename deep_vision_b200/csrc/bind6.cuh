@@ -19,6 +19,7 @@
 #define B6_TOK_LIMIT 704        // inserts stop here; up to 256 racing threads still find a free slot
 #define B6_HW ((B6_CAPB + B6_CAPT) / 32)
 #define B6_FT_BITS 15
+#define B6_LIST 600             // hit-slot list entries (u16) that fit the idle tokenizer buffer of the warp
 #define B6_SPILL 0x80000000u     // bit 31 of a bucket's last slot: an insert continued into the next bucket
 #ifndef B6_CLAIM_RED
 #define B6_CLAIM_RED 1          // claim marks as fire-and-forget REDs, len(A) through the warp's shared bitmap
@@ -42,6 +43,7 @@ struct Bind6Shared {            // static shared memory: every access is [regist
     int next_item, ntok, ovf;
     uint8_t lut[128];
 };
+static_assert(sizeof(dv6_warp_buf) >= B6_LIST * 2, "hit-slot list must fit the tokenizer buffer");
 __shared__ Bind6Shared b6;
 
 // token filter: one probe into 2^15 bits (false positives ~1 % at 350 tokens per claim group)
@@ -216,26 +218,42 @@ __global__ void __launch_bounds__(BIND_THREADS, B6_MIN_CTAS) k_bind_claims(BindP
                 const double fq = p.fact_quality[f0 + f];                 // issued here, consumed after the hit scan
                 const int fdim = p.fact_dim[f0 + f];
                 const uint32_t fhard = p.fact_hard[f0 + f];
-                // hit bitmap -> per-claim overlap counts.  One flat loop per lane over its (hit slot, claim) pairs, so
-                // the warp iterates max-over-lanes of the pair count instead of a sum of per-word maxima.
+                // hit bitmap -> per-claim overlap counts.  Pass 1 compacts the hit slots of the warp's bitmap into a list
+                // (the tokenizer buffer is free now); pass 2 takes one slot per lane, so the L2 loads of the claim masks go
+                // out 32 at a time and the per-claim increments run on full warps.  Slots beyond the list go the direct way.
+                const int lb = min(sh.wcnt[warp], 18);
                 {
-                    uint32_t wd = lane, cur = 0u, base = 0u, cm = 0u;
-                    for (;;) {
-                        if (cm == 0u) {
-                            while (cur == 0u && wd < B6_HW) {
-                                cur = sh.hit[warp][wd];
-                                if (cur) sh.hit[warp][wd] = 0u;
-                                base = wd * 32u; wd += 32u;
-                            }
-                            if (cur == 0u) break;
-                            cm = __ldcg(&cmask[base + (__ffs(cur) - 1)]); cur &= cur - 1u;
-                            if (cm == 0u) continue;
+                    uint16_t* list = reinterpret_cast<uint16_t*>(&sh.wbuf[warp]);
+                    int* cnt = &sh.wcnt[warp];
+                    __syncwarp();
+                    if (lane == 0) *cnt = 0;
+                    __syncwarp();
+#pragma unroll
+                    for (uint32_t wd = lane; wd < B6_HW; wd += 32) {
+                        uint32_t bits = sh.hit[warp][wd];
+                        if (bits) {
+                            sh.hit[warp][wd] = 0u;
+                            int pos = atomicAdd(cnt, __popc(bits));
+                            const uint32_t base = wd * 32u - 1u;
+                            do {
+                                const uint32_t slot = base + __ffs(bits); bits &= bits - 1u;
+                                if (pos < B6_LIST) list[pos] = (uint16_t)slot;
+                                else { uint32_t cm = __ldcg(&cmask[slot]); while (cm) { atomicAdd(&sh.ov[warp][__ffs(cm) - 1], 1u); cm &= cm - 1u; } }
+                                pos++;
+                            } while (bits);
                         }
-                        atomicAdd(&sh.ov[warp][__ffs(cm) - 1], 1u); cm &= cm - 1u;
+                    }
+                    __syncwarp();
+                    const int nl = min(*(volatile int*)cnt, B6_LIST);
+                    for (int i0 = 0; i0 < nl; i0 += 64) {
+                        uint32_t cm0 = 0u, cm1 = 0u;
+                        if (i0 + lane < nl) cm0 = __ldcg(&cmask[list[i0 + lane]]);
+                        if (i0 + 32 + lane < nl) cm1 = __ldcg(&cmask[list[i0 + 32 + lane]]);
+                        while (cm0) { atomicAdd(&sh.ov[warp][__ffs(cm0) - 1], 1u); cm0 &= cm0 - 1u; }
+                        while (cm1) { atomicAdd(&sh.ov[warp][__ffs(cm1) - 1], 1u); cm1 &= cm1 - 1u; }
                     }
                 }
                 __syncwarp();
-                const int lb = min(sh.wcnt[warp], 18);
                 if (lane == 0 && p.len_fact && cg == c0) p.len_fact[f0 + f] = lb;
                 const uint32_t ov = sh.ov[warp][lane];
                 if (lane < ncg && ov > 0u) {

@@ -101,6 +101,8 @@ def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
         i = rng.randrange(max(1, len(f) - 60))
         claims.append(f[i:i + rng.randint(5, 60)])
     claims += ["".join(rng.choice(han) for _ in range(20)) for _ in range(6)]
+    claims = claims[:32]                                   # one claim group
+    facts = facts + ["。".join(claims), " ".join(claims) * 2]  # > 600 distinct hit slots in one fact (hit-list overflow path)
     n_sess = 3
     cu, co = packing.pack_texts(claims * n_sess)
     fu, fo = packing.pack_texts(facts * n_sess)
