@@ -398,13 +398,16 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
     if (use_global) { p.ghit = sc.alloc<uint32_t>((size_t)grid * hit_bytes / 4); if (!p.ghit) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
     BindParams p6 = p;
-    int* d_ovf = nullptr; int h_ovf = 0;
     if (fast) {
+        dvb_lease* l = sc.l;
+        if (!l->flag_h) {                                     // overflow flag: pinned + mapped, the kernel writes it in place
+            DVB_CUDA(ctx, cudaHostAlloc((void**)&l->flag_h, 64, cudaHostAllocMapped));
+            DVB_CUDA(ctx, cudaHostGetDevicePointer((void**)&l->flag_d, l->flag_h, 0));
+        }
+        *(volatile int*)l->flag_h = 0;
         p6.gtable = sc.alloc<unsigned long long>((size_t)grid6 * bind6_ws_u64_per_cta());
-        d_ovf = sc.alloc<int>(1);
-        if (!p6.gtable || !d_ovf) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
-        p6.overflow = d_ovf;
-        DVB_CUDA(ctx, cudaMemsetAsync(d_ovf, 0, 4, st));
+        if (!p6.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        p6.overflow = l->flag_d;
     }
     // one launch over sessions [s0, s1): fast kernel unless the call was routed to the general one
     auto launch = [&](bool use_fast, int64_t s0, int64_t s1) -> cudaError_t {
@@ -459,23 +462,25 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         const cudaError_t pe = run();
         if (pe != cudaSuccess) { if (n_slices > 1) cudaStreamSynchronize(cp); cudaStreamSynchronize(st); DVB_CUDA(ctx, pe); }
     }
-    if (fast) {                                             // a claim group that did not fit the fast tables: exact re-run
-        DVB_CUDA(ctx, cudaMemcpyAsync(&h_ovf, d_ovf, 4, cudaMemcpyDeviceToHost, st));
-        DVB_CUDA(ctx, cudaStreamSynchronize(st));
-        if (h_ovf) {
-            if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
-            DVB_CUDA(ctx, launch(false, 0, n_sessions));
-            if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
-        }
-    }
-    if (mem == DVB_MEM_HOST && n_claims) {
-        DVB_CUDA(ctx, cudaMemcpyAsync(out_best_fact, d_best, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));
-        DVB_CUDA(ctx, cudaMemcpyAsync(out_best_score, d_score, 8 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));
-        DVB_CUDA(ctx, cudaMemcpyAsync(out_bound, d_bound, (size_t)n_claims, cudaMemcpyDeviceToHost, st));
-        if (out_len_claim) DVB_CUDA(ctx, cudaMemcpyAsync(out_len_claim, d_lc, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st));
-        if (out_len_fact && n_facts) DVB_CUDA(ctx, cudaMemcpyAsync(out_len_fact, d_lf, 4 * (size_t)n_facts, cudaMemcpyDeviceToHost, st));
-    }
+    auto queue_host_out = [&]() -> cudaError_t {
+        cudaError_t e = cudaSuccess;
+        if (mem != DVB_MEM_HOST || !n_claims) return e;
+        if ((e = cudaMemcpyAsync(out_best_fact, d_best, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        if ((e = cudaMemcpyAsync(out_best_score, d_score, 8 * (size_t)n_claims, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        if ((e = cudaMemcpyAsync(out_bound, d_bound, (size_t)n_claims, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        if (out_len_claim && (e = cudaMemcpyAsync(out_len_claim, d_lc, 4 * (size_t)n_claims, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        if (out_len_fact && n_facts && (e = cudaMemcpyAsync(out_len_fact, d_lf, 4 * (size_t)n_facts, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
+        return e;
+    };
+    DVB_CUDA(ctx, queue_host_out());
     DVB_CUDA(ctx, cudaStreamSynchronize(st));
+    if (fast && *(volatile int*)sc.l->flag_h) {               // a claim group did not fit the fast tables: exact re-run
+        if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
+        DVB_CUDA(ctx, launch(false, 0, n_sessions));
+        if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
+        DVB_CUDA(ctx, queue_host_out());
+        DVB_CUDA(ctx, cudaStreamSynchronize(st));
+    }
     if (timing) { float ms = 0.f; DVB_CUDA(ctx, cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1)); ctx->last_ms = ms; }
     return DVB_OK;
 }

@@ -28,6 +28,8 @@ struct dvb_lease {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t copy = nullptr;         // H2D stream of pipelined host-buffer calls (created on first use)
     std::vector<cudaEvent_t> pipe_ev;    // one per in-flight input slice
+    int* flag_h = nullptr;               // pinned + mapped word a kernel can raise (read by the host after the stream sync)
+    int* flag_d = nullptr;
     bool busy = false;
 };
 
