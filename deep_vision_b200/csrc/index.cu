@@ -73,26 +73,68 @@ __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sy
     }
 }
 // exclusive scan of int32 counts into int64 offsets (single CTA; n is the number of chunks / blocks)
+#define IX_SCAN_PER 8
 static __global__ void __launch_bounds__(1024) k_ix_scan(const int32_t* __restrict__ cnt, int64_t* __restrict__ off, int64_t n) {
     __shared__ long long warp_tot[32];
     __shared__ long long carry;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = 0; base < n; base += 1024) {
-        const int64_t i = base + threadIdx.x;
-        long long v = i < n ? cnt[i] : 0, x = v;
+    for (int64_t base = 0; base < n; base += 1024 * IX_SCAN_PER) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * IX_SCAN_PER;
+        int32_t c[IX_SCAN_PER];
+        long long v = 0;
+#pragma unroll
+        for (int j = 0; j < IX_SCAN_PER; j++) { c[j] = i0 + j < n ? cnt[i0 + j] : 0; v += c[j]; }
+        long long x = v;
         for (int d = 1; d < 32; d <<= 1) { long long y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
         if (lane == 31) warp_tot[warp] = x;
         __syncthreads();
         long long before = carry;
         for (int w = 0; w < warp; w++) before += warp_tot[w];
-        if (i < n) off[i] = before + x - v;
+        long long run = before + x - v;
+#pragma unroll
+        for (int j = 0; j < IX_SCAN_PER; j++) { if (i0 + j < n) off[i0 + j] = run; run += c[j]; }
         __syncthreads();
         if (threadIdx.x == 1023) carry = before + x;
         __syncthreads();
     }
     if (threadIdx.x == 0) off[n] = carry;
+}
+
+// Large n: block sums -> single-CTA scan of the sums -> per-block local scan + base (three short parallel launches
+// instead of one long single-CTA loop).  tmp_sum: int32[nb], tmp_base: int64[nb + 1], nb = ceil(n / IX_SCAN_TILE).
+#define IX_SCAN_TILE 8192
+static __global__ void __launch_bounds__(256) k_ix_scan_sum(const int32_t* __restrict__ cnt, int64_t n, int32_t* __restrict__ bsum) {
+    __shared__ int s_sum;
+    if (threadIdx.x == 0) s_sum = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * IX_SCAN_TILE;
+    int v = 0;
+    for (int i = threadIdx.x; i < IX_SCAN_TILE; i += 256) if (base + i < n) v += cnt[base + i];
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s_sum, v);
+    __syncthreads();
+    if (threadIdx.x == 0) bsum[blockIdx.x] = s_sum;
+}
+static __global__ void __launch_bounds__(256) k_ix_scan_apply(const int32_t* __restrict__ cnt, int64_t n, const int64_t* __restrict__ bbase,
+                                                              int64_t* __restrict__ off, int64_t nb) {
+    __shared__ long long warp_tot[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t i0 = (int64_t)blockIdx.x * IX_SCAN_TILE + (int64_t)threadIdx.x * 32;      // 32 consecutive counts per thread
+    int32_t c[32];
+    long long v = 0;
+#pragma unroll
+    for (int j = 0; j < 32; j++) { c[j] = i0 + j < n ? cnt[i0 + j] : 0; v += c[j]; }
+    long long x = v;
+    for (int d = 1; d < 32; d <<= 1) { long long y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+    if (lane == 31) warp_tot[warp] = x;
+    __syncthreads();
+    long long run = bbase[blockIdx.x] + x - v;
+    for (int w = 0; w < warp; w++) run += warp_tot[w];
+#pragma unroll
+    for (int j = 0; j < 32; j++) { if (i0 + j < n) off[i0 + j] = run; run += c[j]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0) off[n] = bbase[nb];
 }
 
 // ---- K2c: run heads of equal keys.  Blocks of IX_HEAD_TILE postings: count heads, scan the block counts, write.
@@ -268,9 +310,9 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
         dvb_set_err(ctx, "dvb_chunk_index_build: bad offsets%s%s"); dvb_chunk_index_free(ix); return DVB_E_INVALID; }
     const int64_t nb = hoff[n_chunks];
     ix->n_bytes = nb;
-    uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr;
+    uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr; int64_t* d_scan = nullptr;
     unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
-    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFree(p); };
+    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFree(p); };
 #define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { drop(); IX_CUDA(ctx, ix, e2__); } } while (0)
     IX_TRY(cudaMalloc(&ix->sym, 2 * (size_t)nb + 64));
     IX_TRY(cudaMalloc(&ix->sym_off, 8 * (size_t)(n_chunks + 1)));
@@ -295,12 +337,19 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
         k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc, reinterpret_cast<int32_t*>(d_po));
         int32_t too_long = 0;
         IX_TRY(cudaMemcpyAsync(&too_long, d_po, 4, cudaMemcpyDeviceToHost, st));
-        k_ix_scan<<<1, 1024, 0, st>>>(d_pc, d_po, n_chunks);
+        {                                                    // exclusive scan of the per-chunk posting counts
+            const int64_t nsb = (n_chunks + IX_SCAN_TILE - 1) / IX_SCAN_TILE;
+            IX_TRY(cudaMalloc(&d_scan, 8 * (size_t)(nsb + 1) + 4 * (size_t)nsb + 16));
+            int64_t* d_sbase = d_scan; int32_t* d_ssum = reinterpret_cast<int32_t*>(d_scan + nsb + 1);
+            k_ix_scan_sum<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_ssum);
+            k_ix_scan<<<1, 1024, 0, st>>>(d_ssum, d_sbase, nsb);
+            k_ix_scan_apply<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_sbase, d_po, nsb);
+        }
         int64_t n_post = 0;
         IX_TRY(cudaMemcpyAsync(&n_post, d_po + n_chunks, 8, cudaMemcpyDeviceToHost, st));
         IX_TRY(cudaStreamSynchronize(st));
         if (too_long) { drop(); dvb_chunk_index_free(ix); dvb_set_err(ctx, "dvb_chunk_index_build: a chunk has more than 65535 characters%s%s"); return DVB_E_INVALID; }
-        ctx->launches += 2;
+        ctx->launches += 4;
         ix->n_post = n_post;
         if (mem == DVB_MEM_HOST) { cudaFree(d_text); d_text = nullptr; }
         if (n_post > 0) {

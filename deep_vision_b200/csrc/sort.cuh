@@ -1,14 +1,15 @@
 // sort.cuh — stable LSD radix sort of (u64 key, u32 value) pairs (kernel stage K2: index builds).
-// 8 bits per pass: per-block digit histogram -> per-digit scan over blocks -> stable scatter in which
-// every warp owns a contiguous sub-tile and ranks its 32 items per step with __match_any_sync.
+// 8 bits per pass: per-block digit histogram -> per-digit scan over blocks -> stable scatter staged through
+// shared memory (block-local digit sort, then contiguous digit runs to HBM).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #define RS_THREADS 256
 #define RS_WARPS 8
-#define RS_ITEMS_PER_WARP 1024
-#define RS_TILE (RS_WARPS * RS_ITEMS_PER_WARP)      // 8192 items per block
+#define RS_PER_LANE 16                              // items per lane, held in registers across the phases
+#define RS_ITEMS_PER_WARP (32 * RS_PER_LANE)
+#define RS_TILE (RS_WARPS * RS_ITEMS_PER_WARP)      // 4096 items per block
 
 static __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const unsigned long long* __restrict__ keys, int64_t n, int shift,
                                                          uint32_t* __restrict__ hist /*[256][nb]*/, int64_t nb) {
@@ -55,41 +56,76 @@ static __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* __restrict__ 
     }
 }
 
-static __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
-                                                            unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
-                                                            const uint32_t* __restrict__ hist, int64_t nb) {
-    __shared__ uint32_t cnt[RS_WARPS][256];
+// Stable scatter through shared memory: every lane loads its 16 keys once (independent loads, kept in registers),
+// the block ranks its 4096 items by digit (warps own contiguous sub-tiles, 32 items per step ranked with
+// __match_any_sync), places them digit-sorted in shared memory and then streams them out, so every digit leaves the
+// block as ONE contiguous run instead of 32-byte fragments: DRAM traffic = one read + one write of the data per pass.
+struct RsSmem {
+    unsigned long long key[RS_TILE];
+    uint32_t val[RS_TILE];
+    uint32_t cnt[RS_WARPS][256];     // per warp and digit: count, then block-local position of the warp's next item
+    uint32_t delta[256];             // global offset of the block's digit run minus its block-local start
+    uint32_t wsum[RS_WARPS];
+};
+static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                               unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
+                                                               const uint32_t* __restrict__ hist, int64_t nb) {
+    extern __shared__ __align__(16) unsigned char rs_raw[];
+    RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
+    const int64_t bbase = (int64_t)blockIdx.x * RS_TILE;
+    const int64_t wbase = bbase + (int64_t)warp * RS_ITEMS_PER_WARP;
+    unsigned long long k[RS_PER_LANE];
+    uint32_t v[RS_PER_LANE];
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; k[j] = g < n ? keys[g] : 0ULL; }
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; v[j] = g < n ? vals[g] : 0u; }
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&sm.cnt[0][0])[i] = 0;
     __syncthreads();
-    const int64_t wbase = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * RS_ITEMS_PER_WARP;
     // phase 1: per-warp digit counts
-    for (int s = 0; s < RS_ITEMS_PER_WARP; s += 32) {
-        const int64_t g = wbase + s + lane;
-        if (g < n) atomicAdd(&cnt[warp][(uint32_t)(keys[g] >> shift) & 255u], 1u);
-    }
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++)
+        if (wbase + j * 32 + lane < n) atomicAdd(&sm.cnt[warp][(uint32_t)(k[j] >> shift) & 255u], 1u);
     __syncthreads();
-    // phase 2: cnt[w][d] -> global offset of warp w's first item with digit d
+    // phase 2: thread d: block-local start of digit d (exclusive scan of the digit totals), per-warp positions, delta
     {
         const int d = threadIdx.x;
-        uint32_t run = hist[(int64_t)d * nb + blockIdx.x];
-        for (int w = 0; w < RS_WARPS; w++) { const uint32_t c = cnt[w][d]; cnt[w][d] = run; run += c; }
+        uint32_t tot = 0;
+        for (int w = 0; w < RS_WARPS; w++) tot += sm.cnt[w][d];
+        uint32_t x = tot;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) sm.wsum[warp] = x;
+        __syncthreads();
+        uint32_t before = 0;
+        for (int w = 0; w < warp; w++) before += sm.wsum[w];
+        const uint32_t lstart = before + x - tot;
+        uint32_t run = lstart;
+        for (int w = 0; w < RS_WARPS; w++) { const uint32_t c = sm.cnt[w][d]; sm.cnt[w][d] = run; run += c; }
+        sm.delta[d] = hist[(int64_t)d * nb + blockIdx.x] - lstart;
     }
     __syncthreads();
-    // phase 3: stable scatter, 32 items per step
-    for (int s = 0; s < RS_ITEMS_PER_WARP; s += 32) {
-        const int64_t g = wbase + s + lane;
-        const bool v = g < n;
-        const unsigned long long k = v ? keys[g] : 0ULL;
-        const uint32_t d = v ? ((uint32_t)(k >> shift) & 255u) : 256u + lane;      // invalid lanes never match
+    // phase 3: stable placement into shared memory, 32 items per step
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) {
+        const bool ok = wbase + j * 32 + lane < n;
+        const uint32_t d = ok ? ((uint32_t)(k[j] >> shift) & 255u) : 256u + lane;  // invalid lanes never match
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         uint32_t off = 0;
-        if (v) off = cnt[warp][d];
+        if (ok) off = sm.cnt[warp][d];
         __syncwarp();
-        if (v && rank == 0) cnt[warp][d] = off + __popc(peers);
+        if (ok && rank == 0) sm.cnt[warp][d] = off + __popc(peers);
         __syncwarp();
-        if (v) { okeys[off + rank] = k; ovals[off + rank] = vals[g]; }
+        if (ok) { sm.key[off + rank] = k[j]; sm.val[off + rank] = v[j]; }
+    }
+    __syncthreads();
+    // phase 4: stream the digit-sorted tile out; item i of digit d goes to delta[d] + i
+    const int cnt_tile = (int)min((int64_t)RS_TILE, n - bbase);
+    for (int i = threadIdx.x; i < cnt_tile; i += RS_THREADS) {
+        const unsigned long long kk = sm.key[i];
+        const uint32_t pos = sm.delta[(uint32_t)(kk >> shift) & 255u] + (uint32_t)i;
+        okeys[pos] = kk; ovals[pos] = sm.val[i];
     }
 }
 
@@ -99,6 +135,7 @@ static __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const unsigned
 static inline int dv_radix_sort_pairs(unsigned long long* keys, uint32_t* vals, unsigned long long* tkeys, uint32_t* tvals,
                                       int64_t n, int begin_bit, int end_bit, uint32_t* hist, cudaStream_t st, int64_t* launches) {
     if (n <= 1) return 0;
+    cudaFuncSetAttribute(k_rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
     const int64_t nb = (n + RS_TILE - 1) / RS_TILE;
     uint32_t* totals = hist + 256 * nb;
     int cur = 0;
@@ -108,7 +145,7 @@ static inline int dv_radix_sort_pairs(unsigned long long* keys, uint32_t* vals, 
         k_rs_hist<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, n, shift, hist, nb);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 0);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 1);
-        k_rs_scatter<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, iv, ok, ov, n, shift, hist, nb);
+        k_rs_scatter<<<(unsigned)nb, RS_THREADS, sizeof(RsSmem), st>>>(ik, iv, ok, ov, n, shift, hist, nb);
         if (launches) *launches += 4;
         cur ^= 1;
     }
