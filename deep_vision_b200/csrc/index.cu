@@ -38,6 +38,10 @@ struct dvb_index {
 __device__ __forceinline__ uint32_t ix_code(uint32_t s) { return s >= 0x8000u ? 20992u + (s & 0x7FFFu) : s; }     // 15-bit symbol code
 __device__ __forceinline__ bool ix_same_class(uint32_t a, uint32_t b) { return a != 0u && b != 0u && ((a ^ b) & 0x8000u) == 0u; }
 __device__ __forceinline__ uint32_t ix_pair_key(uint32_t a, uint32_t b) { return (ix_code(a) << 15) | ix_code(b); }
+// A pair's posting list is sub-ordered by the low bits of the symbol AFTER the pair (sort key = pair << 2 | next & 3):
+// a term that continues past the pair only streams the quarter of the list its own next symbol selects.
+#define IX_SUB_BITS 2
+#define IX_SUB_MASK 3u
 
 // ---- K2a: count, then emit postings (one warp per chunk)
 __global__ void __launch_bounds__(256) k_ix_count(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
@@ -65,7 +69,7 @@ __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sy
             const uint32_t bal = __ballot_sync(0xffffffffu, v);
             if (v) {
                 const int64_t o = w + __popc(bal & ((1u << lane) - 1u));
-                pk[o] = ((unsigned long long)c << 32) | ix_pair_key(a, b);
+                pk[o] = ((unsigned long long)c << 32) | (ix_pair_key(a, b) << IX_SUB_BITS) | (nx & IX_SUB_MASK);
                 pv[o] = (uint32_t)i | (nx << 16);                  // position | the symbol AFTER the pair (0 = none / separator)
             }
             w += __popc(bal);
@@ -189,16 +193,23 @@ __global__ void __launch_bounds__(256) k_ix_plan(const uint16_t* __restrict__ te
         int64_t best_lo = 0, best_hi = 0; int32_t best_j = -1; int64_t best_df = -1;
         bool usable = false, bad = L < 2;
         for (int32_t j = 0; j < L; j++) bad |= ts[j] == 0;
-        for (int32_t j = 0; j + 1 < L && !bad; j++) {
+        // L >= 3: only pairs that are followed by a term symbol (one chunk-ordered sub-list); L == 2: the pair's four sub-lists
+        for (int32_t j = 0; j + 1 < L && (j + 2 < L || L == 2) && !bad; j++) {
             if (!ix_same_class(ts[j], ts[j + 1])) continue;
             usable = true;
-            const uint32_t key = ix_pair_key(ts[j], ts[j + 1]);
+            const bool nxt = j + 2 < L, covered = j == 0 && L <= 3;
+            const uint32_t k30 = ix_pair_key(ts[j], ts[j + 1]) << IX_SUB_BITS;
+            const uint64_t key_lo = nxt ? (k30 | (ts[j + 2] & IX_SUB_MASK)) : k30;
+            const uint64_t key_hi = nxt ? key_lo + 1 : (uint64_t)k30 + IX_SUB_MASK + 1;      // exclusive
             int64_t lo = 0, hi = n_keys;
-            while (lo < hi) { const int64_t m = (lo + hi) >> 1; if (ukeys[m] < key) lo = m + 1; else hi = m; }
-            int64_t a = 0, b = 0;
-            if (lo < n_keys && ukeys[lo] == key) { a = uoff[lo]; b = uoff[lo + 1]; }
-            // a pair followed by another term symbol is filtered by the posting's look-ahead symbol (~1/50 survive): weigh it
-            const int64_t cost = (j + 2 < L) ? (b - a + 31) / 32 : (b - a);
+            while (lo < hi) { const int64_t m = (lo + hi) >> 1; if (ukeys[m] < key_lo) lo = m + 1; else hi = m; }
+            int64_t lo2 = lo, hi2 = n_keys;
+            while (lo2 < hi2) { const int64_t m = (lo2 + hi2) >> 1; if (ukeys[m] < key_hi) lo2 = m + 1; else hi2 = m; }
+            const int64_t a = n_keys > 0 ? uoff[lo] : 0, b = n_keys > 0 ? uoff[lo2] : 0;
+            // cost in bytes: every posting of the pair is streamed (12 B); a candidate that is not decided by the pair and
+            // the posting's look-ahead symbol alone costs two random sectors (chunk offset + symbols).  The look-ahead
+            // symbol lets ~1/50 of the postings through.
+            const int64_t cost = (b - a) * 12 + (covered ? 0 : (nxt ? (b - a) * 64 / 12 : (b - a) * 64));
             if (best_df < 0 || cost < best_df) { best_df = cost; best_lo = a; best_hi = b; best_j = j; }
             if (b == a) break;                                    // a pair that occurs nowhere: the term occurs nowhere
         }
@@ -234,26 +245,55 @@ __global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* 
         const int32_t L = term_off[t + 1] - term_off[t], j = plan_j[t];
         const int64_t lo = plan_lo[t], hi = plan_hi[t];
         const int64_t r_lo = lo + (w - item_off[t]) * IX_ITEM, r_hi = min(hi, r_lo + IX_ITEM);
-        const bool use_next = j + 2 < L;
+        const bool use_next = j + 2 < L, covered = j == 0 && L <= 3;
+        // L == 2 walks all four sub-lists of the pair (each chunk-ordered, not the whole range): occurrences are counted
+        // additively.  "xy" cannot overlap itself; "xx" is counted per RUN of x at the run's last pair (look-ahead != x):
+        // a run of r symbols holds floor(r / 2) non-overlapping occurrences, which is what the greedy scan would count.
+        const bool pair_only = L == 2, same2 = pair_only && ts[0] == ts[1];
         const uint32_t next_sym = use_next ? ts[j + 2] : 0u;
         const int64_t skip_chunk = r_lo > lo ? (int64_t)(ix.pk[r_lo - 1] >> 32) : -1;      // owned by the previous item
         const int64_t last_chunk = (int64_t)(ix.pk[r_hi - 1] >> 32);                       // ours to finish
-        if (r_lo > lo && skip_chunk == last_chunk) continue;       // the whole item lies inside a chunk the previous item owns
+        if (!pair_only && r_lo > lo && skip_chunk == last_chunk) continue;   // the whole item lies inside a chunk the previous item owns
         int64_t cur = -1; int32_t cnt = 0, last_end = 0;
-        bool more = true;
+        bool more = true, leading = r_lo > lo;                     // still inside the run of postings the previous item owns
         for (int64_t p0 = r_lo; p0 < hi && more; p0 += 32) {
             const int64_t p = p0 + lane;
-            int64_t chunk = -2; int32_t start = 0; bool match = false, beyond = false;
+            int64_t chunk = -2; int32_t start = 0, wgt = 0; bool beyond = false;
+            uint32_t v = 0;
+            if (p < hi) { v = ix.pv[p]; chunk = (int64_t)(ix.pk[p] >> 32); }
+            bool skip = false;
+            if (leading) {                                         // only the LEADING postings of skip_chunk are skipped (a pair's
+                const uint32_t other = __ballot_sync(0xffffffffu, p < hi && chunk != skip_chunk);   // sub-lists restart the chunk order)
+                skip = other ? lane < __ffs(other) - 1 : true;
+                if (other) leading = false;
+            }
             if (p < hi) {
-                const uint32_t v = ix.pv[p];
-                chunk = (int64_t)(ix.pk[p] >> 32); start = (int32_t)(v & 0xFFFFu) - j;
+                start = (int32_t)(v & 0xFFFFu) - j;
                 beyond = p >= r_hi && chunk != last_chunk;          // first posting of a chunk the next item owns
-                if (!beyond && chunk != skip_chunk && (!use_next || (v >> 16) == next_sym) && start >= 0 && start + L <= ix.sym_cnt[chunk]) {
-                    const uint16_t* s = ix.sym + ix.sym_off[chunk] + start;
-                    match = true;
-                    for (int32_t d = 0; d < L && match; d++) match = s[d] == ts[d];
+                if (!beyond && !skip && start >= 0) {
+                    if (pair_only) {
+                        if (!same2) wgt = 1;
+                        else if ((v >> 16) != ts[0]) {
+                            const uint16_t* s = ix.sym + ix.sym_off[chunk];
+                            int32_t q = start, r = 2;
+                            while (q > 0 && s[q - 1] == ts[0]) { q--; r++; }
+                            wgt = r >> 1;
+                        }
+                    } else if ((v >> 16) == next_sym) {
+                        // the pair and the look-ahead symbol are already matched: only the rest of the term is read back,
+                        // and the chunk length only when the term reaches past the look-ahead symbol
+                        if (covered) wgt = 1;
+                        else if (j + 3 >= L || start + L <= ix.sym_cnt[chunk]) {
+                            const uint16_t* s = ix.sym + ix.sym_off[chunk] + start;
+                            bool match = true;
+                            for (int32_t d = 0; d < j && match; d++) match = s[d] == ts[d];
+                            for (int32_t d = j + 3; d < L && match; d++) match = s[d] == ts[d];
+                            wgt = match ? 1 : 0;
+                        }
+                    }
                 }
             }
+            const bool match = wgt > 0;
             // postings are ordered by chunk: everything after the first `beyond` posting is beyond too
             const uint32_t bey = __ballot_sync(0xffffffffu, beyond);
             uint32_t bal = __ballot_sync(0xffffffffu, match);
@@ -262,11 +302,13 @@ __global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* 
                 const int src = __ffs(bal) - 1; bal &= bal - 1;
                 const int64_t cb = __shfl_sync(0xffffffffu, chunk, src);
                 const int32_t sb = __shfl_sync(0xffffffffu, start, src);
+                const int32_t wb = __shfl_sync(0xffffffffu, wgt, src);
                 if (cb != cur) {
                     if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);
                     cur = cb; cnt = 0; last_end = -2147483647;
                 }
-                if (sb >= last_end) { cnt++; last_end = sb + L; }
+                if (pair_only) cnt += wb;
+                else if (sb >= last_end) { cnt++; last_end = sb + L; }
             }
         }
         if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);

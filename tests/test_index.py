@@ -16,7 +16,10 @@ def test_gpu_index_topk_matches_python_count(gpu_ctx):
     from deep_vision_b200 import reference_material as rm
     chunks, queries = make_corpus(n_chunks=777, nq=25, seed=4)
     chunks += ["aaaa", "AAAAA_aaaa", "abababab x abab", "离线离线离线离线离", "x" * 3000 + "审批" * 700, "", "   ", "İstanbul Kelvin K"]
+    chunks += ["xx" * 40 + "y" + "x" * 41 + " xxy xxz xx9 xx", ("审审批" * 900)[:2700], "批审" * 1200 + "审审审审审"]
     queries += [["aa"], ["abab", "ab"], ["离线离", "离线"], ["审批", "审批审批审批"], ["zzzz"], ["aaaa", "aa", "a_"], ["istanbul", "kelvin"], ["st"]]
+    # 2-symbol terms walk all four next-symbol sub-lists of their pair; "xx"-type terms are counted per run
+    queries += [["xx"], ["xx", "xxx", "xy"], ["审审"], ["批审", "审批"], ["审审", "审审审"], ["ab", "ba"]]
     ix = rm.ChunkIndex(chunks, index_base=1000, ctx=gpu_ctx)
     st = ix.stats()
     assert st["n_chunks"] == len(chunks) and st["postings"] > 0 and st["pair_keys"] > 0
