@@ -16,6 +16,11 @@ extern "C" int32_t dvb_create(int32_t device, dvb_ctx** out) {
         c->num_sm = prop.multiProcessorCount;
         c->smem_optin = prop.sharedMemPerBlockOptin;
     }
+    {                                                    // index builds allocate stream-ordered from the default pool: keep freed blocks
+        cudaMemPool_t pool; unsigned long long keep = ~0ULL;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        cudaGetLastError();
+    }
     for (int i = 0; i < DVB_LEASES; i++) {
         if (cudaStreamCreateWithFlags(&c->leases[i].stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreate(&c->leases[i].ev0) != cudaSuccess || cudaEventCreate(&c->leases[i].ev1) != cudaSuccess) {

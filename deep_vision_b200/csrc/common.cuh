@@ -90,6 +90,9 @@ struct dvb_scope {
         l->arena.base = nullptr; l->arena.cap = 0;
         size_t want = bytes + (bytes >> 2);
         if (cudaMalloc(&l->arena.base, want) != cudaSuccess) {
+            cudaGetLastError();
+            cudaMemPool_t pool;                                  // give cached pool blocks (index builds) back and retry
+            if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
             if (cudaMalloc(&l->arena.base, bytes) != cudaSuccess) { cudaGetLastError(); dvb_set_err(ctx, "out of device memory%s%s"); return DVB_E_NOMEM; }
             want = bytes;
         }

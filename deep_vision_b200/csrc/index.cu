@@ -354,26 +354,26 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
     ix->n_bytes = nb;
     uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr; int64_t* d_scan = nullptr;
     unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
-    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFree(p); };
+    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFreeAsync(p, st); };
 #define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { drop(); IX_CUDA(ctx, ix, e2__); } } while (0)
-    IX_TRY(cudaMalloc(&ix->sym, 2 * (size_t)nb + 64));
-    IX_TRY(cudaMalloc(&ix->sym_off, 8 * (size_t)(n_chunks + 1)));
-    IX_TRY(cudaMalloc(&ix->sym_cnt, 4 * (size_t)n_chunks + 4));
+    IX_TRY(cudaMallocAsync((void**)&ix->sym, 2 * (size_t)nb + 64, st));
+    IX_TRY(cudaMallocAsync((void**)&ix->sym_off, 8 * (size_t)(n_chunks + 1), st));
+    IX_TRY(cudaMallocAsync((void**)&ix->sym_cnt, 4 * (size_t)n_chunks + 4, st));
     IX_TRY(cudaMemcpyAsync(ix->sym_off, hoff.data(), 8 * (size_t)(n_chunks + 1), cudaMemcpyHostToDevice, st));
     const bool timing = ctx->timing.load() != 0;
     if (timing) IX_TRY(cudaEventRecord(sc.l->ev0, st));
     if (n_chunks > 0) {
         const uint8_t* d_utf8 = utf8 + o0;
         if (mem == DVB_MEM_HOST) {
-            IX_TRY(cudaMalloc(&d_text, (size_t)nb + 64));
+            IX_TRY(cudaMallocAsync((void**)&d_text, (size_t)nb + 64, st));
             IX_TRY(cudaMemcpyAsync(d_text, utf8 + o0, (size_t)nb, cudaMemcpyHostToDevice, st));
             d_utf8 = d_text;
         }
         // K1: symbols (sym_off doubles as the rebased byte offsets the symboliser reads)
         dv_launch_symbolize(ctx, st, d_utf8, ix->sym_off, n_chunks, ix->sym, ix->sym_cnt);
         // K2a: postings
-        IX_TRY(cudaMalloc(&d_pc, 4 * (size_t)n_chunks + 4));
-        IX_TRY(cudaMalloc(&d_po, 8 * (size_t)(n_chunks + 1)));
+        IX_TRY(cudaMallocAsync((void**)&d_pc, 4 * (size_t)n_chunks + 4, st));
+        IX_TRY(cudaMallocAsync((void**)&d_po, 8 * (size_t)(n_chunks + 1), st));
         const int grid = (int)std::min<int64_t>((n_chunks + 7) / 8, (int64_t)ctx->num_sm * 16);
         IX_TRY(cudaMemsetAsync(d_po, 0, 8, st));                   // d_po[0] doubles as the error flag until the scan overwrites it
         k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc, reinterpret_cast<int32_t*>(d_po));
@@ -381,7 +381,7 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
         IX_TRY(cudaMemcpyAsync(&too_long, d_po, 4, cudaMemcpyDeviceToHost, st));
         {                                                    // exclusive scan of the per-chunk posting counts
             const int64_t nsb = (n_chunks + IX_SCAN_TILE - 1) / IX_SCAN_TILE;
-            IX_TRY(cudaMalloc(&d_scan, 8 * (size_t)(nsb + 1) + 4 * (size_t)nsb + 16));
+            IX_TRY(cudaMallocAsync((void**)&d_scan, 8 * (size_t)(nsb + 1) + 4 * (size_t)nsb + 16, st));
             int64_t* d_sbase = d_scan; int32_t* d_ssum = reinterpret_cast<int32_t*>(d_scan + nsb + 1);
             k_ix_scan_sum<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_ssum);
             k_ix_scan<<<1, 1024, 0, st>>>(d_ssum, d_sbase, nsb);
@@ -393,12 +393,12 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
         if (too_long) { drop(); dvb_chunk_index_free(ix); dvb_set_err(ctx, "dvb_chunk_index_build: a chunk has more than 65535 characters%s%s"); return DVB_E_INVALID; }
         ctx->launches += 4;
         ix->n_post = n_post;
-        if (mem == DVB_MEM_HOST) { cudaFree(d_text); d_text = nullptr; }
+        if (mem == DVB_MEM_HOST) { cudaFreeAsync(d_text, st); d_text = nullptr; }
         if (n_post > 0) {
             const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
-            IX_TRY(cudaMalloc(&ix->pk, 8 * (size_t)n_post)); IX_TRY(cudaMalloc(&ix->pv, 4 * (size_t)n_post));
-            IX_TRY(cudaMalloc(&t_pk, 8 * (size_t)n_post)); IX_TRY(cudaMalloc(&t_pv, 4 * (size_t)n_post));
-            IX_TRY(cudaMalloc(&d_hist, 4 * (size_t)(256 * nbk + 256)));
+            IX_TRY(cudaMallocAsync((void**)&ix->pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&ix->pv, 4 * (size_t)n_post, st));
+            IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
+            IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * (size_t)(256 * nbk + 256), st));
             k_ix_emit<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_po, ix->pk, ix->pv);
             ctx->launches += 1;
             // K2b: stable sort by the 30 key bits (32 = 4 passes of 8)
@@ -408,14 +408,14 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
             if (which) { std::swap(ix->pk, t_pk); std::swap(ix->pv, t_pv); }
             // K2c: segment heads
             const int64_t nhb = (n_post + IX_HEAD_TILE - 1) / IX_HEAD_TILE;
-            IX_TRY(cudaMalloc(&d_bc, 4 * (size_t)nhb + 4)); IX_TRY(cudaMalloc(&d_bo, 8 * (size_t)(nhb + 1)));
+            IX_TRY(cudaMallocAsync((void**)&d_bc, 4 * (size_t)nhb + 4, st)); IX_TRY(cudaMallocAsync((void**)&d_bo, 8 * (size_t)(nhb + 1), st));
             k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bc);
             k_ix_scan<<<1, 1024, 0, st>>>(d_bc, d_bo, nhb);
             int64_t n_keys = 0;
             IX_TRY(cudaMemcpyAsync(&n_keys, d_bo + nhb, 8, cudaMemcpyDeviceToHost, st));
             IX_TRY(cudaStreamSynchronize(st));
             ix->n_keys = n_keys;
-            IX_TRY(cudaMalloc(&ix->ukeys, 4 * (size_t)n_keys + 4)); IX_TRY(cudaMalloc(&ix->uoff, 8 * (size_t)(n_keys + 1)));
+            IX_TRY(cudaMallocAsync((void**)&ix->ukeys, 4 * (size_t)n_keys + 4, st)); IX_TRY(cudaMallocAsync((void**)&ix->uoff, 8 * (size_t)(n_keys + 1), st));
             k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bo, ix->ukeys, ix->uoff);
             IX_TRY(cudaMemcpyAsync(ix->uoff + n_keys, &n_post, 8, cudaMemcpyHostToDevice, st));
             ctx->launches += 3;
