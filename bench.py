@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--turns", type=int, default=40)
     ap.add_argument("--claims", type=int, default=24)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--index-chunks", type=int, default=200000,
+                    help="chunks per GPU of the bounded config-3 sample behind the `index` key (0 = skip)")
     return ap.parse_args()
 
 
@@ -51,6 +53,43 @@ def workload_config(args, world):
             "sessions_per_gpu": args.sessions, "turns": args.turns, "claims_per_session": args.claims,
             "parallelism": "session-sharded x%d (no collective)" % world,
             "l2_policy": "inputs (0.88 GB/GPU) larger than L2; no flush needed"}
+
+
+def index_arm(ctx, args, rank):
+    """BASELINE metric part 2, chunks indexed/s: a bounded config-3 sample (512-char chunks resident in HBM ->
+    dvb_chunk_index_build -> a queryable positional index), plus the indexed top-8 of 1000 claim queries over it.
+    Returns this rank's numbers; the caller reduces over ranks."""
+    import torch
+    from deep_vision_b200 import _lib, reference_material as rm, synth
+    n = args.index_chunks
+    data, off = synth.make_texts(n, 512, seed=synth.SEED + 1000 + rank)
+    d_data, d_off = torch.from_numpy(data).cuda(), torch.from_numpy(off).cuda()
+    builds, ix = [], None
+    for _ in range(4):                                            # the first build grows the allocation pool
+        if ix is not None:
+            ix.close()
+        torch.cuda.synchronize()
+        ix = rm.ChunkIndex(device_ptrs=(d_data.data_ptr(), d_off.data_ptr(), n), index_base=rank * n, ctx=ctx)
+        builds.append(ix.build_ms)
+    st = ix.stats()
+    qdata, qoff = synth.make_texts(1000, 45, seed=999)
+    raw, qraw = data.tobytes(), qdata.tobytes()
+    rng = np.random.default_rng(7)
+    terms = []
+    for q in range(1000):
+        text = qraw[qoff[q]:qoff[q + 1]].decode("utf-8")
+        if q % 2 == 0:                                            # half of every other query is copied from a chunk
+            c = int(rng.integers(0, n)); src = raw[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, 488))
+            text = text[:22] + src[a:a + 22]
+        terms.append(rm._tokenize_reference_material_query(text))
+    q_ms = []
+    for _ in range(3):
+        ix.topk(terms, 8)
+        q_ms.append(ctx.last_kernel_ms)
+    ix.close()
+    best = min(builds[1:])
+    return {"chunks_per_gpu": n, "build_ms": best, "first_build_ms": builds[0], "postings": st["postings"],
+            "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"], "query_ms_1000_queries": min(q_ms)}
 
 
 class ClockSampler:
@@ -269,6 +308,27 @@ def main():
     h2d = int(sum(a.nbytes for a in host_in)) - 64 * 2
     d2h = n_claims * (4 + 8 + 1)
 
+    # ---------------- chunks indexed/s on a bounded config-3 sample (every rank indexes its own shard)
+    index = None
+    if args.index_chunks > 0:
+        try:
+            mine = index_arm(ctx, args, rank)
+        except Exception as exc:                                  # the headline line must survive a failure here
+            mine = {"error": repr(exc)[:200]}
+        ok = reduce_max(1.0 if "error" in mine else 0.0) == 0.0
+        if ok:
+            b_ms, q_ms = reduce_max(mine["build_ms"]), reduce_max(mine["query_ms_1000_queries"])
+            peak_i, _src = measured_peak()
+            index = {"metric": "chunks_indexed_per_s", "value": world * mine["chunks_per_gpu"] / (b_ms / 1000.0), "unit": "chunks/s",
+                     "workload": "config3 sample: %d chunks/GPU x 512 chars resident in HBM -> positional index (dvb_chunk_index_build)" % mine["chunks_per_gpu"],
+                     "build_ms": b_ms, "first_build_ms": mine["first_build_ms"], "postings_per_gpu": mine["postings"],
+                     "roofline": {"bound": "hbm", "achieved": mine["algorithmic_bytes"] / (b_ms / 1000.0) / 1e9, "peak": peak_i, "unit": "GB/s",
+                                  "frac": mine["algorithmic_bytes"] / (b_ms / 1000.0) / 1e9 / peak_i,
+                                  "algorithmic_bytes": mine["algorithmic_bytes"], "note": "UTF-8 in + 4 B per posting (SURVEY 8d); the build is 4 radix passes over 12 B postings"},
+                     "query": {"effective_pairs_per_s": world * mine["chunks_per_gpu"] * 1000 / (q_ms / 1000.0), "ms_per_1000_queries": q_ms, "k": 8}}
+        else:
+            index = {"error": mine.get("error", "failed on another rank")}
+
     pairs_all = corpus.n_pairs * world
     value = pairs_all * args.steps / (elapsed_ms / 1000.0)
     e2e_value = pairs_all * e2e_steps / (e2e_ms / 1000.0)
@@ -290,6 +350,8 @@ def main():
                              "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src},
                 "clocks": clocks,
                 "pairs_per_step_per_gpu": corpus.n_pairs}
+        if index is not None:
+            line["index"] = index
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             v, secs = cpu_baseline(corpus, cores)
