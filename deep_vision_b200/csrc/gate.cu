@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
                                                               const int32_t* __restrict__ ccnt, int64_t n_cand,
                                                               const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
                                                               const int32_t* __restrict__ hcnt, int64_t n_hist, int32_t tile_h, double thr,
-                                                              int64_t* __restrict__ out) {
+                                                              int64_t* __restrict__ out, int32_t flagged_only) {
     __shared__ long long s_best;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int acc_words = (tile_h + 1) >> 1;
@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
     }
     __syncthreads();
     for (int64_t c = blockIdx.x; c < n_cand; c += gridDim.x) {
+        if (flagged_only && out[c] != -2) continue;                // k_gate_match_prefix already answered this candidate
         const int32_t L = ccnt[c];
         const unsigned long long* ck = ckeys + ccap_off[c];
         if (threadIdx.x == 0) s_best = -1;
@@ -224,6 +225,105 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
         }
         if (threadIdx.x == 0) out[c] = s_best;
         __syncthreads();
+    }
+}
+
+
+// ---- prefix-filtered match (threshold > 0): one WARP per candidate.
+// J(L, R) >= t implies |L & R| >= t |L u R| >= t |L|, so R shares one of ANY |L| - ceil(t |L|) + 1 keys of L (pigeonhole):
+// only the RAREST keys of the candidate (shortest posting lists) generate history ids, a size bound and "not above the
+// best match so far" prune them, and the survivors are verified exactly (|L & R| by probing R's keys in a shared-memory
+// set of L's keys, then the reference's fp64 test).  One key of slack keeps the bound safe against the rounding of the
+// fp64 division.  Candidates with more than GP_MAXL keys are flagged (-2) for k_gate_match.
+#define GP_MAXL 128
+#define GP_SET 256
+struct GpWarp {
+    unsigned long long key[GP_MAXL];
+    unsigned long long set[GP_SET];
+    uint32_t lo[GP_MAXL], df[GP_MAXL], cum[GP_MAXL + 1];
+    uint16_t plist[GP_MAXL];
+};
+__global__ void __launch_bounds__(256) k_gate_match_prefix(const unsigned long long* __restrict__ ckeys, const int64_t* __restrict__ ccap_off,
+                                                             const int32_t* __restrict__ ccnt, int64_t n_cand,
+                                                             const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
+                                                             const unsigned long long* __restrict__ hkeys, const int64_t* __restrict__ hcap_off,
+                                                             const int32_t* __restrict__ hcnt, double thr, int64_t* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char gp_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    GpWarp& W = reinterpret_cast<GpWarp*>(gp_raw)[warp];
+    for (int64_t c = (int64_t)blockIdx.x * 8 + warp; c < n_cand; c += (int64_t)gridDim.x * 8) {
+        const int32_t L = ccnt[c];
+        if (L <= 0) { if (lane == 0) out[c] = -1; continue; }
+        if (L > GP_MAXL) { if (lane == 0) out[c] = -2; continue; }
+        const unsigned long long* ck = ckeys + ccap_off[c];
+        __syncwarp();
+        for (int i = lane; i < GP_SET; i += 32) W.set[i] = ~0ULL;
+        __syncwarp();
+        for (int j = lane; j < L; j += 32) {
+            const unsigned long long key = ck[j];
+            W.key[j] = key;
+            uint32_t sl = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 56);
+            while (atomicCAS(&W.set[sl], ~0ULL, key) != ~0ULL) sl = (sl + 1) & (GP_SET - 1);        // keys are distinct
+            int64_t a = 0, b = n_pairs;
+            while (a < b) { const int64_t m = (a + b) >> 1; if (pk[m] < key) a = m + 1; else b = m; }
+            int64_t a2 = a, b2 = n_pairs;
+            while (a2 < b2) { const int64_t m = (a2 + b2) >> 1; if (pk[m] <= key) a2 = m + 1; else b2 = m; }
+            W.lo[j] = (uint32_t)a; W.df[j] = (uint32_t)(a2 - a);
+        }
+        __syncwarp();
+        int alpha = (int)ceil(thr * (double)L) - 1; if (alpha < 1) alpha = 1;
+        int np_keys = L - alpha + 1; if (np_keys < 1) np_keys = 1; if (np_keys > L) np_keys = L;
+        // the np_keys rarest keys: rank by (df, position)
+        int n_pref = 0; uint32_t run = 0;
+        for (int j0 = 0; j0 < L; j0 += 32) {
+            const int j = j0 + lane;
+            bool in = false; uint32_t d = 0;
+            if (j < L) {
+                d = W.df[j];
+                int rank = 0;
+                for (int i = 0; i < L; i++) { const uint32_t di = W.df[i]; rank += (di < d || (di == d && i < j)) ? 1 : 0; }
+                in = rank < np_keys && d > 0;                      // a key without postings generates nothing
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, in);
+            uint32_t x = in ? d : 0u;                              // inclusive scan of the kept posting counts
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+            if (in) { const int slot = n_pref + __popc(bal & ((1u << lane) - 1u)); W.plist[slot] = (uint16_t)j; W.cum[slot + 1] = run + x; }
+            run += __shfl_sync(0xffffffffu, x, 31);
+            n_pref += __popc(bal);
+        }
+        if (lane == 0) W.cum[0] = 0;
+        __syncwarp();
+        const uint32_t total = run;
+        long long best = -1;
+        for (uint32_t base = 0; base < total; base += 32) {
+            const uint32_t idx = base + lane;
+            long long cand = -1;
+            if (idx < total) {
+                int a = 0, b = n_pref;                             // last m with cum[m] <= idx
+                while (b - a > 1) { const int m = (a + b) >> 1; if (W.cum[m] <= idx) a = m; else b = m; }
+                const int j = W.plist[a];
+                const long long h = pv[(int64_t)W.lo[j] + W.df[j] - 1 - (idx - W.cum[a])];    // most recent history ids first
+                if (h > best) {
+                    const int32_t hc = hcnt[h];
+                    const int32_t mn = hc < L ? hc : L;
+                    int32_t un0 = L + hc - mn; if (un0 < 1) un0 = 1;
+                    if (__ddiv_rn((double)mn, (double)un0) >= thr) {                          // size bound
+                        const unsigned long long* hk = hkeys + hcap_off[h];
+                        int32_t inter = 0;
+                        for (int32_t i = 0; i < hc; i++) {
+                            const unsigned long long key = hk[i];
+                            uint32_t sl = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 56);
+                            for (;;) { const unsigned long long v = W.set[sl]; if (v == key) { inter++; break; } if (v == ~0ULL) break; sl = (sl + 1) & (GP_SET - 1); }
+                        }
+                        int32_t un = L + hc - inter; if (un < 1) un = 1;
+                        if (inter > 0 && __ddiv_rn((double)inter, (double)un) >= thr) cand = h;
+                    }
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) { const long long v = __shfl_xor_sync(0xffffffffu, cand, o); cand = v > cand ? v : cand; }
+            best = cand > best ? cand : best;
+        }
+        if (lane == 0) out[c] = best;
     }
 }
 
@@ -417,7 +517,17 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     const int grid = (int)std::min<int64_t>(n_cand, (int64_t)ctx->num_sm * std::max(1, occ));
     const bool timing = ctx->timing.load() != 0;
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
-    k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out);
+    const char* force = getenv("DVB_GATE_KERNEL");
+    const bool prefix = threshold > 0.0 && n_pairs > 0 && !(force && !strcmp(force, "dense"));
+    if (prefix) {
+        const size_t smem_p = 8 * sizeof(GpWarp);
+        DVB_CUDA(ctx, cudaFuncSetAttribute(k_gate_match_prefix, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+        const int grid_p = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)ctx->num_sm * 32);
+        k_gate_match_prefix<<<grid_p, 256, smem_p, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hk, d_hcap, d_hc, threshold, d_out);
+        ctx->launches += 1;
+    }
+    // dense counters: everything when the prefix filter does not apply, else only the candidates it flagged (> GP_MAXL keys)
+    k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out, prefix ? 1 : 0);
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
     ctx->launches += 1;
     rc = io.finish(ctx);

@@ -64,6 +64,43 @@ def test_gpu_gate_vs_oracle_random(gpu_ctx, oracle):
 
 
 @pytest.mark.gpu
+def test_gpu_gate_prefix_filter_equals_dense_counters(gpu_ctx, oracle, monkeypatch):
+    """threshold > 0 runs k_gate_match_prefix (rarest-keys candidate generation + exact verification); DVB_GATE_KERNEL=dense
+    forces the dense-counter kernel.  Same answers on near-duplicates, repeated history, very long questions
+    (> 128 keys: flagged to the dense kernel) and thresholds from 0.01 to above 1; a sample also against the oracle."""
+    from deep_vision_b200 import question_similarity as qs
+    rng = np.random.default_rng(21)
+    han = [chr(0x4E00 + int(x)) for x in rng.integers(0, 400, size=4000)]
+    def q(n):
+        i = int(rng.integers(0, len(han) - n))
+        return "".join(han[i:i + n])
+    hist = [q(int(rng.integers(1, 45))) for _ in range(3000)]
+    hist += hist[:200]                                              # repeated history: the LAST index must win
+    hist += [q(300), q(200) + "abc" * 40]
+    cands = []
+    for i in range(6000):
+        r = rng.random()
+        if r < 0.3:
+            h = hist[int(rng.integers(0, len(hist)))]
+            k = int(rng.integers(0, max(1, len(h))))
+            cands.append(h[:k] + q(int(rng.integers(0, 4))) + h[k + int(rng.integers(0, 3)):])      # small edit of a history item
+        elif r < 0.35:
+            cands.append(hist[-1][5:] if r < 0.32 else hist[-2][: 250])                              # > 128 keys
+        else:
+            cands.append(q(int(rng.integers(0, 45))))
+    gate = qs.QuestionGate(ctx=gpu_ctx)
+    og = oracle.Gate(gate.synonyms, gate.stopwords)
+    for thr in (0.62, 0.01, 0.2, 0.5, 0.9, 1.0, 1.5):
+        fast = gate.match(cands, hist, thr)
+        monkeypatch.setenv("DVB_GATE_KERNEL", "dense")
+        dense = gate.match(cands, hist, thr)
+        monkeypatch.delenv("DVB_GATE_KERNEL")
+        assert np.array_equal(fast, dense), thr
+        assert fast[:400].tolist() == og.gate(cands[:400], hist, thr).tolist()
+    assert int((gate.match(cands, hist, 0.62) >= 0).sum()) > 500
+
+
+@pytest.mark.gpu
 def test_gpu_solution_jaccard_golden(gpu_ctx, golden, oracle):
     from deep_vision_b200 import question_similarity as qs
     cases = golden("a10_solution_jaccard.json")
