@@ -161,8 +161,10 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
                                                               const int32_t* __restrict__ ccnt, int64_t n_cand,
                                                               const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
                                                               const int32_t* __restrict__ hcnt, int64_t n_hist, int32_t tile_h, double thr,
-                                                              int64_t* __restrict__ out, int32_t flagged_only) {
+                                                              int64_t* __restrict__ out, const int32_t* __restrict__ n_flagged, const int64_t* __restrict__ flagged) {
     __shared__ long long s_best;
+    const int64_t n_items = n_flagged ? (int64_t)*n_flagged : n_cand;       // only what k_gate_match_prefix flagged, or everything
+    if (n_items == 0) return;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int acc_words = (tile_h + 1) >> 1;
     for (int i = threadIdx.x; i < acc_words; i += GATE_THREADS) gate_acc[i] = 0u;
@@ -178,8 +180,8 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
         if (lane == 0 && ln >= 0) atomicMax(&s_last_nonempty, ln);
     }
     __syncthreads();
-    for (int64_t c = blockIdx.x; c < n_cand; c += gridDim.x) {
-        if (flagged_only && out[c] != -2) continue;                // k_gate_match_prefix already answered this candidate
+    for (int64_t it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int64_t c = n_flagged ? flagged[it] : it;
         const int32_t L = ccnt[c];
         const unsigned long long* ck = ckeys + ccap_off[c];
         if (threadIdx.x == 0) s_best = -1;
@@ -247,14 +249,15 @@ __global__ void __launch_bounds__(256) k_gate_match_prefix(const unsigned long l
                                                              const int32_t* __restrict__ ccnt, int64_t n_cand,
                                                              const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
                                                              const unsigned long long* __restrict__ hkeys, const int64_t* __restrict__ hcap_off,
-                                                             const int32_t* __restrict__ hcnt, double thr, int64_t* __restrict__ out) {
+                                                             const int32_t* __restrict__ hcnt, double thr, int64_t* __restrict__ out,
+                                                             int32_t* __restrict__ n_flagged, int64_t* __restrict__ flagged) {
     extern __shared__ __align__(16) unsigned char gp_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     GpWarp& W = reinterpret_cast<GpWarp*>(gp_raw)[warp];
     for (int64_t c = (int64_t)blockIdx.x * 8 + warp; c < n_cand; c += (int64_t)gridDim.x * 8) {
         const int32_t L = ccnt[c];
         if (L <= 0) { if (lane == 0) out[c] = -1; continue; }
-        if (L > GP_MAXL) { if (lane == 0) out[c] = -2; continue; }
+        if (L > GP_MAXL) { if (lane == 0) { out[c] = -2; flagged[atomicAdd(n_flagged, 1)] = c; } continue; }
         const unsigned long long* ck = ckeys + ccap_off[c];
         __syncwarp();
         for (int i = lane; i < GP_SET; i += 32) W.set[i] = ~0ULL;
@@ -519,15 +522,19 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
     const char* force = getenv("DVB_GATE_KERNEL");
     const bool prefix = threshold > 0.0 && n_pairs > 0 && !(force && !strcmp(force, "dense"));
+    int32_t* d_nflag = nullptr; int64_t* d_flagged = nullptr;
     if (prefix) {
+        d_nflag = io.tmp<int32_t>(1); d_flagged = io.tmp<int64_t>((size_t)n_cand);
+        rc = io.check(ctx); if (rc) return rc;
+        DVB_CUDA(ctx, cudaMemsetAsync(d_nflag, 0, 4, io.st));
         const size_t smem_p = 8 * sizeof(GpWarp);
         DVB_CUDA(ctx, cudaFuncSetAttribute(k_gate_match_prefix, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
         const int grid_p = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)ctx->num_sm * 32);
-        k_gate_match_prefix<<<grid_p, 256, smem_p, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hk, d_hcap, d_hc, threshold, d_out);
+        k_gate_match_prefix<<<grid_p, 256, smem_p, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hk, d_hcap, d_hc, threshold, d_out, d_nflag, d_flagged);
         ctx->launches += 1;
     }
     // dense counters: everything when the prefix filter does not apply, else only the candidates it flagged (> GP_MAXL keys)
-    k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out, prefix ? 1 : 0);
+    k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out, d_nflag, d_flagged);
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
     ctx->launches += 1;
     rc = io.finish(ctx);
