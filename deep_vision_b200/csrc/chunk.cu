@@ -177,11 +177,16 @@ __global__ void __launch_bounds__(TOPK_WARPS * 32) k_topk_partial(const int32_t*
 }
 
 // one warp per query merges m candidate lists of k entries; writes k entries + the number of valid ones
+// prev != 0: out_score/out_idx already hold a query's running top-k (an earlier index segment); it is merged as one more list.
 __global__ void __launch_bounds__(256) k_topk_final(const int32_t* __restrict__ part_score, const int64_t* __restrict__ part_idx, int32_t m, int32_t k, int32_t nq,
-                                                     int32_t* __restrict__ out_score, int64_t* __restrict__ out_idx, int32_t* __restrict__ out_n) {
+                                                     int32_t* out_score, int64_t* out_idx, int32_t* __restrict__ out_n, int32_t prev) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int q = blockIdx.x * 8 + warp; q < nq; q += gridDim.x * 8) {
         int32_t es = 0; int64_t ei = 0x7fffffffffffffffLL;
+        if (prev && lane < k) {                                   // already sorted, positives first
+            es = out_score[(int64_t)q * k + lane];
+            if (es > 0) ei = out_idx[(int64_t)q * k + lane];
+        }
         const int64_t tot = (int64_t)m * k;
         for (int64_t b0 = 0; b0 < tot; b0 += 32) {
             const int64_t i = b0 + lane; const bool v = i < tot;
@@ -265,12 +270,12 @@ int64_t dv_topk_splits(dvb_ctx* ctx, int64_t n, int32_t nq) {
 }
 // d_ps / d_pi: nq * n_split * k scratch entries each
 void dv_topk_device(dvb_ctx* ctx, cudaStream_t st, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq, int64_t index_base, int32_t k,
-                    int64_t n_split, int32_t* d_ps, int64_t* d_pi, int64_t* d_oidx, int32_t* d_oscore, int32_t* d_on) {
+                    int64_t n_split, int32_t* d_ps, int64_t* d_pi, int64_t* d_oidx, int32_t* d_oscore, int32_t* d_on, bool merge_prev) {
     const int64_t per = (n + n_split - 1) / n_split;
     dim3 g1((unsigned)n_split, (unsigned)std::min(nq, 65535));
     k_topk_partial<<<g1, TOPK_WARPS * 32, 0, st>>>(d_score, d_idx, n, index_base, k, per > 0 ? per : 1, nq, d_ps, d_pi);
     const int grid2 = std::min((nq + 7) / 8, ctx->num_sm * 8);
-    k_topk_final<<<grid2, 256, 0, st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_oscore, d_oidx, d_on);
+    k_topk_final<<<grid2, 256, 0, st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_oscore, d_oidx, d_on, merge_prev ? 1 : 0);
     ctx->launches += 2;
 }
 
@@ -292,7 +297,7 @@ extern "C" int32_t dvb_topk(dvb_ctx* ctx, int32_t mem, const int32_t* score, con
     dim3 g1((unsigned)n_split, (unsigned)std::min(nq, 65535));
     k_topk_partial<<<g1, TOPK_WARPS * 32, 0, io.st>>>(d_score, d_idx, n, index_base, k, per > 0 ? per : 1, nq, d_ps, d_pi);
     const int grid2 = std::min((nq + 7) / 8, ctx->num_sm * 8);
-    k_topk_final<<<grid2, 256, 0, io.st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_oscore, d_oidx, d_on);
+    k_topk_final<<<grid2, 256, 0, io.st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_oscore, d_oidx, d_on, 0);
     ctx->launches += 2;
     return io.finish(ctx);
 }

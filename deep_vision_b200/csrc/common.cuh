@@ -165,4 +165,4 @@ struct dvb_io {
 void dv_launch_symbolize(dvb_ctx* ctx, cudaStream_t st, const uint8_t* d_utf8, const int64_t* d_off, int64_t n_texts, uint16_t* d_sym, int32_t* d_cnt);
 int64_t dv_topk_splits(dvb_ctx* ctx, int64_t n, int32_t nq);
 void dv_topk_device(dvb_ctx* ctx, cudaStream_t st, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq, int64_t index_base, int32_t k,
-                    int64_t n_split, int32_t* d_ps, int64_t* d_pi, int64_t* d_oidx, int32_t* d_oscore, int32_t* d_on);
+                    int64_t n_split, int32_t* d_ps, int64_t* d_pi, int64_t* d_oidx, int32_t* d_oscore, int32_t* d_on, bool merge_prev = false);

@@ -22,9 +22,12 @@
 #include "common.cuh"
 #include "sort.cuh"
 #include <stdlib.h>
+#include <vector>
 
-struct dvb_index {
-    int device = 0;
+// One segment = a contiguous range of chunks with its own sorted postings (<= IX_SEG_BYTES of text, so that the build's
+// transient sort buffers stay bounded and a 180 GB shard is indexed piece by piece).  Passed BY VALUE to k_ix_score.
+struct IxSeg {
+    int64_t chunk_base = 0;             // position of the segment's first chunk inside the index
     int64_t n_chunks = 0, n_bytes = 0, n_post = 0, n_keys = 0;
     uint16_t* sym = nullptr;            // symbols of chunk c at sym[sym_off[c] .. + sym_cnt[c])
     int64_t* sym_off = nullptr;         // [n_chunks + 1] (= byte offsets rebased to 0)
@@ -34,6 +37,12 @@ struct dvb_index {
     uint32_t* ukeys = nullptr;          // [n_keys] distinct pair keys ascending
     int64_t* uoff = nullptr;            // [n_keys + 1]
 };
+struct dvb_index {
+    int device = 0;
+    int64_t n_chunks = 0, n_bytes = 0, n_post = 0, n_keys = 0;     // totals over the segments (n_keys: sum of per-segment distinct keys)
+    std::vector<IxSeg> segs;
+};
+#define IX_SEG_BYTES (2000LL << 20)     // text bytes per segment: postings <= characters <= bytes < 2^31
 
 __device__ __forceinline__ uint32_t ix_code(uint32_t s) { return s >= 0x8000u ? 20992u + (s & 0x7FFFu) : s; }     // 15-bit symbol code
 __device__ __forceinline__ bool ix_same_class(uint32_t a, uint32_t b) { return a != 0u && b != 0u && ((a ^ b) & 0x8000u) == 0u; }
@@ -227,7 +236,7 @@ __global__ void __launch_bounds__(256) k_ix_items(const int64_t* __restrict__ pl
     for (int32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_terms; t += gridDim.x * blockDim.x)
         n_items[t] = (int32_t)((plan_hi[t] - plan_lo[t] + IX_ITEM - 1) / IX_ITEM);
 }
-__global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* __restrict__ term_sym, const int32_t* __restrict__ term_off,
+__global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __restrict__ term_sym, const int32_t* __restrict__ term_off,
                                                    const int32_t* __restrict__ query_term_off, int32_t q0, int32_t q1,
                                                    const int64_t* __restrict__ plan_lo, const int64_t* __restrict__ plan_hi, const int32_t* __restrict__ plan_j,
                                                    const int64_t* __restrict__ item_off, int32_t* __restrict__ score /* [q1 - q0][n_chunks] */) {
@@ -316,23 +325,111 @@ __global__ void __launch_bounds__(256) k_ix_score(dvb_index ix, const uint16_t* 
 }
 
 // ------------------------------------------------------------------ host side
-#define IX_CUDA(ctx, idx, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
-    dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e__), #expr); dvb_chunk_index_free(idx); cudaGetLastError(); \
-    return e__ == cudaErrorMemoryAllocation ? DVB_E_NOMEM : DVB_E_CUDA; } } while (0)
+static void ix_free_seg(IxSeg& sg) {
+    void* ptrs[] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pk, sg.pv, sg.ukeys, sg.uoff };
+    for (void* p : ptrs) if (p) cudaFree(p);
+    sg = IxSeg();
+}
 
 extern "C" void dvb_chunk_index_free(dvb_index* ix) {
     if (!ix) return;
     cudaSetDevice(ix->device);
-    void* ptrs[] = { ix->sym, ix->sym_off, ix->sym_cnt, ix->pk, ix->pv, ix->ukeys, ix->uoff };
-    for (void* p : ptrs) if (p) cudaFree(p);
+    for (IxSeg& sg : ix->segs) ix_free_seg(sg);
     delete ix;
 }
 
 extern "C" int32_t dvb_chunk_index_stats(const dvb_index* ix, int64_t* out6) {
     if (!ix || !out6) return DVB_E_INVALID;
     out6[0] = ix->n_chunks; out6[1] = ix->n_bytes; out6[2] = ix->n_post; out6[3] = ix->n_keys;
-    out6[4] = 2 * ix->n_bytes + 12 * ix->n_chunks + 8 + 12 * ix->n_post + 12 * ix->n_keys + 8;       // resident device bytes
+    out6[4] = 2 * ix->n_bytes + 12 * ix->n_chunks + 12 * ix->n_post + 12 * ix->n_keys + 80 * (int64_t)ix->segs.size();   // resident device bytes
     out6[5] = ix->device;
+    return DVB_OK;
+}
+
+static int64_t ix_seg_bytes() {                       // test hook: small segments exercise the multi-segment path on small corpora
+    const char* e = getenv("DVB_IX_SEG_BYTES");
+    if (e && *e) { const long long v = atoll(e); if (v > 0) return (int64_t)std::min<long long>(v, IX_SEG_BYTES); }
+    return IX_SEG_BYTES;
+}
+
+// Builds one segment from chunks [0, n_chunks) whose rebased byte offsets are hoff[0 .. n_chunks] (hoff[0] == 0) and whose
+// text starts at `text` (host or device according to mem).  On failure the partially built segment is released.
+static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, int32_t mem, const uint8_t* text, const int64_t* hoff, int64_t n_chunks, IxSeg* sg) {
+    const int64_t nb = hoff[n_chunks];
+    sg->n_chunks = n_chunks; sg->n_bytes = nb;
+    uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr; int64_t* d_scan = nullptr;
+    unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
+    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFreeAsync(p, st); };
+#define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { \
+        dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e2__), #expr); drop(); cudaStreamSynchronize(st); ix_free_seg(*sg); cudaGetLastError(); \
+        return e2__ == cudaErrorMemoryAllocation ? DVB_E_NOMEM : DVB_E_CUDA; } } while (0)
+    IX_TRY(cudaMallocAsync((void**)&sg->sym, 2 * (size_t)nb + 64, st));
+    IX_TRY(cudaMallocAsync((void**)&sg->sym_off, 8 * (size_t)(n_chunks + 1), st));
+    IX_TRY(cudaMallocAsync((void**)&sg->sym_cnt, 4 * (size_t)n_chunks + 4, st));
+    IX_TRY(cudaMemcpyAsync(sg->sym_off, hoff, 8 * (size_t)(n_chunks + 1), cudaMemcpyHostToDevice, st));
+    const uint8_t* d_utf8 = text;
+    if (mem == DVB_MEM_HOST) {
+        IX_TRY(cudaMallocAsync((void**)&d_text, (size_t)nb + 64, st));
+        IX_TRY(cudaMemcpyAsync(d_text, text, (size_t)nb, cudaMemcpyHostToDevice, st));
+        d_utf8 = d_text;
+    }
+    // K1: symbols (sym_off doubles as the rebased byte offsets the symboliser reads)
+    dv_launch_symbolize(ctx, st, d_utf8, sg->sym_off, n_chunks, sg->sym, sg->sym_cnt);
+    // K2a: postings
+    IX_TRY(cudaMallocAsync((void**)&d_pc, 4 * (size_t)n_chunks + 4, st));
+    IX_TRY(cudaMallocAsync((void**)&d_po, 8 * (size_t)(n_chunks + 1), st));
+    const int grid = (int)std::min<int64_t>((n_chunks + 7) / 8, (int64_t)ctx->num_sm * 16);
+    IX_TRY(cudaMemsetAsync(d_po, 0, 8, st));                   // d_po[0] doubles as the error flag until the scan overwrites it
+    k_ix_count<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_pc, reinterpret_cast<int32_t*>(d_po));
+    int32_t too_long = 0;
+    IX_TRY(cudaMemcpyAsync(&too_long, d_po, 4, cudaMemcpyDeviceToHost, st));
+    {                                                    // exclusive scan of the per-chunk posting counts
+        const int64_t nsb = (n_chunks + IX_SCAN_TILE - 1) / IX_SCAN_TILE;
+        IX_TRY(cudaMallocAsync((void**)&d_scan, 8 * (size_t)(nsb + 1) + 4 * (size_t)nsb + 16, st));
+        int64_t* d_sbase = d_scan; int32_t* d_ssum = reinterpret_cast<int32_t*>(d_scan + nsb + 1);
+        k_ix_scan_sum<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_ssum);
+        k_ix_scan<<<1, 1024, 0, st>>>(d_ssum, d_sbase, nsb);
+        k_ix_scan_apply<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_sbase, d_po, nsb);
+    }
+    int64_t n_post = 0;
+    IX_TRY(cudaMemcpyAsync(&n_post, d_po + n_chunks, 8, cudaMemcpyDeviceToHost, st));
+    IX_TRY(cudaStreamSynchronize(st));
+    if (too_long) {
+        drop(); cudaStreamSynchronize(st); ix_free_seg(*sg);
+        dvb_set_err(ctx, "dvb_chunk_index_build: a chunk has more than 65535 characters%s%s"); return DVB_E_INVALID;
+    }
+    ctx->launches += 4;
+    sg->n_post = n_post;
+    if (d_text) { cudaFreeAsync(d_text, st); d_text = nullptr; }
+    if (n_post > 0) {
+        const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
+        IX_TRY(cudaMallocAsync((void**)&sg->pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&sg->pv, 4 * (size_t)n_post, st));
+        IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
+        IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * (size_t)(256 * nbk + 256), st));
+        k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, sg->pk, sg->pv);
+        ctx->launches += 1;
+        // K2b: stable sort by the 30 key bits + 2 sub-list bits (32 = 4 passes of 8)
+        int64_t l = 0;
+        const int which = dv_radix_sort_pairs(sg->pk, sg->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
+        ctx->launches += l;
+        if (which) { std::swap(sg->pk, t_pk); std::swap(sg->pv, t_pv); }
+        // K2c: segment heads
+        const int64_t nhb = (n_post + IX_HEAD_TILE - 1) / IX_HEAD_TILE;
+        IX_TRY(cudaMallocAsync((void**)&d_bc, 4 * (size_t)nhb + 4, st)); IX_TRY(cudaMallocAsync((void**)&d_bo, 8 * (size_t)(nhb + 1), st));
+        k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(sg->pk, n_post, d_bc);
+        k_ix_scan<<<1, 1024, 0, st>>>(d_bc, d_bo, nhb);
+        int64_t n_keys = 0;
+        IX_TRY(cudaMemcpyAsync(&n_keys, d_bo + nhb, 8, cudaMemcpyDeviceToHost, st));
+        IX_TRY(cudaStreamSynchronize(st));
+        sg->n_keys = n_keys;
+        IX_TRY(cudaMallocAsync((void**)&sg->ukeys, 4 * (size_t)n_keys + 4, st)); IX_TRY(cudaMallocAsync((void**)&sg->uoff, 8 * (size_t)(n_keys + 1), st));
+        k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(sg->pk, n_post, d_bo, sg->ukeys, sg->uoff);
+        IX_TRY(cudaMemcpyAsync(sg->uoff + n_keys, &n_post, 8, cudaMemcpyHostToDevice, st));
+        IX_TRY(cudaStreamSynchronize(st));                     // n_post is a stack variable
+        ctx->launches += 3;
+    }
+    drop();
+#undef IX_TRY
     return DVB_OK;
 }
 
@@ -345,88 +442,41 @@ extern "C" int32_t dvb_chunk_index_build(dvb_ctx* ctx, int32_t mem, const uint8_
     ix->device = ctx->device; ix->n_chunks = n_chunks;
     std::vector<int64_t> hoff((size_t)n_chunks + 1);
     if (mem == DVB_MEM_HOST) memcpy(hoff.data(), off, 8 * (size_t)(n_chunks + 1));
-    else { IX_CUDA(ctx, ix, cudaMemcpyAsync(hoff.data(), off, 8 * (size_t)(n_chunks + 1), cudaMemcpyDeviceToHost, st)); IX_CUDA(ctx, ix, cudaStreamSynchronize(st)); }
+    else {
+        cudaError_t e = cudaMemcpyAsync(hoff.data(), off, 8 * (size_t)(n_chunks + 1), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e), "copy of the chunk offsets"); delete ix; cudaGetLastError(); return DVB_E_CUDA; }
+    }
     const int64_t o0 = hoff[0];
     for (int64_t c = 0; c <= n_chunks; c++) hoff[c] -= o0;
     for (int64_t c = 0; c < n_chunks; c++) if (hoff[c + 1] < hoff[c] || hoff[c + 1] - hoff[c] > 0x7fffffffLL / 2) {
-        dvb_set_err(ctx, "dvb_chunk_index_build: bad offsets%s%s"); dvb_chunk_index_free(ix); return DVB_E_INVALID; }
-    const int64_t nb = hoff[n_chunks];
-    ix->n_bytes = nb;
-    uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr; int64_t* d_scan = nullptr;
-    unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
-    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFreeAsync(p, st); };
-#define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { drop(); IX_CUDA(ctx, ix, e2__); } } while (0)
-    IX_TRY(cudaMallocAsync((void**)&ix->sym, 2 * (size_t)nb + 64, st));
-    IX_TRY(cudaMallocAsync((void**)&ix->sym_off, 8 * (size_t)(n_chunks + 1), st));
-    IX_TRY(cudaMallocAsync((void**)&ix->sym_cnt, 4 * (size_t)n_chunks + 4, st));
-    IX_TRY(cudaMemcpyAsync(ix->sym_off, hoff.data(), 8 * (size_t)(n_chunks + 1), cudaMemcpyHostToDevice, st));
+        dvb_set_err(ctx, "dvb_chunk_index_build: bad offsets%s%s"); delete ix; return DVB_E_INVALID; }
+    ix->n_bytes = hoff[n_chunks];
     const bool timing = ctx->timing.load() != 0;
-    if (timing) IX_TRY(cudaEventRecord(sc.l->ev0, st));
-    if (n_chunks > 0) {
-        const uint8_t* d_utf8 = utf8 + o0;
-        if (mem == DVB_MEM_HOST) {
-            IX_TRY(cudaMallocAsync((void**)&d_text, (size_t)nb + 64, st));
-            IX_TRY(cudaMemcpyAsync(d_text, utf8 + o0, (size_t)nb, cudaMemcpyHostToDevice, st));
-            d_utf8 = d_text;
-        }
-        // K1: symbols (sym_off doubles as the rebased byte offsets the symboliser reads)
-        dv_launch_symbolize(ctx, st, d_utf8, ix->sym_off, n_chunks, ix->sym, ix->sym_cnt);
-        // K2a: postings
-        IX_TRY(cudaMallocAsync((void**)&d_pc, 4 * (size_t)n_chunks + 4, st));
-        IX_TRY(cudaMallocAsync((void**)&d_po, 8 * (size_t)(n_chunks + 1), st));
-        const int grid = (int)std::min<int64_t>((n_chunks + 7) / 8, (int64_t)ctx->num_sm * 16);
-        IX_TRY(cudaMemsetAsync(d_po, 0, 8, st));                   // d_po[0] doubles as the error flag until the scan overwrites it
-        k_ix_count<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_pc, reinterpret_cast<int32_t*>(d_po));
-        int32_t too_long = 0;
-        IX_TRY(cudaMemcpyAsync(&too_long, d_po, 4, cudaMemcpyDeviceToHost, st));
-        {                                                    // exclusive scan of the per-chunk posting counts
-            const int64_t nsb = (n_chunks + IX_SCAN_TILE - 1) / IX_SCAN_TILE;
-            IX_TRY(cudaMallocAsync((void**)&d_scan, 8 * (size_t)(nsb + 1) + 4 * (size_t)nsb + 16, st));
-            int64_t* d_sbase = d_scan; int32_t* d_ssum = reinterpret_cast<int32_t*>(d_scan + nsb + 1);
-            k_ix_scan_sum<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_ssum);
-            k_ix_scan<<<1, 1024, 0, st>>>(d_ssum, d_sbase, nsb);
-            k_ix_scan_apply<<<(unsigned)nsb, 256, 0, st>>>(d_pc, n_chunks, d_sbase, d_po, nsb);
-        }
-        int64_t n_post = 0;
-        IX_TRY(cudaMemcpyAsync(&n_post, d_po + n_chunks, 8, cudaMemcpyDeviceToHost, st));
-        IX_TRY(cudaStreamSynchronize(st));
-        if (too_long) { drop(); dvb_chunk_index_free(ix); dvb_set_err(ctx, "dvb_chunk_index_build: a chunk has more than 65535 characters%s%s"); return DVB_E_INVALID; }
-        ctx->launches += 4;
-        ix->n_post = n_post;
-        if (mem == DVB_MEM_HOST) { cudaFreeAsync(d_text, st); d_text = nullptr; }
-        if (n_post > 0) {
-            const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
-            IX_TRY(cudaMallocAsync((void**)&ix->pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&ix->pv, 4 * (size_t)n_post, st));
-            IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
-            IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * (size_t)(256 * nbk + 256), st));
-            k_ix_emit<<<grid, 256, 0, st>>>(ix->sym, ix->sym_off, ix->sym_cnt, n_chunks, d_po, ix->pk, ix->pv);
-            ctx->launches += 1;
-            // K2b: stable sort by the 30 key bits (32 = 4 passes of 8)
-            int64_t l = 0;
-            const int which = dv_radix_sort_pairs(ix->pk, ix->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
-            ctx->launches += l;
-            if (which) { std::swap(ix->pk, t_pk); std::swap(ix->pv, t_pv); }
-            // K2c: segment heads
-            const int64_t nhb = (n_post + IX_HEAD_TILE - 1) / IX_HEAD_TILE;
-            IX_TRY(cudaMallocAsync((void**)&d_bc, 4 * (size_t)nhb + 4, st)); IX_TRY(cudaMallocAsync((void**)&d_bo, 8 * (size_t)(nhb + 1), st));
-            k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bc);
-            k_ix_scan<<<1, 1024, 0, st>>>(d_bc, d_bo, nhb);
-            int64_t n_keys = 0;
-            IX_TRY(cudaMemcpyAsync(&n_keys, d_bo + nhb, 8, cudaMemcpyDeviceToHost, st));
-            IX_TRY(cudaStreamSynchronize(st));
-            ix->n_keys = n_keys;
-            IX_TRY(cudaMallocAsync((void**)&ix->ukeys, 4 * (size_t)n_keys + 4, st)); IX_TRY(cudaMallocAsync((void**)&ix->uoff, 8 * (size_t)(n_keys + 1), st));
-            k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(ix->pk, n_post, d_bo, ix->ukeys, ix->uoff);
-            IX_TRY(cudaMemcpyAsync(ix->uoff + n_keys, &n_post, 8, cudaMemcpyHostToDevice, st));
-            ctx->launches += 3;
-        }
+    if (timing) cudaEventRecord(sc.l->ev0, st);
+    // cut into segments of <= seg_bytes of text (a single chunk larger than that is its own segment)
+    const int64_t seg_bytes = ix_seg_bytes();
+    std::vector<int64_t> seg_off;
+    if (n_chunks == 0) ix->segs.push_back(IxSeg());              // an empty index answers every query with "no positive chunk"
+    for (int64_t c0 = 0; c0 < n_chunks; ) {
+        // largest c1 with hoff[c1] - hoff[c0] <= seg_bytes (at least one chunk)
+        int64_t c1 = std::upper_bound(hoff.begin() + c0, hoff.end(), hoff[c0] + seg_bytes) - hoff.begin() - 1;
+        c1 = std::max(c1, c0 + 1);
+        seg_off.assign(hoff.begin() + c0, hoff.begin() + c1 + 1);
+        const int64_t b0 = seg_off[0];
+        for (int64_t& v : seg_off) v -= b0;
+        IxSeg sg; sg.chunk_base = c0;
+        const int32_t rc = ix_build_segment(ctx, sc, st, mem, utf8 + o0 + b0, seg_off.data(), c1 - c0, &sg);
+        if (rc != DVB_OK) { dvb_chunk_index_free(ix); return rc; }
+        ix->n_post += sg.n_post; ix->n_keys += sg.n_keys;
+        ix->segs.push_back(sg);
+        c0 = c1;
     }
-    if (timing) IX_TRY(cudaEventRecord(sc.l->ev1, st));
-    IX_TRY(cudaStreamSynchronize(st));
-    IX_TRY(cudaGetLastError());
+    if (timing) cudaEventRecord(sc.l->ev1, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e), "dvb_chunk_index_build"); dvb_chunk_index_free(ix); cudaGetLastError(); return DVB_E_CUDA; }
     if (timing) { float ms = 0.f; cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1); ctx->last_ms = ms; }
-    drop();
-#undef IX_TRY
     *out = ix;
     return DVB_OK;
 }
@@ -438,7 +488,8 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
         ix->device != ctx->device) { dvb_set_err(ctx, "dvb_chunk_index_topk: invalid argument (1 <= k <= 32, index of this device)%s%s"); return DVB_E_INVALID; }
     if (nq == 0) return DVB_OK;
     dvb_scope sc(ctx); dvb_io io(sc, mem);
-    const int64_t N = ix->n_chunks;
+    int64_t N = 0;                                               // largest segment: sizes the dense score tile
+    for (const IxSeg& sg : ix->segs) N = std::max(N, sg.n_chunks);
     // terms: sizes come from the offsets
     int32_t n_sym = 0;
     if (mem == DVB_MEM_HOST) n_sym = term_off[n_terms];
@@ -450,9 +501,9 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     // batch of queries sharing one dense score tile (<= 512 MB)
     const int64_t budget = 512LL << 20;
     const int32_t B = (int32_t)std::max<int64_t>(1, std::min<int64_t>(nq, N > 0 ? budget / (4 * N) : nq));
-    const int64_t n_split = dv_topk_splits(ctx, N, B);
+    const size_t n_part = (size_t)B + (size_t)ctx->num_sm * 4;     // nb * dv_topk_splits(., nb) <= max(nb, 4 * num_sm) for every nb <= B
     size_t need = dvb_pad(4 * (size_t)B * (size_t)std::max<int64_t>(N, 1)) + dvb_pad(8 * (size_t)n_terms + 16) * 3 + dvb_pad(4 * (size_t)n_terms + 4) * 2
-                + dvb_pad(4 * (size_t)B * n_split * k) + dvb_pad(8 * (size_t)B * n_split * k) + 4096;
+                + dvb_pad(4 * n_part * k) + dvb_pad(8 * n_part * k) + 4096;
     if (mem == DVB_MEM_HOST) need += dvb_pad(2 * (size_t)n_sym + 2) + dvb_pad(4 * (size_t)n_terms + 4) + dvb_pad(4 * (size_t)nq + 4)
                                    + dvb_pad(8 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq * k) + dvb_pad(4 * (size_t)nq);
     int32_t rc = sc.reserve(need); if (rc) return rc;
@@ -463,29 +514,35 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     int32_t* d_err = io.tmp<int32_t>(1);
     int32_t* d_ni = io.tmp<int32_t>((size_t)n_terms + 1); int64_t* d_io = io.tmp<int64_t>((size_t)n_terms + 2);
     int32_t* d_score = io.tmp<int32_t>((size_t)B * (size_t)std::max<int64_t>(N, 1));
-    int32_t* d_ps = io.tmp<int32_t>((size_t)B * n_split * k); int64_t* d_pi = io.tmp<int64_t>((size_t)B * n_split * k);
+    int32_t* d_ps = io.tmp<int32_t>(n_part * k); int64_t* d_pi = io.tmp<int64_t>(n_part * k);
     rc = io.check(ctx); if (rc) return rc;
     DVB_CUDA(ctx, cudaMemsetAsync(d_err, 0, 4, io.st));
     const bool timing = ctx->timing.load() != 0;
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev0, io.st));
-    if (n_terms > 0) {
-        k_ix_plan<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_ts, d_to, n_terms, ix->ukeys, ix->uoff, ix->n_keys, d_lo, d_hi, d_j, d_err);
-        k_ix_items<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_lo, d_hi, n_terms, d_ni);
-        k_ix_scan<<<1, 1024, 0, io.st>>>(d_ni, d_io, n_terms);
-        ctx->launches += 3;
-    }
-    for (int32_t q0 = 0; q0 < nq; q0 += B) {
-        const int32_t q1 = std::min(nq, q0 + B), nb = q1 - q0;
-        if (N > 0) {
-            DVB_CUDA(ctx, cudaMemsetAsync(d_score, 0, 4 * (size_t)nb * (size_t)N, io.st));
-            const int32_t nt = h_qto[q1] - h_qto[q0];
-            if (nt > 0) {
-                k_ix_score<<<ctx->num_sm * 16, 256, 0, io.st>>>(*ix, d_ts, d_to, d_qto, q0, q1, d_lo, d_hi, d_j, d_io, d_score);
-                ctx->launches += 1;
-            }
+    // segment by segment: the running top-k of a query (out arrays) is one more candidate list of the next segment's merge
+    bool first = true;
+    for (const IxSeg& sg : ix->segs) {
+        const int64_t Ns = sg.n_chunks;
+        if (n_terms > 0) {
+            k_ix_plan<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_ts, d_to, n_terms, sg.ukeys, sg.uoff, sg.n_keys, d_lo, d_hi, d_j, d_err);
+            k_ix_items<<<std::min((n_terms + 255) / 256, ctx->num_sm * 8), 256, 0, io.st>>>(d_lo, d_hi, n_terms, d_ni);
+            k_ix_scan<<<1, 1024, 0, io.st>>>(d_ni, d_io, n_terms);
+            ctx->launches += 3;
         }
-        dv_topk_device(ctx, io.st, d_score, nullptr, N, nb, index_base, k, dv_topk_splits(ctx, N, nb), d_ps, d_pi,
-                       d_oidx + (size_t)q0 * k, d_osc + (size_t)q0 * k, d_on + q0);
+        for (int32_t q0 = 0; q0 < nq; q0 += B) {
+            const int32_t q1 = std::min(nq, q0 + B), nb = q1 - q0;
+            if (Ns > 0) {
+                DVB_CUDA(ctx, cudaMemsetAsync(d_score, 0, 4 * (size_t)nb * (size_t)Ns, io.st));
+                const int32_t nt = h_qto[q1] - h_qto[q0];
+                if (nt > 0) {
+                    k_ix_score<<<ctx->num_sm * 16, 256, 0, io.st>>>(sg, d_ts, d_to, d_qto, q0, q1, d_lo, d_hi, d_j, d_io, d_score);
+                    ctx->launches += 1;
+                }
+            }
+            dv_topk_device(ctx, io.st, d_score, nullptr, Ns, nb, index_base + sg.chunk_base, k, dv_topk_splits(ctx, Ns, nb), d_ps, d_pi,
+                           d_oidx + (size_t)q0 * k, d_osc + (size_t)q0 * k, d_on + q0, /*merge_prev=*/!first);
+        }
+        first = false;
     }
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
     int32_t h_err = 0;

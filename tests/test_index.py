@@ -104,3 +104,31 @@ def test_gpu_index_work_items_do_not_split_chunks(gpu_ctx):
     for q, terms in enumerate(queries):
         wi, ws = _ref_topk(chunks, terms, 32)
         assert idx[q][: nv[q]].tolist() == wi and sc[q][: nv[q]].tolist() == ws, terms
+
+
+@pytest.mark.gpu
+def test_gpu_index_segments_equal_single_segment(gpu_ctx, monkeypatch):
+    """A shard larger than IX_SEG_BYTES is indexed in segments (bounded sort buffers); the running top-k carried from
+    segment to segment must equal the one-segment answer, ties (score, index asc) included."""
+    from deep_vision_b200 import reference_material as rm
+    chunks, queries = make_corpus(n_chunks=1500, nq=40, seed=21)
+    chunks[700] = "x" * 9000                                        # a chunk larger than a whole segment is its own segment
+    chunks += ["离线审批"] * 40                                      # equal scores across segment borders: order by index
+    queries += [["离线审批", "离线"], ["xx"], ["zzzzzz"]]
+    one = rm.ChunkIndex(chunks, index_base=7, ctx=gpu_ctx)
+    assert one.stats()["n_chunks"] == len(chunks)
+    wi, ws, wn = one.topk(queries, 8)
+    monkeypatch.setenv("DVB_IX_SEG_BYTES", "4096")
+    seg = rm.ChunkIndex(chunks, index_base=7, ctx=gpu_ctx)
+    monkeypatch.delenv("DVB_IX_SEG_BYTES")
+    st1, st2 = one.stats(), seg.stats()
+    assert st2["n_chunks"] == st1["n_chunks"] and st2["postings"] == st1["postings"] and st2["pair_keys"] > st1["pair_keys"]
+    for k in (1, 8, 32):
+        a = one.topk(queries, k); b = seg.topk(queries, k)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+    for q, terms in enumerate(queries[-3:]):
+        ri, rs = _ref_topk(chunks, terms, 8, base=7)
+        qq = len(queries) - 3 + q
+        assert wi[qq][: wn[qq]].tolist() == ri and ws[qq][: wn[qq]].tolist() == rs
+    one.close(); seg.close()

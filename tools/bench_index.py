@@ -18,6 +18,9 @@ ap.add_argument("--chars", type=int, default=512)
 ap.add_argument("--queries", type=int, default=100000)
 ap.add_argument("--k", type=int, default=8)
 ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--qreps", type=int, default=0, help="query repetitions (default: --reps)")
+ap.add_argument("--replicate", type=int, default=1,
+                help="generate 1/R of the shard on the host and tile it R times in HBM (config-5 sized shards without minutes of numpy)")
 args = ap.parse_args()
 rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(lr)
@@ -28,7 +31,8 @@ from deep_vision_b200 import _lib, parallel, reference_material as rm, synth
 ctx = _lib.Context.get(lr)
 lo, hi = parallel.shard_range(args.chunks, rank, world)
 t0 = time.time()
-data, off = synth.make_texts(hi - lo, args.chars, seed=synth.SEED + 1000 + rank)
+n_gen = (hi - lo + args.replicate - 1) // args.replicate
+data, off = synth.make_texts(n_gen, args.chars, seed=synth.SEED + 1000 + rank)
 gen_s = time.time() - t0
 # queries: 30-60 chars, half copied from a chunk of rank 0's shard (same on every rank: generated from seed)
 qdata, qoff = synth.make_texts(args.queries, 45, seed=999)
@@ -45,12 +49,24 @@ for q in range(args.queries):
 if world == 1:
     raw0 = data.tobytes()
     for q in range(0, args.queries, 2):
-        c = int(rng.integers(0, hi - lo)); s = raw0[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, args.chars - 24))
+        c = int(rng.integers(0, n_gen)); s = raw0[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, args.chars - 24))
         queries[q] = queries[q][:22] + s[a:a + 22]
 t0 = time.time()
 terms = [rm._tokenize_reference_material_query(t) for t in queries]
 tok_s = time.time() - t0
 d_data = torch.from_numpy(data).cuda(); d_off = torch.from_numpy(off).cuda()
+if args.replicate > 1:
+    nb = int(off[-1])
+    small = d_data
+    d_data = torch.zeros(nb * args.replicate + 64, dtype=torch.uint8, device="cuda")
+    d_data[: nb * args.replicate].view(args.replicate, nb).copy_(small[:nb][None, :].expand(args.replicate, nb))
+    del small
+    reps_off = (torch.arange(args.replicate, device="cuda", dtype=torch.int64) * nb)[:, None] + d_off[None, :-1]
+    d_off = torch.cat([reps_off.reshape(-1)[: hi - lo], torch.tensor([0], device="cuda", dtype=torch.int64)])
+    last = (hi - lo - 1) % n_gen
+    d_off[-1] = d_off[-2] + int(off[last + 1] - off[last])
+    del reps_off
+    torch.cuda.empty_cache()
 ctx.set_timing(True)
 build_ms = []
 ix = None
@@ -64,7 +80,7 @@ st = ix.stats()
 tsym, toff, qto = rm.terms_to_symbols(terms)
 oi = np.full((args.queries, args.k), -1, np.int64); os_ = np.zeros((args.queries, args.k), np.int32); on = np.zeros(args.queries, np.int32)
 q_ms = []
-for _ in range(args.reps):
+for _ in range(args.qreps or args.reps):
     rc = ctx.lib.dvb_chunk_index_topk(ctx.handle, ix._h, _lib.MEM_HOST, rm.ptr(tsym), rm.ptr(toff), len(toff) - 1, rm.ptr(qto), args.queries,
                                       lo, args.k, rm.ptr(oi), rm.ptr(os_), rm.ptr(on))
     ctx.check(rc, "topk")
@@ -77,7 +93,7 @@ algo_query = 8 * int(os_.sum()) + 16 * args.k * args.queries   # lower bound fro
 if rank == 0:
     b, qm = min(build_ms), min(q_ms)
     print(json.dumps({"world": world, "chunks_per_gpu": hi - lo, "queries": args.queries, "k": args.k, "stats": st,
-                      "build_ms": build_ms, "chunks_indexed_per_s_per_gpu": (hi - lo) / (b / 1e3), "build_GBps_algorithmic": algo_build / b / 1e6,
+                      "replicate": args.replicate, "segments_est": -(-st["text_bytes"] // (2000 << 20)), "build_ms": build_ms, "chunks_indexed_per_s_per_gpu": (hi - lo) / (b / 1e3), "build_GBps_algorithmic": algo_build / b / 1e6,
                       "query_ms": q_ms, "effective_pairs_per_s_per_gpu": (hi - lo) * args.queries / (qm / 1e3),
                       "merge_s_host_incl_allgather": merge_s, "n_terms": int(len(toff) - 1), "mean_hits": float(gn.mean()),
                       "host_gen_s": gen_s, "host_tokenize_s": tok_s}))
