@@ -43,6 +43,8 @@ _SIGS = {
     "dvb_chunk_index_free": (None, [_vp]),
     "dvb_chunk_index_stats": (C.c_int32, [_vp, _vp]),
     "dvb_chunk_index_topk": (C.c_int32, [_vp, _vp, C.c_int32, _vp, _vp, C.c_int32, _vp, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),
+    "dvb_chunk_index_save": (C.c_int32, [_vp, _vp, C.c_char_p, _vp]),
+    "dvb_chunk_index_load": (C.c_int32, [_vp, C.c_char_p, _vp, C.POINTER(_vp)]),
     "dvb_bind_claims": (C.c_int32, [_vp, C.c_int32] + [_vp] * 6 + [C.c_int64] + [_vp] * 10 + [C.c_int64]),
 }
 

@@ -21,28 +21,8 @@
 // of one class, so each term has at least one indexed pair.
 #include "common.cuh"
 #include "sort.cuh"
+#include "index.cuh"
 #include <stdlib.h>
-#include <vector>
-
-// One segment = a contiguous range of chunks with its own sorted postings (<= IX_SEG_BYTES of text, so that the build's
-// transient sort buffers stay bounded and a 180 GB shard is indexed piece by piece).  Passed BY VALUE to k_ix_score.
-struct IxSeg {
-    int64_t chunk_base = 0;             // position of the segment's first chunk inside the index
-    int64_t n_chunks = 0, n_bytes = 0, n_post = 0, n_keys = 0;
-    uint16_t* sym = nullptr;            // symbols of chunk c at sym[sym_off[c] .. + sym_cnt[c])
-    int64_t* sym_off = nullptr;         // [n_chunks + 1] (= byte offsets rebased to 0)
-    int32_t* sym_cnt = nullptr;         // [n_chunks]
-    unsigned long long* pk = nullptr;   // [n_post] chunk << 32 | pair key, sorted by (key, chunk, pos)
-    uint32_t* pv = nullptr;             // [n_post] position
-    uint32_t* ukeys = nullptr;          // [n_keys] distinct pair keys ascending
-    int64_t* uoff = nullptr;            // [n_keys + 1]
-};
-struct dvb_index {
-    int device = 0;
-    int64_t n_chunks = 0, n_bytes = 0, n_post = 0, n_keys = 0;     // totals over the segments (n_keys: sum of per-segment distinct keys)
-    std::vector<IxSeg> segs;
-};
-#define IX_SEG_BYTES (2000LL << 20)     // text bytes per segment: postings <= characters <= bytes < 2^31
 
 __device__ __forceinline__ uint32_t ix_code(uint32_t s) { return s >= 0x8000u ? 20992u + (s & 0x7FFFu) : s; }     // 15-bit symbol code
 __device__ __forceinline__ bool ix_same_class(uint32_t a, uint32_t b) { return a != 0u && b != 0u && ((a ^ b) & 0x8000u) == 0u; }
@@ -325,7 +305,7 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
 }
 
 // ------------------------------------------------------------------ host side
-static void ix_free_seg(IxSeg& sg) {
+void ix_free_seg(IxSeg& sg) {
     void* ptrs[] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pk, sg.pv, sg.ukeys, sg.uoff };
     for (void* p : ptrs) if (p) cudaFree(p);
     sg = IxSeg();

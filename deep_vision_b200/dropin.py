@@ -60,8 +60,22 @@ def _gate(mod, ctx) -> qs.QuestionGate:
     return gate
 
 
-def build_bindings(mod, ctx=None) -> Dict[str, Any]:
-    """The replacement callables, keyed by the reference name (signatures of SURVEY.md §8b)."""
+def build_bindings(mod, ctx=None, sidecar_cache: Optional["rm.ChunkIndexCache"] = None) -> Dict[str, Any]:
+    """The replacement callables, keyed by the reference name (signatures of SURVEY.md §8b).
+    sidecar_cache (opt-in): keep / persist a resident chunk index per uploaded document (chunks.dvbidx next
+    to chunks.json, found through the module's own `_resolve_data_ref`); selection results are unchanged."""
+
+    def _index_provider(doc, chunks):
+        sha = str((doc or {}).get("full_content_sha256") or "")          # written into the doc record at web/server.py:32013, 32357
+        if not sha:
+            return None
+        side = None
+        ref = str((doc or {}).get("chunk_manifest_ref") or "").strip()
+        resolve = getattr(mod, "_resolve_data_ref", None)
+        if ref and resolve is not None:
+            from pathlib import Path
+            side = Path(resolve(ref)).with_name(rm.SIDECAR_NAME)
+        return sidecar_cache.get(side, sha, chunks)
 
     def _tokenize_similarity_text_v3(text):
         return evidence._tokenize_similarity_text_v3(text, ctx=ctx)
@@ -85,7 +99,8 @@ def build_bindings(mod, ctx=None) -> Dict[str, Any]:
     def select_reference_material_context(doc, *, query_text="", max_chars=0, chunk_limit=0):
         loader = getattr(mod, "load_reference_material_chunks", None)
         return rm.select_reference_material_context(doc, query_text=query_text, max_chars=max_chars, chunk_limit=chunk_limit,
-                                                    chunk_loader=loader, config=_rm_cfg(mod), ctx=ctx)
+                                                    chunk_loader=loader, config=_rm_cfg(mod), ctx=ctx,
+                                                    index_provider=_index_provider if sidecar_cache is not None else None)
 
     def normalize_interview_question_text(text):
         return _gate(mod, ctx).normalize_interview_question_text(text)
@@ -103,7 +118,7 @@ def build_bindings(mod, ctx=None) -> Dict[str, Any]:
         return qs._solution_jaccard_similarity(left, right, int(getattr(mod, "SOLUTION_SIMILARITY_NGRAM_SIZE", 2)), ctx=ctx)
 
     bindings = dict(locals())
-    for k in ("mod", "ctx"):
+    for k in ("mod", "ctx", "sidecar_cache", "_index_provider"):
         bindings.pop(k, None)
     try:                                             # a11-a13 (annotation path); present once annotations.py is built
         from . import annotations
@@ -113,9 +128,11 @@ def build_bindings(mod, ctx=None) -> Dict[str, Any]:
     return {k: v for k, v in bindings.items() if k in HOT_NAMES}
 
 
-def install(server_module, ctx=None, names: Optional[tuple] = None) -> Dict[str, Any]:
-    """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent."""
-    bindings = build_bindings(server_module, ctx)
+def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cache=None) -> Dict[str, Any]:
+    """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent.
+    sidecar_cache: a reference_material.ChunkIndexCache to serve select_reference_material_context from resident /
+    persisted chunk indexes (off by default: the drop-in then writes nothing into the data directory)."""
+    bindings = build_bindings(server_module, ctx, sidecar_cache)
     saved = _SAVED.setdefault(id(server_module), {})
     done = {}
     for name, fn in bindings.items():

@@ -229,8 +229,11 @@ def load_chunks_from_manifest(path) -> List[dict]:
 
 def select_reference_material_context(doc: dict, *, query_text: str = "", max_chars: int = 0, chunk_limit: int = 0,
                                       chunk_loader: Optional[Callable[[dict], List[dict]]] = None,
-                                      config: ReferenceMaterialConfig = DEFAULT_CONFIG, ctx=None) -> Tuple[str, dict]:
-    """Drop-in for web/server.py:32054.  `chunk_loader` is the reference's load_reference_material_chunks."""
+                                      config: ReferenceMaterialConfig = DEFAULT_CONFIG, ctx=None,
+                                      index_provider: Optional[Callable[[dict, List[dict]], Optional["ChunkIndex"]]] = None) -> Tuple[str, dict]:
+    """Drop-in for web/server.py:32054.  `chunk_loader` is the reference's load_reference_material_chunks.
+    `index_provider(doc, chunks)` may return a resident ChunkIndex over exactly these chunks (ChunkIndexCache + sidecar,
+    SURVEY §8(f)1): the query then walks posting lists instead of re-lowering every chunk; results are identical."""
     cfg = config.normalized()
     chunks = chunk_loader(doc) if chunk_loader is not None else []
     limit = max(1, int(max_chars or cfg.max_doc_length))
@@ -243,21 +246,30 @@ def select_reference_material_context(doc: dict, *, query_text: str = "", max_ch
     selected: List[dict] = []
     picked = []
     if terms:
-        texts = [str(c.get("text") or "") for c in chunks]
-        scores = chunk_scores(texts, [terms], ctx=ctx)[0]
         order_index = np.asarray([int(c.get("index", 0) or 0) for c in chunks], np.int64)
         pos = np.arange(len(chunks), dtype=np.int64)
-        if np.array_equal(order_index, pos):
-            k = min(max_chunks, 32)
-            idx, _sc, n_valid = topk(scores, k, ctx=ctx)
-            picked = idx[0][: int(n_valid[0])].tolist()
-            if max_chunks > 32 and int(n_valid[0]) == 32:
-                picked = None                        # rare: more than 32 chunks requested -> generic path below
+        ix = None
+        if index_provider is not None and max_chunks <= 32 and np.array_equal(order_index, pos):
+            try:
+                ix = index_provider(doc, chunks)
+            except _lib.DvbError:
+                raise
+            except Exception:
+                ix = None                                # provider trouble (I/O, bad ref) never breaks the prompt build
+        if ix is not None:                           # resident posting lists: same counts, same (score desc, index asc) order
+            idx, _sc, n_valid = ix.topk([terms], max_chunks)
+            picked = (idx[0][: int(n_valid[0])] - ix.index_base).tolist()
         else:
+            scores = chunk_scores([str(c.get("text") or "") for c in chunks], [terms], ctx=ctx)[0]
             picked = None
-        if picked is None:                           # chunk["index"] is not the list position, or k > 32:
-            ranked = sorted((i for i in range(len(chunks)) if scores[i] > 0), key=lambda i: (-int(scores[i]), int(order_index[i]), i))
-            picked = ranked[:max_chunks]
+            if np.array_equal(order_index, pos):
+                idx, _sc, n_valid = topk(scores, min(max_chunks, 32), ctx=ctx)
+                picked = idx[0][: int(n_valid[0])].tolist()
+                if max_chunks > 32 and int(n_valid[0]) == 32:
+                    picked = None                    # rare: more than 32 chunks requested -> generic path below
+            if picked is None:                       # chunk["index"] is not the list position, or k > 32:
+                ranked = sorted((i for i in range(len(chunks)) if scores[i] > 0), key=lambda i: (-int(scores[i]), int(order_index[i]), i))
+                picked = ranked[:max_chunks]
     if picked:
         selected = [chunks[i] for i in picked]
         selected.sort(key=lambda item: int(item.get("index", 0) or 0))
@@ -293,6 +305,97 @@ def select_reference_material_context(doc: dict, *, query_text: str = "", max_ch
 
 
 # ----------------------------------------------------------------------------- bulk path: resident inverted index (configs 3/5)
+SIDECAR_NAME = "chunks.dvbidx"
+
+
+def _tag32(tag: bytes) -> bytes:
+    tag = bytes(tag)
+    if len(tag) != 32:
+        raise ValueError("a sidecar tag is exactly 32 bytes")
+    return tag
+
+
+def sidecar_tag(content_sha256: str, chunks: Sequence[dict]) -> bytes:
+    """32-byte identity of what a chunk index was built from: the document's content hash (`content_sha256` of the
+    manifest == `full_content_sha256` of the doc record, web/server.py:31995, 32015) and the (index, start, end) of every
+    indexed chunk — so re-chunking with other parameters, or another document, never matches an old sidecar."""
+    h = hashlib.sha256()
+    h.update(b"dvbidx1|" + str(content_sha256 or "").encode("utf-8"))
+    for c in chunks:
+        h.update(b"|%d,%d,%d" % (int(c.get("index", 0) or 0), int(c.get("start", 0) or 0), int(c.get("end", 0) or 0)))
+    return h.digest()
+
+
+def _indexable_chunks(chunks) -> List[dict]:
+    """The chunks load_reference_material_chunks returns (web/server.py:32033-32034), in manifest order."""
+    return [c for c in (chunks or []) if isinstance(c, dict) and str(c.get("text") or "").strip()]
+
+
+def save_chunk_index_sidecar(manifest_path, manifest: Optional[dict] = None, ctx=None) -> Path:
+    """Build the index over a chunks.json manifest and write chunks.dvbidx beside it.  Returns the sidecar path."""
+    manifest_path = Path(manifest_path)
+    if manifest is None:
+        manifest = json.loads(manifest_path.read_text(encoding="utf-8"))
+    chunks = _indexable_chunks(manifest.get("chunks", []))
+    ix = ChunkIndex([str(c.get("text") or "") for c in chunks], ctx=ctx)
+    try:
+        out = manifest_path.with_name(SIDECAR_NAME)
+        ix.save(out, sidecar_tag(manifest.get("content_sha256", ""), chunks))
+    finally:
+        ix.close()
+    return out
+
+
+class ChunkIndexCache:
+    """Resident indexes of recently queried documents, keyed by sidecar tag (LRU).  get() loads chunks.dvbidx when its
+    tag matches, else builds from the chunk texts and (write_back) rewrites the sidecar."""
+
+    def __init__(self, capacity: int = 64, ctx=None, write_back: bool = True):
+        from collections import OrderedDict
+        self.capacity, self.ctx, self.write_back = int(capacity), ctx, write_back
+        self._lru: "OrderedDict[bytes, ChunkIndex]" = OrderedDict()
+        self.hits = self.loads = self.builds = 0
+
+    def get(self, sidecar_path, content_sha256: str, chunks: Sequence[dict]) -> "ChunkIndex":
+        """`chunks` = what the reference's loader returned (already filtered to non-blank text)."""
+        tag = sidecar_tag(content_sha256, chunks)
+        ix = self._lru.get(tag)
+        if ix is not None:
+            self._lru.move_to_end(tag)
+            self.hits += 1
+            return ix
+        side = Path(sidecar_path) if sidecar_path else None
+        ix = None
+        if side is not None and side.exists():
+            try:
+                ix = ChunkIndex.load(side, tag, ctx=self.ctx)
+                if ix.stats()["n_chunks"] != len(chunks):
+                    ix.close()
+                    ix = None
+                else:
+                    self.loads += 1
+            except _lib.DvbError:
+                ix = None                                # stale / truncated / corrupt: rebuild below
+        if ix is None:
+            ix = ChunkIndex([str(c.get("text") or "") for c in chunks], ctx=self.ctx)
+            self.builds += 1
+            if self.write_back and side is not None:
+                try:
+                    ix.save(side, tag)
+                except _lib.DvbError:
+                    pass                                 # read-only data dir: the resident copy still serves this process
+        self._lru[tag] = ix
+        while len(self._lru) > self.capacity:
+            _, old = self._lru.popitem(last=False)
+            old.close()
+        return ix
+
+    def clear(self) -> None:
+        for ix in self._lru.values():
+            ix.close()
+        self._lru.clear()
+
+
 class ChunkIndex:
     """Device-resident positional inverted index over a chunk corpus (csrc/index.cu).  Same results as
     chunk_scores() + topk() — exact non-overlapping counts, (score desc, index asc), positives only — for many
@@ -312,6 +415,26 @@ class ChunkIndex:
             rc = self.ctx.lib.dvb_chunk_index_build(self.ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), len(off) - 1, C.byref(self._h))
         self.ctx.check(rc, "dvb_chunk_index_build")
         self.build_ms = self.ctx.last_kernel_ms
+
+    # ---- persistent sidecar next to chunks.json
+    def save(self, path, tag: Optional[bytes] = None) -> None:
+        """Write the resident index to `path` (atomic rename).  `tag` = 32 bytes naming the content (see sidecar_tag)."""
+        import ctypes as C
+        t = (C.c_uint8 * 32).from_buffer_copy(_tag32(tag)) if tag is not None else None
+        self.ctx.check(self.ctx.lib.dvb_chunk_index_save(self.ctx.handle, self._h, str(path).encode(), t), "dvb_chunk_index_save")
+
+    @classmethod
+    def load(cls, path, tag: Optional[bytes] = None, *, index_base: int = 0, ctx=None) -> "ChunkIndex":
+        """Load a sidecar written by save(); raises DvbError if it is missing, stale (tag), truncated or corrupt."""
+        import ctypes as C
+        self = cls.__new__(cls)
+        self.ctx = ctx or _lib.Context.get()
+        self.index_base = int(index_base)
+        self._h = C.c_void_p()
+        self.build_ms = 0.0
+        t = (C.c_uint8 * 32).from_buffer_copy(_tag32(tag)) if tag is not None else None
+        self.ctx.check(self.ctx.lib.dvb_chunk_index_load(self.ctx.handle, str(path).encode(), t, C.byref(self._h)), "dvb_chunk_index_load")
+        return self
 
     def stats(self) -> dict:
         out = np.zeros(6, np.int64)

@@ -199,6 +199,15 @@ int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* index, int32_t mem, 
                              const int32_t* query_term_off, int32_t nq, int64_t index_base, int32_t k,
                              int64_t* out_idx, int32_t* out_score, int32_t* out_n);
 
+/* ---- §8(f)1  persistent sidecar of a chunk index, written next to chunks.json (web/server.py:31986-31999) so that a
+ * later process does not re-parse and re-lower every chunk per prompt build (web/server.py:32028, 32075).
+ * save: writes `path` atomically (path + ".tmp", then rename).  tag32 = 32 caller bytes identifying the content the index
+ * was built from (may be NULL = all zero).  load: refuses a file whose tag differs from tag32 (NULL = accept any), whose
+ * device-side checksums or structural validation fail, or whose format version differs: DVB_E_INVALID, never a stale or
+ * partial index.  The loaded index belongs to ctx's device and is freed with dvb_chunk_index_free. */
+int32_t dvb_chunk_index_save(dvb_ctx* ctx, const dvb_index* index, const char* path, const uint8_t* tag32);
+int32_t dvb_chunk_index_load(dvb_ctx* ctx, const char* path, const uint8_t* tag32, dvb_index** out);
+
 #ifdef __cplusplus
 }
 #endif

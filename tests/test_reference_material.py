@@ -183,3 +183,115 @@ def test_gpu_chunk_build_batch_and_ragged(gpu_ctx, oracle):
             raw = text.encode("utf-8")
             for (_a, _b, ts, te, b0, b1) in sp:
                 assert raw[b0:b1].decode("utf-8") == text[ts:te]
+
+
+# ------------------------------------------------------------------ chunks.dvbidx sidecar
+
+def test_sidecar_tag_identifies_content_and_chunking():
+    from deep_vision_b200 import reference_material as rm
+    chunks = [{"index": 0, "start": 0, "end": 1800, "text": "a"}, {"index": 1, "start": 1640, "end": 3000, "text": "b"}]
+    t = rm.sidecar_tag("ab" * 32, chunks)
+    assert len(t) == 32 and t == rm.sidecar_tag("ab" * 32, [dict(c) for c in chunks])
+    assert t != rm.sidecar_tag("cd" * 32, chunks)                                     # other document
+    assert t != rm.sidecar_tag("ab" * 32, chunks[:1])                                 # other chunk count
+    moved = [dict(chunks[0]), dict(chunks[1], start=1600)]
+    assert t != rm.sidecar_tag("ab" * 32, moved)                                      # re-chunked with another overlap
+    with pytest.raises(ValueError):
+        rm._tag32(b"short")
+
+
+@pytest.mark.gpu
+def test_gpu_sidecar_roundtrip_and_rejections(gpu_ctx, tmp_path, monkeypatch):
+    from deep_vision_b200 import _lib, reference_material as rm
+    from test_parallel import make_corpus
+    chunks, queries = make_corpus(n_chunks=900, nq=30, seed=33)
+    chunks += ["", "aaaa aa", "离线审批" * 30]
+    queries += [["aa"], ["离线审批", "审批离线"]]
+    tag = bytes(range(32))
+    for seg_bytes in (None, "8192"):                                                   # one segment / many segments
+        if seg_bytes:
+            monkeypatch.setenv("DVB_IX_SEG_BYTES", seg_bytes)
+        ix = rm.ChunkIndex(chunks, index_base=5, ctx=gpu_ctx)
+        monkeypatch.delenv("DVB_IX_SEG_BYTES", raising=False)
+        want = ix.topk(queries, 8)
+        p = tmp_path / f"chunks_{seg_bytes}.dvbidx"
+        ix.save(p, tag)
+        assert p.exists() and not (tmp_path / (p.name + ".tmp")).exists()
+        back = rm.ChunkIndex.load(p, tag, index_base=5, ctx=gpu_ctx)
+        assert back.stats() == ix.stats()
+        for a, b in zip(want, back.topk(queries, 8)):
+            assert np.array_equal(a, b)
+        back.close()
+        rm.ChunkIndex.load(p, None, ctx=gpu_ctx).close()                              # NULL tag accepts any content
+        with pytest.raises(_lib.DvbError, match="tag mismatch"):
+            rm.ChunkIndex.load(p, bytes(32), ctx=gpu_ctx)
+        raw = bytearray(p.read_bytes())
+        bad = tmp_path / "bad.dvbidx"
+        bad.write_bytes(raw[: len(raw) // 2])                                          # truncated
+        with pytest.raises(_lib.DvbError):
+            rm.ChunkIndex.load(bad, tag, ctx=gpu_ctx)
+        flip = bytearray(raw); flip[len(flip) - 100] ^= 0x40                           # bit rot in the last array
+        bad.write_bytes(flip)
+        with pytest.raises(_lib.DvbError, match="checksum"):
+            rm.ChunkIndex.load(bad, tag, ctx=gpu_ctx)
+        bad.write_bytes(b"not an index" * 20)
+        with pytest.raises(_lib.DvbError):
+            rm.ChunkIndex.load(bad, tag, ctx=gpu_ctx)
+        ix.close()
+    with pytest.raises(_lib.DvbError):
+        rm.ChunkIndex.load(tmp_path / "missing.dvbidx", tag, ctx=gpu_ctx)
+    empty = rm.ChunkIndex([], ctx=gpu_ctx)
+    empty.save(tmp_path / "e.dvbidx", tag)
+    e2 = rm.ChunkIndex.load(tmp_path / "e.dvbidx", tag, ctx=gpu_ctx)
+    assert e2.stats()["n_chunks"] == 0 and e2.topk([["离线"]], 4)[2].tolist() == [0]
+
+
+@pytest.mark.gpu
+def test_gpu_select_through_sidecar_cache_matches_golden(gpu_ctx, golden, tmp_path):
+    """The resident / persisted index gives exactly the reference's selections (a7 goldens), first from a fresh build
+    (sidecar written), then from a second cache that can only load the sidecar, then with a stale sidecar."""
+    import json
+    from deep_vision_b200 import reference_material as rm
+    d = docs(golden)
+    cases = [c for c in golden("a7_select.json") if c["doc"] in d]
+    dirs, recs = {}, {}
+    for name in {c["doc"] for c in cases}:
+        man = rm.build_chunk_manifest(doc_id=name, filename=name + ".md", content=d[name], ext=".md", ctx=gpu_ctx)
+        (tmp_path / name).mkdir()
+        (tmp_path / name / "chunks.json").write_text(json.dumps(man, ensure_ascii=False), encoding="utf-8")
+        dirs[name] = tmp_path / name
+        recs[name] = {"content": d[name][:10000], "full_content_sha256": man["content_sha256"], "name": name}
+
+    def run(cache):
+        def provider(doc, chunks):
+            return cache.get(dirs[doc["name"]] / rm.SIDECAR_NAME, doc["full_content_sha256"], chunks)
+        n = 0
+        for case in cases:
+            chunks = rm.load_chunks_from_manifest(dirs[case["doc"]] / "chunks.json")
+            text, meta = rm.select_reference_material_context(recs[case["doc"]], query_text=case["query"], max_chars=case["max_chars"],
+                                                              chunk_limit=case["chunk_limit"], chunk_loader=lambda doc: chunks,
+                                                              ctx=gpu_ctx, index_provider=provider)
+            assert meta == case["meta"], (case["doc"], case["query"])
+            assert sha(text) == case["context_sha"] and len(text) == case["context_len"]
+            n += 1
+        return n
+
+    c1 = rm.ChunkIndexCache(ctx=gpu_ctx)
+    assert run(c1) >= 30 and c1.builds == len(dirs) and c1.loads == 0 and c1.hits > 0
+    assert all((p / rm.SIDECAR_NAME).exists() for p in dirs.values())
+    c1.clear()
+    c2 = rm.ChunkIndexCache(ctx=gpu_ctx, write_back=False)
+    run(c2)
+    assert c2.builds == 0 and c2.loads == len(dirs)
+    c2.clear()
+    # a sidecar left over from other content is ignored and replaced
+    names = sorted(dirs)
+    if len(names) >= 2:
+        (dirs[names[0]] / rm.SIDECAR_NAME).write_bytes((dirs[names[1]] / rm.SIDECAR_NAME).read_bytes())
+        c3 = rm.ChunkIndexCache(ctx=gpu_ctx)
+        run(c3)
+        assert c3.builds == 1 and c3.loads == len(dirs) - 1
+        c3.clear()
+    # explicit helper used by bulk jobs
+    out = rm.save_chunk_index_sidecar(dirs[names[0]] / "chunks.json", ctx=gpu_ctx)
+    assert out.name == rm.SIDECAR_NAME and out.stat().st_size > 256

@@ -21,6 +21,7 @@ ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--qreps", type=int, default=0, help="query repetitions (default: --reps)")
 ap.add_argument("--replicate", type=int, default=1,
                 help="generate 1/R of the shard on the host and tile it R times in HBM (config-5 sized shards without minutes of numpy)")
+ap.add_argument("--sidecar", default="", help="also time dvb_chunk_index_save / _load through this path (SURVEY 8(f)1)")
 args = ap.parse_args()
 rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(lr)
@@ -85,6 +86,17 @@ for _ in range(args.qreps or args.reps):
                                       lo, args.k, rm.ptr(oi), rm.ptr(os_), rm.ptr(on))
     ctx.check(rc, "topk")
     q_ms.append(ctx.last_kernel_ms)
+side = {}
+if args.sidecar and rank == 0:
+    p = Path(args.sidecar)
+    t0 = time.time(); ix.save(p, bytes(32)); side["save_s"] = time.time() - t0
+    side["file_bytes"] = p.stat().st_size
+    t0 = time.time(); ix2 = rm.ChunkIndex.load(p, bytes(32), index_base=lo, ctx=ctx); side["load_s"] = time.time() - t0
+    nqs = min(args.queries, 2000)
+    a = ix2.topk(terms[:nqs], args.k)
+    side["same_topk_as_built_index"] = bool(np.array_equal(a[0], oi[:nqs]) and np.array_equal(a[1], os_[:nqs]) and np.array_equal(a[2], on[:nqs]))
+    side["save_GBps"] = side["file_bytes"] / side["save_s"] / 1e9; side["load_GBps"] = side["file_bytes"] / side["load_s"] / 1e9
+    ix2.close(); p.unlink()
 t0 = time.time()
 gi, gs, gn = parallel.merge_topk(oi, os_, args.k, ctx=ctx)
 merge_s = time.time() - t0
@@ -96,6 +108,6 @@ if rank == 0:
                       "replicate": args.replicate, "segments_est": -(-st["text_bytes"] // (2000 << 20)), "build_ms": build_ms, "chunks_indexed_per_s_per_gpu": (hi - lo) / (b / 1e3), "build_GBps_algorithmic": algo_build / b / 1e6,
                       "query_ms": q_ms, "effective_pairs_per_s_per_gpu": (hi - lo) * args.queries / (qm / 1e3),
                       "merge_s_host_incl_allgather": merge_s, "n_terms": int(len(toff) - 1), "mean_hits": float(gn.mean()),
-                      "host_gen_s": gen_s, "host_tokenize_s": tok_s}))
+                      "host_gen_s": gen_s, "host_tokenize_s": tok_s, "sidecar": side}))
 if world > 1:
     dist.barrier(); dist.destroy_process_group()
