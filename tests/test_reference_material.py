@@ -253,7 +253,14 @@ def test_gpu_select_through_sidecar_cache_matches_golden(gpu_ctx, golden, tmp_pa
     import json
     from deep_vision_b200 import reference_material as rm
     d = docs(golden)
-    cases = [c for c in golden("a7_select.json") if c["doc"] in d]
+    def hashable(text):                              # the reference's own manifest writer hashes content.encode("utf-8") (31995):
+        try:                                         # documents with lone surrogates never get a manifest, hence no sidecar
+            text.encode("utf-8")
+            return True
+        except UnicodeEncodeError:
+            return False
+    cases = [c for c in golden("a7_select.json") if c["doc"] in d and hashable(d[c["doc"]])]
+    assert len(cases) >= 20
     dirs, recs = {}, {}
     for name in {c["doc"] for c in cases}:
         man = rm.build_chunk_manifest(doc_id=name, filename=name + ".md", content=d[name], ext=".md", ctx=gpu_ctx)
@@ -262,8 +269,11 @@ def test_gpu_select_through_sidecar_cache_matches_golden(gpu_ctx, golden, tmp_pa
         dirs[name] = tmp_path / name
         recs[name] = {"content": d[name][:10000], "full_content_sha256": man["content_sha256"], "name": name}
 
+    called = set()
+
     def run(cache):
         def provider(doc, chunks):
+            called.add(doc["name"])
             return cache.get(dirs[doc["name"]] / rm.SIDECAR_NAME, doc["full_content_sha256"], chunks)
         n = 0
         for case in cases:
@@ -277,21 +287,25 @@ def test_gpu_select_through_sidecar_cache_matches_golden(gpu_ctx, golden, tmp_pa
         return n
 
     c1 = rm.ChunkIndexCache(ctx=gpu_ctx)
-    assert run(c1) >= 30 and c1.builds == len(dirs) and c1.loads == 0 and c1.hits > 0
-    assert all((p / rm.SIDECAR_NAME).exists() for p in dirs.values())
+    assert run(c1) >= 20
+    assert len(called) >= 4 and c1.builds == len(called) and c1.loads == 0 and c1.hits > 0      # blank documents have no chunks
+    assert all((dirs[n] / rm.SIDECAR_NAME).exists() for n in called)
     c1.clear()
     c2 = rm.ChunkIndexCache(ctx=gpu_ctx, write_back=False)
     run(c2)
-    assert c2.builds == 0 and c2.loads == len(dirs)
+    assert c2.builds == 0 and c2.loads == len(called)
     c2.clear()
     # a sidecar left over from other content is ignored and replaced
-    names = sorted(dirs)
-    if len(names) >= 2:
-        (dirs[names[0]] / rm.SIDECAR_NAME).write_bytes((dirs[names[1]] / rm.SIDECAR_NAME).read_bytes())
-        c3 = rm.ChunkIndexCache(ctx=gpu_ctx)
-        run(c3)
-        assert c3.builds == 1 and c3.loads == len(dirs) - 1
-        c3.clear()
+    names = sorted(called)
+    (dirs[names[0]] / rm.SIDECAR_NAME).write_bytes((dirs[names[1]] / rm.SIDECAR_NAME).read_bytes())
+    c3 = rm.ChunkIndexCache(ctx=gpu_ctx)
+    run(c3)
+    assert c3.builds == 1 and c3.loads == len(called) - 1
+    c3.clear()
+    c4 = rm.ChunkIndexCache(ctx=gpu_ctx, write_back=False)                                      # ... and was rewritten by c3
+    run(c4)
+    assert c4.builds == 0
+    c4.clear()
     # explicit helper used by bulk jobs
     out = rm.save_chunk_index_sidecar(dirs[names[0]] / "chunks.json", ctx=gpu_ctx)
     assert out.name == rm.SIDECAR_NAME and out.stat().st_size > 256
