@@ -153,12 +153,42 @@ __global__ void __launch_bounds__(TOPK_WARPS * 32) k_topk_partial(const int32_t*
     const int32_t* sc = score + (int64_t)q * n;
     const int64_t* ix = idx ? idx + (int64_t)q * n : nullptr;
     int32_t es = 0; int64_t ei = 0x7fffffffffffffffLL;
-    for (int64_t b0 = lo + (int64_t)warp * 32; b0 < hi; b0 += TOPK_WARPS * 32) {
-        const int64_t i = b0 + lane;
-        const bool v = i < hi;
-        const int32_t cs = v ? sc[i] : 0;
-        const int64_t ci = v ? (ix ? ix[i] : index_base + i) : 0;
-        if (__any_sync(0xffffffffu, cs > 0)) warp_topk_insert(es, ei, cs, ci, v, k, lane);
+    if (ix) {
+        for (int64_t b0 = lo + (int64_t)warp * 32; b0 < hi; b0 += TOPK_WARPS * 32) {
+            const int64_t i = b0 + lane;
+            const bool v = i < hi;
+            const int32_t cs = v ? sc[i] : 0;
+            const int64_t ci = v ? ix[i] : 0;
+            if (__any_sync(0xffffffffu, cs > 0)) warp_topk_insert(es, ei, cs, ci, v, k, lane);
+        }
+    } else {
+        // dense score rows are almost all zero: stream them as 16-byte vectors (two per lane and step), insert rarely
+        const int64_t v0 = min(hi, lo + (int64_t)((4 - ((reinterpret_cast<uintptr_t>(sc + lo) >> 2) & 3)) & 3));   // first 16-byte aligned item
+        const int64_t nvec = (hi - v0) >> 2, v1 = v0 + 4 * nvec;
+        if (warp == 0) {                                          // <= 3 + 3 unaligned items at the two ends
+            const int64_t i = lane < 3 ? lo + lane : v1 + (lane - 3);
+            const bool v = lane < 3 ? i < v0 : (lane < 6 && i < hi);
+            const int32_t cs = v ? sc[i] : 0;
+            if (__any_sync(0xffffffffu, cs > 0)) warp_topk_insert(es, ei, cs, index_base + i, v, k, lane);
+        }
+        const int4* vec = reinterpret_cast<const int4*>(sc + v0);
+        for (int64_t g0 = (int64_t)warp * 64; g0 < nvec; g0 += TOPK_WARPS * 64) {
+            const int64_t ga = g0 + lane, gb = g0 + 32 + lane;
+            int4 a = make_int4(0, 0, 0, 0), b = make_int4(0, 0, 0, 0);
+            if (ga < nvec) a = vec[ga];
+            if (gb < nvec) b = vec[gb];
+            if (__any_sync(0xffffffffu, (a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) != 0)) {
+                const int64_t ia = index_base + v0 + 4 * ga, ib = index_base + v0 + 4 * gb;
+                if (__any_sync(0xffffffffu, a.x > 0)) warp_topk_insert(es, ei, a.x, ia, true, k, lane);
+                if (__any_sync(0xffffffffu, a.y > 0)) warp_topk_insert(es, ei, a.y, ia + 1, true, k, lane);
+                if (__any_sync(0xffffffffu, a.z > 0)) warp_topk_insert(es, ei, a.z, ia + 2, true, k, lane);
+                if (__any_sync(0xffffffffu, a.w > 0)) warp_topk_insert(es, ei, a.w, ia + 3, true, k, lane);
+                if (__any_sync(0xffffffffu, b.x > 0)) warp_topk_insert(es, ei, b.x, ib, true, k, lane);
+                if (__any_sync(0xffffffffu, b.y > 0)) warp_topk_insert(es, ei, b.y, ib + 1, true, k, lane);
+                if (__any_sync(0xffffffffu, b.z > 0)) warp_topk_insert(es, ei, b.z, ib + 2, true, k, lane);
+                if (__any_sync(0xffffffffu, b.w > 0)) warp_topk_insert(es, ei, b.w, ib + 3, true, k, lane);
+            }
+        }
     }
     s_s[warp][lane] = es; s_i[warp][lane] = ei;
     __syncthreads();
@@ -266,7 +296,7 @@ void dv_launch_symbolize(dvb_ctx* ctx, cudaStream_t st, const uint8_t* d_utf8, c
     ctx->launches += 1;
 }
 int64_t dv_topk_splits(dvb_ctx* ctx, int64_t n, int32_t nq) {
-    return std::max<int64_t>(1, std::min<int64_t>((n + 8191) / 8192, std::max<int64_t>(1, (int64_t)ctx->num_sm * 4 / std::max(1, nq))));
+    return std::max<int64_t>(1, std::min<int64_t>((n + 8191) / 8192, std::max<int64_t>(1, (int64_t)ctx->num_sm * 8 / std::max(1, nq))));
 }
 // d_ps / d_pi: nq * n_split * k scratch entries each
 void dv_topk_device(dvb_ctx* ctx, cudaStream_t st, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq, int64_t index_base, int32_t k,

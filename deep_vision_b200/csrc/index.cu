@@ -147,15 +147,18 @@ __global__ void __launch_bounds__(256) k_ix_head_count(const unsigned long long*
     __syncthreads();
     if (threadIdx.x == 0) blk_cnt[blockIdx.x] = s_cnt;
 }
+// Also writes the resident form of the sorted postings: the chunk id alone (the key is implied by the key's offset range).
 __global__ void __launch_bounds__(256) k_ix_head_write(const unsigned long long* __restrict__ pk, int64_t n, const int64_t* __restrict__ blk_off,
-                                                        uint32_t* __restrict__ ukeys, int64_t* __restrict__ uoff) {
+                                                        uint32_t* __restrict__ ukeys, int64_t* __restrict__ uoff, uint32_t* __restrict__ pc) {
     __shared__ int s_warp[8];
     const int64_t base = (int64_t)blockIdx.x * IX_HEAD_TILE;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int64_t w = blk_off[blockIdx.x];
     for (int i0 = 0; i0 < IX_HEAD_TILE; i0 += 256) {                 // ordered: 256 consecutive postings per step
         const int64_t g = base + i0 + threadIdx.x;
-        const bool head = g < n && (g == 0 || (uint32_t)pk[g] != (uint32_t)pk[g - 1]);
+        const unsigned long long kg = g < n ? pk[g] : 0ull;
+        const bool head = g < n && (g == 0 || (uint32_t)kg != (uint32_t)pk[g - 1]);
+        if (g < n) pc[g] = (uint32_t)(kg >> 32);
         const uint32_t bal = __ballot_sync(0xffffffffu, head);
         if (lane == 0) s_warp[warp] = __popc(bal);
         __syncthreads();
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(256) k_ix_head_write(const unsigned long long*
         for (int k = 0; k < 8; k++) { if (k < warp) before += s_warp[k]; total += s_warp[k]; }
         if (head) {
             const int64_t o = w + before + __popc(bal & ((1u << lane) - 1u));
-            ukeys[o] = (uint32_t)pk[g]; uoff[o] = g;
+            ukeys[o] = (uint32_t)kg; uoff[o] = g;
         }
         w += total;
         __syncthreads();
@@ -195,10 +198,11 @@ __global__ void __launch_bounds__(256) k_ix_plan(const uint16_t* __restrict__ te
             int64_t lo2 = lo, hi2 = n_keys;
             while (lo2 < hi2) { const int64_t m = (lo2 + hi2) >> 1; if (ukeys[m] < key_hi) lo2 = m + 1; else hi2 = m; }
             const int64_t a = n_keys > 0 ? uoff[lo] : 0, b = n_keys > 0 ? uoff[lo2] : 0;
-            // cost in bytes: every posting of the pair is streamed (12 B); a candidate that is not decided by the pair and
-            // the posting's look-ahead symbol alone costs two random sectors (chunk offset + symbols).  The look-ahead
-            // symbol lets ~1/50 of the postings through.
-            const int64_t cost = (b - a) * 12 + (covered ? 0 : (nxt ? (b - a) * 64 / 12 : (b - a) * 64));
+            // cost in bytes: every posting of the pair streams its 4-byte position word; the chunk id (a 32-byte sector) is
+            // only fetched for postings whose look-ahead symbol matches (~1/12 of a sub-list), and a candidate the pair and
+            // the look-ahead symbol do not decide costs two more random sectors (chunk offset + symbols).  A 2-symbol term
+            // needs the chunk of every posting.
+            const int64_t cost = nxt ? (b - a) * 4 + (b - a) * (32 + (covered ? 0 : 64)) / 12 : (b - a) * 8;
             if (best_df < 0 || cost < best_df) { best_df = cost; best_lo = a; best_hi = b; best_j = j; }
             if (b == a) break;                                    // a pair that occurs nowhere: the term occurs nowhere
         }
@@ -240,16 +244,22 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
         // a run of r symbols holds floor(r / 2) non-overlapping occurrences, which is what the greedy scan would count.
         const bool pair_only = L == 2, same2 = pair_only && ts[0] == ts[1];
         const uint32_t next_sym = use_next ? ts[j + 2] : 0u;
-        const int64_t skip_chunk = r_lo > lo ? (int64_t)(ix.pk[r_lo - 1] >> 32) : -1;      // owned by the previous item
-        const int64_t last_chunk = (int64_t)(ix.pk[r_hi - 1] >> 32);                       // ours to finish
+        const int64_t skip_chunk = r_lo > lo ? (int64_t)ix.pc[r_lo - 1] : -1;             // owned by the previous item
+        const int64_t last_chunk = (int64_t)ix.pc[r_hi - 1];                              // ours to finish
         if (!pair_only && r_lo > lo && skip_chunk == last_chunk) continue;   // the whole item lies inside a chunk the previous item owns
         int64_t cur = -1; int32_t cnt = 0, last_end = 0;
         bool more = true, leading = r_lo > lo;                     // still inside the run of postings the previous item owns
+        uint32_t vn = r_lo + lane < hi ? ix.pv[r_lo + lane] : 0u;  // position words are prefetched one step ahead
         for (int64_t p0 = r_lo; p0 < hi && more; p0 += 32) {
             const int64_t p = p0 + lane;
+            const uint32_t v = vn;
+            if (p + 32 < hi) vn = ix.pv[p + 32];
             int64_t chunk = -2; int32_t start = 0, wgt = 0; bool beyond = false;
-            uint32_t v = 0;
-            if (p < hi) { v = ix.pv[p]; chunk = (int64_t)(ix.pk[p] >> 32); }
+            // The chunk id is needed by every lane only at the item's borders (ownership of the first / last chunk) and by
+            // 2-symbol terms; inside the item a term with a look-ahead symbol fetches it for the lanes that pass the filter.
+            const bool border = leading || p0 + 32 > r_hi || pair_only;
+            const bool cand = p < hi && (int32_t)(v & 0xFFFFu) >= j && (pair_only || (v >> 16) == next_sym);
+            if (p < hi && (border || cand)) chunk = (int64_t)ix.pc[p];
             bool skip = false;
             if (leading) {                                         // only the LEADING postings of skip_chunk are skipped (a pair's
                 const uint32_t other = __ballot_sync(0xffffffffu, p < hi && chunk != skip_chunk);   // sub-lists restart the chunk order)
@@ -259,7 +269,7 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
             if (p < hi) {
                 start = (int32_t)(v & 0xFFFFu) - j;
                 beyond = p >= r_hi && chunk != last_chunk;          // first posting of a chunk the next item owns
-                if (!beyond && !skip && start >= 0) {
+                if (!beyond && !skip && cand) {
                     if (pair_only) {
                         if (!same2) wgt = 1;
                         else if ((v >> 16) != ts[0]) {
@@ -268,7 +278,7 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
                             while (q > 0 && s[q - 1] == ts[0]) { q--; r++; }
                             wgt = r >> 1;
                         }
-                    } else if ((v >> 16) == next_sym) {
+                    } else {
                         // the pair and the look-ahead symbol are already matched: only the rest of the term is read back,
                         // and the chunk length only when the term reaches past the look-ahead symbol
                         if (covered) wgt = 1;
@@ -306,7 +316,7 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
 
 // ------------------------------------------------------------------ host side
 void ix_free_seg(IxSeg& sg) {
-    void* ptrs[] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pk, sg.pv, sg.ukeys, sg.uoff };
+    void* ptrs[] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pc, sg.pv, sg.ukeys, sg.uoff };
     for (void* p : ptrs) if (p) cudaFree(p);
     sg = IxSeg();
 }
@@ -321,7 +331,7 @@ extern "C" void dvb_chunk_index_free(dvb_index* ix) {
 extern "C" int32_t dvb_chunk_index_stats(const dvb_index* ix, int64_t* out6) {
     if (!ix || !out6) return DVB_E_INVALID;
     out6[0] = ix->n_chunks; out6[1] = ix->n_bytes; out6[2] = ix->n_post; out6[3] = ix->n_keys;
-    out6[4] = 2 * ix->n_bytes + 12 * ix->n_chunks + 12 * ix->n_post + 12 * ix->n_keys + 80 * (int64_t)ix->segs.size();   // resident device bytes
+    out6[4] = 2 * ix->n_bytes + 12 * ix->n_chunks + 8 * ix->n_post + 12 * ix->n_keys + 80 * (int64_t)ix->segs.size();   // resident device bytes
     out6[5] = ix->device;
     return DVB_OK;
 }
@@ -338,8 +348,8 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
     const int64_t nb = hoff[n_chunks];
     sg->n_chunks = n_chunks; sg->n_bytes = nb;
     uint8_t* d_text = nullptr; int32_t* d_pc = nullptr; int64_t* d_po = nullptr; int64_t* d_scan = nullptr;
-    unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
-    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFreeAsync(p, st); };
+    unsigned long long* s_pk = nullptr; unsigned long long* t_pk = nullptr; uint32_t* t_pv = nullptr; uint32_t* d_hist = nullptr; int32_t* d_bc = nullptr; int64_t* d_bo = nullptr;
+    auto drop = [&]() { void* t[] = { d_text, d_pc, d_po, d_scan, s_pk, t_pk, t_pv, d_hist, d_bc, d_bo }; for (void* p : t) if (p) cudaFreeAsync(p, st); };
 #define IX_TRY(expr) do { cudaError_t e2__ = (expr); if (e2__ != cudaSuccess) { \
         dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e2__), #expr); drop(); cudaStreamSynchronize(st); ix_free_seg(*sg); cudaGetLastError(); \
         return e2__ == cudaErrorMemoryAllocation ? DVB_E_NOMEM : DVB_E_CUDA; } } while (0)
@@ -383,27 +393,29 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
     if (d_text) { cudaFreeAsync(d_text, st); d_text = nullptr; }
     if (n_post > 0) {
         const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
-        IX_TRY(cudaMallocAsync((void**)&sg->pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&sg->pv, 4 * (size_t)n_post, st));
+        IX_TRY(cudaMallocAsync((void**)&s_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&sg->pv, 4 * (size_t)n_post, st));
         IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
         IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * (size_t)(256 * nbk + 256), st));
-        k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, sg->pk, sg->pv);
+        k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, s_pk, sg->pv);
         ctx->launches += 1;
         // K2b: stable sort by the 30 key bits + 2 sub-list bits (32 = 4 passes of 8)
         int64_t l = 0;
-        const int which = dv_radix_sort_pairs(sg->pk, sg->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
+        const int which = dv_radix_sort_pairs(s_pk, sg->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
         ctx->launches += l;
-        if (which) { std::swap(sg->pk, t_pk); std::swap(sg->pv, t_pv); }
+        if (which) { std::swap(s_pk, t_pk); std::swap(sg->pv, t_pv); }
+        cudaFreeAsync(t_pk, st); t_pk = nullptr; cudaFreeAsync(t_pv, st); t_pv = nullptr;      // the pool hands these bytes to pc below
+        IX_TRY(cudaMallocAsync((void**)&sg->pc, 4 * (size_t)n_post + 64, st));
         // K2c: segment heads
         const int64_t nhb = (n_post + IX_HEAD_TILE - 1) / IX_HEAD_TILE;
         IX_TRY(cudaMallocAsync((void**)&d_bc, 4 * (size_t)nhb + 4, st)); IX_TRY(cudaMallocAsync((void**)&d_bo, 8 * (size_t)(nhb + 1), st));
-        k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(sg->pk, n_post, d_bc);
+        k_ix_head_count<<<(unsigned)nhb, 256, 0, st>>>(s_pk, n_post, d_bc);
         k_ix_scan<<<1, 1024, 0, st>>>(d_bc, d_bo, nhb);
         int64_t n_keys = 0;
         IX_TRY(cudaMemcpyAsync(&n_keys, d_bo + nhb, 8, cudaMemcpyDeviceToHost, st));
         IX_TRY(cudaStreamSynchronize(st));
         sg->n_keys = n_keys;
         IX_TRY(cudaMallocAsync((void**)&sg->ukeys, 4 * (size_t)n_keys + 4, st)); IX_TRY(cudaMallocAsync((void**)&sg->uoff, 8 * (size_t)(n_keys + 1), st));
-        k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(sg->pk, n_post, d_bo, sg->ukeys, sg->uoff);
+        k_ix_head_write<<<(unsigned)nhb, 256, 0, st>>>(s_pk, n_post, d_bo, sg->ukeys, sg->uoff, sg->pc);
         IX_TRY(cudaMemcpyAsync(sg->uoff + n_keys, &n_post, 8, cudaMemcpyHostToDevice, st));
         IX_TRY(cudaStreamSynchronize(st));                     // n_post is a stack variable
         ctx->launches += 3;
@@ -481,7 +493,7 @@ extern "C" int32_t dvb_chunk_index_topk(dvb_ctx* ctx, const dvb_index* ix, int32
     // batch of queries sharing one dense score tile (<= 512 MB)
     const int64_t budget = 512LL << 20;
     const int32_t B = (int32_t)std::max<int64_t>(1, std::min<int64_t>(nq, N > 0 ? budget / (4 * N) : nq));
-    const size_t n_part = (size_t)B + (size_t)ctx->num_sm * 4;     // nb * dv_topk_splits(., nb) <= max(nb, 4 * num_sm) for every nb <= B
+    const size_t n_part = (size_t)B + (size_t)ctx->num_sm * 8;     // nb * dv_topk_splits(., nb) <= max(nb, 8 * num_sm) for every nb <= B
     size_t need = dvb_pad(4 * (size_t)B * (size_t)std::max<int64_t>(N, 1)) + dvb_pad(8 * (size_t)n_terms + 16) * 3 + dvb_pad(4 * (size_t)n_terms + 4) * 2
                 + dvb_pad(4 * n_part * k) + dvb_pad(8 * n_part * k) + 4096;
     if (mem == DVB_MEM_HOST) need += dvb_pad(2 * (size_t)n_sym + 2) + dvb_pad(4 * (size_t)n_terms + 4) + dvb_pad(4 * (size_t)nq + 4)

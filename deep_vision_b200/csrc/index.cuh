@@ -11,8 +11,8 @@ struct IxSeg {
     uint16_t* sym = nullptr;            // symbols of chunk c at sym[sym_off[c] .. + sym_cnt[c])
     int64_t* sym_off = nullptr;         // [n_chunks + 1] (= byte offsets rebased to 0)
     int32_t* sym_cnt = nullptr;         // [n_chunks]
-    unsigned long long* pk = nullptr;   // [n_post] chunk << 32 | pair key, sorted by (key, chunk, pos)
-    uint32_t* pv = nullptr;             // [n_post] position
+    uint32_t* pc = nullptr;             // [n_post] chunk (segment-local) of every posting, sorted by (key, chunk, position)
+    uint32_t* pv = nullptr;             // [n_post] position | symbol after the pair << 16
     uint32_t* ukeys = nullptr;          // [n_keys] distinct pair keys ascending
     int64_t* uoff = nullptr;            // [n_keys + 1]
 };

@@ -8,7 +8,7 @@
 // File (little-endian, every array starts on a 16-byte boundary):
 //   header   "DVBIDX\1\0", u32 version, u32 n_segments, i64 n_chunks, n_bytes, n_post, n_keys, u8 tag[32], u32 sub_bits, pad to 128
 //   segment  i64 chunk_base, n_chunks, n_bytes, n_post, n_keys, u64 checksum[7]  (128 B), then the 7 arrays
-//            sym u16[n_bytes] | sym_off i64[n_chunks+1] | sym_cnt i32[n_chunks] | pk u64[n_post] | pv u32[n_post] |
+//            sym u16[n_bytes] | sym_off i64[n_chunks+1] | sym_cnt i32[n_chunks] | pc u32[n_post] | pv u32[n_post] |
 //            ukeys u32[n_keys] | uoff i64[n_keys+1]
 // Checksums are computed ON THE DEVICE (k_ix_checksum: position-weighted 64-bit sum) when saving and again after the
 // upload when loading, so truncation, bit rot and a failed copy all surface as DVB_E_INVALID.
@@ -63,11 +63,9 @@ __global__ void __launch_bounds__(256) k_ix_validate(IxSeg sg, int* __restrict__
         }
         if (t0 == 0) b |= sg.uoff[0] != 0 || sg.uoff[sg.n_keys] != sg.n_post || sg.n_keys < 1;
         for (int64_t p = t0; p < sg.n_post; p += step) {
-            const unsigned long long k = sg.pk[p];
-            const int64_t c = (int64_t)(k >> 32);
+            const int64_t c = (int64_t)sg.pc[p];
             if (c >= sg.n_chunks) { b = true; continue; }
             b |= (int64_t)(sg.pv[p] & 0xFFFFu) + 1 >= (int64_t)sg.sym_cnt[c];                    // a pair needs position + 1 inside the chunk
-            if (p > 0) { const unsigned long long k0 = sg.pk[p - 1]; b |= (uint32_t)k0 > (uint32_t)k || ((uint32_t)k0 == (uint32_t)k && (k0 >> 32) > (k >> 32)); }
         }
     }
     if (b) atomicExch(bad, 1);
@@ -77,8 +75,8 @@ namespace {
 struct SegArrays { void* ptr[7]; size_t bytes[7]; };
 SegArrays seg_arrays(const IxSeg& sg) {
     SegArrays a;
-    void* p[7] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pk, sg.pv, sg.ukeys, sg.uoff };
-    const size_t b[7] = { 2 * (size_t)sg.n_bytes, 8 * (size_t)(sg.n_chunks + 1), 4 * (size_t)sg.n_chunks, 8 * (size_t)sg.n_post, 4 * (size_t)sg.n_post,
+    void* p[7] = { sg.sym, sg.sym_off, sg.sym_cnt, sg.pc, sg.pv, sg.ukeys, sg.uoff };
+    const size_t b[7] = { 2 * (size_t)sg.n_bytes, 8 * (size_t)(sg.n_chunks + 1), 4 * (size_t)sg.n_chunks, 4 * (size_t)sg.n_post, 4 * (size_t)sg.n_post,
                           sg.n_post > 0 ? 4 * (size_t)sg.n_keys : 0, sg.n_post > 0 ? 8 * (size_t)(sg.n_keys + 1) : 0 };
     for (int i = 0; i < 7; i++) { a.ptr[i] = p[i]; a.bytes[i] = sg.n_chunks > 0 ? b[i] : 0; }     // the empty index owns no arrays
     return a;
@@ -221,7 +219,7 @@ extern "C" int32_t dvb_chunk_index_load(dvb_ctx* ctx, const char* path, const ui
             sh.n_keys > sh.n_post || sh.n_bytes > (1LL << 40) || sh.n_chunks > (1LL << 32)) { rc = DVB_E_INVALID; why = "inconsistent segment header"; break; }
         IxSeg sg; sg.chunk_base = sh.chunk_base; sg.n_chunks = sh.n_chunks; sg.n_bytes = sh.n_bytes; sg.n_post = sh.n_post; sg.n_keys = sh.n_keys;
         SegArrays a = seg_arrays(sg);
-        void** slot[7] = { (void**)&sg.sym, (void**)&sg.sym_off, (void**)&sg.sym_cnt, (void**)&sg.pk, (void**)&sg.pv, (void**)&sg.ukeys, (void**)&sg.uoff };
+        void** slot[7] = { (void**)&sg.sym, (void**)&sg.sym_off, (void**)&sg.sym_cnt, (void**)&sg.pc, (void**)&sg.pv, (void**)&sg.ukeys, (void**)&sg.uoff };
         for (int i = 0; i < 7 && rc == DVB_OK; i++) {
             if (a.bytes[i] == 0 && i >= 3) continue;                                   // an index without postings has no sort arrays
             if (cudaMallocAsync(slot[i], a.bytes[i] + 64, st) != cudaSuccess) { cudaGetLastError(); rc = DVB_E_NOMEM; why = "out of device memory"; break; }
