@@ -244,31 +244,44 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
         // a run of r symbols holds floor(r / 2) non-overlapping occurrences, which is what the greedy scan would count.
         const bool pair_only = L == 2, same2 = pair_only && ts[0] == ts[1];
         const uint32_t next_sym = use_next ? ts[j + 2] : 0u;
-        const int64_t skip_chunk = r_lo > lo ? (int64_t)ix.pc[r_lo - 1] : -1;             // owned by the previous item
-        const int64_t last_chunk = (int64_t)ix.pc[r_hi - 1];                              // ours to finish
-        if (!pair_only && r_lo > lo && skip_chunk == last_chunk) continue;   // the whole item lies inside a chunk the previous item owns
+        // A term can overlap itself only if it has a border (a proper prefix that is also a suffix: "aaa", "abab").  Without
+        // one — and for 2-symbol terms, whose "xx" case is counted per run — matches simply add up.
+        bool bordered = false;
+        if (!pair_only) {
+            for (int32_t d = 1 + lane; d < L; d += 32) {
+                bool eq = true;
+                for (int32_t q = 0; q + d < L && eq; q++) eq = ts[q] == ts[q + d];
+                bordered |= eq;
+            }
+            bordered = __any_sync(0xffffffffu, bordered);
+        }
+        const bool additive = pair_only || !bordered;
+        // Only a greedy (bordered) term needs whole chunks per item: its items own the chunks that START inside them.  An
+        // additive term counts exactly the postings of its own range.
+        const int64_t lim = additive ? r_hi : hi;
+        const int64_t skip_chunk = !additive && r_lo > lo ? (int64_t)ix.pc[r_lo - 1] : -1;   // owned by the previous item
+        const int64_t last_chunk = !additive ? (int64_t)ix.pc[r_hi - 1] : -1;               // ours to finish
+        if (!additive && r_lo > lo && skip_chunk == last_chunk) continue;   // the whole item lies inside a chunk the previous item owns
         int64_t cur = -1; int32_t cnt = 0, last_end = 0;
-        bool more = true, leading = r_lo > lo;                     // still inside the run of postings the previous item owns
-        uint32_t vn = r_lo + lane < hi ? ix.pv[r_lo + lane] : 0u;  // position words are prefetched one step ahead
-        for (int64_t p0 = r_lo; p0 < hi && more; p0 += 32) {
+        bool more = true, leading = !additive && r_lo > lo;                     // still inside the run of postings the previous item owns
+        // One step = 32 postings (position words v of postings p0 + lane).
+        auto step = [&](const int64_t p0, const uint32_t v) {
             const int64_t p = p0 + lane;
-            const uint32_t v = vn;
-            if (p + 32 < hi) vn = ix.pv[p + 32];
             int64_t chunk = -2; int32_t start = 0, wgt = 0; bool beyond = false;
             // The chunk id is needed by every lane only at the item's borders (ownership of the first / last chunk) and by
             // 2-symbol terms; inside the item a term with a look-ahead symbol fetches it for the lanes that pass the filter.
-            const bool border = leading || p0 + 32 > r_hi || pair_only;
-            const bool cand = p < hi && (int32_t)(v & 0xFFFFu) >= j && (pair_only || (v >> 16) == next_sym);
-            if (p < hi && (border || cand)) chunk = (int64_t)ix.pc[p];
+            const bool border = leading || (!additive && p0 + 32 > r_hi) || pair_only;
+            const bool cand = p < lim && (int32_t)(v & 0xFFFFu) >= j && (pair_only || (v >> 16) == next_sym);
+            if (p < lim && (border || cand)) chunk = (int64_t)ix.pc[p];
             bool skip = false;
             if (leading) {                                         // only the LEADING postings of skip_chunk are skipped (a pair's
-                const uint32_t other = __ballot_sync(0xffffffffu, p < hi && chunk != skip_chunk);   // sub-lists restart the chunk order)
+                const uint32_t other = __ballot_sync(0xffffffffu, p < lim && chunk != skip_chunk);   // sub-lists restart the chunk order)
                 skip = other ? lane < __ffs(other) - 1 : true;
                 if (other) leading = false;
             }
-            if (p < hi) {
+            if (p < lim) {
                 start = (int32_t)(v & 0xFFFFu) - j;
-                beyond = p >= r_hi && chunk != last_chunk;          // first posting of a chunk the next item owns
+                beyond = !additive && p >= r_hi && chunk != last_chunk;          // first posting of a chunk the next item owns
                 if (!beyond && !skip && cand) {
                     if (pair_only) {
                         if (!same2) wgt = 1;
@@ -297,6 +310,18 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
             const uint32_t bey = __ballot_sync(0xffffffffu, beyond);
             uint32_t bal = __ballot_sync(0xffffffffu, match);
             if (bey) { bal &= (1u << (__ffs(bey) - 1)) - 1u; more = false; }
+            if (additive) {
+                // occurrences cannot overlap: the count of a chunk is the number of its matching postings, whatever the
+                // order — one atomic per (chunk, step) from the first lane of each group of equal chunks
+                if ((bal >> lane) & 1u) {
+                    if (same2) atomicAdd(&row[chunk], wgt);
+                    else {
+                        const uint32_t grp = __match_any_sync(bal, (uint32_t)chunk);
+                        if (__ffs(grp) - 1 == lane) atomicAdd(&row[chunk], __popc(grp));
+                    }
+                }
+                bal = 0u;
+            }
             while (bal) {                                          // greedy, left to right: non-overlapping == str.count
                 const int src = __ffs(bal) - 1; bal &= bal - 1;
                 const int64_t cb = __shfl_sync(0xffffffffu, chunk, src);
@@ -309,6 +334,27 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
                 if (pair_only) cnt += wb;
                 else if (sb >= last_end) { cnt++; last_end = sb + L; }
             }
+        };
+        int64_t p0 = r_lo;
+        while (p0 < lim && more) {
+            // Interior of the item, term with a look-ahead symbol: 128 postings per iteration, and nothing but the four
+            // position words is touched unless one of them passes the look-ahead filter (about 1 posting in 12 does on
+            // a Zipf corpus; on rarer symbols whole iterations are skipped).
+            if (!leading && use_next && p0 + 128 <= r_hi) {
+                uint32_t v4[4]; bool c4[4]; bool any = false;
+#pragma unroll
+                for (int u = 0; u < 4; u++) v4[u] = ix.pv[p0 + 32 * u + lane];
+#pragma unroll
+                for (int u = 0; u < 4; u++) { c4[u] = (v4[u] >> 16) == next_sym && (int32_t)(v4[u] & 0xFFFFu) >= j; any |= c4[u]; }
+                if (__any_sync(0xffffffffu, any)) {
+#pragma unroll
+                    for (int u = 0; u < 4; u++) if (__any_sync(0xffffffffu, c4[u])) step(p0 + 32 * u, v4[u]);
+                }
+                p0 += 128;
+                continue;
+            }
+            step(p0, p0 + lane < lim ? ix.pv[p0 + lane] : 0u);
+            p0 += 32;
         }
         if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);
     }
