@@ -347,8 +347,37 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
 #pragma unroll
                 for (int u = 0; u < 4; u++) { c4[u] = (v4[u] >> 16) == next_sym && (int32_t)(v4[u] & 0xFFFFu) >= j; any |= c4[u]; }
                 if (__any_sync(0xffffffffu, any)) {
+                    if (additive) {
+                        // the four sub-steps are independent: their dependent loads (chunk id -> symbol offset -> symbols)
+                        // are issued side by side instead of one chain after the other
+                        uint32_t ch[4]; int64_t so[4]; int32_t sc[4];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) if (__any_sync(0xffffffffu, c4[u])) step(p0 + 32 * u, v4[u]);
+                        for (int u = 0; u < 4; u++) ch[u] = c4[u] ? ix.pc[p0 + 32 * u + lane] : 0u;
+                        if (!covered) {
+#pragma unroll
+                            for (int u = 0; u < 4; u++) { so[u] = c4[u] ? ix.sym_off[ch[u]] : 0; sc[u] = c4[u] && j + 3 < L ? ix.sym_cnt[ch[u]] : 0x7fffffff; }
+#pragma unroll
+                            for (int u = 0; u < 4; u++) if (c4[u]) {
+                                const int32_t start = (int32_t)(v4[u] & 0xFFFFu) - j;
+                                bool m = start + L <= sc[u];
+                                const uint16_t* sp = ix.sym + so[u] + start;
+                                for (int32_t d = 0; d < j && m; d++) m = sp[d] == ts[d];
+                                for (int32_t d = j + 3; d < L && m; d++) m = sp[d] == ts[d];
+                                c4[u] = m;
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const uint32_t bal = __ballot_sync(0xffffffffu, c4[u]);
+                            if (c4[u]) {
+                                const uint32_t grp = __match_any_sync(bal, ch[u]);
+                                if (__ffs(grp) - 1 == lane) atomicAdd(&row[ch[u]], __popc(grp));
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 4; u++) if (__any_sync(0xffffffffu, c4[u])) step(p0 + 32 * u, v4[u]);
+                    }
                 }
                 p0 += 128;
                 continue;
