@@ -322,6 +322,28 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
                 }
                 bal = 0u;
             }
+            if (bal) {
+                // bordered term: occurrences CAN overlap, but rarely do.  If no match of this step starts inside the previous
+                // match of the same chunk (the one before it in the step, or the carried one), greedy counts them all.
+                const uint32_t pm = bal & ((1u << lane) - 1u);
+                const int srcp = pm ? 31 - __clz(pm) : 0;
+                const int64_t pch = __shfl_sync(0xffffffffu, chunk, srcp);
+                const int32_t pst = __shfl_sync(0xffffffffu, start, srcp);
+                bool conflict = false;
+                if ((bal >> lane) & 1u) conflict = pm ? (pch == chunk && start - pst < L) : (chunk == cur && start < last_end);
+                if (!__any_sync(0xffffffffu, conflict)) {
+                    if (cnt > 0 && lane == 0) atomicAdd(&row[cur], cnt);
+                    cnt = 0;
+                    if ((bal >> lane) & 1u) {
+                        const uint32_t grp = __match_any_sync(bal, (uint32_t)chunk);
+                        if (__ffs(grp) - 1 == lane) atomicAdd(&row[chunk], __popc(grp));
+                    }
+                    const int lastl = 31 - __clz(bal);
+                    cur = __shfl_sync(0xffffffffu, chunk, lastl);
+                    last_end = __shfl_sync(0xffffffffu, start, lastl) + L;
+                    bal = 0u;
+                }
+            }
             while (bal) {                                          // greedy, left to right: non-overlapping == str.count
                 const int src = __ffs(bal) - 1; bal &= bal - 1;
                 const int64_t cb = __shfl_sync(0xffffffffu, chunk, src);
@@ -378,6 +400,19 @@ __global__ void __launch_bounds__(256) k_ix_score(IxSeg ix, const uint16_t* __re
 #pragma unroll
                         for (int u = 0; u < 4; u++) if (__any_sync(0xffffffffu, c4[u])) step(p0 + 32 * u, v4[u]);
                     }
+                }
+                p0 += 128;
+                continue;
+            }
+            if (pair_only && !same2 && p0 + 128 <= r_hi) {
+                // "xy" with x != y: every posting of the pair is one occurrence; only the chunk ids are read
+                uint32_t ch[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) ch[u] = ix.pc[p0 + 32 * u + lane];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t grp = __match_any_sync(0xffffffffu, ch[u]);
+                    if (__ffs(grp) - 1 == lane) atomicAdd(&row[ch[u]], __popc(grp));
                 }
                 p0 += 128;
                 continue;
