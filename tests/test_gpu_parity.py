@@ -92,8 +92,8 @@ def _adversarial_long_texts():
 
 
 def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
-    """facts >= 384 bytes take text7.cuh (lane = 64-byte chunk automaton): tile/chunk boundaries, long runs (restart),
-    exotic case mappings (restart), long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
+    """long facts (the byte-mask scanner of text8.cuh, with hand-backs to text6.cuh): tile/chunk boundaries, long runs,
+    exotic case mappings, long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
     from deep_vision_b200 import evidence, packing
     facts, rng, han = _adversarial_long_texts()
     claims = []
@@ -118,6 +118,46 @@ def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
     assert np.array_equal(got["best_fact"], ref["best_fact"])
     assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
     assert np.array_equal(got["bound"], ref["bound"])
+
+
+def test_a2_every_pair_of_long_facts(gpu_ctx, oracle):
+    """one fact per session, so best_score exposes the overlap of EVERY (claim, fact) pair — the byte-mask scanner
+    (text8.cuh: facts >= 192 bytes) against the oracle on piece boundaries (12/13/14/24/25/36/37-character runs), ASCII
+    tokens across lane chunks and tiles, every text alignment, and texts that hand back to the exact path."""
+    from deep_vision_b200 import evidence, packing
+    facts, rng, han = _adversarial_long_texts()
+    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
+    for run in (11, 12, 13, 14, 23, 24, 25, 26, 35, 36, 37, 38, 48, 49, 50, 96, 97):
+        for pre in range(0, 9):                              # shifts the run across the 8-byte lane units
+            facts.append("x" * pre + "，" + cjk(run) + "。" + cjk(40) + " tail_token9 " + cjk(run) + "，ab" + cjk(30) + "c" + cjk(12) + "z" * 63)
+    facts.append(cjk(70) + " " + "q" * 64 + " " + cjk(70) + " " + "r" * 65 + cjk(5))       # 64 fits, 65 hands back
+    facts.append(cjk(100) + "K" + cjk(100))                # U+212A
+    facts.append(cjk(100) + "İ" + cjk(100))                # U+0130
+    facts.append("“" + cjk(90) + "”——" + cjk(90) + "…")    # E2 80 xx punctuation must NOT hand back
+    facts.append("ab " * 100)                               # no bigram at all: distinct count by the exact path
+    facts.append((cjk(2) + "，") * 80)                      # 2-character runs only
+    facts.append((cjk(1) + " ") * 150)                      # single characters: no token
+    facts.append(cjk(7) * 40)                               # few distinct bigrams repeated
+    claims = []
+    for f in facts[::3]:
+        i = rng.randrange(max(1, len(f) - 60))
+        claims.append(f[i:i + rng.randint(5, 60)])
+    claims = claims[-26:] + [cjk(12), cjk(13), "tail_token9 ab c", "q" * 64, "r" * 65, "k i"]
+    assert len(claims) == 32
+    n_sess = len(facts)
+    cu, co = packing.pack_texts(claims * n_sess)
+    fu, fo = packing.pack_texts(facts)
+    sco = np.arange(n_sess + 1, dtype=np.int64) * len(claims)
+    sfo = np.arange(n_sess + 1, dtype=np.int64)
+    nf, nc = n_sess, len(claims) * n_sess
+    fq = np.full(nf, 0.5); fd = np.zeros(nf, np.int32); fh = np.zeros(nf, np.uint8)
+    cp = np.full(nc, -1, np.int32); ct = np.full(nc, 0.46, np.float64)
+    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
+    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
+    assert np.array_equal(got["len_fact"], np.minimum(ref["len_fact"], 18))
+    bad = np.nonzero(got["best_score"].view(np.uint64) != ref["best_score"].view(np.uint64))[0]
+    assert bad.size == 0, [(int(i) // 32, int(i) % 32, got["best_score"][i], ref["best_score"][i]) for i in bad[:8]]
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
 
 
 def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
