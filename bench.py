@@ -55,7 +55,7 @@ def workload_config(args, world):
             "l2_policy": "inputs (0.88 GB/GPU) larger than L2; no flush needed"}
 
 
-def index_arm(ctx, args, rank):
+def index_arm(ctx, args, rank, world=1):
     """BASELINE metric part 2, chunks indexed/s: a bounded config-3 sample (512-char chunks resident in HBM ->
     dvb_chunk_index_build -> a queryable positional index), plus the indexed top-8 of 1000 claim queries over it.
     Returns this rank's numbers; the caller reduces over ranks."""
@@ -82,6 +82,28 @@ def index_arm(ctx, args, rank):
             c = int(rng.integers(0, n)); src = raw[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, 488))
             text = text[:22] + src[a:a + 22]
         terms.append(rm._tokenize_reference_material_query(text))
+    sharded = None
+    if world > 1:
+        # the queries are replicated (rank 0's), every rank answers them over its shard, ONE all-gather of nq x k
+        # candidates over NCCL, merge on every rank (parallel.sharded_index_topk); host wall clock, max over ranks
+        import hashlib
+        import torch.distributed as dist
+        from deep_vision_b200 import parallel
+        box = [terms]
+        dist.broadcast_object_list(box, src=0)
+        terms = box[0]
+        wall = []
+        for _ in range(3):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            gi, gs, gn = parallel.sharded_index_topk(ix, terms, 8)
+            torch.cuda.synchronize()
+            wall.append(1000.0 * (time.perf_counter() - t0))
+        digest = int.from_bytes(hashlib.sha256(gi.tobytes() + gs.tobytes() + gn.tobytes()).digest()[:7], "little")
+        lo_hi = torch.tensor([digest, -digest], dtype=torch.int64, device="cuda")
+        dist.all_reduce(lo_hi, op=dist.ReduceOp.MAX)
+        sharded = {"ms_1000_queries_allgather_merge": min(wall), "identical_on_all_ranks": bool(int(lo_hi[0]) == -int(lo_hi[1])),
+                   "allgather_bytes": world * len(terms) * 8 * 12}
     q_ms = []
     for _ in range(3):
         ix.topk(terms, 8)
@@ -89,7 +111,7 @@ def index_arm(ctx, args, rank):
     ix.close()
     best = min(builds[1:])
     return {"chunks_per_gpu": n, "build_ms": best, "first_build_ms": builds[0], "postings": st["postings"],
-            "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"], "query_ms_1000_queries": min(q_ms)}
+            "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"], "query_ms_1000_queries": min(q_ms), "sharded": sharded}
 
 
 class ClockSampler:
@@ -314,7 +336,7 @@ def main():
     index = None
     if args.index_chunks > 0:
         try:
-            mine = index_arm(ctx, args, rank)
+            mine = index_arm(ctx, args, rank, world)
         except Exception as exc:                                  # the headline line must survive a failure here
             mine = {"error": repr(exc)[:200]}
         ok = reduce_max(1.0 if "error" in mine else 0.0) == 0.0
@@ -328,6 +350,11 @@ def main():
                                   "frac": mine["algorithmic_bytes"] / (b_ms / 1000.0) / 1e9 / peak_i,
                                   "algorithmic_bytes": mine["algorithmic_bytes"], "note": "UTF-8 in + 4 B per posting (SURVEY 8d); the build is 4 radix passes over 12 B postings"},
                      "query": {"effective_pairs_per_s": world * mine["chunks_per_gpu"] * 1000 / (q_ms / 1000.0), "ms_per_1000_queries": q_ms, "k": 8}}
+            if mine.get("sharded"):
+                sh = dict(mine["sharded"])
+                sh["ms_1000_queries_allgather_merge"] = reduce_max(sh["ms_1000_queries_allgather_merge"])
+                sh["effective_pairs_per_s"] = world * mine["chunks_per_gpu"] * 1000 / (sh["ms_1000_queries_allgather_merge"] / 1000.0)
+                index["query"]["sharded_topk"] = sh
         else:
             index = {"error": mine.get("error", "failed on another rank")}
 

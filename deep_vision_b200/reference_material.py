@@ -76,26 +76,27 @@ def _tokenize_reference_material_query(query_text: str) -> List[str]:
 
 def terms_to_symbols(queries_terms: Sequence[Sequence[str]]) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
     """Terms -> the kernels' symbol alphabet (include/dvb200.h): (term_sym u16, term_off i32, query_term_off i32)."""
-    syms: List[int] = []
-    toff = [0]
-    qoff = [0]
-    for terms in queries_terms:
-        for t in terms:
-            for ch in t:
-                o = ord(ch)
-                if 0x4E00 <= o <= 0x9FFF:
-                    syms.append(o - 0x4E00 + 1)
-                elif "a" <= ch <= "z":
-                    syms.append(0x8000 | (o - 97 + 1))
-                elif "0" <= ch <= "9":
-                    syms.append(0x8000 | (o - 48 + 27))
-                elif ch == "_":
-                    syms.append(0x8000 | 37)
-                else:
-                    raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
-            toff.append(len(syms))
-        qoff.append(len(toff) - 1)
-    return (np.asarray(syms if syms else [0], np.uint16), np.asarray(toff, np.int32), np.asarray(qoff, np.int32))
+    flat = [t for terms in queries_terms for t in terms]
+    lens = np.fromiter(map(len, flat), np.int64, len(flat))
+    cp = np.frombuffer("".join(flat).encode("utf-32-le"), np.uint32)           # one code point per term character
+    if cp.size != int(lens.sum()):
+        raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
+    sym = np.zeros(cp.size, np.uint32)
+    cjk = (cp >= 0x4E00) & (cp <= 0x9FFF)
+    low = (cp >= 97) & (cp <= 122)
+    dig = (cp >= 48) & (cp <= 57)
+    us = cp == 95
+    if not bool(np.all(cjk | low | dig | us)):
+        raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
+    sym[cjk] = cp[cjk] - 0x4E00 + 1
+    sym[low] = 0x8000 | (cp[low] - 97 + 1)
+    sym[dig] = 0x8000 | (cp[dig] - 48 + 27)
+    sym[us] = 0x8000 | 37
+    toff = np.zeros(len(flat) + 1, np.int64)
+    np.cumsum(lens, out=toff[1:])
+    qoff = np.zeros(len(queries_terms) + 1, np.int64)
+    np.cumsum(np.fromiter(map(len, queries_terms), np.int64, len(queries_terms)), out=qoff[1:])
+    return (sym.astype(np.uint16) if sym.size else np.zeros(1, np.uint16), toff.astype(np.int32), qoff.astype(np.int32))
 
 
 # ----------------------------------------------------------------------------- GPU primitives
