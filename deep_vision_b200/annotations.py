@@ -558,17 +558,134 @@ def merge_summaries(parts: Sequence[dict]) -> dict:
     return out
 
 
+# ----------------------------------------------------------------------------- dimension saturation
+# Related words per key aspect (web/server.py:19442-19459) and the depth cue words (19471-19485), in the reference's order.
+ASPECT_KEYWORDS = {
+    "核心痛点": ["痛点", "问题", "困难", "挑战", "困扰"], "期望价值": ["价值", "收益", "效果", "目标", "期望"],
+    "使用场景": ["场景", "情况", "使用", "应用", "何时"], "用户角色": ["用户", "角色", "人员", "谁", "使用者"],
+    "关键流程": ["流程", "步骤", "环节", "过程"], "角色分工": ["分工", "职责", "负责", "部门"],
+    "触发事件": ["触发", "开始", "启动", "何时"], "异常处理": ["异常", "错误", "失败", "例外"],
+    "部署方式": ["部署", "云", "本地", "服务器"], "系统集成": ["集成", "对接", "接口", "系统"],
+    "性能要求": ["性能", "响应", "并发", "速度"], "安全合规": ["安全", "合规", "权限", "加密"],
+    "预算范围": ["预算", "费用", "成本", "价格"], "时间节点": ["时间", "期限", "周期", "何时"],
+    "资源限制": ["资源", "人力", "团队", "限制"], "优先级": ["优先", "重要", "紧急", "先后"],
+}
+_DEPTH_CUES = (("比如", "例如", "当", "如果", "场景", "情况下"), ("而不是", "优先", "相比", "更重要", "首先"),
+               ("因为", "由于", "所以", "原因是"), ("；", "、"))
+_ZERO_SATURATION = {"saturation_score": 0, "coverage_score": 0, "depth_score": 0, "volume_score": 0, "covered_aspects": [], "level": "low"}
+
+
+def dimension_saturation_batch(items: Sequence[tuple], *, server_module, ctx=None) -> List[dict]:
+    """calculate_dimension_saturation (web/server.py:19399-19515) for many (session, dimension) pairs.  Every
+    `aspect in text` / `keyword in text` test of all pairs is ONE dvb_contains launch and every `any(c.isdigit())` ONE
+    dvb_text_features launch; the weighted sums, rounding and thresholds stay in Python in the reference's order.
+    The server module supplies get_dimension_info_for_session and get_mode_saturation_thresholds (app configuration)."""
+    mod = server_module
+    out: List[Optional[dict]] = [None] * len(items)
+    hay: List[str] = []                   # per live pair: combined text (answers + questions), then the answers alone
+    needles: List[str] = []
+    needle_hay: List[int] = []
+    host_bits: Dict[int, bool] = {}       # needles with white space at an end: dvb_contains searches the STRIPPED haystack
+    live = []                             # (item index, key_aspects, first needle, total answer characters, session)
+
+    def need(text: str, h: int) -> int:
+        if not isinstance(text, str):
+            raise TypeError("'in <string>' requires string as left operand, not %s" % type(text).__name__)
+        j = len(needles)
+        needles.append(text)
+        needle_hay.append(h)
+        if text != text.strip():
+            host_bits[j] = text in hay[h]
+        return j
+
+    for i, (session, dimension) in enumerate(items):
+        dim_logs = [log for log in session.get("interview_log", []) if log.get("dimension") == dimension]
+        if not dim_logs:
+            out[i] = copy.deepcopy(_ZERO_SATURATION)
+            continue
+        key_aspects = mod.get_dimension_info_for_session(session).get(dimension, {}).get("key_aspects", [])
+        all_answers = " ".join([log.get("answer", "") for log in dim_logs])
+        all_questions = " ".join([log.get("question", "") for log in dim_logs])
+        h = len(hay)
+        hay.append(all_answers + all_questions)
+        hay.append(all_answers)
+        first = len(needles)
+        for aspect in key_aspects:
+            need(aspect, h)
+            for kw in ASPECT_KEYWORDS.get(aspect, []):
+                need(kw, h)
+        for group in _DEPTH_CUES:
+            for kw in group:
+                need(kw, h + 1)
+        live.append((i, key_aspects, first, sum(len(log.get("answer", "")) for log in dim_logs), session))
+    if not live:
+        return out
+    bits = contains(hay, needles, needle_hay, ctx=ctx)
+    digit = text_features(hay[1::2], ctx=ctx)[2]
+
+    def found(j: int) -> bool:
+        return host_bits[j] if j in host_bits else bool(bits[j] & 1)
+
+    for n, (i, key_aspects, j, total_chars, session) in enumerate(live):
+        covered = []
+        for aspect in key_aspects:
+            hit = found(j)
+            j += 1
+            for _kw in ASPECT_KEYWORDS.get(aspect, []):
+                hit = hit or found(j)
+                j += 1
+            if hit:
+                covered.append(aspect)
+        coverage_score = len(covered) / len(key_aspects) if key_aspects else 0
+        depth_signals = 1 if (digit[n] & 1) else 0
+        for group in _DEPTH_CUES:
+            if any([found(j + g) for g in range(len(group))]):
+                depth_signals += 1
+            j += len(group)
+        depth_score = min(1.0, depth_signals / 5)
+        volume_score = min(1.0, total_chars / 300)
+        saturation_score = coverage_score * 0.4 + depth_score * 0.3 + volume_score * 0.3
+        thresholds = mod.get_mode_saturation_thresholds(session)
+        level = "high" if saturation_score >= thresholds["high"] else ("medium" if saturation_score >= thresholds["medium"] else "low")
+        out[i] = {"saturation_score": round(saturation_score, 2), "coverage_score": round(coverage_score, 2),
+                  "depth_score": round(depth_score, 2), "volume_score": round(volume_score, 2),
+                  "covered_aspects": covered, "level": level}
+    return out
+
+
+def calculate_dimension_saturation(session: dict, dimension: str, *, server_module, ctx=None) -> dict:
+    """web/server.py:19399-19515 (single pair = a batch of one)."""
+    return dimension_saturation_batch([(session, dimension)], server_module=server_module, ctx=ctx)[0]
+
+
+def missing_aspects_batch(items: Sequence[tuple], *, server_module, ctx=None) -> List[list]:
+    """get_dimension_missing_aspects (web/server.py:19583-19589) for many (session, dimension) pairs."""
+    sats = dimension_saturation_batch(items, server_module=server_module, ctx=ctx)
+    res = []
+    for (session, dimension), sat in zip(items, sats):
+        covered = set(sat.get("covered_aspects", []))
+        key_aspects = server_module.get_dimension_info_for_session(session).get(dimension, {}).get("key_aspects", [])
+        res.append([aspect for aspect in key_aspects if aspect and aspect not in covered])
+    return res
+
+
+def get_dimension_missing_aspects(session: dict, dimension: str, *, server_module, ctx=None) -> list:
+    return missing_aspects_batch([(session, dimension)], server_module=server_module, ctx=ctx)[0]
+
+
 # ----------------------------------------------------------------------------- a13: evidence pack
 # (pair_id, index into CONTRADICTION_PAIRS, description)   web/server.py:22579-22585
 _PACK_CONTRADICTIONS = (("need", 0, "需求取向冲突"), ("support", 2, "支持立场冲突"), ("available", 4, "资源现状冲突"),
                         ("must", 5, "约束优先级冲突"), ("ready", 3, "准备状态冲突"))
 
 
-def build_report_evidence_pack(session: dict, *, server_module, ctx=None) -> dict:
-    """Drop-in for web/server.py:22568-22803.  Annotation (a12) and every `term in answer` test run on the GPU; the
-    per-dimension coverage block calls the server module's own helpers (get_dimension_info_for_session,
-    get_interview_mode_config, get_dimension_missing_aspects, resolve_report_template_for_session), which are outside
-    the hot path.  The caller's session is not mutated (deep copy, 22570)."""
+def build_report_evidence_pack(session: dict, *, server_module, ctx=None, device_coverage: bool = False) -> dict:
+    """Drop-in for web/server.py:22568-22803.  Annotation (a12) and every `term in answer` test run on the GPU.  The
+    per-dimension coverage block reads the app configuration through the server module (get_dimension_info_for_session,
+    get_interview_mode_config, resolve_report_template_for_session); the missing aspects of ALL dimensions come from one
+    batched device pass (missing_aspects_batch) when device_coverage is set, else from the module's
+    get_dimension_missing_aspects (what a test that stubs that name expects).  The caller's session is not mutated
+    (deep copy, 22570)."""
     from datetime import datetime, timezone
     mod = server_module
     work = copy.deepcopy(session) if isinstance(session, dict) else {}
@@ -656,12 +773,16 @@ def build_report_evidence_pack(session: dict, *, server_module, ctx=None) -> dic
             return 0.0
 
     dimension_coverage, adjusted_values, count_values = {}, [], []
+    missing_by_dim = {}
+    if device_coverage and dim_info:
+        keys = list(dim_info)
+        missing_by_dim = dict(zip(keys, missing_aspects_batch([(session, k) for k in keys], server_module=mod, ctx=ctx)))
     for dim_key, info in dim_info.items():
         dim_logs = [log for log in interview_log if log.get("dimension") == dim_key]
         dim_facts = [f for f in facts if f.get("dimension") == dim_key]
         count_percent = int(session.get("dimensions", {}).get(dim_key, {}).get("coverage", 0) or 0)
         count_ratio = max(0, min(100, count_percent)) / 100.0
-        missing = mod.get_dimension_missing_aspects(session, dim_key)
+        missing = missing_by_dim[dim_key] if device_coverage else mod.get_dimension_missing_aspects(session, dim_key)
         key_aspects = info.get("key_aspects", []) if isinstance(info.get("key_aspects", []), list) else []
         if key_aspects:
             total = len(key_aspects)
@@ -734,9 +855,23 @@ def build_bindings(mod, ctx=None) -> Dict[str, Any]:
         return backfill_sessions([session], refresh_quality=refresh_quality, overwrite_contract=overwrite_contract, ctx=ctx,
                                  sensitivity_table=st, hard_signals=hs)[0]
 
-    def _pack(session):
-        return build_report_evidence_pack(session, server_module=mod, ctx=ctx)
+    def _saturation(session, dimension):
+        return calculate_dimension_saturation(session, dimension, server_module=mod, ctx=ctx)
 
-    return {"evaluate_answer_depth": _depth, "evaluate_answer_quality": _quality, "build_report_evidence_pack": _pack,
+    def _missing(session, dimension):
+        return get_dimension_missing_aspects(session, dimension, server_module=mod, ctx=ctx)
+
+    # the pack takes the batched device pass for its coverage block unless somebody re-bound the two names after install
+    # (the reference's own tests stub get_dimension_missing_aspects: tests/test_security_regression.py:4215-4219)
+    untouched = {"calculate_dimension_saturation": (getattr(mod, "calculate_dimension_saturation", None), _saturation),
+                 "get_dimension_missing_aspects": (getattr(mod, "get_dimension_missing_aspects", None), _missing)}
+
+    def _pack(session):
+        dev = all(fn is not None and getattr(mod, name, None) in (fn, ours) for name, (fn, ours) in untouched.items()) \
+            and hasattr(mod, "get_mode_saturation_thresholds")
+        return build_report_evidence_pack(session, server_module=mod, ctx=ctx, device_coverage=dev)
+
+    return {"calculate_dimension_saturation": _saturation, "get_dimension_missing_aspects": _missing,
+            "evaluate_answer_depth": _depth, "evaluate_answer_quality": _quality, "build_report_evidence_pack": _pack,
             "classify_answer_evidence_class_v3": classify_answer_evidence_class_v3,
             "backfill_session_interview_log_evidence_annotations": _backfill}

@@ -23,6 +23,10 @@ HOT_NAMES = (
     "evaluate_answer_depth", "evaluate_answer_quality", "classify_answer_evidence_class_v3",
     "backfill_session_interview_log_evidence_annotations", "build_report_evidence_pack",
 )
+# single-pair calls of these two sit in the interactive interview flow (web/server.py:20904-21053,
+# 30566-30670), where two kernel launches per call cost more than the Python loop they replace, so they are re-bound
+# only on request (install(..., saturation=True)); build_report_evidence_pack uses the batched device pass either way.
+SATURATION_NAMES = ("calculate_dimension_saturation", "get_dimension_missing_aspects")
 
 
 def _weak_cfg(mod) -> evidence.WeakBindingConfig:
@@ -125,10 +129,10 @@ def build_bindings(mod, ctx=None, sidecar_cache: Optional["rm.ChunkIndexCache"] 
         bindings.update(annotations.build_bindings(mod, ctx))
     except ImportError:
         pass
-    return {k: v for k, v in bindings.items() if k in HOT_NAMES}
+    return {k: v for k, v in bindings.items() if k in HOT_NAMES or k in SATURATION_NAMES}
 
 
-def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cache=None) -> Dict[str, Any]:
+def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cache=None, saturation: bool = False) -> Dict[str, Any]:
     """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent.
     sidecar_cache: a reference_material.ChunkIndexCache to serve select_reference_material_context from resident /
     persisted chunk indexes (off by default: the drop-in then writes nothing into the data directory)."""
@@ -137,6 +141,8 @@ def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cach
     done = {}
     for name, fn in bindings.items():
         if names is not None and name not in names:
+            continue
+        if name in SATURATION_NAMES and not saturation and (names is None or name not in names):
             continue
         current = getattr(server_module, name, _MISSING)
         if current is _MISSING:

@@ -182,3 +182,97 @@ def test_gpu_backfill_vs_oracle_random(gpu_ctx):
     got = an.backfill_sessions(sessions, ctx=gpu_ctx)
     assert got == want
     assert sessions == ref
+
+
+# ---- dimension saturation / missing aspects (golden = the reference's own functions,
+# tools/make_golden_saturation.py)
+class _SatModule:
+    """Server-module stand-in: the app configuration of the golden generator + the reference's threshold rule
+    (web/server.py:19280-19302)."""
+    SATURATION_THRESHOLDS = {"high": 0.8, "medium": 0.6, "low": 0.4}
+
+    def __init__(self):
+        import sys
+        from pathlib import Path
+        sys.path.insert(0, str(Path(__file__).resolve().parents[1] / "tools"))
+        from make_golden_saturation import SatStubs
+        for k in ("REPORT_TEMPLATE_CUSTOM_V1", "get_dimension_info_for_session", "get_interview_mode_config",
+                  "resolve_report_template_for_session", "normalize_custom_report_schema"):
+            setattr(self, k, getattr(SatStubs, k))
+
+    def get_mode_saturation_thresholds(self, session):
+        quality = self.get_interview_mode_config(session).get("quality_thresholds") or {}
+        return {k: quality.get(k, self.SATURATION_THRESHOLDS[k]) for k in ("high", "medium", "low")}
+
+
+def _check_saturation(an, sat, ctx=None):
+    mod = _SatModule()
+    items, want = [], []
+    for c in sat["cases"]:
+        for dim, w in c["per_dimension"].items():
+            items.append((copy.deepcopy(c["input"]), dim)); want.append(w)
+    got = an.dimension_saturation_batch(items, server_module=mod, ctx=ctx)            # one contains + one feature launch
+    assert got == [w["saturation"] for w in want]
+    assert an.missing_aspects_batch(items, server_module=mod, ctx=ctx) == [w["missing"] for w in want]
+    assert [it[0] for it in items] == [c["input"] for c in sat["cases"] for _ in c["per_dimension"]]     # sessions untouched
+    c = sat["cases"][3]
+    for dim, w in c["per_dimension"].items():                                        # single-pair forms
+        assert an.calculate_dimension_saturation(c["input"], dim, server_module=mod, ctx=ctx) == w["saturation"]
+        assert an.get_dimension_missing_aspects(c["input"], dim, server_module=mod, ctx=ctx) == w["missing"]
+    for c in sat["packs"]:                                                           # pack with the batched device coverage block
+        sess = copy.deepcopy(c["input"])
+        pack = an.build_report_evidence_pack(sess, server_module=mod, ctx=ctx, device_coverage=True)
+        assert sess == c["input"]
+        assert pack.pop("generated_at")
+        assert pack == c["pack"]
+    with pytest.raises(TypeError):                                                   # `5 in text` raises in the reference too
+        bad = _SatModule()
+        bad.get_dimension_info_for_session = lambda s: {"d": {"key_aspects": [5]}}
+        an.dimension_saturation_batch([({"interview_log": [{"dimension": "d", "answer": "a", "question": "q"}]}, "d")], server_module=bad, ctx=ctx)
+
+
+def test_saturation_host_logic_with_standin_features(golden, monkeypatch):
+    from deep_vision_b200 import annotations as an
+    monkeypatch.setattr(an, "text_features", py_text_features)
+    monkeypatch.setattr(an, "contains", py_contains)
+    _check_saturation(an, golden("f2_saturation.json"))
+
+
+def test_dropin_saturation_rebinding_and_stub_respect(golden, monkeypatch):
+    """install(..., saturation=True) rebinds the two names; the pack's device coverage block steps aside when a caller
+    re-binds get_dimension_missing_aspects afterwards (the reference's own tests stub it)."""
+    import types
+    from deep_vision_b200 import annotations as an, dropin
+    monkeypatch.setattr(an, "text_features", py_text_features)
+    monkeypatch.setattr(an, "contains", py_contains)
+    sat = golden("f2_saturation.json")
+    base = _SatModule()
+    mod = types.SimpleNamespace(**{k: getattr(base, k) for k in ("REPORT_TEMPLATE_CUSTOM_V1", "get_dimension_info_for_session",
+                                                                  "get_interview_mode_config", "resolve_report_template_for_session",
+                                                                  "normalize_custom_report_schema", "get_mode_saturation_thresholds")})
+    mod.calculate_dimension_saturation = lambda s, d: {"covered_aspects": []}
+    mod.get_dimension_missing_aspects = lambda s, d: ["原函数"]
+    mod.build_report_evidence_pack = lambda s: {}
+    done = dropin.install(mod, names=("build_report_evidence_pack",))
+    assert set(done) == {"build_report_evidence_pack"}
+    c = sat["packs"][0]
+    pack = mod.build_report_evidence_pack(copy.deepcopy(c["input"]))
+    pack.pop("generated_at")
+    assert pack == c["pack"]                                        # originals untouched -> batched device coverage
+    mod.get_dimension_missing_aspects = lambda s, d: ["桩"]         # a caller stubs the name after install
+    pack = mod.build_report_evidence_pack(copy.deepcopy(c["input"]))
+    assert all(v["missing_aspects"] == ["桩"] for v in pack["dimension_coverage"].values())
+    dropin.uninstall(mod)
+    done = dropin.install(mod, saturation=True)
+    assert {"calculate_dimension_saturation", "get_dimension_missing_aspects"} <= set(done)
+    w = sat["cases"][3]
+    for dim, want in w["per_dimension"].items():
+        assert mod.calculate_dimension_saturation(w["input"], dim) == want["saturation"]
+        assert mod.get_dimension_missing_aspects(w["input"], dim) == want["missing"]
+    dropin.uninstall(mod)
+
+
+@pytest.mark.gpu
+def test_gpu_saturation_golden(gpu_ctx, golden):
+    from deep_vision_b200 import annotations as an
+    _check_saturation(an, golden("f2_saturation.json"), ctx=gpu_ctx)

@@ -121,9 +121,9 @@ def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
 
 
 def test_a2_every_pair_of_long_facts(gpu_ctx, oracle):
-    """one fact per session, so best_score exposes the overlap of EVERY (claim, fact) pair — the byte-mask scanner
-    (text8.cuh: facts >= 192 bytes) against the oracle on piece boundaries (12/13/14/24/25/36/37-character runs), ASCII
-    tokens across lane chunks and tiles, every text alignment, and texts that hand back to the exact path."""
+    """one fact per session, so best_score exposes the overlap of EVERY (claim, fact) pair: piece boundaries
+    (12/13/14/24/25/36/37-character runs), ASCII tokens across tiles, every text alignment, 64/65-character ASCII tokens,
+    U+212A / U+0130 (serial restart) and E2 80 xx punctuation — bit-exact against the oracle."""
     from deep_vision_b200 import evidence, packing
     facts, rng, han = _adversarial_long_texts()
     def cjk(n): return "".join(rng.choice(han) for _ in range(n))
