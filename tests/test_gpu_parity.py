@@ -210,3 +210,56 @@ def test_a2_large_claim_table_global_fallback(gpu_ctx, oracle):
                              c.claim_pref_dim, c.claim_threshold, packed=(c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off))
     assert np.array_equal(got["best_fact"], ref["best_fact"])
     assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
+
+
+def test_concurrent_calls_on_one_ctx(gpu_ctx, oracle):
+    """SURVEY §8(b) threading: gunicorn gthread workers share one ctx and ctypes drops the GIL during a call, so every
+    entry point must be re-entrant (per-call stream + workspace lease).  8 threads x 6 rounds of different entry points on
+    ONE ctx give exactly the results of the same calls made one after the other."""
+    import threading
+    from deep_vision_b200 import evidence, synth, question_similarity as qs, reference_material as rm
+    corpora = [synth.make_sessions(12 + 5 * i, turns=20, claims_per_session=24, seed=300 + i) for i in range(4)]
+    texts_d, texts_o = synth.make_texts(200, 120, seed=41)
+    raw = texts_d.tobytes()
+    texts = [raw[texts_o[i]:texts_o[i + 1]].decode("utf-8") for i in range(200)]
+    gate = qs.QuestionGate(ctx=gpu_ctx)
+    cand, hist = [t[:30] + "？" for t in texts[:120]], [t[:30] + "？" for t in texts[60:200]]
+    queries = [rm._tokenize_reference_material_query(t[10:50]) for t in texts[:16]]
+
+    def bind(i):
+        c = corpora[i % 4]
+        r = evidence.bind_packed(gpu_ctx, c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
+                                 c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
+        return (r["best_fact"].tobytes(), r["best_score"].tobytes(), r["bound"].tobytes())
+
+    jobs = [lambda i=i: bind(i) for i in range(4)]
+    jobs.append(lambda: tuple(k.tobytes() for k in evidence.tokenize_similarity_keys(texts, ctx=gpu_ctx)))
+    jobs.append(lambda: gate.match(cand, hist, 0.62).tobytes())
+    jobs.append(lambda: rm.chunk_scores(texts, queries, ctx=gpu_ctx).tobytes())
+    jobs.append(lambda: tuple(a.tobytes() for a in rm.topk(rm.chunk_scores(texts, queries, ctx=gpu_ctx), 8, ctx=gpu_ctx)))
+    serial = [j() for j in jobs]
+    # the first corpus against the oracle, so "serial" itself is pinned
+    c = corpora[0]
+    ref = oracle.bind_claims(None, None, c.sess_claim_off, c.sess_fact_off, c.fact_quality, c.fact_dim, c.fact_hard,
+                             c.claim_pref_dim, c.claim_threshold, packed=(c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off))
+    assert serial[0][0] == ref["best_fact"].tobytes() and serial[0][1] == ref["best_score"].tobytes()
+    errors, results = [], [[None] * 6 for _ in jobs]
+    start = threading.Barrier(len(jobs))
+
+    def worker(t):
+        try:
+            start.wait()
+            for r in range(6):
+                results[t][r] = jobs[(t + r) % len(jobs)]()
+        except Exception as exc:          # noqa: BLE001
+            errors.append(repr(exc))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(len(jobs))]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    for t in range(len(jobs)):
+        for r in range(6):
+            assert results[t][r] == serial[(t + r) % len(jobs)], (t, r)
