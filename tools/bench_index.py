@@ -39,19 +39,17 @@ gen_s = time.time() - t0
 qdata, qoff = synth.make_texts(args.queries, 45, seed=999)
 qraw = qdata.tobytes()
 rng = np.random.default_rng(7)
-if rank == 0:
-    raw0 = data.tobytes()
-queries = []
-for q in range(args.queries):
-    text = qraw[qoff[q]:qoff[q + 1]].decode("utf-8")
-    if rank == 0 or world == 1:
-        pass
-    queries.append(text)
-if world == 1:
+queries = [qraw[qoff[q]:qoff[q + 1]].decode("utf-8") for q in range(args.queries)]
+if rank == 0:                                   # every other query: half of it copied from a chunk of rank 0's shard
     raw0 = data.tobytes()
     for q in range(0, args.queries, 2):
-        c = int(rng.integers(0, n_gen)); s = raw0[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, args.chars - 24))
+        c = int(rng.integers(0, n_gen)); s = raw0[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, max(1, args.chars - 24)))
         queries[q] = queries[q][:22] + s[a:a + 22]
+    del raw0
+if world > 1:                                   # queries are replicated: rank 0's list on every rank
+    box = [queries]
+    dist.broadcast_object_list(box, src=0)
+    queries = box[0]
 t0 = time.time()
 terms = [rm._tokenize_reference_material_query(t) for t in queries]
 tok_s = time.time() - t0
@@ -97,9 +95,24 @@ if args.sidecar and rank == 0:
     side["same_topk_as_built_index"] = bool(np.array_equal(a[0], oi[:nqs]) and np.array_equal(a[1], os_[:nqs]) and np.array_equal(a[2], on[:nqs]))
     side["save_GBps"] = side["file_bytes"] / side["save_s"] / 1e9; side["load_GBps"] = side["file_bytes"] / side["load_s"] / 1e9
     ix2.close(); p.unlink()
+if world > 1:
+    dist.barrier()
+torch.cuda.synchronize()
 t0 = time.time()
 gi, gs, gn = parallel.merge_topk(oi, os_, args.k, ctx=ctx)
 merge_s = time.time() - t0
+same = True
+if world > 1:                                   # max over ranks of the device times; merged result identical on every rank
+    import hashlib
+    t = torch.tensor([min(build_ms), min(q_ms), merge_s], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    max_build, max_query, max_merge = (float(x) for x in t.tolist())
+    dg = int.from_bytes(hashlib.sha256(gi.tobytes() + gs.tobytes() + gn.tobytes()).digest()[:7], "little")
+    t2 = torch.tensor([dg, -dg], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    same = bool(int(t2[0]) == -int(t2[1]))
+else:
+    max_build, max_query, max_merge = min(build_ms), min(q_ms), merge_s
 algo_build = st["text_bytes"] + 4 * st["postings"]            # UTF-8 in + 4 B per posting
 algo_query = 8 * int(os_.sum()) + 16 * args.k * args.queries   # lower bound from the reported top-k only; see DESIGN.md
 if rank == 0:
@@ -107,7 +120,11 @@ if rank == 0:
     print(json.dumps({"world": world, "chunks_per_gpu": hi - lo, "queries": args.queries, "k": args.k, "stats": st,
                       "replicate": args.replicate, "segments_est": -(-st["text_bytes"] // (2000 << 20)), "build_ms": build_ms, "chunks_indexed_per_s_per_gpu": (hi - lo) / (b / 1e3), "build_GBps_algorithmic": algo_build / b / 1e6,
                       "query_ms": q_ms, "effective_pairs_per_s_per_gpu": (hi - lo) * args.queries / (qm / 1e3),
-                      "merge_s_host_incl_allgather": merge_s, "n_terms": int(len(toff) - 1), "mean_hits": float(gn.mean()),
+                      "merge_s_host_incl_allgather": merge_s,
+                      "max_over_ranks": {"build_ms": max_build, "query_ms": max_query, "merge_s": max_merge,
+                                         "chunks_indexed_per_s_all_gpus": args.chunks / (max_build / 1e3),
+                                         "effective_pairs_per_s_all_gpus": args.chunks * args.queries / (max_query / 1e3 + max_merge)},
+                      "merged_topk_identical_on_all_ranks": same, "allgather_bytes_per_rank": world * args.queries * args.k * 12, "n_terms": int(len(toff) - 1), "mean_hits": float(gn.mean()),
                       "host_gen_s": gen_s, "host_tokenize_s": tok_s, "sidecar": side}))
 if world > 1:
     dist.barrier(); dist.destroy_process_group()
