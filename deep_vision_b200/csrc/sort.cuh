@@ -105,19 +105,36 @@ static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsig
         sm.delta[d] = hist[(int64_t)d * nb + blockIdx.x] - lstart;
     }
     __syncthreads();
-    // phase 3: stable placement into shared memory, 32 items per step
+    // phase 3: stable placement into shared memory, 32 items per step.  The lanes holding the same digit are found
+    // with 8 ballots (one per digit bit) instead of MATCH.ANY: on uniformly distributed digits the match instruction
+    // was 39 % of the kernel's stall samples (its latency grows with the number of distinct values in the warp).
 #pragma unroll
-    for (int j = 0; j < RS_PER_LANE; j++) {
-        const bool ok = wbase + j * 32 + lane < n;
-        const uint32_t d = ok ? ((uint32_t)(k[j] >> shift) & 255u) : 256u + lane;  // invalid lanes never match
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const int rank = __popc(peers & ((1u << lane) - 1u));
-        uint32_t off = 0;
-        if (ok) off = sm.cnt[warp][d];
-        __syncwarp();
-        if (ok && rank == 0) sm.cnt[warp][d] = off + __popc(peers);
-        __syncwarp();
-        if (ok) { sm.key[off + rank] = k[j]; sm.val[off + rank] = v[j]; }
+    for (int j0 = 0; j0 < RS_PER_LANE; j0 += 4) {
+        uint32_t dd[4], peers[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool ok = wbase + (j0 + u) * 32 + lane < n;
+            dd[u] = (uint32_t)(k[j0 + u] >> shift) & 255u;
+            uint32_t m = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const uint32_t bit = (dd[u] >> b) & 1u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, bit != 0u);
+                m &= bit ? bal : ~bal;
+            }
+            peers[u] = m;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool ok = wbase + (j0 + u) * 32 + lane < n;
+            const int rank = __popc(peers[u] & ((1u << lane) - 1u));
+            uint32_t off = 0;
+            if (ok) off = sm.cnt[warp][dd[u]];
+            __syncwarp();
+            if (ok && rank == 0) sm.cnt[warp][dd[u]] = off + __popc(peers[u]);
+            __syncwarp();
+            if (ok) { sm.key[off + rank] = k[j0 + u]; sm.val[off + rank] = v[j0 + u]; }
+        }
     }
     __syncthreads();
     // phase 4: stream the digit-sorted tile out; item i of digit d goes to delta[d] + i
