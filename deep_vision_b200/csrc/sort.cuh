@@ -117,10 +117,12 @@ static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsig
             dd[u] = (uint32_t)(k[j0 + u] >> shift) & 255u;
             uint32_t m = __ballot_sync(0xffffffffu, ok);
 #pragma unroll
-            for (int b = 0; b < 8; b++) {
-                const uint32_t bit = (dd[u] >> b) & 1u;
-                const uint32_t bal = __ballot_sync(0xffffffffu, bit != 0u);
-                m &= bit ? bal : ~bal;
+            for (int b = 0; b < 8; b++) {                 // lanes whose digit bit b equals mine: and, setp, vote, @!p not (+ the and below)
+                uint32_t same;
+                asm volatile("{\n\t.reg .pred p;\n\tand.b32 %0, %1, %2;\n\tsetp.ne.u32 p, %0, 0;\n\t"
+                             "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t@!p not.b32 %0, %0;\n\t}"
+                             : "=r"(same) : "r"(dd[u]), "r"(1u << b));
+                m &= same;
             }
             peers[u] = m;
         }
