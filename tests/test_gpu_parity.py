@@ -263,3 +263,29 @@ def test_concurrent_calls_on_one_ctx(gpu_ctx, oracle):
     for t in range(len(jobs)):
         for r in range(6):
             assert results[t][r] == serial[(t + r) % len(jobs)], (t, r)
+
+
+def test_a2_degenerate_sessions(gpu_ctx, oracle):
+    """zero sessions; sessions without claims / without facts; empty and white-space-only claim and fact texts."""
+    from deep_vision_b200 import evidence, packing
+    z64 = np.zeros(1, np.int64)
+    e = evidence.bind_packed(gpu_ctx, np.zeros(16, np.uint8), z64, np.zeros(16, np.uint8), z64, z64, z64, np.zeros(0), np.zeros(0, np.int32),
+                             np.zeros(0, np.uint8), np.zeros(0, np.int32), np.zeros(0))
+    assert len(e["best_fact"]) == 0
+    claims = ["", "   ", "预算有限 budget_2024", "，。；", "a", "审批流程太慢需要优化"]
+    facts = ["", " \n ", "我们的预算有限，budget_2024 已经确定。审批流程太慢需要优化", "a b c", "流程"]
+    # session 0: claims, no facts; 1: facts, no claims; 2: both; 3: nothing; 4: both again
+    sco = np.array([0, 6, 6, 12, 12, 18], np.int64)
+    sfo = np.array([0, 0, 5, 10, 10, 15], np.int64)
+    cu, co = packing.pack_texts(claims * 3)
+    fu, fo = packing.pack_texts(facts * 3)
+    nf, nc = 15, 18
+    fq = np.linspace(0.0, 1.0, nf); fd = (np.arange(nf) % 3).astype(np.int32); fh = (np.arange(nf) % 2).astype(np.uint8)
+    cp = (np.arange(nc) % 4 - 1).astype(np.int32); ct = np.full(nc, 0.3, np.float64)
+    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
+    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
+    assert np.array_equal(got["bound"], ref["bound"])
+    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
+    assert got["best_fact"][:6].tolist() == [-1] * 6                   # no facts to bind to
