@@ -376,7 +376,9 @@ def main():
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": ncu_traffic(), "kernel": "k_bind_claims", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": corpus.algorithmic_bytes,
-                             "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src},
+                             "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src,
+                             "limiter": "instruction issue, not DRAM: 3.8 warp instructions per input byte, 69 % of the issue slots busy, "
+                                        "DRAM traffic 1.03 x algorithmic (profiles/r01_bind_v6_config2_ncu_full.json; DESIGN.md section 5)"},
                 "clocks": clocks,
                 "pairs_per_step_per_gpu": corpus.n_pairs}
         if index is not None:
