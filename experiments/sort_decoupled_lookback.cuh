@@ -6,8 +6,12 @@
 // 21.65 ms vs 22.0 ms for the adopted per-pass histogram + scan + scatter: the four k_rs_hist + eight k_rs_scan launches
 // (4.2 ms) disappear, but every scatter pass grows from ~2.6 to 3.3-3.6 ms (2.9 us per tile: the CTA sits at the phase-2
 // barrier while its 256 digit threads wait for the predecessors' words), so the net gain is 1.6 % for spin-waits in
-// production code.  What would make it pay: a ninth warp that does the look-back while the other eight rank (needs
-// <= 72 registers to keep 3 CTAs per SM).
+// production code.  A second variant advanced the look-back one predecessor per poll BETWEEN the ranking steps of phase 3
+// (state machine per digit thread, no blocking before the final barrier): 21.45 ms; ncu: 3.0-3.3 ms and 1.88 G warp
+// instructions per scatter pass against ~2.65 ms / 1.73 G without look-back — with 444 tiles in flight and a tile living
+// ~12 us, the chain back to the first inclusive prefix costs more L2 round trips than the histogram kernel it replaces.
+// What would make it pay: larger tiles per CTA (fewer tiles in flight per unit of work) or a ninth warp that does a
+// 4-wide look-back while the other eight rank (needs <= 72 registers to keep 3 CTAs per SM).
 // sort.cuh — stable LSD radix sort of (u64 key, u32 value) pairs (kernel stage K2: index builds).
 // 8 bits per pass.  ONE read of the keys up front gives the global digit histogram of every pass (k_rs_ghist; digit
 // counts do not depend on the order of the items); a pass is then a single kernel: tiles take tickets in order,
