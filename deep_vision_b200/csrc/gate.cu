@@ -25,6 +25,7 @@ struct GateUnicode {            // device copies of the CPython tables
 struct GateTablesDev {          // synonym / stop-word tables as code-point CSR, caller order
     const uint32_t* syn_src; const int32_t* syn_src_off; const uint32_t* syn_dst; const int32_t* syn_dst_off; int32_t n_syn;
     const uint32_t* stop; const int32_t* stop_off; int32_t n_stop;
+    int32_t growth;             // worst-case length factor of the synonym replaces (gate_tables)
 };
 
 __device__ __forceinline__ bool gate_in_ranges(uint32_t cp, const uint32_t* lo, const uint32_t* hi, int n) {
@@ -46,7 +47,24 @@ __device__ __forceinline__ bool gate_is_punct(uint32_t c) {          // web/serv
     }
 }
 // CPython str.lower() of in[0..n) -> out; returns new length (<= n + #U+0130)
-__device__ int64_t gate_lower(const uint32_t* in, int64_t n, uint32_t* out, const GateUnicode& U) {
+// Scratch views.  Questions whose capacity fits GQ_CAP code points keep their two buffers in shared memory, element i of
+// thread t at word i * 128 + t (conflict-free when the lanes of a warp work on the same i); longer ones use the
+// per-question regions of the global scratch.  The helpers below are written once against operator[] / operator+.
+#define GQ_THREADS 128
+#define GQ_CAP 64
+#define GQ_SMEM_BYTES (2 * GQ_CAP * GQ_THREADS * 4)
+struct GqShared {
+    uint32_t* p;
+    __device__ __forceinline__ uint32_t& operator[](int64_t i) const { return p[i * GQ_THREADS]; }
+    __device__ __forceinline__ GqShared operator+(int64_t k) const { return GqShared{ p + k * GQ_THREADS }; }
+};
+struct GqGlobal {
+    uint32_t* p;
+    __device__ __forceinline__ uint32_t& operator[](int64_t i) const { return p[i]; }
+    __device__ __forceinline__ GqGlobal operator+(int64_t k) const { return GqGlobal{ p + k }; }
+};
+template <class In, class Out>
+__device__ int64_t gate_lower(const In in, int64_t n, const Out out, const GateUnicode& U) {
     int64_t k = 0;
     for (int64_t i = 0; i < n; i++) {
         const uint32_t cp = in[i];
@@ -71,7 +89,8 @@ __device__ int64_t gate_lower(const uint32_t* in, int64_t n, uint32_t* out, cons
     return k;
 }
 // str.replace(src, dst): left-to-right, non-overlapping
-__device__ int64_t gate_replace(const uint32_t* in, int64_t n, const uint32_t* src, int32_t ns, const uint32_t* dst, int32_t nd, uint32_t* out) {
+template <class In, class Out>
+__device__ int64_t gate_replace(const In in, int64_t n, const uint32_t* src, int32_t ns, const uint32_t* dst, int32_t nd, const Out out) {
     if (ns <= 0) { for (int64_t i = 0; i < n; i++) out[i] = in[i]; return n; }
     int64_t i = 0, k = 0;
     while (i < n) {
@@ -82,67 +101,126 @@ __device__ int64_t gate_replace(const uint32_t* in, int64_t n, const uint32_t* s
     }
     return k;
 }
-__device__ void gate_heapsort(unsigned long long* a, int64_t n) {
+// 64-bit key arrays: plain global memory, or split over the two shared-memory buffers of a question (high word | low word)
+struct GqKeysGlobal {
+    unsigned long long* p;
+    __device__ __forceinline__ unsigned long long get(int64_t i) const { return p[i]; }
+    __device__ __forceinline__ void set(int64_t i, unsigned long long v) const { p[i] = v; }
+};
+struct GqKeysShared {
+    GqShared hi, lo;
+    __device__ __forceinline__ unsigned long long get(int64_t i) const { return ((unsigned long long)hi[i] << 32) | lo[i]; }
+    __device__ __forceinline__ void set(int64_t i, unsigned long long v) const { hi[i] = (uint32_t)(v >> 32); lo[i] = (uint32_t)v; }
+};
+template <class K>
+__device__ void gate_heapsort_v(const K a, int64_t n) {
     for (int64_t start = n / 2 - 1; start >= 0; start--) {
         int64_t root = start;
-        for (;;) { int64_t c = 2 * root + 1; if (c >= n) break; if (c + 1 < n && a[c] < a[c + 1]) c++; if (a[root] >= a[c]) break; const unsigned long long t = a[root]; a[root] = a[c]; a[c] = t; root = c; }
+        for (;;) {
+            int64_t c = 2 * root + 1; if (c >= n) break;
+            unsigned long long vc = a.get(c);
+            if (c + 1 < n) { const unsigned long long v2 = a.get(c + 1); if (vc < v2) { c++; vc = v2; } }
+            const unsigned long long vr = a.get(root);
+            if (vr >= vc) break;
+            a.set(root, vc); a.set(c, vr); root = c;
+        }
     }
     for (int64_t end = n - 1; end > 0; end--) {
-        const unsigned long long t0 = a[0]; a[0] = a[end]; a[end] = t0;
+        const unsigned long long t0 = a.get(0); a.set(0, a.get(end)); a.set(end, t0);
         int64_t root = 0;
-        for (;;) { int64_t c = 2 * root + 1; if (c >= end) break; if (c + 1 < end && a[c] < a[c + 1]) c++; if (a[root] >= a[c]) break; const unsigned long long t = a[root]; a[root] = a[c]; a[c] = t; root = c; }
+        for (;;) {
+            int64_t c = 2 * root + 1; if (c >= end) break;
+            unsigned long long vc = a.get(c);
+            if (c + 1 < end) { const unsigned long long v2 = a.get(c + 1); if (vc < v2) { c++; vc = v2; } }
+            const unsigned long long vr = a.get(root);
+            if (vr >= vc) break;
+            a.set(root, vc); a.set(c, vr); root = c;
+        }
     }
 }
+__device__ void gate_heapsort(unsigned long long* a, int64_t n) { gate_heapsort_v(GqKeysGlobal{ a }, n); }
 
 // one thread per question.  Scratch: two code-point buffers of cap_off[s+1]-cap_off[s] entries each;
 // keys of question s are written at keys[cap_off[s] ...], their count to key_cnt[s]; the normalised text
 // (optional) to norm[cap_off[s] ...] / norm_len[s].
-__global__ void __launch_bounds__(128) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
-                                                        const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
-                                                        GateUnicode U, GateTablesDev T,
-                                                        unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
-                                                        uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
-    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
-        const uint8_t* t = utf8 + off[s];
-        const int64_t nb = off[s + 1] - off[s];
-        uint32_t* a = bufA + cap_off[s]; uint32_t* b = bufB + cap_off[s];
-        // decode
-        int64_t m = 0;
-        for (int64_t i = 0; i < nb;) {
-            uint32_t c = t[i], cp; int len;
-            if (c < 0x80u) { cp = c; len = 1; } else if (c < 0xE0u) { cp = c & 0x1Fu; len = 2; } else if (c < 0xF0u) { cp = c & 0x0Fu; len = 3; } else { cp = c & 0x07u; len = 4; }
-            for (int j = 1; j < len && i + j < nb; j++) cp = (cp << 6) | (t[i + j] & 0x3Fu);
-            i += len; a[m++] = cp;
-        }
-        // strip().lower()
-        int64_t lo = 0, hi = m;
-        while (lo < hi && gate_is_space(a[lo])) lo++;
-        while (hi > lo && gate_is_space(a[hi - 1])) hi--;
-        m = gate_lower(a + lo, hi - lo, b, U);
-        uint32_t* cur = b; uint32_t* oth = a;
-        for (int32_t y = 0; y < T.n_syn; y++) {
-            m = gate_replace(cur, m, T.syn_src + T.syn_src_off[y], T.syn_src_off[y + 1] - T.syn_src_off[y],
-                             T.syn_dst + T.syn_dst_off[y], T.syn_dst_off[y + 1] - T.syn_dst_off[y], oth);
-            uint32_t* tmp = cur; cur = oth; oth = tmp;
-        }
-        { int64_t k = 0; for (int64_t i = 0; i < m; i++) { const uint32_t c = cur[i]; if (!gate_is_space(c) && !gate_is_punct(c)) cur[k++] = c; } m = k; }
-        for (int32_t y = 0; y < T.n_stop; y++) {
-            m = gate_replace(cur, m, T.stop + T.stop_off[y], T.stop_off[y + 1] - T.stop_off[y], nullptr, 0, oth);
-            uint32_t* tmp = cur; cur = oth; oth = tmp;
-        }
-        if (norm) { for (int64_t i = 0; i < m; i++) norm[cap_off[s] + i] = cur[i]; norm_len[s] = (int32_t)m; }
-        // bigram keys, sorted distinct
-        unsigned long long* ks = keys + cap_off[s];
-        int64_t nk = 0;
-        if (m == 1) { ks[0] = (1ULL << 42) | cur[0]; nk = 1; }
-        else if (m > 1) {
+template <class Buf>
+__device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, const Buf a, const Buf b, const GateUnicode& U, const GateTablesDev& T,
+                                              unsigned long long* ks, int32_t* key_cnt_s, uint32_t* norm_s, int32_t* norm_len_s, bool keys_in_scratch) {
+    // decode
+    int64_t m = 0;
+    for (int64_t i = 0; i < nb;) {
+        uint32_t c = t[i], cp; int len;
+        if (c < 0x80u) { cp = c; len = 1; } else if (c < 0xE0u) { cp = c & 0x1Fu; len = 2; } else if (c < 0xF0u) { cp = c & 0x0Fu; len = 3; } else { cp = c & 0x07u; len = 4; }
+        for (int j = 1; j < len && i + j < nb; j++) cp = (cp << 6) | (t[i + j] & 0x3Fu);
+        i += len; a[m++] = cp;
+    }
+    // strip().lower()
+    int64_t lo = 0, hi = m;
+    while (lo < hi && gate_is_space(a[lo])) lo++;
+    while (hi > lo && gate_is_space(a[hi - 1])) hi--;
+    m = gate_lower(a + lo, hi - lo, b, U);
+    Buf cur = b, oth = a;
+    for (int32_t y = 0; y < T.n_syn; y++) {
+        m = gate_replace(cur, m, T.syn_src + T.syn_src_off[y], T.syn_src_off[y + 1] - T.syn_src_off[y],
+                         T.syn_dst + T.syn_dst_off[y], T.syn_dst_off[y + 1] - T.syn_dst_off[y], oth);
+        const Buf tmp = cur; cur = oth; oth = tmp;
+    }
+    { int64_t k = 0; for (int64_t i = 0; i < m; i++) { const uint32_t c = cur[i]; if (!gate_is_space(c) && !gate_is_punct(c)) cur[k++] = c; } m = k; }
+    for (int32_t y = 0; y < T.n_stop; y++) {
+        m = gate_replace(cur, m, T.stop + T.stop_off[y], T.stop_off[y + 1] - T.stop_off[y], (const uint32_t*)nullptr, 0, oth);
+        const Buf tmp = cur; cur = oth; oth = tmp;
+    }
+    if (norm_s) { for (int64_t i = 0; i < m; i++) norm_s[i] = cur[i]; *norm_len_s = (int32_t)m; }
+    // bigram keys, sorted distinct
+    int64_t nk = 0;
+    if (m == 1) { ks[0] = (1ULL << 42) | cur[0]; nk = 1; }
+    else if (m > 1) {
+        nk = m - 1;
+        if (keys_in_scratch) {
+            // key i = (cur[i] << 21) | cur[i + 1]: its high word replaces cur[i] (not needed any more), its low word goes to oth[i]
+            uint32_t c0 = cur[0];
+            for (int64_t i = 0; i + 1 < m; i++) {
+                const uint32_t c1 = cur[i + 1];
+                const unsigned long long k = ((unsigned long long)c0 << 21) | c1;
+                cur[i] = (uint32_t)(k >> 32); oth[i] = (uint32_t)k;
+                c0 = c1;
+            }
+            // (views over the same scratch; Buf is GqShared on this path)
+            gate_heapsort_v(GqKeysShared{ GqShared{ &cur[0] }, GqShared{ &oth[0] } }, nk);      // only taken with Buf = GqShared
+            unsigned long long prev = ((unsigned long long)cur[0] << 32) | oth[0];
+            ks[0] = prev;
+            int64_t u = 1;
+            for (int64_t i = 1; i < nk; i++) { const unsigned long long k = ((unsigned long long)cur[i] << 32) | oth[i]; if (k != prev) { ks[u++] = k; prev = k; } }
+            nk = u;
+        } else {
             for (int64_t i = 0; i + 1 < m; i++) ks[i] = ((unsigned long long)cur[i] << 21) | cur[i + 1];
-            nk = m - 1;
             gate_heapsort(ks, nk);
             int64_t u = 1; for (int64_t i = 1; i < nk; i++) if (ks[i] != ks[u - 1]) ks[u++] = ks[i];
             nk = u;
         }
-        key_cnt[s] = (int32_t)nk;
+    }
+    *key_cnt_s = (int32_t)nk;
+}
+
+// one thread per question.  Scratch: two code-point buffers of cap_off[s+1]-cap_off[s] entries each (shared memory when
+// that is <= GQ_CAP, else the question's region of bufA / bufB); keys of question s are written at keys[cap_off[s] ...],
+// their count to key_cnt[s]; the normalised text (optional) to norm[cap_off[s] ...] / norm_len[s].
+extern __shared__ uint32_t gq_smem[];
+__global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
+                                                        const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
+                                                        GateUnicode U, GateTablesDev T,
+                                                        unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
+                                                        uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
+    const GqShared sa{ gq_smem + threadIdx.x }, sb{ gq_smem + GQ_CAP * GQ_THREADS + threadIdx.x };
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
+        const uint8_t* t = utf8 + off[s];
+        const int64_t nb = off[s + 1] - off[s];
+        const int64_t c0 = cap_off[s];
+        // code points (+1 for every 2-byte character: U+0130 lower-cases to two), times the synonym growth, bound the scratch use
+        int64_t ncp = 2;
+        for (int64_t i = 0; i < nb && ncp <= GQ_CAP; i++) { const uint32_t c = t[i]; ncp += ((c & 0xC0u) != 0x80u) + ((c & 0xE0u) == 0xC0u); }
+        if (ncp * T.growth <= GQ_CAP) gate_question(t, nb, sa, sb, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, true);
+        else gate_question(t, nb, GqGlobal{ bufA + c0 }, GqGlobal{ bufB + c0 }, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, false);
     }
 }
 
@@ -403,7 +481,7 @@ static int32_t gate_tables(dvb_ctx* ctx, dvb_io& io, const uint32_t* syn_src, co
         const int32_t ns = H->sso[y + 1] - H->sso[y], nd = H->sdo[y + 1] - H->sdo[y];
         if (ns > 0 && nd > ns) { H->growth *= (nd + ns - 1) / ns; if (H->growth > 64) { dvb_set_err(ctx, "gate tables: synonym growth too large%s%s"); return DVB_E_INVALID; } }
     }
-    T->n_syn = n_syn; T->n_stop = n_stop;
+    T->n_syn = n_syn; T->n_stop = n_stop; T->growth = (int32_t)H->growth;
     T->syn_src = io.in(syn_src, (size_t)H->sso[n_syn]); T->syn_src_off = io.in(syn_src_off, (size_t)n_syn + 1);
     T->syn_dst = io.in(syn_dst, (size_t)H->sdo[n_syn]); T->syn_dst_off = io.in(syn_dst_off, (size_t)n_syn + 1);
     T->stop = io.in(stop, (size_t)H->sto[n_stop]); T->stop_off = io.in(stop_off, (size_t)n_stop + 1);
@@ -451,8 +529,9 @@ extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* u
     DVB_CUDA(ctx, cudaMemcpyAsync(d_cap, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
     if (mem == DVB_MEM_HOST) memcpy(out_cap_off, cap.data(), 8 * (size_t)(n + 1));
     else DVB_CUDA(ctx, cudaMemcpyAsync(out_cap_off, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
-    const int grid = (int)std::min<int64_t>((n + 127) / 128, (int64_t)ctx->num_sm * 16);
-    k_question_keys<<<grid, 128, 0, io.st>>>(d_utf8, d_off, n, d_cap, bufA, bufB, U, T, d_keys, d_cnt, d_norm, d_nl);
+    DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
+    const int grid = (int)std::min<int64_t>((n + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    k_question_keys<<<grid, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_utf8, d_off, n, d_cap, bufA, bufB, U, T, d_keys, d_cnt, d_norm, d_nl);
     ctx->launches += 1;
     return io.finish(ctx);          // synchronises: `cap` stays alive until here
 }
@@ -490,10 +569,11 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     rc = io.check(ctx); if (rc) return rc;
     DVB_CUDA(ctx, cudaMemcpyAsync(d_ccap, ccap.data(), 8 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaMemcpyAsync(d_hcap, hcap.data(), 8 * (size_t)(n_hist + 1), cudaMemcpyHostToDevice, io.st));
-    const int gh = (int)std::min<int64_t>((n_hist + 127) / 128, (int64_t)ctx->num_sm * 16);
-    k_question_keys<<<gh, 128, 0, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
-    const int gc = (int)std::min<int64_t>((n_cand + 127) / 128, (int64_t)ctx->num_sm * 16);
-    k_question_keys<<<gc, 128, 0, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
+    DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
+    const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
+    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
     k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
     int64_t n_pairs = 0;
     DVB_CUDA(ctx, cudaMemcpyAsync(&n_pairs, d_poff + n_hist, 8, cudaMemcpyDeviceToHost, io.st));
