@@ -63,6 +63,7 @@ struct GqGlobal {
     __device__ __forceinline__ uint32_t& operator[](int64_t i) const { return p[i]; }
     __device__ __forceinline__ GqGlobal operator+(int64_t k) const { return GqGlobal{ p + k }; }
 };
+__device__ __forceinline__ uint32_t gq_bit(uint32_t cp) { return (cp * 0x9E3779B1u) >> 26; }
 template <class In, class Out>
 __device__ int64_t gate_lower(const In in, int64_t n, const Out out, const GateUnicode& U) {
     int64_t k = 0;
@@ -160,14 +161,29 @@ __device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, cons
     while (hi > lo && gate_is_space(a[hi - 1])) hi--;
     m = gate_lower(a + lo, hi - lo, b, U);
     Buf cur = b, oth = a;
+    // `present`: a 64-bit set (one hashed bit per code point) that always covers the characters of the current text.  A
+    // replace whose source has a character outside the set cannot match and is skipped without touching the buffers
+    // (most of the 9 + 17 patterns never occur in a given question); replacements add their characters, deletions
+    // leave the set a superset.
+    unsigned long long present = 0ULL;
+    for (int64_t i = 0; i < m; i++) present |= 1ULL << gq_bit(cur[i]);
     for (int32_t y = 0; y < T.n_syn; y++) {
-        m = gate_replace(cur, m, T.syn_src + T.syn_src_off[y], T.syn_src_off[y + 1] - T.syn_src_off[y],
-                         T.syn_dst + T.syn_dst_off[y], T.syn_dst_off[y + 1] - T.syn_dst_off[y], oth);
+        const uint32_t* src = T.syn_src + T.syn_src_off[y]; const int32_t ns = T.syn_src_off[y + 1] - T.syn_src_off[y];
+        const uint32_t* dst = T.syn_dst + T.syn_dst_off[y]; const int32_t nd = T.syn_dst_off[y + 1] - T.syn_dst_off[y];
+        unsigned long long need = 0ULL;
+        for (int32_t j = 0; j < ns; j++) need |= 1ULL << gq_bit(src[j]);
+        if (ns <= 0 || (present & need) != need) continue;                 // replace("", x) is not a rule the tables carry: copy = no-op
+        m = gate_replace(cur, m, src, ns, dst, nd, oth);
+        for (int32_t j = 0; j < nd; j++) present |= 1ULL << gq_bit(dst[j]);
         const Buf tmp = cur; cur = oth; oth = tmp;
     }
     { int64_t k = 0; for (int64_t i = 0; i < m; i++) { const uint32_t c = cur[i]; if (!gate_is_space(c) && !gate_is_punct(c)) cur[k++] = c; } m = k; }
     for (int32_t y = 0; y < T.n_stop; y++) {
-        m = gate_replace(cur, m, T.stop + T.stop_off[y], T.stop_off[y + 1] - T.stop_off[y], (const uint32_t*)nullptr, 0, oth);
+        const uint32_t* src = T.stop + T.stop_off[y]; const int32_t ns = T.stop_off[y + 1] - T.stop_off[y];
+        unsigned long long need = 0ULL;
+        for (int32_t j = 0; j < ns; j++) need |= 1ULL << gq_bit(src[j]);
+        if (ns <= 0 || (present & need) != need) continue;
+        m = gate_replace(cur, m, src, ns, (const uint32_t*)nullptr, 0, oth);
         const Buf tmp = cur; cur = oth; oth = tmp;
     }
     if (norm_s) { for (int64_t i = 0; i < m; i++) norm_s[i] = cur[i]; *norm_len_s = (int32_t)m; }
@@ -530,7 +546,7 @@ extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* u
     if (mem == DVB_MEM_HOST) memcpy(out_cap_off, cap.data(), 8 * (size_t)(n + 1));
     else DVB_CUDA(ctx, cudaMemcpyAsync(out_cap_off, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
-    const int grid = (int)std::min<int64_t>((n + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    const int grid = (int)std::min<int64_t>((n + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
     k_question_keys<<<grid, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_utf8, d_off, n, d_cap, bufA, bufB, U, T, d_keys, d_cnt, d_norm, d_nl);
     ctx->launches += 1;
     return io.finish(ctx);          // synchronises: `cap` stays alive until here
@@ -570,9 +586,9 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     DVB_CUDA(ctx, cudaMemcpyAsync(d_ccap, ccap.data(), 8 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaMemcpyAsync(d_hcap, hcap.data(), 8 * (size_t)(n_hist + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
-    const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
     k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
-    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 3);
+    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
     k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
     k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
     int64_t n_pairs = 0;
