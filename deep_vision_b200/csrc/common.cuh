@@ -30,6 +30,8 @@ struct dvb_lease {
     std::vector<cudaEvent_t> pipe_ev;    // one per in-flight input slice
     int* flag_h = nullptr;               // pinned + mapped word a kernel can raise (read by the host after the stream sync)
     int* flag_d = nullptr;
+    uint8_t* bounce = nullptr;           // pinned staging of large PAGEABLE inputs: DVB_H2D_THREADS x DVB_H2D_CHUNK bytes (first use)
+    cudaEvent_t bounce_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     bool busy = false;
 };
 
@@ -117,6 +119,48 @@ struct dvb_scope {
 
 static inline size_t dvb_pad(size_t bytes) { return (bytes + 255 + 64) & ~size_t(255); }
 
+// Large inputs in PAGEABLE host memory (what numpy hands the ctypes shim): cudaMemcpyAsync stages them through the
+// driver's own bounce buffer with one copying thread (12 GB/s on the B200 boxes against 40 GB/s from pinned memory).
+// Here DVB_H2D_THREADS host threads copy alternate chunks into pinned buffers of the lease and queue the DMA of each
+// chunk on the call's stream, so the host memcpy of one chunk overlaps the DMA of the others.  Returns after every chunk
+// has left its bounce buffer (the stream still orders later kernels behind the copies).
+#define DVB_H2D_THREADS 4
+#define DVB_H2D_CHUNK (size_t(4) << 20)
+#define DVB_H2D_MIN (size_t(8) << 20)
+static inline bool dvb_is_pageable(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return at.type == cudaMemoryTypeUnregistered;
+}
+static inline cudaError_t dvb_h2d_staged(dvb_lease* l, int device, void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    if (!l->bounce) {
+        if (cudaHostAlloc((void**)&l->bounce, DVB_H2D_THREADS * DVB_H2D_CHUNK, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); l->bounce = nullptr; }
+        for (int i = 0; l->bounce && i < DVB_H2D_THREADS; i++)
+            if (cudaEventCreateWithFlags(&l->bounce_ev[i], cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); cudaFreeHost(l->bounce); l->bounce = nullptr; }
+    }
+    if (!l->bounce) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st);
+    const size_t n_chunks = (bytes + DVB_H2D_CHUNK - 1) / DVB_H2D_CHUNK;
+    cudaError_t errs[DVB_H2D_THREADS];
+    auto work = [&](int t) {
+        cudaError_t e = cudaSetDevice(device);
+        uint8_t* buf = l->bounce + (size_t)t * DVB_H2D_CHUNK;
+        for (size_t c = (size_t)t; c < n_chunks && e == cudaSuccess; c += DVB_H2D_THREADS) {
+            const size_t o = c * DVB_H2D_CHUNK, nb = std::min(DVB_H2D_CHUNK, bytes - o);
+            memcpy(buf, (const uint8_t*)src + o, nb);
+            e = cudaMemcpyAsync((uint8_t*)dst + o, buf, nb, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) e = cudaEventRecord(l->bounce_ev[t], st);
+            if (e == cudaSuccess) e = cudaEventSynchronize(l->bounce_ev[t]);       // the buffer is free again
+        }
+        errs[t] = e;
+    };
+    std::thread th[DVB_H2D_THREADS - 1];
+    for (int t = 1; t < DVB_H2D_THREADS; t++) th[t - 1] = std::thread(work, t);
+    work(0);
+    for (int t = 1; t < DVB_H2D_THREADS; t++) th[t - 1].join();
+    for (int t = 0; t < DVB_H2D_THREADS; t++) if (errs[t] != cudaSuccess) return errs[t];
+    return cudaSuccess;
+}
+
 // Stage a caller array: HOST -> async copy into `dst` (device); DEVICE -> use in place.
 template <typename T>
 static inline const T* dvb_in(int mem, const T* src, T* dst, size_t n, cudaStream_t s, cudaError_t* err) {
@@ -136,7 +180,12 @@ struct dvb_io {
         if (mem == DVB_MEM_DEVICE || !p) return p;
         T* d = sc.alloc<T>(n ? n : 1);
         if (!d) { oom = true; return nullptr; }
-        if (n) { cudaError_t e = cudaMemcpyAsync(d, p, n * sizeof(T), cudaMemcpyHostToDevice, st); if (e != cudaSuccess) err = e; }
+        if (n) {
+            const size_t bytes = n * sizeof(T);
+            cudaError_t e = (bytes >= DVB_H2D_MIN && dvb_is_pageable(p)) ? dvb_h2d_staged(sc.l, sc.ctx->device, d, p, bytes, st)
+                                                                         : cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) err = e;
+        }
         return d;
     }
     template <typename T> T* out(T* p, size_t n) {
