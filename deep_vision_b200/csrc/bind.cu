@@ -441,6 +441,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             }
             cp = l->copy;
         }
+        const bool facts_pageable = dvb_is_pageable(h_fu);
         auto run = [&]() -> cudaError_t {
             cudaError_t e = cudaSuccess;
             #define BIND_TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
@@ -451,7 +452,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
                 const int64_t cb0 = h_co_rel[sess_claim_off[s0]], cb1 = h_co_rel[sess_claim_off[s1]];
                 const int64_t fb0 = h_fo_rel[sess_fact_off[s0]], fb1 = h_fo_rel[sess_fact_off[s1]];
                 if (cb1 > cb0) BIND_TRY(cudaMemcpyAsync(d_cu_w + cb0, h_cu + cb0, (size_t)(cb1 - cb0), cudaMemcpyHostToDevice, cp));
-                if (fb1 > fb0) BIND_TRY(cudaMemcpyAsync(d_fu_w + fb0, h_fu + fb0, (size_t)(fb1 - fb0), cudaMemcpyHostToDevice, cp));
+                // fact text of a slice from PAGEABLE memory (numpy behind the ctypes shim): 4 host threads stage it through pinned buffers
+                if (fb1 > fb0 && (size_t)(fb1 - fb0) >= DVB_H2D_MIN && facts_pageable) BIND_TRY(dvb_h2d_staged(l, ctx->device, d_fu_w + fb0, h_fu + fb0, (size_t)(fb1 - fb0), cp));
+                else if (fb1 > fb0) BIND_TRY(cudaMemcpyAsync(d_fu_w + fb0, h_fu + fb0, (size_t)(fb1 - fb0), cudaMemcpyHostToDevice, cp));
                 if (n_slices > 1) { BIND_TRY(cudaEventRecord(l->pipe_ev[i + 1], cp)); BIND_TRY(cudaStreamWaitEvent(st, l->pipe_ev[i + 1], 0)); }
                 BIND_TRY(launch(fast, s0, s1));
             }

@@ -128,6 +128,8 @@ static inline size_t dvb_pad(size_t bytes) { return (bytes + 255 + 64) & ~size_t
 #define DVB_H2D_CHUNK (size_t(4) << 20)
 #define DVB_H2D_MIN (size_t(8) << 20)
 static inline bool dvb_is_pageable(const void* p) {
+    static const bool off = [] { const char* e = getenv("DVB_H2D_STAGED"); return e && e[0] == '0'; }();     // A/B switch
+    if (off) return false;
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return true; }
     return at.type == cudaMemoryTypeUnregistered;

@@ -470,7 +470,8 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
     const uint8_t* d_utf8 = text;
     if (mem == DVB_MEM_HOST) {
         IX_TRY(cudaMallocAsync((void**)&d_text, (size_t)nb + 64, st));
-        IX_TRY(cudaMemcpyAsync(d_text, text, (size_t)nb, cudaMemcpyHostToDevice, st));
+        if ((size_t)nb >= DVB_H2D_MIN && dvb_is_pageable(text)) IX_TRY(dvb_h2d_staged(sc.l, ctx->device, d_text, text, (size_t)nb, st));
+        else IX_TRY(cudaMemcpyAsync(d_text, text, (size_t)nb, cudaMemcpyHostToDevice, st));
         d_utf8 = d_text;
     }
     // K1: symbols (sym_off doubles as the rebased byte offsets the symboliser reads)
