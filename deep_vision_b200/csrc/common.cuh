@@ -31,7 +31,7 @@ struct dvb_lease {
     int* flag_h = nullptr;               // pinned + mapped word a kernel can raise (read by the host after the stream sync)
     int* flag_d = nullptr;
     uint8_t* bounce = nullptr;           // pinned staging of large PAGEABLE inputs: DVB_H2D_THREADS x DVB_H2D_CHUNK bytes (first use)
-    cudaEvent_t bounce_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t bounce_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool busy = false;
 };
 
@@ -121,11 +121,11 @@ static inline size_t dvb_pad(size_t bytes) { return (bytes + 255 + 64) & ~size_t
 
 // Large inputs in PAGEABLE host memory (what numpy hands the ctypes shim): cudaMemcpyAsync stages them through the
 // driver's own bounce buffer with one copying thread (12 GB/s on the B200 boxes against 40 GB/s from pinned memory).
-// Here DVB_H2D_THREADS host threads copy alternate chunks into pinned buffers of the lease and queue the DMA of each
+// Here DVB_H2D_THREADS host threads copy alternate 2 MB chunks into pinned buffers of the lease and queue the DMA of each
 // chunk on the call's stream, so the host memcpy of one chunk overlaps the DMA of the others.  Returns after every chunk
 // has left its bounce buffer (the stream still orders later kernels behind the copies).
-#define DVB_H2D_THREADS 4
-#define DVB_H2D_CHUNK (size_t(4) << 20)
+#define DVB_H2D_THREADS 8
+#define DVB_H2D_CHUNK (size_t(2) << 20)
 #define DVB_H2D_MIN (size_t(8) << 20)
 static inline bool dvb_is_pageable(const void* p) {
     static const bool off = [] { const char* e = getenv("DVB_H2D_STAGED"); return e && e[0] == '0'; }();     // A/B switch
