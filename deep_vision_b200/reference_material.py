@@ -77,26 +77,36 @@ def _tokenize_reference_material_query(query_text: str) -> List[str]:
 def terms_to_symbols(queries_terms: Sequence[Sequence[str]]) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
     """Terms -> the kernels' symbol alphabet (include/dvb200.h): (term_sym u16, term_off i32, query_term_off i32)."""
     flat = [t for terms in queries_terms for t in terms]
-    lens = np.fromiter(map(len, flat), np.int64, len(flat))
-    cp = np.frombuffer("".join(flat).encode("utf-32-le"), np.uint32)           # one code point per term character
-    if cp.size != int(lens.sum()):
+    # one join + one encode for all terms: U+0000 cannot occur in a term, so it separates them
+    cp = np.frombuffer("\x00".join(flat).encode("utf-32-le", "surrogatepass"), np.uint32)
+    if cp.size and int(cp.max()) > 0xFFFF:
         raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
-    sym = np.zeros(cp.size, np.uint32)
-    cjk = (cp >= 0x4E00) & (cp <= 0x9FFF)
-    low = (cp >= 97) & (cp <= 122)
-    dig = (cp >= 48) & (cp <= 57)
-    us = cp == 95
-    if not bool(np.all(cjk | low | dig | us)):
+    sym_all = _SYM_LUT[cp]
+    sep = cp == 0
+    if flat and (int(np.count_nonzero(sep)) != len(flat) - 1 or bool(np.any((sym_all == 0) & ~sep))):
         raise ValueError("query terms may only contain [a-z0-9_] or CJK characters")
-    sym[cjk] = cp[cjk] - 0x4E00 + 1
-    sym[low] = 0x8000 | (cp[low] - 97 + 1)
-    sym[dig] = 0x8000 | (cp[dig] - 48 + 27)
-    sym[us] = 0x8000 | 37
+    sym = sym_all[~sep] if flat else np.zeros(0, np.uint16)
     toff = np.zeros(len(flat) + 1, np.int64)
-    np.cumsum(lens, out=toff[1:])
+    if flat:
+        ends = np.flatnonzero(sep)
+        toff[1:-1] = ends - np.arange(len(ends))                   # symbols before the k-th separator
+        toff[-1] = sym.size
     qoff = np.zeros(len(queries_terms) + 1, np.int64)
     np.cumsum(np.fromiter(map(len, queries_terms), np.int64, len(queries_terms)), out=qoff[1:])
-    return (sym.astype(np.uint16) if sym.size else np.zeros(1, np.uint16), toff.astype(np.int32), qoff.astype(np.int32))
+    return (sym if sym.size else np.zeros(1, np.uint16), toff.astype(np.int32), qoff.astype(np.int32))
+
+
+def _make_sym_lut() -> np.ndarray:
+    """code point (BMP) -> kernel symbol (include/dvb200.h): CJK 1..20992, 0x8000 | class for [a-z0-9_], 0 = not a term character."""
+    lut = np.zeros(0x10000, np.uint16)
+    lut[0x4E00:0xA000] = np.arange(1, 20993, dtype=np.uint16)
+    lut[97:123] = 0x8000 | np.arange(1, 27, dtype=np.uint16)
+    lut[48:58] = 0x8000 | np.arange(27, 37, dtype=np.uint16)
+    lut[95] = 0x8000 | 37
+    return lut
+
+
+_SYM_LUT = _make_sym_lut()
 
 
 # ----------------------------------------------------------------------------- GPU primitives
