@@ -195,11 +195,14 @@ def cpu_baseline(corpus, threads, repeats=1, min_seconds=0.0):
     total, passes = 0.0, 0
     while passes < repeats or total < min_seconds:
         t0 = time.perf_counter()
-        dv_oracle.bind_claims(None, None, corpus.sess_claim_off, corpus.sess_fact_off, corpus.fact_quality, corpus.fact_dim,
-                              corpus.fact_hard, corpus.claim_pref_dim, corpus.claim_threshold, packed=packed, n_threads=threads)
+        cpu_baseline.last = dv_oracle.bind_claims(None, None, corpus.sess_claim_off, corpus.sess_fact_off, corpus.fact_quality, corpus.fact_dim,
+                                                  corpus.fact_hard, corpus.claim_pref_dim, corpus.claim_threshold, packed=packed, n_threads=threads)
         total += time.perf_counter() - t0
         passes += 1
     return corpus.n_pairs * passes / total, total, passes
+
+
+cpu_baseline.last = None
 
 
 def run_reference(args, rank, world):
@@ -302,6 +305,7 @@ def main():
     elapsed_ms = reduce_max(ev0.elapsed_time(ev1))
     launches = ctx.launches - l0
     res_best = d_best.cpu().numpy()
+    res_score, res_bound = d_score.cpu().numpy(), d_bound.cpu().numpy()
 
     # ---------------- end-to-end arm: pinned host buffers through the C-ABI (H2D + kernel + D2H timed)
     pinned = [torch.from_numpy(a).pin_memory() for a in host_in]
@@ -386,6 +390,13 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             v, secs, passes = cpu_baseline(corpus, cores, repeats=2, min_seconds=10.0)
+            ref = cpu_baseline.last                           # the oracle's answer on the FULL workload checks the GPU's (checker use)
+            same = bool(np.array_equal(ref["best_fact"], res_best) and np.array_equal(ref["bound"], res_bound)
+                        and np.array_equal(ref["best_score"].view(np.uint64), res_score.view(np.uint64)))
+            line["parity"] = {"vs": "oracle C port on all %d claims of the bench workload" % n_claims,
+                              "best_fact_bound_and_fp64_score_bits_identical": same}
+            if not same:
+                print("bench.py: GPU results differ from the oracle on the bench workload", file=sys.stderr)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "all %d sessions (%d pairs) x %d passes, %.1f s wall, oracle C port of web/server.py:24780-24864, %d threads"
                                               % (corpus.n_sessions, corpus.n_pairs, passes, secs, cores)}
