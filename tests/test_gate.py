@@ -112,3 +112,31 @@ def test_gpu_solution_jaccard_golden(gpu_ctx, golden, oracle):
         for (l, r), i, u in zip(pairs, inter, union):
             _j, oi, ou = oracle.solution_jaccard(l, r, n)
             assert (int(i), int(u)) == (oi, ou), (l, r, n)
+
+
+@pytest.mark.gpu
+def test_gpu_gate_config4_history_size_slice_vs_oracle(gpu_ctx, oracle):
+    """Parity at scale: the FULL 50 k-question history of config 4, 100 k candidates (2 % of them a history question with one
+    edit); a slice of the candidates against the C oracle over the whole history, and every planted near-duplicate must
+    come back with a history index at least as recent as its source."""
+    from deep_vision_b200 import question_similarity as qs, synth
+    rng = np.random.default_rng(44)
+    hd, ho = synth.make_texts(50000, 30, seed=31)
+    hraw = hd.tobytes()
+    hist = [hraw[ho[i]:ho[i + 1]].decode("utf-8") + "？" for i in range(50000)]
+    cd, co = synth.make_texts(100000, 30, seed=1000)
+    craw = cd.tobytes()
+    cands = [craw[co[i]:co[i + 1]].decode("utf-8") + "？" for i in range(100000)]
+    planted = {}
+    for i in np.nonzero(rng.random(100000) < 0.02)[0].tolist():
+        h = int(rng.integers(0, 50000))
+        cands[i] = "请问" + hist[h][1:]                      # stop word in front, first character dropped
+        planted[i] = h
+    gate = qs.QuestionGate(ctx=gpu_ctx)
+    got = gate.match(cands, hist, 0.62)
+    og = oracle.Gate(gate.synonyms, gate.stopwords)
+    sl = sorted(planted)[:60] + list(range(0, 90))
+    want = og.gate([cands[i] for i in sl], hist, 0.62)
+    assert got[sl].tolist() == want.tolist()
+    hit = [i for i, h in planted.items() if got[i] >= h]
+    assert len(hit) >= 0.95 * len(planted), (len(hit), len(planted))
