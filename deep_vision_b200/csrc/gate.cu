@@ -331,6 +331,30 @@ __global__ void __launch_bounds__(GATE_THREADS) k_gate_match(const unsigned long
 // best match so far" prune them, and the survivors are verified exactly (|L & R| by probing R's keys in a shared-memory
 // set of L's keys, then the reference's fp64 test).  One key of slack keeps the bound safe against the rounding of the
 // fp64 division.  Candidates with more than GP_MAXL keys are flagged (-2) for k_gate_match.
+// Key -> posting range of the sorted (key, history id) pairs: an open-addressing table (empty = ~0) filled from the
+// run heads / tails of the sorted pairs, so a candidate key costs one or two L2 probes instead of two 21-step binary
+// searches over the pair array.
+struct GateKeyTable { unsigned long long* key; uint32_t* lo; uint32_t* df; uint32_t mask; };
+__device__ __forceinline__ uint32_t gkt_hash(unsigned long long key) { return (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 32); }
+__global__ void k_gate_table_heads(const unsigned long long* __restrict__ pk, int64_t n_pairs, GateKeyTable T) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = pk[i];
+        if (i > 0 && pk[i - 1] == key) continue;
+        uint32_t sl = gkt_hash(key) & T.mask;
+        while (atomicCAS(&T.key[sl], ~0ULL, key) != ~0ULL) sl = (sl + 1) & T.mask;      // every head key is distinct
+        T.lo[sl] = (uint32_t)i;
+    }
+}
+__global__ void k_gate_table_tails(const unsigned long long* __restrict__ pk, int64_t n_pairs, GateKeyTable T) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = pk[i];
+        if (i + 1 < n_pairs && pk[i + 1] == key) continue;
+        uint32_t sl = gkt_hash(key) & T.mask;
+        while (T.key[sl] != key) sl = (sl + 1) & T.mask;
+        T.df[sl] = (uint32_t)(i + 1) - T.lo[sl];
+    }
+}
+
 #define GP_MAXL 128
 #define GP_SET 256
 struct GpWarp {
@@ -344,7 +368,7 @@ __global__ void __launch_bounds__(256) k_gate_match_prefix(const unsigned long l
                                                              const unsigned long long* __restrict__ pk, const uint32_t* __restrict__ pv, int64_t n_pairs,
                                                              const unsigned long long* __restrict__ hkeys, const int64_t* __restrict__ hcap_off,
                                                              const int32_t* __restrict__ hcnt, double thr, int64_t* __restrict__ out,
-                                                             int32_t* __restrict__ n_flagged, int64_t* __restrict__ flagged) {
+                                                             int32_t* __restrict__ n_flagged, int64_t* __restrict__ flagged, GateKeyTable KT) {
     extern __shared__ __align__(16) unsigned char gp_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     GpWarp& W = reinterpret_cast<GpWarp*>(gp_raw)[warp];
@@ -361,11 +385,14 @@ __global__ void __launch_bounds__(256) k_gate_match_prefix(const unsigned long l
             W.key[j] = key;
             uint32_t sl = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 56);
             while (atomicCAS(&W.set[sl], ~0ULL, key) != ~0ULL) sl = (sl + 1) & (GP_SET - 1);        // keys are distinct
-            int64_t a = 0, b = n_pairs;
-            while (a < b) { const int64_t m = (a + b) >> 1; if (pk[m] < key) a = m + 1; else b = m; }
-            int64_t a2 = a, b2 = n_pairs;
-            while (a2 < b2) { const int64_t m = (a2 + b2) >> 1; if (pk[m] <= key) a2 = m + 1; else b2 = m; }
-            W.lo[j] = (uint32_t)a; W.df[j] = (uint32_t)(a2 - a);
+            uint32_t ks = gkt_hash(key) & KT.mask, plo = 0u, pdf = 0u;          // posting range of the key (df = 0: not in the history)
+            for (;;) {
+                const unsigned long long tk = KT.key[ks];
+                if (tk == key) { plo = KT.lo[ks]; pdf = KT.df[ks]; break; }
+                if (tk == ~0ULL) break;
+                ks = (ks + 1) & KT.mask;
+            }
+            W.lo[j] = plo; W.df[j] = pdf;
         }
         __syncwarp();
         int alpha = (int)ceil(thr * (double)L) - 1; if (alpha < 1) alpha = 1;
@@ -619,15 +646,23 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     const char* force = getenv("DVB_GATE_KERNEL");
     const bool prefix = threshold > 0.0 && n_pairs > 0 && !(force && !strcmp(force, "dense"));
     int32_t* d_nflag = nullptr; int64_t* d_flagged = nullptr;
+    GateKeyTable KT{ nullptr, nullptr, nullptr, 0u };
     if (prefix) {
         d_nflag = io.tmp<int32_t>(1); d_flagged = io.tmp<int64_t>((size_t)n_cand);
+        uint32_t cap = 1024; while ((int64_t)cap < 2 * n_pairs) cap <<= 1;            // <= half full (distinct keys <= pairs)
+        KT.mask = cap - 1;
+        KT.key = io.tmp<unsigned long long>((size_t)cap); KT.lo = io.tmp<uint32_t>((size_t)cap); KT.df = io.tmp<uint32_t>((size_t)cap);
         rc = io.check(ctx); if (rc) return rc;
         DVB_CUDA(ctx, cudaMemsetAsync(d_nflag, 0, 4, io.st));
         const size_t smem_p = 8 * sizeof(GpWarp);
         DVB_CUDA(ctx, cudaFuncSetAttribute(k_gate_match_prefix, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
         const int grid_p = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)ctx->num_sm * 32);
-        k_gate_match_prefix<<<grid_p, 256, smem_p, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hk, d_hcap, d_hc, threshold, d_out, d_nflag, d_flagged);
-        ctx->launches += 1;
+        DVB_CUDA(ctx, cudaMemsetAsync(KT.key, 0xFF, 8 * (size_t)(KT.mask + 1), io.st));
+        const int grid_t = (int)std::min<int64_t>((n_pairs + 255) / 256, (int64_t)ctx->num_sm * 16);
+        k_gate_table_heads<<<grid_t, 256, 0, io.st>>>(pk, n_pairs, KT);
+        k_gate_table_tails<<<grid_t, 256, 0, io.st>>>(pk, n_pairs, KT);
+        k_gate_match_prefix<<<grid_p, 256, smem_p, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hk, d_hcap, d_hc, threshold, d_out, d_nflag, d_flagged, KT);
+        ctx->launches += 3;
     }
     // dense counters: everything when the prefix filter does not apply, else only the candidates it flagged (> GP_MAXL keys)
     k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out, d_nflag, d_flagged);
