@@ -625,7 +625,7 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     if (n_pairs >= 0x7FFFFFFFLL) { dvb_set_err(ctx, "dvb_question_gate: history too large%s%s"); return DVB_E_CAPACITY; }
     unsigned long long* pk = io.tmp<unsigned long long>((size_t)n_pairs + 1); unsigned long long* pk2 = io.tmp<unsigned long long>((size_t)n_pairs + 1);
     uint32_t* pv = io.tmp<uint32_t>((size_t)n_pairs + 1); uint32_t* pv2 = io.tmp<uint32_t>((size_t)n_pairs + 1);
-    uint32_t* hist = io.tmp<uint32_t>((size_t)(256 * ((n_pairs + RS_TILE - 1) / RS_TILE + 1) + 256));
+    uint32_t* hist = io.tmp<uint32_t>(dv_radix_hist_words(n_pairs) + 256);
     rc = io.check(ctx); if (rc) return rc;
     if (n_pairs > 0) {
         k_gate_pairs<<<(int)std::min<int64_t>(n_hist, (int64_t)ctx->num_sm * 8), 128, 0, io.st>>>(d_hk, d_hcap, d_hc, d_poff, n_hist, pk, pv);

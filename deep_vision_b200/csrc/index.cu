@@ -503,10 +503,9 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
     sg->n_post = n_post;
     if (d_text) { cudaFreeAsync(d_text, st); d_text = nullptr; }
     if (n_post > 0) {
-        const int64_t nbk = (n_post + RS_TILE - 1) / RS_TILE;
         IX_TRY(cudaMallocAsync((void**)&s_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&sg->pv, 4 * (size_t)n_post, st));
         IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
-        IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * (size_t)(256 * nbk + 256), st));
+        IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * dv_radix_hist_words(n_post), st));
         k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, s_pk, sg->pv);
         ctx->launches += 1;
         // K2b: stable sort by the 30 key bits + 2 sub-list bits (32 = 4 passes of 8)

@@ -25,6 +25,32 @@ static __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const unsigned lo
     hist[(int64_t)threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
 }
 
+// Same histogram from ONE BYTE per item: the scatter of the previous pass wrote the digit every item will have in this
+// pass next to its new position, so passes after the first read n bytes instead of the 8 n bytes of the keys.
+static __global__ void __launch_bounds__(RS_THREADS) k_rs_hist8(const uint8_t* __restrict__ digits, int64_t n, uint32_t* __restrict__ hist /*[256][nb]*/, int64_t nb) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * RS_TILE;                     // RS_TILE is a multiple of 16; digits is 16-byte aligned
+    const int64_t g = base + (int64_t)threadIdx.x * 16;
+    if (g + 16 <= n) {
+        const uint4 v = *reinterpret_cast<const uint4*>(digits + g);
+        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+#pragma unroll
+            for (int b = 0; b < 4; b++) atomicAdd(&h[(w[q] >> (8 * b)) & 255u], 1u);
+    } else {
+        for (int64_t i = g; i < n && i < g + 16; i++) atomicAdd(&h[digits[i]], 1u);
+    }
+    __syncthreads();
+    hist[(int64_t)threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
+}
+static inline size_t dv_radix_hist_words(int64_t n) {                      // uint32 words the sort needs behind `hist`
+    const int64_t nb = (n + RS_TILE - 1) / RS_TILE;
+    return (size_t)(256 * nb + 256) + 4 + (size_t)((n + 15) / 16) * 4;      // histogram matrix + totals | 16-byte aligned digit bytes
+}
+
 // block d scans hist[d][0..nb) in place (exclusive) and adds the base of digit d
 static __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* __restrict__ hist, int64_t nb, uint32_t* __restrict__ totals /*[256]*/, int phase) {
     __shared__ uint32_t warp_tot[32];
@@ -69,7 +95,7 @@ struct RsSmem {
 };
 static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                                unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
-                                                               const uint32_t* __restrict__ hist, int64_t nb) {
+                                                               const uint32_t* __restrict__ hist, int64_t nb, uint8_t* __restrict__ next_digit, int next_shift) {
     extern __shared__ __align__(16) unsigned char rs_raw[];
     RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -145,26 +171,30 @@ static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsig
         const unsigned long long kk = sm.key[i];
         const uint32_t pos = sm.delta[(uint32_t)(kk >> shift) & 255u] + (uint32_t)i;
         okeys[pos] = kk; ovals[pos] = sm.val[i];
+        if (next_digit) next_digit[pos] = (uint8_t)(kk >> next_shift);       // the digit of the NEXT pass, for its histogram
     }
 }
 
 // Sorts n pairs by bits [begin_bit, end_bit) of the key.  keys/vals and tkeys/tvals are ping-pong
 // buffers; returns which pair of buffers holds the result (0 = keys/vals, 1 = tkeys/tvals).
-// hist needs 256 * ceil(n / RS_TILE) + 256 uint32.
+// hist needs dv_radix_hist_words(n) uint32 and 16-byte alignment.
 static inline int dv_radix_sort_pairs(unsigned long long* keys, uint32_t* vals, unsigned long long* tkeys, uint32_t* tvals,
                                       int64_t n, int begin_bit, int end_bit, uint32_t* hist, cudaStream_t st, int64_t* launches) {
     if (n <= 1) return 0;
     cudaFuncSetAttribute(k_rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
     const int64_t nb = (n + RS_TILE - 1) / RS_TILE;
     uint32_t* totals = hist + 256 * nb;
+    uint8_t* digits = reinterpret_cast<uint8_t*>(hist + (((size_t)(256 * nb + 256) + 3) & ~size_t(3)));    // 16-byte aligned (hist is)
     int cur = 0;
     for (int shift = begin_bit; shift < end_bit; shift += 8) {
         unsigned long long* ik = cur ? tkeys : keys; uint32_t* iv = cur ? tvals : vals;
         unsigned long long* ok = cur ? keys : tkeys; uint32_t* ov = cur ? vals : tvals;
-        k_rs_hist<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, n, shift, hist, nb);
+        const bool more = shift + 8 < end_bit;
+        if (shift == begin_bit) k_rs_hist<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, n, shift, hist, nb);
+        else k_rs_hist8<<<(unsigned)nb, RS_THREADS, 0, st>>>(digits, n, hist, nb);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 0);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 1);
-        k_rs_scatter<<<(unsigned)nb, RS_THREADS, sizeof(RsSmem), st>>>(ik, iv, ok, ov, n, shift, hist, nb);
+        k_rs_scatter<<<(unsigned)nb, RS_THREADS, sizeof(RsSmem), st>>>(ik, iv, ok, ov, n, shift, hist, nb, more ? digits : nullptr, shift + 8);
         if (launches) *launches += 4;
         cur ^= 1;
     }
