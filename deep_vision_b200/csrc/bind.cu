@@ -85,16 +85,17 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bind_claims_general, BIND_THREADS, smem));
     if (occ < 1) occ = 1;
     const int grid = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ);
-    // ---- fast kernel (bind6.cuh): bigram table in shared memory, sized from the same bound (load factor <= 1/2)
+    // ---- fast kernel (bind7.cuh): per-session capacity checks happen on the device (sess_fallback)
     const char* force = getenv("DVB_BIND_KERNEL");
-    const bool fast = cap <= B6_CAPB && !(force && !strcmp(force, "general"));
-    const size_t smem6 = 0;                                  // static shared memory
-    int grid6 = 1;
+    const bool fast = !(force && !strcmp(force, "general"));
+    const size_t smem7 = bind7_smem_bytes();
+    int grid7 = 1;
     if (fast) {
-        int occ6 = 1;
-        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_bind_claims, BIND_THREADS, smem6));
-        if (occ6 < 1) occ6 = 1;
-        grid6 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ6);
+        int occ7 = 1;
+        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_claims, BIND_THREADS, smem7));
+        if (occ7 < 1) occ7 = 1;
+        grid7 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ7);
     }
     // ---- workspace
     size_t need = 8192;
@@ -105,7 +106,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     }
     need += dvb_pad((size_t)grid * (size_t)cap * 12);
     if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
-    if (fast) need += dvb_pad((size_t)grid6 * bind6_ws_u64_per_cta() * 8) + dvb_pad(4);
+    if (fast) need += dvb_pad((size_t)grid7 * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
@@ -151,7 +152,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     p.gtable = sc.alloc<unsigned long long>(((size_t)grid * (size_t)cap * 12 + 7) / 8);
     if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
     if (use_global) { p.ghit = sc.alloc<uint32_t>((size_t)grid * hit_bytes / 4); if (!p.ghit) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; } }
-    BindParams p6 = p;
+    BindParams p7 = p;
     if (fast) {
         dvb_lease* l = sc.l;
         if (!l->flag_h) {                                     // overflow flag: pinned + mapped, the kernel writes it in place
@@ -159,15 +160,17 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             DVB_CUDA(ctx, cudaHostGetDevicePointer((void**)&l->flag_d, l->flag_h, 0));
         }
         *(volatile int*)l->flag_h = 0;
-        p6.gtable = sc.alloc<unsigned long long>((size_t)grid6 * bind6_ws_u64_per_cta());
-        if (!p6.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
-        p6.overflow = l->flag_d;
+        p7.gtable = sc.alloc<unsigned long long>((size_t)grid7 * bind7_ws_u64_per_cta());
+        p7.sess_fallback = sc.alloc<uint8_t>((size_t)n_sessions);
+        if (!p7.gtable || !p7.sess_fallback) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        DVB_CUDA(ctx, cudaMemsetAsync(p7.sess_fallback, 0, (size_t)n_sessions, st));
+        p7.overflow = l->flag_d;
     }
     // one launch over sessions [s0, s1): fast kernel unless the call was routed to the general one
     auto launch = [&](bool use_fast, int64_t s0, int64_t s1) -> cudaError_t {
-        BindParams q = use_fast ? p6 : p;
+        BindParams q = use_fast ? p7 : p;
         q.s_begin = s0; q.s_end = s1;
-        if (use_fast) k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid6), BIND_THREADS, smem6, st>>>(q);
+        if (use_fast) k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
         else k_bind_claims_general<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(q);
         ctx->launches += 1;
         return cudaGetLastError();
@@ -231,8 +234,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     };
     DVB_CUDA(ctx, queue_host_out());
     DVB_CUDA(ctx, cudaStreamSynchronize(st));
-    if (fast && *(volatile int*)sc.l->flag_h) {               // a claim group did not fit the fast tables: exact re-run
-        if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
+    if (fast && *(volatile int*)sc.l->flag_h) {               // sessions the cell walk handed back: exact re-run of exactly those
+        p.only_flagged = p7.sess_fallback;
         DVB_CUDA(ctx, launch(false, 0, n_sessions));
         if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, st));
         DVB_CUDA(ctx, queue_host_out());
