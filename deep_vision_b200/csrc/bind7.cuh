@@ -28,7 +28,7 @@
 #define B7_BSHIFT 22                 // 32 - log2(B7_CAPB / 4)
 #define B7_CAPT 1024                 // piece / ASCII token slots (64-bit keys, L2-resident workspace)
 #define B7_TOK_LIMIT 704
-#define B7_TCAP 2560                 // dense token indices per claim group = flag bytes per warp
+#define B7_TCAP 3072                 // dense token indices per claim group = flag bytes per warp
 #define B7_FT_BITS 14                // signature filter in front of the ASCII-token probes
 #define B7_SPILL 0x80000000u
 #define B7_CELL 12

@@ -1,6 +1,11 @@
 """GPU parity (B200): CUDA path through the C-ABI vs the CPU oracle and the golden fixtures."""
+import sys
+from pathlib import Path
+
 import numpy as np
 import pytest
+
+sys.path.insert(0, str(Path(__file__).resolve().parent))
 
 pytestmark = pytest.mark.gpu
 
@@ -64,100 +69,39 @@ def test_a2_synthetic_bit_exact(gpu_ctx, oracle, n_sessions, turns, claims):
     assert np.array_equal(got2["best_fact"], ref["best_fact"])
 
 
-def _adversarial_long_texts():
-    import random
-    rng = random.Random(2024)
-    han = [chr(0x4E00 + rng.randrange(3000)) for _ in range(400)]
-    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
-    def word(n): return "".join(rng.choice("abcdefghijklmnopqrstuvwxyz0123456789_") for _ in range(n))
-    pieces = [lambda: cjk(rng.randint(1, 30)), lambda: cjk(rng.randint(40, 70)), lambda: word(rng.randint(1, 12)),
-              lambda: word(rng.randint(60, 70)), lambda: rng.choice(["，", "。", "\n", " ", "  ", "é", "ß", "😀", "Ω", "…", "Ａ", "ｂ"]),
-              lambda: rng.choice(["İ", "K", "ǅ", "ſ", "ı"]), lambda: cjk(12), lambda: cjk(13), lambda: cjk(24) + word(3), lambda: "A" + cjk(2) + "Z9_"]
-    weights = [30, 2, 14, 1, 30, 1, 4, 4, 4, 4]
-    texts = []
-    for target in [383, 384, 385, 500, 1000, 2030, 2047, 2048, 2049, 2050, 2111, 2112, 2113, 3000, 4096, 4097, 6200, 9000] * 3:
-        t = ""
-        while len(t.encode("utf-8")) < target:
-            t += rng.choices(pieces, weights)[0]()
-        texts.append(t)
-    # exact byte lengths around the tile / chunk boundaries (ASCII filler keeps the byte count exact)
-    for nbytes in (2048, 2048 + 64, 4096, 2048 - 16, 2048 * 2 + 63):
-        t = cjk(300)
-        b = len(t.encode("utf-8"))
-        texts.append(t + " " + "x" * 3 + " " + "y" * (nbytes - b - 5 - 6) + " " + cjk(1) + "ab")
-    texts.append(cjk(2000))                         # one run, far longer than the staged history
-    texts.append((word(5) + " ") * 500)             # ASCII only
-    texts.append(("😀" + cjk(3)) * 300)             # 4-byte characters between short runs
-    return texts, rng, han
+def _bind_vs_oracle(gpu_ctx, oracle, a, check_len_fact=True):
+    from deep_vision_b200 import evidence
+    cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct = a
+    got = evidence.bind_packed(gpu_ctx, *a, want_lens=True)
+    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
+    if check_len_fact:
+        has_claims = np.repeat(np.diff(sco) > 0, np.diff(sfo))
+        assert np.array_equal(got["len_fact"][has_claims], np.minimum(ref["len_fact"], 18)[has_claims])
+    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
+    bad = np.nonzero(got["best_score"].view(np.uint64) != ref["best_score"].view(np.uint64))[0]
+    assert bad.size == 0, [(int(i), got["best_score"][i], ref["best_score"][i]) for i in bad[:8]]
+    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    assert np.array_equal(got["bound"], ref["bound"])
+    return got
 
 
 def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
-    """long facts (the byte-mask scanner of text8.cuh, with hand-backs to text6.cuh): tile/chunk boundaries, long runs,
-    exotic case mappings, long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
-    from deep_vision_b200 import evidence, packing
-    facts, rng, han = _adversarial_long_texts()
-    claims = []
-    for f in facts[::2]:
-        i = rng.randrange(max(1, len(f) - 60))
-        claims.append(f[i:i + rng.randint(5, 60)])
-    claims += ["".join(rng.choice(han) for _ in range(20)) for _ in range(6)]
-    claims = claims[:32]                                   # one claim group
-    facts = facts + ["。".join(claims), " ".join(claims) * 2]  # > 600 distinct hit slots in one fact (hit-list overflow path)
-    n_sess = 3
-    cu, co = packing.pack_texts(claims * n_sess)
-    fu, fo = packing.pack_texts(facts * n_sess)
-    sco = np.arange(n_sess + 1, dtype=np.int64) * len(claims)
-    sfo = np.arange(n_sess + 1, dtype=np.int64) * len(facts)
-    nf, nc = len(facts) * n_sess, len(claims) * n_sess
-    fq = np.linspace(0.05, 0.95, nf); fd = (np.arange(nf) % 4).astype(np.int32); fh = (np.arange(nf) % 3 == 0).astype(np.uint8)
-    cp = (np.arange(nc) % 5 - 1).astype(np.int32); ct = np.full(nc, 0.46, np.float64)
-    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
-    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
-    assert np.array_equal(got["len_fact"], np.minimum(ref["len_fact"], 18))
-    assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
-    assert np.array_equal(got["best_fact"], ref["best_fact"])
-    assert np.array_equal(got["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
-    assert np.array_equal(got["bound"], ref["bound"])
+    """long facts (tests/bind_cases.py): cell/step boundaries, long runs, exotic case mappings (handed back to the general
+    kernel), long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
+    import bind_cases as bc
+    _bind_vs_oracle(gpu_ctx, oracle, bc.long_facts(3))
 
 
 def test_a2_every_pair_of_long_facts(gpu_ctx, oracle):
-    """one fact per session, so best_score exposes the overlap of EVERY (claim, fact) pair: piece boundaries
-    (12/13/14/24/25/36/37-character runs), ASCII tokens across tiles, every text alignment, 64/65-character ASCII tokens,
-    U+212A / U+0130 (serial restart) and E2 80 xx punctuation — bit-exact against the oracle."""
-    from deep_vision_b200 import evidence, packing
-    facts, rng, han = _adversarial_long_texts()
-    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
-    for run in (11, 12, 13, 14, 23, 24, 25, 26, 35, 36, 37, 38, 48, 49, 50, 96, 97):
-        for pre in range(0, 9):                              # shifts the run across the 8-byte lane units
-            facts.append("x" * pre + "，" + cjk(run) + "。" + cjk(40) + " tail_token9 " + cjk(run) + "，ab" + cjk(30) + "c" + cjk(12) + "z" * 63)
-    facts.append(cjk(70) + " " + "q" * 64 + " " + cjk(70) + " " + "r" * 65 + cjk(5))       # 64 fits, 65 hands back
-    facts.append(cjk(100) + "K" + cjk(100))                # U+212A
-    facts.append(cjk(100) + "İ" + cjk(100))                # U+0130
-    facts.append("“" + cjk(90) + "”——" + cjk(90) + "…")    # E2 80 xx punctuation must NOT hand back
-    facts.append("ab " * 100)                               # no bigram at all: distinct count by the exact path
-    facts.append((cjk(2) + "，") * 80)                      # 2-character runs only
-    facts.append((cjk(1) + " ") * 150)                      # single characters: no token
-    facts.append(cjk(7) * 40)                               # few distinct bigrams repeated
-    claims = []
-    for f in facts[::3]:
-        i = rng.randrange(max(1, len(f) - 60))
-        claims.append(f[i:i + rng.randint(5, 60)])
-    claims = claims[-26:] + [cjk(12), cjk(13), "tail_token9 ab c", "q" * 64, "r" * 65, "k i"]
-    assert len(claims) == 32
-    n_sess = len(facts)
-    cu, co = packing.pack_texts(claims * n_sess)
-    fu, fo = packing.pack_texts(facts)
-    sco = np.arange(n_sess + 1, dtype=np.int64) * len(claims)
-    sfo = np.arange(n_sess + 1, dtype=np.int64)
-    nf, nc = n_sess, len(claims) * n_sess
-    fq = np.full(nf, 0.5); fd = np.zeros(nf, np.int32); fh = np.zeros(nf, np.uint8)
-    cp = np.full(nc, -1, np.int32); ct = np.full(nc, 0.46, np.float64)
-    got = evidence.bind_packed(gpu_ctx, cu, co, fu, fo, sco, sfo, fq, fd, fh, cp, ct, want_lens=True)
-    ref = oracle.bind_claims(None, None, sco, sfo, fq, fd, fh, cp, ct, packed=(cu, co, fu, fo))
-    assert np.array_equal(got["len_fact"], np.minimum(ref["len_fact"], 18))
-    bad = np.nonzero(got["best_score"].view(np.uint64) != ref["best_score"].view(np.uint64))[0]
-    assert bad.size == 0, [(int(i) // 32, int(i) % 32, got["best_score"][i], ref["best_score"][i]) for i in bad[:8]]
-    assert np.array_equal(got["best_fact"], ref["best_fact"])
+    """one fact per session, so best_score exposes the overlap of EVERY (claim, fact) pair (tests/bind_cases.py)."""
+    import bind_cases as bc
+    _bind_vs_oracle(gpu_ctx, oracle, bc.every_pair())
+
+
+def test_a2_short_facts_and_mixed_scripts(gpu_ctx, oracle):
+    import bind_cases as bc
+    _bind_vs_oracle(gpu_ctx, oracle, bc.mixed_real_text())
+    _bind_vs_oracle(gpu_ctx, oracle, bc.big_claim_groups())
 
 
 def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
