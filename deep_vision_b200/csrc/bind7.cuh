@@ -245,6 +245,22 @@ __device__ __forceinline__ uint32_t b7_code3(const B7Tok& t, int32_t p) {      /
     const uint32_t code = (((b0 & 0x0Fu) << 12) | ((b1 & 0x3Fu) << 6) | (b2 & 0x3Fu)) - 0x4E00u;
     return code < 20992u ? code + 1u : 0u;
 }
+// word at offset o (4-aligned, o < total) with the bytes at and beyond `total` read as spaces
+__device__ __forceinline__ uint32_t b7_ldw_tail(const B7Tok& t, int32_t o) {
+    uint32_t w = *reinterpret_cast<const uint32_t*>(t.base + o);
+    const int hi = t.total - o;
+    if (hi < 4) { const uint32_t km = (1u << (8 * hi)) - 1u; w = (w & km) | (0x20202020u & ~km); }
+    return w;
+}
+
+// ASCII tokens are keyed by two 32-bit multiplicative hashes over the case-folded bytes (internal to this kernel: claims
+// and facts of a launch use the same function; the general kernel has its own tables and keys)
+#define B7_AH1 0x811C9DC5u
+#define B7_AH2 0x2F0B4A37u
+__device__ __forceinline__ uint64_t b7_ascii_key(uint32_t h1, uint32_t h2, uint32_t len) {
+    h2 = (h2 ^ len) * 0xC2B2AE35u;
+    return (1ULL << 62) | ((((uint64_t)h1 << 32) | h2) >> 2);
+}
 
 // Lanes [0, cnt) own one queued cell each: every ASCII token ([a-z0-9_]{2,} after lower-casing) that STARTS in the cell
 // is keyed by walking its bytes; a 0xC4 byte (lead of U+0130) hands the session back.
@@ -265,22 +281,23 @@ __device__ void b7_ascii_round(B7Tok& t, int cnt) {
         const bool has = starts != 0u;
         const int j = __ffs(starts) - 1;
         starts &= starts - 1u;
-        uint64_t mm = 0; uint32_t len = 0, sp = 0, sl = 0;
+        uint32_t h1 = B7_AH1, h2 = B7_AH2, len = 0;
         if (has) {
-            const int32_t p0 = o + j;
+            const uint8_t* bp = t.base + o + j;
+            const int32_t room = t.total - (o + j);
             for (;;) {
-                const int32_t p = p0 + (int32_t)len;
-                if (p >= t.total) break;
-                const uint32_t b = t.base[p];
+                if ((int32_t)len >= room) break;
+                const uint32_t b = bp[len];
                 const uint32_t code = b < 0x80u ? (uint32_t)sh.lut[b] : 0u;
                 if (!code) break;
-                mm += (uint64_t)code * dv_kpos(len, sh.ktab);
-                sp = sl; sl = DV_SYM_ASCII | code; len++;
+                h1 = (h1 ^ code) * 0x01000193u;
+                h2 = (h2 + code) * 0x9E3779B1u;
+                len++;
             }
         }
         const bool tk = has && len >= 2u;
-        const uint64_t key = dv_token_key(mm, len, false);
-        const uint32_t sig = dv_token_sig(sp, sl, len);
+        const uint64_t key = b7_ascii_key(h1, h2, len);
+        const uint32_t sig = (h1 ^ (h2 >> 7)) * 0x85EBCA6Bu;
         if (CLAIM) b7_token_insert(t, tk, key, sig);
         else b7_token_probe(t, tk && b7_ft_pass(sh, sig), key);
     }
@@ -288,7 +305,7 @@ __device__ void b7_ascii_round(B7Tok& t, int cnt) {
 
 // Lanes [0, cnt) own one queued piece end each: entry = byte offset of the last character << 4 | (length - 1).
 // The end is verified (the next character is not an adjacent CJK character unless the piece is 12 long), the piece is
-// keyed by walking back over its characters.
+// keyed by walking back over its characters (all CJK by construction of the position counter).
 template <bool CLAIM>
 __device__ void b7_piece_round(B7Tok& t, int cnt) {
     B7Shared& sh = *t.sh;
@@ -300,10 +317,12 @@ __device__ void b7_piece_round(B7Tok& t, int cnt) {
     if (ok && L < 12u && b7_code3(t, p + 3) != 0u) ok = false;
     uint64_t mm = 0; uint32_t sp = 0, sl = 0;
     if (ok) {
+        const uint8_t* bp = t.base + p - 3 * (int32_t)(L - 1u);
         for (uint32_t d = 0; d < L; d++) {
-            const uint32_t s = b7_code3(t, p - 3 * (int32_t)(L - 1u - d));
-            mm += (uint64_t)(s & 0x7FFFu) * sh.ktab[d];
-            sp = sl; sl = s;
+            const uint32_t b0 = bp[0], b1 = bp[1], b2 = bp[2];
+            const uint32_t s = ((((b0 & 0x0Fu) << 12) | ((b1 & 0x3Fu) << 6) | (b2 & 0x3Fu)) - 0x4E00u) + 1u;
+            mm += (uint64_t)s * sh.ktab[d];
+            sp = sl; sl = s; bp += 3;
         }
     }
     const uint64_t key = dv_token_key(mm, L, true);
@@ -340,6 +359,21 @@ __device__ __forceinline__ void b7_flush_queues(B7Tok& t, bool all) {
 }
 
 // ---------------------------------------------------------------- the cell walk
+// Leads of 3-byte characters are >= 3 bytes apart, so each of the four 3-byte GROUPS of a cell (bytes 3i..3i+2) holds at
+// most one: slot i = group i, lead offset inside the group g_i in {0, 1, 2}; no search loop, constant-shift windows.
+__device__ __forceinline__ void b7_load_cell(const B7Tok& t, int32_t o, uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& w3) {
+    if (o + 16 <= t.total) {
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(t.base + o);
+        w0 = wp[0]; w1 = wp[1]; w2 = wp[2]; w3 = wp[3];
+    } else {
+        w0 = o < t.total ? b7_ldw_tail(t, o) : 0x20202020u;
+        w1 = o + 4 < t.total ? b7_ldw_tail(t, o + 4) : 0x20202020u;
+        w2 = o + 8 < t.total ? b7_ldw_tail(t, o + 8) : 0x20202020u;
+        w3 = o + 12 < t.total ? b7_ldw_tail(t, o + 12) : 0x20202020u;
+    }
+}
+__device__ __forceinline__ uint32_t b7_gather4(uint32_t m) { return (((m >> 7) * 0x00204081u) >> 21) & 0xFu; }   // bits 7,15,23,31 -> 0..3
+
 template <bool CLAIM>
 __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
     B7Shared& sh = *t.sh;
@@ -351,75 +385,66 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
     t.aqn = 0; t.pqn = 0;
     if (n <= 0) return;
     const int nsteps = (t.total + B7_STEP - 1) / B7_STEP;
-    uint32_t carry_pk = 15u << 16;                 // previous step's last lead: (byte offset in its cell) << 16 | symbol
+    uint32_t carry_pk = 0;                         // previous step's last group: symbol << 2 | g, 0 = no CJK character there
     int carryP = 0;                                // position in the run (mod 12) of the previous step's last character
     uint32_t n0, n1, n2, n3;
-    {
-        const int32_t o = lane * B7_CELL;
-        n0 = b7_ldw(t, o); n1 = b7_ldw(t, o + 4); n2 = b7_ldw(t, o + 8); n3 = b7_ldw(t, o + 12);
-    }
+    b7_load_cell(t, lane * B7_CELL, n0, n1, n2, n3);
+    if (t.a && lane == 0) { const uint32_t km = (1u << (8 * t.a)) - 1u; n0 = (n0 & ~km) | (0x20202020u & km); }
+    const uint4* tab4 = reinterpret_cast<const uint4*>(sh.tab);
+    const uint2* tix2 = reinterpret_cast<const uint2*>(sh.tix);
     for (int s = 0; s < nsteps; s++) {
         const int32_t o = s * B7_STEP + lane * B7_CELL;
         const uint32_t w0 = n0, w1 = n1, w2 = n2, w3 = n3;
-        if (s + 1 < nsteps) {
-            const int32_t on = o + B7_STEP;
-            if (on + 16 <= t.total) {             // interior cell: plain loads (on >= 384 > a)
-                const uint32_t* wp = reinterpret_cast<const uint32_t*>(t.base + on);
-                n0 = wp[0]; n1 = wp[1]; n2 = wp[2]; n3 = wp[3];
-            } else { n0 = b7_ldw(t, on); n1 = b7_ldw(t, on + 4); n2 = b7_ldw(t, on + 8); n3 = b7_ldw(t, on + 12); }
-        }
-        // ---- cell masks
-        uint32_t mm = b7_lead4(w0) | (b7_lead4(w1) << 4) | (b7_lead4(w2) << 8);
-        const int K = __popc(mm);
-        const uint32_t asc = ~(w0 & w1 & w2) & 0x80808080u;                              // a byte < 0x80
-        const uint32_t ld2 = ((w0 & (w0 << 1) & ~(w0 << 2)) | (w1 & (w1 << 1) & ~(w1 << 2)) | (w2 & (w2 << 1) & ~(w2 << 2))) & 0x80808080u;   // a byte C0..DF
-        // ---- phase A: the cell's leads
-        uint32_t q[4], sy[4], nb[4]; bool has[4];
-        bool bad = K > 4;
+        if (s + 1 < nsteps) b7_load_cell(t, o + B7_STEP, n0, n1, n2, n3);
+        // ---- cell masks: leads >= 0xE0 (12 bits), any ASCII byte or 2-byte lead
+        const uint32_t u0 = w0 & (w0 << 1), u1 = w1 & (w1 << 1), u2 = w2 & (w2 << 1);
+        const uint32_t mm = b7_gather4(u0 & (w0 << 2) & 0x80808080u) | (b7_gather4(u1 & (w1 << 2) & 0x80808080u) << 4) |
+                            (b7_gather4(u2 & (w2 << 2) & 0x80808080u) << 8);
+        const uint32_t rare = (~(w0 & w1 & w2) | (u0 & ~(w0 << 2)) | (u1 & ~(w1 << 2)) | (u2 & ~(w2 << 2))) & 0x80808080u;
+        bool bad = (((mm & (mm >> 1)) & 0x6DBu) | ((mm & (mm >> 2)) & 0x249u)) != 0u;      // two leads in one group: malformed
+        // ---- slots: windows, decode
+        const uint32_t v1l = __funnelshift_r(w0, w1, 24), v1h = __funnelshift_r(w1, w2, 24);
+        const uint32_t v2l = __funnelshift_r(w1, w2, 16), v2h = __funnelshift_r(w2, w3, 16);
+        const uint32_t v3l = __funnelshift_r(w2, w3, 8), v3h = w3 >> 8;
+        uint32_t g[4], x[4], sy[4];
+        g[0] = (mm >> 1) & 3u; g[1] = (mm >> 4) & 3u; g[2] = (mm >> 7) & 3u; g[3] = (mm >> 10) & 3u;     // bits {1,2,4} >> 1
+        x[0] = __funnelshift_r(w0, w1, g[0] * 8u); x[1] = __funnelshift_r(v1l, v1h, g[1] * 8u);
+        x[2] = __funnelshift_r(v2l, v2h, g[2] * 8u); x[3] = __funnelshift_r(v3l, v3h, g[3] * 8u);
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            has[i] = mm != 0u;
-            q[i] = (uint32_t)(__ffs(mm) - 1) & 15u;
-            mm &= mm - 1u;
-            const uint32_t x = b7_fetch(w0, w1, w2, w3, q[i]);
-            const uint32_t cp = ((x & 0x0Fu) << 12) | ((x >> 2) & 0xFC0u) | ((x >> 16) & 0x3Fu);
-            const uint32_t code = cp - 0x4E00u;
-            const bool isE = (x & 0xF0u) == 0xE0u, cont = (x & 0x00C0C000u) == 0x00808000u;
-            sy[i] = (has[i] && isE && cont && code < 20992u) ? code + 1u : 0u;
-            bad |= has[i] && isE && (!cont || cp == 0x212Au);                            // malformed, or U+212A (lower-cases to 'k')
-            nb[i] = x >> 24;
+            const uint32_t xi = x[i];
+            const uint32_t code = (((xi & 0x0Fu) << 12) | ((xi >> 2) & 0xFC0u) | ((xi >> 16) & 0x3Fu)) - 0x4E00u;
+            sy[i] = ((xi & 0x00C0C0F0u) == 0x008080E0u && code < 20992u) ? code + 1u : 0u;
+            bad |= (xi & 0x00FFFFFFu) == 0x00AA84E2u;                                    // U+212A lower-cases to 'k'
         }
         if (bad) t.exotic = true;
-        bool ad[4];
-        const int L = K < 4 ? K - 1 : 3;
-        const uint32_t qL = L <= 0 ? q[0] : (L == 1 ? q[1] : (L == 2 ? q[2] : q[3]));
-        const uint32_t sL = L <= 0 ? sy[0] : (L == 1 ? sy[1] : (L == 2 ? sy[2] : sy[3]));
-        const uint32_t pk = K ? ((qL << 16) | sL) : (15u << 16);
+        // ---- adjacency, position of the lane's first character in its run
+        const uint32_t pk = sy[3] ? ((sy[3] << 2) | g[3]) : 0u;
         uint32_t pv = __shfl_up_sync(B7_FULL, pk, 1);
         if (lane == 0) pv = carry_pk;
         carry_pk = __shfl_sync(B7_FULL, pk, 31);
-        ad[0] = sy[0] != 0u && (pv & 0xFFFFu) != 0u && (pv >> 16) == q[0] + 9u;
+        bool ad[4];
+        ad[0] = sy[0] != 0u && pv != 0u && (pv & 3u) == g[0];
 #pragma unroll
-        for (int i = 1; i < 4; i++) ad[i] = sy[i] != 0u && sy[i - 1] != 0u && q[i] == q[i - 1] + 3u;
+        for (int i = 1; i < 4; i++) ad[i] = sy[i] != 0u && sy[i - 1] != 0u && g[i] == g[i - 1];
         const bool transparent = ad[0] && ad[1] && ad[2] && ad[3];
-        int ploc = 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++) if (has[i]) ploc = ad[i] ? ploc + 1 : 0;
+        const int ploc = ad[3] ? (ad[2] ? (ad[1] ? (ad[0] ? 4 : 3) : 2) : 1) : 0;
         const uint32_t T = __ballot_sync(B7_FULL, transparent);
         const uint32_t nt = ~T & lt;
         const int jn = nt ? 31 - __clz((int)nt) : 0;
         const int pj = __shfl_sync(B7_FULL, ploc, jn);
         int p = nt ? pj + 4 * (lane - 1 - jn) : carryP + 4 * lane;
         p = (int)((uint32_t)p % 12u);
-        // ---- phase B: positions, bigrams
-        uint32_t candm = 0, candp = 0;
-        uint32_t prev = pv & 0xFFFFu;
+        // ---- slots: positions, bigrams
+        uint32_t candm = 0, candp = 0, lfp = 0, pp = 0;
+        uint32_t prev = pv >> 2;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            if (has[i]) p = ad[i] ? (p == 11 ? 0 : p + 1) : 0;
-            const bool v = has[i] && ad[i] && p != 0;
+            p = ad[i] ? p + 1 : 0;
+            if (p == 12) p = 0;
+            const bool v = ad[i] && p != 0;
             const uint32_t id = (prev << 15) | sy[i];
-            bool pend = has[i] && sy[i] != 0u && ad[i] && p >= 2 && (p == 11 || (nb[i] - 0xE5u) > 4u);   // a piece of >= 3 may end here
+            pp |= (uint32_t)p << (4 * i);
             if (CLAIM) b7_bigram_insert(t, v, id);
             else {
                 if (!t.cert) {                    // min(len(B), 18): >= 18 distinct valid bigrams in one slot round certify it
@@ -427,44 +452,54 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
                     const uint32_t nd = (uint32_t)__popc(__ballot_sync(B7_FULL, v && (__ffs(ma) - 1 == lane)));
                     if (nd >= 18u) t.cert = true;
                 }
-                uint32_t lf = 0; bool hit = false;
-                if (v) {
-                    uint32_t b = (id * 0x9E3779B1u) >> B7_BSHIFT;
+                uint32_t b = (id * 0x9E3779B1u) >> B7_BSHIFT;
+                const uint4 e = tab4[b];
+                const uint2 tq = tix2[b];
+                const bool m1 = e.y == id, m2 = e.z == id, m3 = (e.w & 0x7FFFFFFFu) == id;
+                const uint32_t wsel = (m2 || m3) ? tq.y : tq.x;
+                uint32_t t16 = (m1 || m3) ? (wsel >> 16) : (wsel & 0xFFFFu);
+                bool hit = v && (e.x == id || m1 || m2 || m3);
+                if (v && !hit && (e.w & B7_SPILL)) {                                     // rare: the chain continues in the next bucket(s)
                     for (;;) {
-                        const uint4 e = *reinterpret_cast<const uint4*>(&sh.tab[b * 4u]);
-                        const uint32_t e3 = e.w & 0x7FFFFFFFu;
-                        const int j = e.x == id ? 0 : (e.y == id ? 1 : (e.z == id ? 2 : (e3 == id ? 3 : -1)));
-                        if (j >= 0) {
-                            const uint32_t tv = sh.tix[b * 4u + (uint32_t)j];
-                            t.H[(tv & 0xFFFu) - 1u] = 1;
-                            lf = tv >> 12; hit = true;
-                            break;
-                        }
-                        if (!(e.w & B7_SPILL)) break;
                         b = (b + 1u) & B7_NBM;
+                        const uint4 f = tab4[b];
+                        const int j = f.x == id ? 0 : (f.y == id ? 1 : (f.z == id ? 2 : ((f.w & 0x7FFFFFFFu) == id ? 3 : -1)));
+                        if (j >= 0) { t16 = sh.tix[b * 4u + (uint32_t)j]; hit = true; break; }
+                        if (!(f.w & B7_SPILL)) break;
                     }
                 }
-                pend = pend && hit && (lf == 15u || lf == (uint32_t)p - 1u);             // flag = length - 2 = p - 1
+                if (hit) { t.H[(t16 & 0xFFFu) - 1u] = 1; lfp |= (t16 >> 12) << (4 * i); }
             }
-            if (pend) { candm |= 1u << i; candp |= (uint32_t)p << (4 * i); }
-            if (has[i]) prev = sy[i];
+            prev = sy[i];
         }
         carryP = __shfl_sync(B7_FULL, p, 31);
-        // ---- queue the rare work
+        // ---- piece ends: claims queue every end of a piece of >= 3, facts only ends whose last bigram hit an entry that
+        //      ends a claim piece of the same length
+        if (CLAIM || lfp != 0u) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t pi = (pp >> (4 * i)) & 15u;
+                const uint32_t lf = (lfp >> (4 * i)) & 15u;
+                const bool ends = pi == 11u || (i < 3 ? !ad[i < 3 ? i + 1 : 3] : ((x[3] >> 24) - 0xE5u) > 4u);
+                const bool want = CLAIM ? true : (lf == 15u || lf == pi - 1u);          // flag = length - 2 = position - 1
+                if (ad[i] && pi >= 2u && ends && want) { candm |= 1u << i; candp |= pi << (4 * i); }
+            }
+        }
         while (__any_sync(B7_FULL, candm != 0u)) {
             const bool c = candm != 0u;
             const int i = __ffs(candm) - 1;
             candm &= candm - 1u;
             const uint32_t bal = __ballot_sync(B7_FULL, c);
             if (c) {
-                const uint32_t qi = i == 0 ? q[0] : (i == 1 ? q[1] : (i == 2 ? q[2] : q[3]));
-                t.scr->pq[t.pqn + __popc(bal & lt)] = ((uint32_t)(o + (int32_t)qi) << 4) | ((candp >> (4 * i)) & 15u);
+                const uint32_t gi = i == 0 ? g[0] : (i == 1 ? g[1] : (i == 2 ? g[2] : g[3]));
+                t.scr->pq[t.pqn + __popc(bal & lt)] = ((uint32_t)(o + 3 * i + (int32_t)gi) << 4) | ((candp >> (4 * i)) & 15u);
             }
             t.pqn += __popc(bal);
             if (t.pqn >= 32) b7_flush_queues<CLAIM>(t, false);
         }
+        // ---- cells holding ASCII bytes or 2-byte leads are looked at 32 at a time
         {
-            const bool need = (asc | ld2) != 0u && o < t.total;
+            const bool need = rare != 0u && o < t.total;
             const uint32_t bal = __ballot_sync(B7_FULL, need);
             if (bal) {
                 if (need) t.scr->aq[t.aqn + __popc(bal & lt)] = (uint32_t)o;
