@@ -37,7 +37,7 @@
 
 struct __align__(16) B7Scratch {     // per warp
     union {
-        struct { uint32_t aq[64]; uint32_t pq[64]; };                                   // cell queue, piece-end queue
+        struct { uint32_t aq[64]; uint32_t pq[160]; };                                  // cell queue, piece-end queue (< 32 + 4 x 32 per step)
         struct { unsigned long long queue[32]; uint32_t qsig[32]; uint32_t qkind; uint32_t pad_;
                  unsigned long long wset[BIND_WSET]; };                                 // exact serial count (text.cuh)
     };
@@ -265,10 +265,10 @@ __device__ __forceinline__ uint64_t b7_ascii_key(uint32_t h1, uint32_t h2, uint3
 // Lanes [0, cnt) own one queued cell each: every ASCII token ([a-z0-9_]{2,} after lower-casing) that STARTS in the cell
 // is keyed by walking its bytes; a 0xC4 byte (lead of U+0130) hands the session back.
 template <bool CLAIM>
-__device__ void b7_ascii_round(B7Tok& t, int cnt) {
+__device__ void b7_ascii_round(B7Tok& t, int head, int cnt) {
     B7Shared& sh = *t.sh;
     const bool act = t.lane < cnt;
-    const int32_t o = act ? (int32_t)t.scr->aq[t.lane] : 0;
+    const int32_t o = act ? (int32_t)t.scr->aq[head + t.lane] : 0;
     uint32_t starts = 0;
     if (act) {
         const uint32_t wp = b7_ldw(t, o - 4), w0 = b7_ldw(t, o), w1 = b7_ldw(t, o + 4), w2 = b7_ldw(t, o + 8);
@@ -307,10 +307,10 @@ __device__ void b7_ascii_round(B7Tok& t, int cnt) {
 // The end is verified (the next character is not an adjacent CJK character unless the piece is 12 long), the piece is
 // keyed by walking back over its characters (all CJK by construction of the position counter).
 template <bool CLAIM>
-__device__ void b7_piece_round(B7Tok& t, int cnt) {
+__device__ void b7_piece_round(B7Tok& t, int head, int cnt) {
     B7Shared& sh = *t.sh;
     const bool act = t.lane < cnt;
-    const uint32_t e = act ? t.scr->pq[t.lane] : 0u;
+    const uint32_t e = act ? t.scr->pq[head + t.lane] : 0u;
     const int32_t p = (int32_t)(e >> 4);
     const uint32_t L = (e & 15u) + 1u;
     bool ok = act;
@@ -335,25 +335,32 @@ __device__ void b7_piece_round(B7Tok& t, int cnt) {
 
 template <bool CLAIM>
 __device__ __forceinline__ void b7_flush_queues(B7Tok& t, bool all) {
-    while (t.aqn >= 32 || (all && t.aqn > 0)) {
+    int head = 0;
+    __syncwarp();
+    while (t.aqn - head >= 32 || (all && t.aqn > head)) {
+        const int n = t.aqn - head < 32 ? t.aqn - head : 32;
+        b7_ascii_round<CLAIM>(t, head, n);
+        head += n;
+    }
+    if (head) {
         __syncwarp();
-        const int n = t.aqn < 32 ? t.aqn : 32;
-        b7_ascii_round<CLAIM>(t, n);
-        __syncwarp();
-        const uint32_t rest = (t.lane + 32 < t.aqn) ? t.scr->aq[t.lane + 32] : 0u;
+        const uint32_t rest = (t.lane < t.aqn - head) ? t.scr->aq[head + t.lane] : 0u;
         __syncwarp();
         t.scr->aq[t.lane] = rest;
-        t.aqn -= n;
+        t.aqn -= head;
     }
-    while (t.pqn >= 32 || (all && t.pqn > 0)) {
+    head = 0;
+    while (t.pqn - head >= 32 || (all && t.pqn > head)) {
+        const int n = t.pqn - head < 32 ? t.pqn - head : 32;
+        b7_piece_round<CLAIM>(t, head, n);
+        head += n;
+    }
+    if (head) {
         __syncwarp();
-        const int n = t.pqn < 32 ? t.pqn : 32;
-        b7_piece_round<CLAIM>(t, n);
-        __syncwarp();
-        const uint32_t rest = (t.lane + 32 < t.pqn) ? t.scr->pq[t.lane + 32] : 0u;
+        const uint32_t rest = (t.lane < t.pqn - head) ? t.scr->pq[head + t.lane] : 0u;
         __syncwarp();
         t.scr->pq[t.lane] = rest;
-        t.pqn -= n;
+        t.pqn -= head;
     }
     __syncwarp();
 }
@@ -495,7 +502,6 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
                 t.scr->pq[t.pqn + __popc(bal & lt)] = ((uint32_t)(o + 3 * i + (int32_t)gi) << 4) | ((candp >> (4 * i)) & 15u);
             }
             t.pqn += __popc(bal);
-            if (t.pqn >= 32) b7_flush_queues<CLAIM>(t, false);
         }
         // ---- cells holding ASCII bytes or 2-byte leads are looked at 32 at a time
         {
@@ -504,11 +510,11 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             if (bal) {
                 if (need) t.scr->aq[t.aqn + __popc(bal & lt)] = (uint32_t)o;
                 t.aqn += __popc(bal);
-                if (t.aqn >= 32) b7_flush_queues<CLAIM>(t, false);
             }
         }
+        // the one call site of the deferred rounds: whenever a queue holds a full round, and at the end of the text
+        if (t.aqn >= 32 || t.pqn >= 32 || s + 1 == nsteps) b7_flush_queues<CLAIM>(t, s + 1 == nsteps);
     }
-    b7_flush_queues<CLAIM>(t, true);
 }
 
 // exact min(len(B), 18) of a fact the walk could not certify (short or repetitive facts): the serial tokenizer of
