@@ -137,7 +137,7 @@ __device__ __forceinline__ void b7_claim_slot(B7Tok& t, bool act, uint32_t slot,
     bool isnew = false; uint32_t tt = 0;
     if (act && !created) {
         uint32_t v;
-        do { v = *(volatile uint16_t*)&sh.tix[slot]; } while ((v & 0xFFFu) == 0u);   // the creator (another warp) is a few instructions away
+        for (;;) { v = *(volatile uint16_t*)&sh.tix[slot]; if ((v & 0xFFFu) != 0u) break; DV_SPIN_PAUSE(); }   // the creator (another warp) is a few instructions away
         tt = (v & 0xFFFu) - 1u;
         if ((tt < t.rb || tt >= t.re) && !t.H[tt]) { t.H[tt] = 1; isnew = true; }
     }

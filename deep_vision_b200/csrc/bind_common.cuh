@@ -11,6 +11,14 @@
 #define BIND_FT_BITS 13         // token filter: 2^13 bits = 1 KB
 #define BIND_QCAP 64
 
+// a lane that polls memory another lane (possibly of its own warp) is about to write: the GPU schedules diverged lanes
+// independently; the CPU emulator of the tests runs lanes as cooperative fibers and has to be told to switch
+#ifdef DV_EMU
+#define DV_SPIN_PAUSE() emu::yield()
+#else
+#define DV_SPIN_PAUSE() ((void)0)
+#endif
+
 struct BindParams {
     const uint8_t* claim_utf8; const int64_t* claim_off; const uint8_t* fact_utf8; const int64_t* fact_off;
     const int64_t* sess_claim_off; const int64_t* sess_fact_off; int64_t s_begin, s_end;   // session range of this launch
