@@ -31,6 +31,7 @@ _SIGS = {
     "dvb_symbolize": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp]),
     "dvb_chunk_scores": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, C.c_int32, _vp, C.c_int32, _vp]),
     "dvb_topk": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),
+    "dvb_topk_static": (C.c_int32, [_vp, _vp, _vp, _vp, C.c_int64, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),
     "dvb_chunk_build": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, C.c_int32, _vp] + [_vp] * 7),
     "dvb_question_keys": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp, C.c_int32,
                                       _vp, _vp, _vp, _vp, _vp, C.c_int64]),

@@ -27,6 +27,7 @@ extern "C" int32_t dvb_create(int32_t device, dvb_ctx** out) {
             dvb_destroy(c); return DVB_E_CUDA;
         }
     }
+    if (dv_topk_static_setup(device, nullptr) != cudaSuccess) { cudaGetLastError(); dvb_destroy(c); return DVB_E_CUDA; }   // set-up of dvb_topk_static
     *out = c;
     return DVB_OK;
 }

@@ -332,6 +332,66 @@ extern "C" int32_t dvb_topk(dvb_ctx* ctx, int32_t mem, const int32_t* score, con
     return io.finish(ctx);
 }
 
+// ------------------------------------------------------------------ dvb_topk_static: the same two kernels, no allocation
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, serving loops, harnesses that forbid it).  The partial lists live in ONE file-scope device array
+// that every GPU loading the library holds until exit.  Host code may not pass the array's name to a kernel (it is a
+// host-side stand-in, not a device address): the address is resolved once per device with cudaGetSymbolAddress while
+// that device is current (dv_topk_static_setup), and only that pointer reaches the kernels.
+static __device__ __align__(256) unsigned char g_topk_static_scratch[DVB_TOPK_STATIC_SCRATCH_BYTES];
+#define DV_TOPK_STATIC_MAX_DEVICES 64
+static std::mutex g_topk_static_mu;
+static unsigned char* g_topk_static_ptr[DV_TOPK_STATIC_MAX_DEVICES] = { nullptr };
+
+// `device` must be current.  Called from dvb_create; the entry point repeats it if a ctx of that device was never created.
+cudaError_t dv_topk_static_setup(int device, unsigned char** out) {
+    if (device < 0 || device >= DV_TOPK_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> g(g_topk_static_mu);
+    if (!g_topk_static_ptr[device]) {
+        unsigned char* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_topk_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_topk_static_ptr[device] = ptr;
+    }
+    if (out) *out = g_topk_static_ptr[device];
+    return cudaSuccess;
+}
+
+extern "C" int32_t dvb_topk_static(dvb_ctx* ctx, void* stream, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq,
+                                    int64_t index_base, int32_t k, int64_t* d_out_idx, int32_t* d_out_score, int32_t* d_out_n) {
+    if (!ctx || n < 0 || nq < 0 || k < 1 || k > 32 || !d_out_idx || !d_out_score || !d_out_n || (n > 0 && !d_score)) {
+        dvb_set_err(ctx, "dvb_topk_static: invalid argument (1 <= k <= 32)%s%s"); return DVB_E_INVALID; }
+    if (nq == 0) return DVB_OK;
+    // one partial entry = 4 B score + 8 B index; the split count shrinks to what the array holds, a single split must fit
+    const int64_t entry_cap = (int64_t)DVB_TOPK_STATIC_SCRATCH_BYTES / 12;
+    if ((int64_t)nq * k > entry_cap) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "nq * k = %lld partial entries exceed the static scratch (%lld entries of 12 bytes, %d bytes)",
+                 (long long)nq * k, (long long)entry_cap, (int)DVB_TOPK_STATIC_SCRATCH_BYTES);
+        dvb_set_err(ctx, "dvb_topk_static: %s%s", msg); return DVB_E_CAPACITY;
+    }
+    int dev = -1;
+    DVB_CUDA(ctx, cudaGetDevice(&dev));
+    if (dev != ctx->device) DVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char* scratch = nullptr;
+    DVB_CUDA(ctx, dv_topk_static_setup(ctx->device, &scratch));
+    int64_t n_split = std::max<int64_t>(1, std::min<int64_t>((n + 8191) / 8192, std::max<int64_t>(1, (int64_t)ctx->num_sm * 4 / std::max(1, nq))));
+    n_split = std::min<int64_t>(n_split, entry_cap / ((int64_t)nq * k));
+    const int64_t entries = (int64_t)nq * n_split * k;
+    int64_t* d_pi = reinterpret_cast<int64_t*>(scratch);                                  // indices first (8-byte aligned), then scores
+    int32_t* d_ps = reinterpret_cast<int32_t*>(scratch + 8 * (size_t)entries);
+    const int64_t per = (n + n_split - 1) / n_split;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 g1((unsigned)n_split, (unsigned)std::min(nq, 65535));
+    // every (query, split) CTA writes all k entries of its list before k_topk_final reads them: nothing has to start at zero
+    k_topk_partial<<<g1, TOPK_WARPS * 32, 0, st>>>(d_score, d_idx, n, index_base, k, per > 0 ? per : 1, nq, d_ps, d_pi);
+    const int grid2 = std::min((nq + 7) / 8, ctx->num_sm * 8);
+    k_topk_final<<<grid2, 256, 0, st>>>(d_ps, d_pi, (int32_t)n_split, k, nq, d_out_score, d_out_idx, d_out_n, 0);
+    ctx->launches += 2;
+    DVB_CUDA(ctx, cudaGetLastError());
+    return DVB_OK;
+}
+
 // ================================================================== a4: chunk builder
 // replaces: _build_reference_material_chunks   (reference web/server.py:31932-31970)
 // Offsets are CODE-POINT indices (Python str indexing).  k_cp_index builds cp -> byte offset per

@@ -212,6 +212,8 @@ struct dvb_io {
     }
 };
 
+// chunk.cu: address of the static scratch of dvb_topk_static on `device` (which must be current)
+cudaError_t dv_topk_static_setup(int device, unsigned char** out);
 // launchers defined in chunk.cu, used by index.cu
 void dv_launch_symbolize(dvb_ctx* ctx, cudaStream_t st, const uint8_t* d_utf8, const int64_t* d_off, int64_t n_texts, uint16_t* d_sym, int32_t* d_cnt);
 int64_t dv_topk_splits(dvb_ctx* ctx, int64_t n, int32_t nq);

@@ -120,6 +120,24 @@ int32_t dvb_chunk_scores(dvb_ctx* ctx, int32_t mem, const uint8_t* chunk_utf8, c
 int32_t dvb_topk(dvb_ctx* ctx, int32_t mem, const int32_t* score, const int64_t* idx, int64_t n, int32_t nq,
                  int64_t index_base, int32_t k, int64_t* out_idx, int32_t* out_score, int32_t* out_n);
 
+/* ---- dvb_topk_static: NO counterpart in the reference — added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as dvb_topk(DVB_MEM_DEVICE) — same kernels, same total order — but the call allocates nothing: no
+ * cudaMalloc / cudaFree, no workspace lease, no host<->device copy, no synchronisation.  The per-split partial lists
+ * live in one file-scope device array of DVB_TOPK_STATIC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit; its device address is resolved once per device at dvb_create (cudaGetSymbolAddress with that device current).
+ *  - ALL pointers are device pointers on ctx's device; the two kernels are queued on `stream` (a cudaStream_t owned
+ *    by the caller; NULL = the legacy default stream) and the call returns without waiting: the outputs are valid once
+ *    `stream` has passed this point.
+ *  - limit: nq * k * 12 bytes <= DVB_TOPK_STATIC_SCRATCH_BYTES (nq * k <= 349 525 entries), else DVB_E_CAPACITY with the
+ *    sizes in dvb_last_error; within the limit the split count shrinks to what the array holds (results do not change).
+ *  - every call on a device shares the array and finds the previous call's contents in it.  Nothing has to start at
+ *    zero (every list slot a call reads was written by that call first), but two calls that OVERLAP on the GPU — different
+ *    streams, or graph branches without a dependency — race on it: order them. */
+#define DVB_TOPK_STATIC_SCRATCH_BYTES (4 << 20)
+int32_t dvb_topk_static(dvb_ctx* ctx, void* stream, const int32_t* d_score, const int64_t* d_idx, int64_t n, int32_t nq,
+                        int64_t index_base, int32_t k, int64_t* d_out_idx, int32_t* d_out_score, int32_t* d_out_n);
+
 /* ---- a4  replaces: _build_reference_material_chunks(content)   web/server.py:31932-31970
  * Per document d the chunks are written at [cap_off[d], cap_off[d] + out_count[d]) of the output arrays
  * (cap_off[n_docs+1]: caller-chosen capacities; a document of B bytes never yields more than
