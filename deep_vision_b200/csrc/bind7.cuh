@@ -9,10 +9,11 @@
 //   (the greedy {2,12} pieces of the reference); bigram (previous, this) valid iff adjacent and position % 12 != 0.
 // The position a lane starts with comes from the nearest lane below it that is not "transparent" (4 adjacent CJK
 // characters continuing the previous lane's run): one ballot, one clz, one shuffle per step.
-//   facts : valid bigram -> ONE 16-byte bucket load of the exact claim table in shared memory -> on a hit a byte flag
-//           H[t] = 1 (t = dense index of the claim token; plain store, no atomic).  Pieces (3..12 characters) and ASCII
-//           tokens are rare: a piece end is queued only when its last bigram hit an entry that ends a claim piece of the
-//           same length; cells holding ASCII bytes are queued; both queues are worked off 32 items at a time.
+//   facts : valid bigram -> ONE 16-byte bucket load of the exact claim table in shared memory, four XORs and three
+//           minima (entry layout below) -> on a hit a byte flag H[t] = 1 (t = dense index of the claim token; plain
+//           store, no atomic).  Pieces (3..12 characters) and ASCII tokens are rare: a piece end is queued only when its
+//           last bigram hit an entry that ends a claim piece; cells holding ASCII bytes are queued; both queues are
+//           worked off 32 items at a time.
 //   claims: the same walk inserts instead of probing; the first claim to insert a token owns it (t inside the claim's
 //           own range), other claims list it as shared.  len(A) = own + shared.
 //   per fact: lane c adds the flags of claim c's own range (16 flags per LDS.128 + 4 dp4a) and of its shared list,
@@ -23,47 +24,78 @@
 #include "bind_common.cuh"
 #include "text.cuh"
 
-#define B7_CAPB 4096                 // bigram-table slots (4 ids per 16-byte bucket)
-#define B7_NBM (B7_CAPB / 4 - 1)
-#define B7_BSHIFT 22                 // 32 - log2(B7_CAPB / 4)
+// Cost ladder (profiles/r02_bind_ladder.json): builds with -DB7_RUNG=n keep the persistent-CTA skeleton and the claim phase
+// and stop the FACT side after stage n: 0 no walk, 1 cell loads + checksum, 2 + lead masks and decode, 3 + adjacency, bigram
+// id, table probe, hit flag, 4 + run positions mod 12, valid bigrams, piece ends, certification, 5 + ASCII cells and the
+// deferred piece / ASCII rounds (the whole walk), 6 + per-fact epilogue = the product kernel (the default).
+#ifndef B7_RUNG
+#define B7_RUNG 6
+#endif
+#define B7_NB 2048                   // bigram-table buckets of four 32-bit entries (32 KB)
+#define B7_HASH 0x9E3779B1u          // id -> h = id * B7_HASH: a bijection on the 30-bit ids (mod 2^30)
+#define B7_STASH 32                  // exact side list for the keys of buckets that are full
 #define B7_CAPT 1024                 // piece / ASCII token slots (64-bit keys, L2-resident workspace)
 #define B7_TOK_LIMIT 704
 #define B7_TCAP 3072                 // dense token indices per claim group = flag bytes per warp
-#define B7_FT_BITS 14                // signature filter in front of the ASCII-token probes
-#define B7_SPILL 0x80000000u
+#define B7_HSTRIDE 4096              // per warp: B7_TCAP flag bytes, then the warp's scratch
+#define B7_FT_BITS 12                // signature filter in front of the ASCII-token probes
 #define B7_CELL 12
 #define B7_STEP (32 * B7_CELL)
 #define B7_FULL 0xffffffffu
+#define B7_SLOT_STASH 0x8000u        // claim-side slot numbers: [0, 4 B7_NB) table entry, | STASH side list, | TOKEN token table
+#define B7_SLOT_TOKEN 0x10000u
 
+// Bigram table entry (32 bits):  chk << 13 | piece << 12 | (t + 1)
+//   h = id * B7_HASH;  bucket = bits 19..29 of h;  chk = bits 0..18 of h  — (bucket, chk) <-> id is one to one
+//   t = dense index of the claim token (t + 1 in 1..B7_TCAP; 0 = entry claimed, index not published yet)
+//   piece = the bigram ends a claim piece of 3..12 characters (facts look at piece ends only behind such a hit)
+// A probe XORs the four entries of its bucket with k = chk << 13: the entry of the probed id — and nothing else, a key
+// with chk == 0 is never stored (the session is handed back) — comes out below 8192 and IS piece << 12 | (t + 1).
 struct __align__(16) B7Scratch {     // per warp
     union {
         struct { uint32_t aq[64]; uint32_t pq[160]; };                                  // cell queue, piece-end queue (< 32 + 4 x 32 per step)
         struct { unsigned long long queue[32]; uint32_t qsig[32]; uint32_t qkind; uint32_t pad_;
                  unsigned long long wset[BIND_WSET]; };                                 // exact serial count (text.cuh)
+        struct { double rbest[BIND_CLAIMS]; int ridx[BIND_CLAIMS]; };                   // end of the fact phase: the warp's best per claim
     };
 };
 
 struct __align__(16) B7Shared {
-    uint32_t tab[B7_CAPB];                         // 30-bit bigram ids, 0 = free; bit 31 of a bucket's last slot = spilled
-    uint8_t H[BIND_WARPS][B7_TCAP];                // facts: hit flags by token index; claims: "already listed" flags
-    uint16_t tix[B7_CAPB + B7_CAPT];               // slot -> (t + 1) | piece-length flag << 12
+    uint32_t tab[B7_NB * 4];
+    uint8_t H[BIND_WARPS][B7_HSTRIDE];             // [0, B7_TCAP): facts: hit flags by token index; claims: "already listed" flags; then B7Scratch
+    uint16_t tixT[B7_CAPT];                        // token-table slot -> t + 1
     uint16_t slist[B7_TCAP];                       // claim c's shared tokens at [rbase[c], rbase[c] + shc[c])
     uint32_t ft[1u << (B7_FT_BITS - 5)];
-    B7Scratch scr[BIND_WARPS];
+    uint32_t ovb[B7_NB / 32];                      // bucket b has keys in the side list
+    uint32_t stash_id[B7_STASH], stash_e[B7_STASH];
     unsigned long long ktab[DV_KTAB];
-    double rbest[BIND_WARPS][BIND_CLAIMS];
-    int ridx[BIND_WARPS][BIND_CLAIMS];
     uint16_t rbase[BIND_CLAIMS + 1];
     uint16_t ownc[BIND_CLAIMS], shc[BIND_CLAIMS];
     uint8_t lut[128];
     int next_item, ntok, ovf, exotic, wcnt[BIND_WARPS];
 };
+static_assert(sizeof(B7Scratch) <= B7_HSTRIDE - B7_TCAP, "the warp scratch lives behind the warp's flag bytes");
+static_assert(sizeof(B7Shared) <= 76800, "three CTAs per SM");
 
 #ifdef DV_EMU
 static B7Shared b7_emu_shared;
 #define B7_SH() (b7_emu_shared)
+typedef uintptr_t b7_saddr;                         // the emulator has no shared window: plain pointers
+static inline b7_saddr b7_sa(const void* p) { return (uintptr_t)p; }
+static inline uint4 b7_lds128(b7_saddr a) { return *reinterpret_cast<const uint4*>(a); }
+static inline void b7_sts8(b7_saddr a, uint32_t v) { *reinterpret_cast<volatile uint8_t*>(a) = (uint8_t)v; }
 #else
 #define B7_SH() (*reinterpret_cast<B7Shared*>(bind_smem))
+// 32-bit shared-window addresses kept in registers: the compiler otherwise rebuilds the window base (S2R + MOV + LEA) at
+// every access it reaches through a pointer
+typedef uint32_t b7_saddr;
+__device__ __forceinline__ b7_saddr b7_sa(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint4 b7_lds128(b7_saddr a) {
+    uint4 v;
+    asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));    // the table is read-only while facts are walked: free to schedule
+    return v;
+}
+__device__ __forceinline__ void b7_sts8(b7_saddr a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
 #endif
 
 struct B7Tok {                       // per-warp tokenizer state (registers)
@@ -121,6 +153,9 @@ __device__ __forceinline__ bool b7_ft_pass(const B7Shared& sh, uint32_t sig) {
 }
 
 // ---------------------------------------------------------------- claim side: insert, token index, shared lists
+__device__ __forceinline__ uint32_t* b7_entry(B7Shared& sh, uint32_t slot) {       // bigram slots only
+    return (slot & B7_SLOT_STASH) ? &sh.stash_e[slot & (B7_SLOT_STASH - 1u)] : &sh.tab[slot];
+}
 // Convergent.  `act` lanes hold DISTINCT slots of tokens of the warp's claim; `created` = this lane made the entry.
 // A created token gets the next index of the claim's own range; a token another claim (or an earlier step of this
 // claim) created is listed as shared unless it is the claim's own or already listed (flag in the warp's H array).
@@ -131,13 +166,18 @@ __device__ __forceinline__ void b7_claim_slot(B7Tok& t, bool act, uint32_t slot,
     if (act && created) {
         uint32_t tt = t.rb + (uint32_t)t.own + (uint32_t)__popc(cm & lt);
         if (tt >= t.re) { sh.ovf = 1; tt = t.rb; }                 // cannot happen (range bound = bytes / 3 + 2); keeps waiters from spinning
-        *(volatile uint16_t*)&sh.tix[slot] = (uint16_t)(tt + 1u);
+        if (slot & B7_SLOT_TOKEN) *(volatile uint16_t*)&sh.tixT[slot & 0xFFFFu] = (uint16_t)(tt + 1u);
+        else atomicOr(b7_entry(sh, slot), tt + 1u);                // the piece bit of the entry may be raised concurrently
     }
     t.own += __popc(cm);
     bool isnew = false; uint32_t tt = 0;
     if (act && !created) {
         uint32_t v;
-        for (;;) { v = *(volatile uint16_t*)&sh.tix[slot]; if ((v & 0xFFFu) != 0u) break; DV_SPIN_PAUSE(); }   // the creator (another warp) is a few instructions away
+        for (;;) {                                                 // the creator (another warp) is a few instructions away
+            v = (slot & B7_SLOT_TOKEN) ? (uint32_t)*(volatile uint16_t*)&sh.tixT[slot & 0xFFFFu] : *(volatile uint32_t*)b7_entry(sh, slot);
+            if ((v & 0xFFFu) != 0u) break;
+            DV_SPIN_PAUSE();
+        }
         tt = (v & 0xFFFu) - 1u;
         if ((tt < t.rb || tt >= t.re) && !t.H[tt]) { t.H[tt] = 1; isnew = true; }
     }
@@ -149,41 +189,40 @@ __device__ __forceinline__ void b7_claim_slot(B7Tok& t, bool act, uint32_t slot,
     t.shd += __popc(sm);
 }
 
+// slot of bigram id (claim side): finds it or claims a free entry of its bucket, else of the side list.  -1: no room.
+__device__ __forceinline__ int b7_bigram_slot(B7Shared& sh, uint32_t id, bool insert, bool& created) {
+    const uint32_t h = id * B7_HASH, k = h << 13, b = (h >> 19) & (B7_NB - 1u);
+    created = false;
+    if (k == 0u) return -1;                                        // chk == 0 would look like a free entry
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        uint32_t prev = *(volatile uint32_t*)&sh.tab[b * 4u + j];
+        if (prev == 0u && insert) prev = atomicCAS(&sh.tab[b * 4u + j], 0u, k);
+        if (prev == 0u) { created = insert; return insert ? (int)(b * 4u + j) : -1; }
+        if (((prev ^ k) >> 13) == 0u) return (int)(b * 4u + j);
+    }
+    if (insert) atomicOr(&sh.ovb[b >> 5], 1u << (b & 31u));
+    else if (!((sh.ovb[b >> 5] >> (b & 31u)) & 1u)) return -1;
+    for (int j = 0; j < B7_STASH; j++) {
+        uint32_t prev = *(volatile uint32_t*)&sh.stash_id[j];
+        if (prev == 0u && insert) prev = atomicCAS(&sh.stash_id[j], 0u, id);
+        if (prev == 0u) { created = insert; return insert ? (int)(B7_SLOT_STASH | (uint32_t)j) : -1; }
+        if (prev == id) return (int)(B7_SLOT_STASH | (uint32_t)j);
+    }
+    return -1;
+}
+
 // Convergent: valid lanes insert their bigram id into the bucketed table.
 __device__ __forceinline__ void b7_bigram_insert(B7Tok& t, bool v, uint32_t id) {
     B7Shared& sh = *t.sh;
     const uint32_t mm = __match_any_sync(B7_FULL, v ? id : (0x80000000u | (uint32_t)t.lane));
     const bool leader = v && (__ffs(mm) - 1 == t.lane);
-    uint32_t slot = 0; bool created = false, ok = false;
+    int slot = -1; bool created = false;
     if (leader) {
-        uint32_t b = (id * 0x9E3779B1u) >> B7_BSHIFT;
-        for (uint32_t tries = 0; tries <= B7_NBM && !ok; tries++) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                if (ok) break;
-                const uint32_t prev = atomicCAS(&sh.tab[b * 4u + j], 0u, id) & 0x7FFFFFFFu;
-                if (prev == 0u || prev == id) { slot = b * 4u + j; created = (prev == 0u); ok = true; }
-            }
-            if (!ok) { atomicOr(&sh.tab[b * 4u + 3u], B7_SPILL); b = (b + 1u) & B7_NBM; }
-        }
-        if (!ok) sh.ovf = 1;
+        slot = b7_bigram_slot(sh, id, true, created);
+        if (slot < 0) sh.ovf = 1;
     }
-    b7_claim_slot(t, ok, slot, created);
-}
-
-// slot of a bigram id that is in the table (claims: the last bigram of a piece was inserted before the piece is keyed)
-__device__ __forceinline__ int b7_bigram_find(const B7Shared& sh, uint32_t id) {
-    uint32_t b = (id * 0x9E3779B1u) >> B7_BSHIFT;
-    for (uint32_t tries = 0; tries <= B7_NBM; tries++) {
-        const uint4 e = *reinterpret_cast<const uint4*>(&sh.tab[b * 4u]);
-        if (e.x == id) return (int)(b * 4u);
-        if (e.y == id) return (int)(b * 4u + 1u);
-        if (e.z == id) return (int)(b * 4u + 2u);
-        if ((e.w & 0x7FFFFFFFu) == id) return (int)(b * 4u + 3u);
-        if (!(e.w & B7_SPILL)) return -1;
-        b = (b + 1u) & B7_NBM;
-    }
-    return -1;
+    b7_claim_slot(t, slot >= 0, (uint32_t)slot, created);
 }
 
 // Convergent: piece / ASCII tokens of the claim (64-bit keys) go to the open-addressing table in the workspace.
@@ -208,21 +247,21 @@ __device__ __forceinline__ void b7_token_insert(B7Tok& t, bool v, uint64_t key, 
             ok = true;
         }
     }
-    b7_claim_slot(t, ok, B7_CAPB + slot, created);
+    b7_claim_slot(t, ok, B7_SLOT_TOKEN | slot, created);
 }
 
-// piece-length flag of the entry of a piece's last bigram: 0 none, f = len - 2 (1..10), 15 = several lengths
-__device__ __forceinline__ void b7_set_lenflag(B7Shared& sh, int slot, uint32_t f) {
-    uint32_t* wp = reinterpret_cast<uint32_t*>(&sh.tix[slot & ~1]);
-    const uint32_t shf = (uint32_t)(slot & 1) * 16u + 12u;
-    for (;;) {
-        const uint32_t old = *(volatile uint32_t*)wp;
-        const uint32_t cur = (old >> shf) & 15u;
-        const uint32_t nf = cur == 0u ? f : (cur == f ? f : 15u);
-        if (nf == cur) return;
-        const uint32_t nw = (old & ~(15u << shf)) | (nf << shf);
-        if (atomicCAS(wp, old, nw) == old) return;
+// ---------------------------------------------------------------- fact side: a miss in a full bucket
+// piece << 12 | (t + 1) of id if it lives in the side list, else 0.  ~1 % of the probes get here; the loop stays rolled.
+__device__ __forceinline__ uint32_t b7_side_lookup(const B7Shared* sh, uint32_t h, uint32_t id) {
+    const uint32_t bk = (h >> 19) & (B7_NB - 1u);
+    if (!((sh->ovb[bk >> 5] >> (bk & 31u)) & 1u)) return 0u;
+#pragma unroll 1
+    for (int j = 0; j < B7_STASH; j++) {
+        const uint32_t sid = sh->stash_id[j];
+        if (sid == 0u) break;
+        if (sid == id) return sh->stash_e[j] & 0x1FFFu;
     }
+    return 0u;
 }
 
 // ---------------------------------------------------------------- fact side: probe of a piece / ASCII token key
@@ -231,7 +270,7 @@ __device__ __forceinline__ void b7_token_probe(B7Tok& t, bool v, uint64_t key) {
     uint32_t slot = bind_hash(key) & (B7_CAPT - 1);
     for (;;) {
         const unsigned long long k = __ldcg(&t.tkeys[slot]);
-        if (k == key) { t.H[(t.sh->tix[B7_CAPB + slot] & 0xFFFu) - 1u] = 1; return; }
+        if (k == key) { t.H[(uint32_t)t.sh->tixT[slot] - 1u] = 1; return; }
         if (k == 0ULL) return;
         slot = (slot + 1) & (B7_CAPT - 1);
     }
@@ -329,7 +368,7 @@ __device__ void b7_piece_round(B7Tok& t, int head, int cnt) {
     const uint32_t sig = dv_token_sig(sp, sl, L);
     if (CLAIM) {
         b7_token_insert(t, ok, key, sig);
-        if (ok) { const int slot = b7_bigram_find(sh, (sp << 15) | sl); if (slot >= 0) b7_set_lenflag(sh, slot, L - 2u); else sh.ovf = 1; }
+        if (ok) { bool cr; const int slot = b7_bigram_slot(sh, (sp << 15) | sl, false, cr); if (slot >= 0) atomicOr(b7_entry(sh, (uint32_t)slot), 1u << 12); else sh.ovf = 1; }
     } else b7_token_probe(t, ok, key);
 }
 
@@ -397,12 +436,13 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
     uint32_t n0, n1, n2, n3;
     b7_load_cell(t, lane * B7_CELL, n0, n1, n2, n3);
     if (t.a && lane == 0) { const uint32_t km = (1u << (8 * t.a)) - 1u; n0 = (n0 & ~km) | (0x20202020u & km); }
-    const uint4* tab4 = reinterpret_cast<const uint4*>(sh.tab);
-    const uint2* tix2 = reinterpret_cast<const uint2*>(sh.tix);
+    const b7_saddr tabS = b7_sa(sh.tab), hitS = b7_sa(t.H) - 1u;                  // entry t + 1 -> flag byte t
+    uint32_t ladder = 0;
     for (int s = 0; s < nsteps; s++) {
         const int32_t o = s * B7_STEP + lane * B7_CELL;
         const uint32_t w0 = n0, w1 = n1, w2 = n2, w3 = n3;
         if (s + 1 < nsteps) b7_load_cell(t, o + B7_STEP, n0, n1, n2, n3);
+        if (!CLAIM && B7_RUNG == 1) { ladder ^= w0 ^ w1 ^ w2 ^ w3; continue; }
         // ---- cell masks: leads >= 0xE0 (12 bits), any ASCII byte or 2-byte lead
         const uint32_t u0 = w0 & (w0 << 1), u1 = w1 & (w1 << 1), u2 = w2 & (w2 << 1);
         const uint32_t mm = b7_gather4(u0 & (w0 << 2) & 0x80808080u) | (b7_gather4(u1 & (w1 << 2) & 0x80808080u) << 4) |
@@ -425,6 +465,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             bad |= (xi & 0x00FFFFFFu) == 0x00AA84E2u;                                    // U+212A lower-cases to 'k'
         }
         if (bad) t.exotic = true;
+        if (!CLAIM && B7_RUNG == 2) { ladder ^= sy[0] ^ sy[1] ^ sy[2] ^ sy[3] ^ rare; continue; }
         // ---- adjacency, position of the lane's first character in its run
         const uint32_t pk = sy[3] ? ((sy[3] << 2) | g[3]) : 0u;
         uint32_t pv = __shfl_up_sync(B7_FULL, pk, 1);
@@ -434,62 +475,58 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
         ad[0] = sy[0] != 0u && pv != 0u && (pv & 3u) == g[0];
 #pragma unroll
         for (int i = 1; i < 4; i++) ad[i] = sy[i] != 0u && sy[i - 1] != 0u && g[i] == g[i - 1];
+        int p = 0;
+        if (CLAIM || B7_RUNG >= 4) {
         const bool transparent = ad[0] && ad[1] && ad[2] && ad[3];
         const int ploc = ad[3] ? (ad[2] ? (ad[1] ? (ad[0] ? 4 : 3) : 2) : 1) : 0;
         const uint32_t T = __ballot_sync(B7_FULL, transparent);
         const uint32_t nt = ~T & lt;
         const int jn = nt ? 31 - __clz((int)nt) : 0;
         const int pj = __shfl_sync(B7_FULL, ploc, jn);
-        int p = nt ? pj + 4 * (lane - 1 - jn) : carryP + 4 * lane;
+        p = nt ? pj + 4 * (lane - 1 - jn) : carryP + 4 * lane;
         p = (int)((uint32_t)p % 12u);
-        // ---- slots: positions, bigrams
-        uint32_t candm = 0, candp = 0, lfp = 0, pp = 0;
+        }
+        // ---- slots: positions, bigrams; piece ends: claims queue every end of a piece of >= 3, facts only ends whose last
+        //      bigram hit an entry that ends a claim piece
+        uint32_t candm = 0, candp = 0, vm = 0;
         uint32_t prev = pv >> 2;
+        bool adn[4];                                 // the next character continues the run (last slot: possibly)
+        adn[0] = ad[1]; adn[1] = ad[2]; adn[2] = ad[3]; adn[3] = ((x[3] >> 24) - 0xE5u) <= 4u;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             p = ad[i] ? p + 1 : 0;
             if (p == 12) p = 0;
-            const bool v = ad[i] && p != 0;
+            const bool v = ad[i] && (p != 0 || (!CLAIM && B7_RUNG == 3));
             const uint32_t id = (prev << 15) | sy[i];
-            pp |= (uint32_t)p << (4 * i);
+            bool pend = v && p >= 2 && (p == 11 || !adn[i]);
             if (CLAIM) b7_bigram_insert(t, v, id);
             else {
-                if (!t.cert) {                    // min(len(B), 18): >= 18 distinct valid bigrams in one slot round certify it
-                    const uint32_t ma = __match_any_sync(B7_FULL, v ? id : (0x80000000u | (uint32_t)lane));
-                    const uint32_t nd = (uint32_t)__popc(__ballot_sync(B7_FULL, v && (__ffs(ma) - 1 == lane)));
-                    if (nd >= 18u) t.cert = true;
+                const uint32_t h = id * B7_HASH, k = h << 13;
+                const uint4 e = b7_lds128(tabS + ((h >> 15) & ((B7_NB - 1u) << 4)));
+                uint32_t m = min(min(e.x ^ k, e.y ^ k), min(e.z ^ k, e.w ^ k));
+                bool hit = v && (m - 1u) < 8191u;
+                if (v && !hit && e.w != 0u) {                                            // rare: full bucket, the key may be in the side list
+                    const uint32_t sm_ = b7_side_lookup(t.sh, h, id);
+                    if (sm_) { m = sm_; hit = true; }
                 }
-                uint32_t b = (id * 0x9E3779B1u) >> B7_BSHIFT;
-                const uint4 e = tab4[b];
-                const uint2 tq = tix2[b];
-                const bool m1 = e.y == id, m2 = e.z == id, m3 = (e.w & 0x7FFFFFFFu) == id;
-                const uint32_t wsel = (m2 || m3) ? tq.y : tq.x;
-                uint32_t t16 = (m1 || m3) ? (wsel >> 16) : (wsel & 0xFFFFu);
-                bool hit = v && (e.x == id || m1 || m2 || m3);
-                if (v && !hit && (e.w & B7_SPILL)) {                                     // rare: the chain continues in the next bucket(s)
-                    for (;;) {
-                        b = (b + 1u) & B7_NBM;
-                        const uint4 f = tab4[b];
-                        const int j = f.x == id ? 0 : (f.y == id ? 1 : (f.z == id ? 2 : ((f.w & 0x7FFFFFFFu) == id ? 3 : -1)));
-                        if (j >= 0) { t16 = sh.tix[b * 4u + (uint32_t)j]; hit = true; break; }
-                        if (!(f.w & B7_SPILL)) break;
-                    }
-                }
-                if (hit) { t.H[(t16 & 0xFFFu) - 1u] = 1; lfp |= (t16 >> 12) << (4 * i); }
+                if (hit) b7_sts8(hitS + (m & 0xFFFu), 1u);
+                pend = pend && hit && m >= 4096u;
+                vm |= (v ? 1u : 0u) << i;
             }
+            if (pend) { candm |= 1u << i; candp |= (uint32_t)p << (4 * i); }
             prev = sy[i];
         }
+        if (!CLAIM && B7_RUNG == 3) continue;
         carryP = __shfl_sync(B7_FULL, p, 31);
-        // ---- piece ends: claims queue every end of a piece of >= 3, facts only ends whose last bigram hit an entry that
-        //      ends a claim piece of the same length
-        if (CLAIM || lfp != 0u) {
-#pragma unroll
+        if (!CLAIM && !t.cert) {                 // min(len(B), 18): >= 18 distinct valid bigrams in one slot round certify it
+#pragma unroll 1
             for (int i = 0; i < 4; i++) {
-                const uint32_t pi = (pp >> (4 * i)) & 15u;
-                const uint32_t lf = (lfp >> (4 * i)) & 15u;
-                const bool ends = pi == 11u || (i < 3 ? !ad[i < 3 ? i + 1 : 3] : ((x[3] >> 24) - 0xE5u) > 4u);
-                const bool want = CLAIM ? true : (lf == 15u || lf == pi - 1u);          // flag = length - 2 = position - 1
-                if (ad[i] && pi >= 2u && ends && want) { candm |= 1u << i; candp |= pi << (4 * i); }
+                const uint32_t pr = i == 0 ? (pv >> 2) : (i == 1 ? sy[0] : (i == 2 ? sy[1] : sy[2]));
+                const uint32_t sc = i == 0 ? sy[0] : (i == 1 ? sy[1] : (i == 2 ? sy[2] : sy[3]));
+                const bool v = ((vm >> i) & 1u) != 0u;
+                const uint32_t ma = __match_any_sync(B7_FULL, v ? ((pr << 15) | sc) : (0x80000000u | (uint32_t)lane));
+                const uint32_t nd = (uint32_t)__popc(__ballot_sync(B7_FULL, v && (__ffs(ma) - 1 == lane)));
+                if (nd >= 18u) { t.cert = true; break; }
             }
         }
         while (__any_sync(B7_FULL, candm != 0u)) {
@@ -503,6 +540,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             }
             t.pqn += __popc(bal);
         }
+        if (!CLAIM && B7_RUNG == 4) { t.pqn = 0; continue; }
         // ---- cells holding ASCII bytes or 2-byte leads are looked at 32 at a time
         {
             const bool need = rare != 0u && o < t.total;
@@ -515,6 +553,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
         // the one call site of the deferred rounds: whenever a queue holds a full round, and at the end of the text
         if (t.aqn >= 32 || t.pqn >= 32 || s + 1 == nsteps) b7_flush_queues<CLAIM>(t, s + 1 == nsteps);
     }
+    if (!CLAIM && B7_RUNG < 3 && ladder == 0x9E3779B1u) t.exotic = true;          // keeps the ladder builds' loads alive
 }
 
 // exact min(len(B), 18) of a fact the walk could not certify (short or repetitive facts): the serial tokenizer of
@@ -549,10 +588,10 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     dv_fill_ktab(sh.ktab);
     for (int b = tid; b < 128; b += BIND_THREADS) sh.lut[b] = (uint8_t)(dv_ascii_sym((uint32_t)b) & 0xFFu);
-    for (uint32_t i = tid; i < BIND_WARPS * B7_TCAP / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     B7Tok t;
-    t.sh = &sh; t.tkeys = tkeys; t.H = sh.H[warp]; t.scr = &sh.scr[warp]; t.lane = lane;
+    t.sh = &sh; t.tkeys = tkeys; t.H = sh.H[warp]; t.scr = reinterpret_cast<B7Scratch*>(sh.H[warp] + B7_TCAP); t.lane = lane;
     t.base = nullptr; t.a = 0; t.total = 0; t.aqn = 0; t.pqn = 0; t.rb = 0; t.re = 0; t.own = 0; t.shd = 0; t.cert = false; t.exotic = false;
 
     for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
@@ -562,8 +601,10 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
         for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
             // ---- clear tables, token-index ranges of the claims
-            for (uint32_t i = tid; i < (B7_CAPB >> 2); i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
-            for (uint32_t i = tid; i < (B7_CAPB + B7_CAPT) / 8; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tix)[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t i = tid; i < B7_NB; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t i = tid; i < B7_CAPT / 8; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tixT)[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (tid < B7_NB / 32) sh.ovb[tid] = 0u;
+            if (tid < B7_STASH) { sh.stash_id[tid] = 0u; sh.stash_e[tid] = 0u; }
             for (uint32_t i = tid; i < B7_CAPT; i += BIND_THREADS) tkeys[i] = 0ULL;
             for (uint32_t i = tid; i < (1u << (B7_FT_BITS - 5)); i += BIND_THREADS) sh.ft[i] = 0u;
             if (warp == 0) {
@@ -619,8 +660,9 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
                 if (f >= nf) break;
                 const int64_t b = p.fact_off[f0 + f], e = p.fact_off[f0 + f + 1];
                 t.cert = false;
-                b7_text<false>(t, p.fact_utf8 + b, (int32_t)(e - b));
+                if (B7_RUNG >= 1) b7_text<false>(t, p.fact_utf8 + b, (int32_t)(e - b));
                 __syncwarp();
+                if (B7_RUNG < 6) continue;
                 const double fq = p.fact_quality[f0 + f];
                 const int fdim = p.fact_dim[f0 + f];
                 const uint32_t fhard = p.fact_hard[f0 + f];
@@ -665,14 +707,16 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
                 __syncwarp();
             }
             if (__any_sync(B7_FULL, t.exotic)) sh.exotic = 1;
-            sh.rbest[warp][lane] = best; sh.ridx[warp][lane] = best_f;
+            __syncwarp();
+            t.scr->rbest[lane] = best; t.scr->ridx[lane] = best_f;
             __syncthreads();
             if (sh.exotic) handback = true;                          // uniform; no writer until the next barrier
             // ---- phase R
             if (tid < ncg) {
                 double b = -1.0; int bf = 0x7fffffff;
                 for (int w = 0; w < BIND_WARPS; w++) {
-                    const double sc = sh.rbest[w][tid]; const int fi = sh.ridx[w][tid];
+                    const B7Scratch* ws = reinterpret_cast<const B7Scratch*>(sh.H[w] + B7_TCAP);
+                    const double sc = ws->rbest[tid]; const int fi = ws->ridx[tid];
                     if (sc > b || (sc == b && fi < bf)) { b = sc; bf = fi; }
                 }
                 const int64_t c = cg + tid;
@@ -689,7 +733,7 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
             if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
             // the H arrays may hold stale flags of an abandoned claim phase
             __syncthreads();
-            for (uint32_t i = tid; i < BIND_WARPS * B7_TCAP / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
             __syncthreads();
         }
     }

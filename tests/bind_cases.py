@@ -140,3 +140,31 @@ def mixed_real_text():
 def big_claim_groups():
     """claim groups whose token ranges exceed the fast kernel's flag array -> handed back to the general kernel"""
     return synthetic(2, 6, 30, seed=5, claim_chars=4000, copy_frac=0.05)
+
+
+def _bucket_mates(n_buckets_bits=11, want=48, seed=5):
+    """CJK bigrams whose ids land in ONE bucket of the fast kernel's bigram table (bits 19..29 of id * 0x9E3779B1)"""
+    import random
+    rng = random.Random(seed)
+    target, out = None, []
+    while len(out) < want:
+        a, b = rng.randrange(1, 20993), rng.randrange(1, 20993)
+        h = (((a << 15) | b) * 0x9E3779B1) & 0xFFFFFFFF
+        bk = (h >> 19) & ((1 << n_buckets_bits) - 1)
+        if target is None:
+            target = bk
+        if bk == target:
+            out.append(chr(0x4E00 + a - 1) + chr(0x4E00 + b - 1))
+    return out
+
+
+def crowded_bucket(n_keys):
+    """n_keys claim bigrams in one table bucket: beyond four the keys live in the side list (exact), beyond 4 + 32 the
+    session is handed back.  Facts hold some of them (hits through the side list), near misses and fillers."""
+    mates = _bucket_mates(want=n_keys + 8)
+    inb, out = mates[:n_keys], mates[n_keys:]
+    claims = ["，".join(inb[i::6]) for i in range(6)] + ["，".join(inb[:5]), inb[-1] + "，" + inb[0]]
+    facts = ["。".join(inb[::2]), "。".join(inb[1::2] + out), "。".join(out), "，".join(inb), inb[-1], inb[3] + " " + inb[4] + " " + out[0]]
+    nc, nf = len(claims), len(facts)
+    return _pack(claims * 2, facts * 2, [0, nc, 2 * nc], [0, nf, 2 * nf], np.linspace(0.2, 0.8, 2 * nf), np.arange(2 * nf) % 3,
+                 np.arange(2 * nf) % 2, np.arange(2 * nc) % 4 - 1, np.full(2 * nc, 0.3))

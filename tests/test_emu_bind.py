@@ -56,6 +56,12 @@ def test_emu_handbacks(emu, oracle):
     _check(emu, oracle, bc.long_facts(1), expect_handback=1)                 # U+0130 / U+212A inside
 
 
+def test_emu_crowded_bucket_side_list(emu, oracle):
+    _check(emu, oracle, bc.crowded_bucket(5), expect_handback=0)             # one key in the side list
+    _check(emu, oracle, bc.crowded_bucket(30), expect_handback=0)            # 26 keys in the side list
+    _check(emu, oracle, bc.crowded_bucket(40), expect_handback=2)            # more than the side list holds
+
+
 def test_emu_general_kernel_alone(emu, oracle):
     _check(emu, oracle, bc.synthetic(3, 12, 40), mode=2)
     _check(emu, oracle, bc.mixed_real_text(), mode=2)

@@ -102,6 +102,8 @@ def test_a2_short_facts_and_mixed_scripts(gpu_ctx, oracle):
     import bind_cases as bc
     _bind_vs_oracle(gpu_ctx, oracle, bc.mixed_real_text())
     _bind_vs_oracle(gpu_ctx, oracle, bc.big_claim_groups())
+    for n in (5, 30, 40):                                   # one table bucket: side list, side list overflow (hand-back)
+        _bind_vs_oracle(gpu_ctx, oracle, bc.crowded_bucket(n))
 
 
 def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
