@@ -42,8 +42,11 @@ def parse_args():
     ap.add_argument("--turns", type=int, default=40)
     ap.add_argument("--claims", type=int, default=24)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--index-chunks", type=int, default=200000,
-                    help="chunks per GPU of the bounded config-3 sample behind the `index` key (0 = skip)")
+    ap.add_argument("--index-chunks", type=int, default=1000000, help="config 3: chunks per GPU behind the `index` key (0 = skip)")
+    ap.add_argument("--index-queries", type=int, default=100000, help="config 3: claim queries, top-8")
+    ap.add_argument("--gate-candidates", type=int, default=1000000, help="config 4: candidate questions per GPU behind the `gate` key (0 = skip)")
+    ap.add_argument("--gate-history", type=int, default=50000)
+    ap.add_argument("--no-latency", action="store_true", help="skip the config-1 latency and Python-API arms")
     return ap.parse_args()
 
 
@@ -55,14 +58,29 @@ def workload_config(args, world):
             "l2_policy": "inputs (0.88 GB/GPU) larger than L2; no flush needed"}
 
 
+def make_texts_blocked(n, chars, seed, block=125000):
+    """synth.make_texts in blocks (bounded host memory): n texts of `chars` code points, packed CSR."""
+    from deep_vision_b200 import synth
+    parts, offs, base = [], [np.zeros(1, np.int64)], 0
+    for i, b0 in enumerate(range(0, n, block)):
+        d, o = synth.make_texts(min(block, n - b0), chars, seed=seed + 7919 * i)
+        nb = int(o[-1])
+        parts.append(d[:nb]); offs.append(o[1:] + base); base += nb
+    parts.append(np.zeros(64, np.uint8))
+    return np.concatenate(parts), np.concatenate(offs)
+
+
 def index_arm(ctx, args, rank, world=1):
-    """BASELINE metric part 2, chunks indexed/s: a bounded config-3 sample (512-char chunks resident in HBM ->
-    dvb_chunk_index_build -> a queryable positional index), plus the indexed top-8 of 1000 claim queries over it.
-    Returns this rank's numbers; the caller reduces over ranks."""
+    """BASELINE metric part 2 on config 3: N chunks/GPU x 512 chars resident in HBM -> dvb_chunk_index_build (chunks
+    indexed/s), then the indexed top-8 of Q claim queries (effective (query, chunk) pairs/s) with terms and candidates
+    resident on the device; at N > 1 the sharded top-k (one all_gather_into_tensor + device merge).  Rank-local numbers;
+    the caller reduces over ranks."""
     import torch
-    from deep_vision_b200 import _lib, reference_material as rm, synth
-    n = args.index_chunks
-    data, off = synth.make_texts(n, 512, seed=synth.SEED + 1000 + rank)
+    from deep_vision_b200 import parallel, reference_material as rm, synth
+    n, nq, k = args.index_chunks, args.index_queries, 8
+    t0 = time.perf_counter()
+    data, off = make_texts_blocked(n, 512, synth.SEED + 1000 + rank)
+    gen_s = time.perf_counter() - t0
     d_data, d_off = torch.from_numpy(data).cuda(), torch.from_numpy(off).cuda()
     builds, ix = [], None
     for _ in range(4):                                            # the first build grows the allocation pool
@@ -72,46 +90,212 @@ def index_arm(ctx, args, rank, world=1):
         ix = rm.ChunkIndex(device_ptrs=(d_data.data_ptr(), d_off.data_ptr(), n), index_base=rank * n, ctx=ctx)
         builds.append(ix.build_ms)
     st = ix.stats()
-    qdata, qoff = synth.make_texts(1000, 45, seed=999)
+    # queries: 30-60 chars, every other one half copied from a chunk of THIS rank's shard (replicated from rank 0 below)
+    qdata, qoff = synth.make_texts(nq, 45, seed=999)
     raw, qraw = data.tobytes(), qdata.tobytes()
     rng = np.random.default_rng(7)
-    terms = []
-    for q in range(1000):
+    src_chunk = rng.integers(0, n, size=nq); src_pos = rng.integers(0, 488, size=nq)
+    queries = []
+    for q in range(nq):
         text = qraw[qoff[q]:qoff[q + 1]].decode("utf-8")
-        if q % 2 == 0:                                            # half of every other query is copied from a chunk
-            c = int(rng.integers(0, n)); src = raw[off[c]:off[c + 1]].decode("utf-8"); a = int(rng.integers(0, 488))
-            text = text[:22] + src[a:a + 22]
-        terms.append(rm._tokenize_reference_material_query(text))
+        if q % 2 == 0:
+            c = int(src_chunk[q]); a = int(src_pos[q])
+            text = text[:22] + raw[off[c]:off[c + 1]].decode("utf-8")[a:a + 22]
+        queries.append(text)
+    del raw
+    if world > 1:
+        import torch.distributed as dist
+        box = [queries]
+        dist.broadcast_object_list(box, src=0)
+        queries = box[0]
+    t0 = time.perf_counter()
+    terms = [rm._tokenize_reference_material_query(t) for t in queries]
+    tok_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    dev_terms = parallel.terms_to_device(terms)
+    sym_s = time.perf_counter() - t0
+    q_ms, li = [], None
+    for _ in range(2):
+        li, ls, ln = ix.topk_device(dev_terms, nq, k)
+        q_ms.append(ctx.last_kernel_ms)
+    li_h, ls_h, ln_h = li.cpu().numpy(), ls.cpu().numpy(), ln.cpu().numpy()
     sharded = None
     if world > 1:
-        # the queries are replicated (rank 0's), every rank answers them over its shard, ONE all-gather of nq x k
-        # candidates over NCCL, merge on every rank (parallel.sharded_index_topk); host wall clock, max over ranks
         import hashlib
         import torch.distributed as dist
-        from deep_vision_b200 import parallel
-        box = [terms]
-        dist.broadcast_object_list(box, src=0)
-        terms = box[0]
-        wall = []
-        for _ in range(3):
-            dist.barrier(); torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            gi, gs, gn = parallel.sharded_index_topk(ix, terms, 8)
-            torch.cuda.synchronize()
-            wall.append(1000.0 * (time.perf_counter() - t0))
-        digest = int.from_bytes(hashlib.sha256(gi.tobytes() + gs.tobytes() + gn.tobytes()).digest()[:7], "little")
-        lo_hi = torch.tensor([digest, -digest], dtype=torch.int64, device="cuda")
-        dist.all_reduce(lo_hi, op=dist.ReduceOp.MAX)
-        sharded = {"ms_1000_queries_allgather_merge": min(wall), "identical_on_all_ranks": bool(int(lo_hi[0]) == -int(lo_hi[1])),
-                   "allgather_bytes": world * len(terms) * 8 * 12}
-    q_ms = []
-    for _ in range(3):
-        ix.topk(terms, 8)
-        q_ms.append(ctx.last_kernel_ms)
+        sharded = {}
+        for label, m in (("1000_queries", min(1000, nq)), ("all_queries", nq)):
+            sub = parallel.terms_to_device(terms[:m]) if m < nq else dev_terms
+            local_ms, wall = [], []
+            for _ in range(3):
+                ix.topk_device(sub, m, k); local_ms.append(ctx.last_kernel_ms)
+                dist.barrier(); torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                gi, gs, gn = parallel.sharded_index_topk_device(ix, sub, m, k)
+                torch.cuda.synchronize()
+                wall.append(1000.0 * (time.perf_counter() - t0))
+            digest = int.from_bytes(hashlib.sha256(gi.tobytes() + gs.tobytes() + gn.tobytes()).digest()[:7], "little")
+            lo_hi = torch.tensor([digest, -digest], dtype=torch.int64, device="cuda")
+            dist.all_reduce(lo_hi, op=dist.ReduceOp.MAX)
+            sharded[label] = {"queries": m, "local_device_ms": min(local_ms), "ms_with_allgather_merge_and_d2h": min(wall),
+                              "identical_on_all_ranks": bool(int(lo_hi[0]) == -int(lo_hi[1])), "allgather_bytes": world * m * k * 16}
+    # parity: exact scores of a query slice over the WHOLE shard by the C oracle (all host threads), rank 0 only
+    parity = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oracle import dv_oracle        # checker (allowed use)
+        dv_oracle.build()
+        cores = os.cpu_count() or 1
+        ok, checked, t0 = True, 0, time.perf_counter()
+        for q in range(0, nq, max(1, nq // 6))[:6]:
+            if not terms[q]:
+                continue
+            sc = dv_oracle.chunk_scores(None, terms[q], n_threads=cores, packed=(data, off))
+            wi, ws = dv_oracle.topk(sc, k)
+            nv = int(ln_h[q])
+            ok = ok and (li_h[q][:nv] - rank * n).tolist() == wi.tolist() and ls_h[q][:nv].tolist() == ws.tolist()
+            checked += 1
+        parity = {"vs": "oracle C exact substring counts over all %d chunks for %d queries of the batch" % (n, checked),
+                  "topk_indices_and_scores_identical": bool(ok), "seconds": time.perf_counter() - t0}
     ix.close()
     best = min(builds[1:])
-    return {"chunks_per_gpu": n, "build_ms": best, "first_build_ms": builds[0], "postings": st["postings"],
-            "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"], "query_ms_1000_queries": min(q_ms), "sharded": sharded}
+    return {"chunks_per_gpu": n, "queries": nq, "build_ms": best, "first_build_ms": builds[0], "postings": st["postings"],
+            "text_bytes": st["text_bytes"], "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"],
+            "query_ms": min(q_ms), "query_algorithmic_bytes_lower_bound": 8 * int(ls_h.sum()) + 16 * k * nq,
+            "host_gen_s": gen_s, "host_tokenize_s": tok_s, "host_symbols_s": sym_s, "sharded": sharded, "parity": parity}
+
+
+def _gather_segments(src, src_off, idx):
+    """concatenation of src[src_off[i]:src_off[i+1]] for i in idx (vectorised) -> (values, offsets[len(idx)+1])"""
+    lens = src_off[idx + 1] - src_off[idx]
+    out_off = np.zeros(len(idx) + 1, np.int64); np.cumsum(lens, out=out_off[1:])
+    pos = np.arange(int(out_off[-1]), dtype=np.int64) - np.repeat(out_off[:-1], lens) + np.repeat(src_off[idx], lens)
+    return src[pos], out_off
+
+
+def gate_arm(ctx, args, rank, world=1):
+    """Config 4: question-similarity gate, C candidate questions/GPU (20-40 chars + '？') against a replicated history of
+    H questions, char-bigram Jaccard >= 0.62, most recent match wins; 2 % of the candidates are a history question with
+    one character edited.  Host buffers through dvb_question_gate (H2D, normalise + keys, inverted index, match, D2H)."""
+    import torch
+    from deep_vision_b200 import question_similarity as qs, synth
+    nc, nh, thr = args.gate_candidates, args.gate_history, 0.62
+
+    def questions(n, seed):
+        rng = np.random.default_rng(seed)
+        lens = rng.integers(20, 41, size=n)
+        off = np.zeros(n + 1, np.int64); np.cumsum(lens + 1, out=off[1:])
+        cp = synth.code_points(rng, int(off[-1]))
+        cp[off[1:] - 1] = 0xFF1F
+        return cp, off
+
+    hcp, hoff = questions(nh, 31)
+    ccp, coff = questions(nc, 1000 + rank)
+    rng = np.random.default_rng(5 + rank)
+    pick = np.nonzero(rng.random(nc) < 0.02)[0]
+    src_h = rng.integers(0, nh, size=len(pick))
+    both = np.concatenate([ccp, hcp]); both_off = np.concatenate([coff, hoff[1:] + coff[-1]])
+    which = np.arange(nc, dtype=np.int64); which[pick] = nc + src_h
+    cand_cp, cand_off = _gather_segments(both, both_off, which)
+    cand_cp = cand_cp.copy()
+    cand_cp[cand_off[pick]] = 0x4E00 + rng.integers(0, 3000, size=len(pick)).astype(np.uint32)     # one edit: the first character
+    cu, cbo = synth.utf8_encode(cand_cp); co = cbo[cand_off]
+    hu, hbo = synth.utf8_encode(hcp); ho = hbo[hoff]
+    gate = qs.QuestionGate(ctx=ctx)
+    wall, dev, out = [], [], None
+    for _ in range(3):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        out = gate.match(None, None, thr, packed=(cu, co, hu, ho))
+        torch.cuda.synchronize(); wall.append(1000.0 * (time.perf_counter() - t0)); dev.append(ctx.last_kernel_ms)
+    parity = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oracle import dv_oracle        # checker (allowed use)
+        dv_oracle.build()
+        og = dv_oracle.Gate(qs.DEFAULT_SYNONYMS, qs.DEFAULT_STOPWORDS)
+        cb = cu.tobytes()
+        sel = np.unique(np.concatenate([pick[:150], np.arange(0, nc, max(1, nc // 150))[:150]]))
+        cu2, co2 = dv_oracle.pack([cb[co[i]:co[i + 1]].decode("utf-8") for i in sel])
+        t0 = time.perf_counter()
+        want = np.asarray(og.gate(None, None, thr, n_threads=os.cpu_count() or 1, packed=(cu2, co2, hu, ho)), np.int64)
+        parity = {"vs": "oracle C gate: %d candidates (150 planted near-duplicates) x all %d history questions" % (len(sel), nh),
+                  "match_index_identical": bool(np.array_equal(want, out[sel])), "planted_recalled": int((out[pick] >= 0).sum()),
+                  "planted": int(len(pick)), "seconds": time.perf_counter() - t0}
+    in_bytes = int(co[-1] + ho[-1])
+    return {"candidates_per_gpu": nc, "history": nh, "threshold": thr, "call_ms": min(wall), "device_ms": min(dev),
+            "matches": int((out >= 0).sum()), "input_bytes": in_bytes, "algorithmic_bytes_lower_bound": in_bytes + 8 * nc, "parity": parity}
+
+
+def latency_arm(ctx):
+    """Config 1 (the only shape a live request has): per-call latency of the three drop-in-bound functions on the
+    fixtures session — 8 bindable claims x 31 facts (tests/golden/a2_bind.json, pack C1), the reference's own tail-recall
+    document (tests/test_api_comprehensive.py:3754-3806, 8 chunks), 60 history questions (tests/golden/a8_a9_gate.json)."""
+    import types
+    from deep_vision_b200 import dropin
+    gold = ROOT / "tests" / "golden"
+    a2 = json.loads((gold / "a2_bind.json").read_text(encoding="utf-8"))
+    g9 = json.loads((gold / "a8_a9_gate.json").read_text(encoding="utf-8"))
+    mod = types.SimpleNamespace(load_reference_material_chunks=None)
+    b = dropin.build_bindings(mod, ctx)
+    pack = a2["packs"]["C1"]
+    cases = [c for c in a2["cases"] if c["pack"] == "C1" and c["field"] in ("risks", "actions", "open_questions")]
+    doc_text = "开头普通说明。" * 1800 + "\n\n尾部关键需求：必须支持离线审批和断网补录，并保留审批链路证据。"
+    chunks = b["_build_reference_material_chunks"](doc_text)
+    mod.load_reference_material_chunks = lambda doc: chunks
+    logs = [{"question": h} for h in g9["history"]]
+
+    def pct(us):
+        us = np.sort(np.asarray(us))
+        return {"p50_us": float(us[len(us) // 2]), "p99_us": float(us[min(len(us) - 1, int(len(us) * 0.99))]), "calls": int(len(us))}
+
+    out, ok = {}, True
+    t = []
+    for rep in range(40):
+        for c in cases:
+            t0 = time.perf_counter(); r = b["infer_weak_evidence_refs_v3"](c["field"], c["item"], pack, c["min_score"]); t.append(1e6 * (time.perf_counter() - t0))
+            ok = ok and r == c["result"]
+    out["infer_weak_evidence_refs_v3"] = dict(pct(t[len(cases):]), shape="%d claims x %d facts, one call per claim" % (len(cases), len(pack["facts"])),
+                                             equals_reference_golden=bool(ok))
+    t = []
+    for rep in range(200):
+        t0 = time.perf_counter(); ctx_text, meta = b["select_reference_material_context"]({"doc_id": "d"}, query_text="离线审批能力验证", chunk_limit=4)
+        t.append(1e6 * (time.perf_counter() - t0))
+    out["select_reference_material_context"] = dict(pct(t[5:]), shape="%d chunks, 1 query" % len(chunks),
+                                                   tail_chunk_selected=bool(meta["selected_chunks"] and meta["selected_chunks"][-1]["index"] == len(chunks) - 1))
+    t, hits = [], 0
+    for rep in range(3):
+        for i, cand in enumerate(g9["candidates"]):
+            t0 = time.perf_counter(); r = b["find_similar_interview_question_log"](logs, cand, g9["threshold"]); t.append(1e6 * (time.perf_counter() - t0))
+            want = g9["match"][i]
+            ok_i = (r is None and want < 0) or (r is not None and want >= 0 and r is logs[want])
+            hits += 1 if ok_i else 0
+    out["find_similar_interview_question_log"] = dict(pct(t[5:]), shape="%d history questions" % len(logs),
+                                                     equals_reference_golden=bool(hits == len(t)))
+    return out
+
+
+def python_api_arm(ctx, args):
+    """What a drop-in caller pays: evidence.bind_batch from Python dicts (packing, pageable numpy buffers, H2D, kernel,
+    D2H, result dicts) on a bounded config-2 sample."""
+    from deep_vision_b200 import evidence, synth
+    ns = min(args.sessions, 500)
+    c = synth.make_sessions(ns, turns=args.turns, claims_per_session=args.claims, seed=synth.SEED + 77)
+    claims, facts = c.texts()
+    fields = ["risks", "actions", "open_questions"]
+    keys = {"risks": "risk", "actions": "action", "open_questions": "question"}
+    requests = []
+    for s_ in range(ns):
+        f0, f1 = int(c.sess_fact_off[s_]), int(c.sess_fact_off[s_ + 1])
+        pack = {"facts": [{"q_id": "Q%d" % (i - f0 + 1), "question": facts[i][:41], "answer": facts[i][41:], "dimension": synth.DIMENSIONS[int(c.fact_dim[i])],
+                           "quality_score": float(c.fact_quality[i]), "hard_triggered": bool(c.fact_hard[i])} for i in range(f0, f1)]}
+        for j in range(int(c.sess_claim_off[s_]), int(c.sess_claim_off[s_ + 1])):
+            fld = fields[(j - int(c.sess_claim_off[s_])) * 3 // max(1, args.claims)]
+            requests.append((fld, {keys[fld]: claims[j]}, pack, 0.46))
+    evidence.bind_batch(requests, ctx=ctx)
+    wall = []
+    for _ in range(3):
+        t0 = time.perf_counter(); res = evidence.bind_batch(requests, ctx=ctx); wall.append(time.perf_counter() - t0)
+    pairs = ns * args.turns * args.claims
+    return {"value": pairs / min(wall), "unit": UNIT, "sample": "%d sessions (%d pairs) as Python dicts through evidence.bind_batch, pageable buffers" % (ns, pairs),
+            "ms_per_call": 1000.0 * min(wall), "bound_claims": int(sum(1 for r in res if r["refs"]))}
 
 
 class ClockSampler:
@@ -336,31 +520,93 @@ def main():
     h2d = int(sum(a.nbytes for a in host_in)) - 64 * 2
     d2h = n_claims * (4 + 8 + 1)
 
-    # ---------------- chunks indexed/s on a bounded config-3 sample (every rank indexes its own shard)
+    # the corpus of the headline arm is no longer needed on the device
+    del dev_in, pinned, pin_np
+    torch.cuda.empty_cache()
+    ctx.set_stream(None)                                          # the arms below run on the library's own streams
+
+    def index_traffic():
+        p_ = ROOT / "profiles" / "index_traffic.json"
+        try:
+            return json.loads(p_.read_text()).get("dram_bytes_per_build")
+        except Exception:
+            return None
+
+    # ---------------- config 3: chunks indexed/s + indexed top-8 (every rank indexes its own shard)
     index = None
     if args.index_chunks > 0:
         try:
             mine = index_arm(ctx, args, rank, world)
         except Exception as exc:                                  # the headline line must survive a failure here
-            mine = {"error": repr(exc)[:200]}
+            mine = {"error": repr(exc)[:300]}
         ok = reduce_max(1.0 if "error" in mine else 0.0) == 0.0
         if ok:
-            b_ms, q_ms = reduce_max(mine["build_ms"]), reduce_max(mine["query_ms_1000_queries"])
+            b_ms, q_ms = reduce_max(mine["build_ms"]), reduce_max(mine["query_ms"])
             peak_i, _src = measured_peak()
+            nq = mine["queries"]
             index = {"metric": "chunks_indexed_per_s", "value": world * mine["chunks_per_gpu"] / (b_ms / 1000.0), "unit": "chunks/s",
-                     "workload": "config3 sample: %d chunks/GPU x 512 chars resident in HBM -> positional index (dvb_chunk_index_build)" % mine["chunks_per_gpu"],
+                     "workload": "config3: %d chunks/GPU x 512 chars resident in HBM -> positional index (dvb_chunk_index_build); %d claim queries, top-8"
+                                 % (mine["chunks_per_gpu"], nq),
                      "build_ms": b_ms, "first_build_ms": mine["first_build_ms"], "postings_per_gpu": mine["postings"],
                      "roofline": {"bound": "hbm", "achieved": mine["algorithmic_bytes"] / (b_ms / 1000.0) / 1e9, "peak": peak_i, "unit": "GB/s",
                                   "frac": mine["algorithmic_bytes"] / (b_ms / 1000.0) / 1e9 / peak_i,
-                                  "algorithmic_bytes": mine["algorithmic_bytes"], "note": "UTF-8 in + 4 B per posting (SURVEY 8d); the build is 4 radix passes over 12 B postings"},
-                     "query": {"effective_pairs_per_s": world * mine["chunks_per_gpu"] * 1000 / (q_ms / 1000.0), "ms_per_1000_queries": q_ms, "k": 8}}
+                                  "algorithmic_bytes": mine["algorithmic_bytes"], "traffic": index_traffic(),
+                                  "note": "UTF-8 in + 4 B per posting (SURVEY 8d) over the whole build (symbolise, emit, radix sort, heads)"},
+                     "query": {"effective_pairs_per_s": world * mine["chunks_per_gpu"] * nq / (q_ms / 1000.0), "queries": nq, "device_ms": q_ms, "k": 8,
+                               "ms_per_1000_queries": q_ms * 1000.0 / nq,
+                               "roofline": {"bound": "hbm", "achieved": mine["query_algorithmic_bytes_lower_bound"] / (q_ms / 1000.0) / 1e9, "peak": peak_i,
+                                            "unit": "GB/s", "frac": mine["query_algorithmic_bytes_lower_bound"] / (q_ms / 1000.0) / 1e9 / peak_i,
+                                            "algorithmic_bytes": mine["query_algorithmic_bytes_lower_bound"], "traffic": None,
+                                            "note": "lower bound: 8 B per term occurrence in the RETURNED top-k chunks + 16 B x k out (SURVEY 8d counts every chunk; the kernel is bound by dependent-load latency, DESIGN.md section 4)"},
+                               "host_tokenize_s": mine["host_tokenize_s"], "host_symbols_s": mine["host_symbols_s"]},
+                     "host_gen_s": mine["host_gen_s"], "parity": mine["parity"]}
             if mine.get("sharded"):
-                sh = dict(mine["sharded"])
-                sh["ms_1000_queries_allgather_merge"] = reduce_max(sh["ms_1000_queries_allgather_merge"])
-                sh["effective_pairs_per_s"] = world * mine["chunks_per_gpu"] * 1000 / (sh["ms_1000_queries_allgather_merge"] / 1000.0)
+                sh = {}
+                for label, d in mine["sharded"].items():
+                    d = dict(d)
+                    d["ms_with_allgather_merge_and_d2h"] = reduce_max(d["ms_with_allgather_merge_and_d2h"])
+                    d["local_device_ms"] = reduce_max(d["local_device_ms"])
+                    d["effective_pairs_per_s"] = world * mine["chunks_per_gpu"] * d["queries"] / (d["ms_with_allgather_merge_and_d2h"] / 1000.0)
+                    d["efficiency"] = d["local_device_ms"] / d["ms_with_allgather_merge_and_d2h"]     # sharded rate / (N x the local rate)
+                    sh[label] = d
                 index["query"]["sharded_topk"] = sh
         else:
             index = {"error": mine.get("error", "failed on another rank")}
+
+    # ---------------- config 4: question-similarity gate (history replicated, candidates partitioned, no exchange)
+    gate = None
+    if args.gate_candidates > 0:
+        try:
+            mine = gate_arm(ctx, args, rank, world)
+        except Exception as exc:
+            mine = {"error": repr(exc)[:300]}
+        ok = reduce_max(1.0 if "error" in mine else 0.0) == 0.0
+        if ok:
+            c_ms, d_ms = reduce_max(mine["call_ms"]), reduce_max(mine["device_ms"])
+            peak_g, _src = measured_peak()
+            gate = {"metric": "gate_candidates_per_s", "value": world * mine["candidates_per_gpu"] / (c_ms / 1000.0), "unit": "candidates/s",
+                    "workload": "config4: %d candidate questions/GPU vs %d history questions, char-bigram Jaccard >= %.2f, host buffers through dvb_question_gate"
+                                % (mine["candidates_per_gpu"], mine["history"], mine["threshold"]),
+                    "effective_pairs_per_s": world * mine["candidates_per_gpu"] * mine["history"] / (c_ms / 1000.0),
+                    "call_ms": c_ms, "device_ms": d_ms, "matches_per_gpu": mine["matches"],
+                    "roofline": {"bound": "hbm", "achieved": mine["algorithmic_bytes_lower_bound"] / (d_ms / 1000.0) / 1e9, "peak": peak_g, "unit": "GB/s",
+                                 "frac": mine["algorithmic_bytes_lower_bound"] / (d_ms / 1000.0) / 1e9 / peak_g,
+                                 "algorithmic_bytes": mine["algorithmic_bytes_lower_bound"], "traffic": None,
+                                 "note": "inputs once + 8 B out per candidate; the postings term of SURVEY 8d is not counted (lower bound); limiter: issue / shared-memory, see profiles/"},
+                    "parity": mine["parity"]}
+        else:
+            gate = {"error": mine.get("error", "failed on another rank")}
+
+    latency = api = None
+    if rank == 0 and not args.no_latency:
+        try:
+            latency = latency_arm(ctx)
+        except Exception as exc:
+            latency = {"error": repr(exc)[:300]}
+        try:
+            api = python_api_arm(ctx, args)
+        except Exception as exc:
+            api = {"error": repr(exc)[:300]}
 
     pairs_all = corpus.n_pairs * world
     value = pairs_all * args.steps / (elapsed_ms / 1000.0)
@@ -381,12 +627,19 @@ def main():
                              "traffic": ncu_traffic(), "kernel": "k_bind_claims", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": corpus.algorithmic_bytes,
                              "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src,
-                             "limiter": "instruction issue, not DRAM: 3.8 warp instructions per input byte, 69 % of the issue slots busy, "
-                                        "DRAM traffic 1.03 x algorithmic (profiles/r01_bind_v6_config2_ncu_full.json; DESIGN.md section 5)"},
+                             "limiter": "instruction issue, not DRAM: 2.6 warp instructions per input byte at 22 of 32 lanes, 0.5 issued per scheduler "
+                                        "cycle with 5.8 resident warps, DRAM traffic 1.03 x algorithmic (profiles/r02_bind7_v2_ncu_full.json, "
+                                        "profiles/r02_bind_ladder.json; DESIGN.md section 5)"},
                 "clocks": clocks,
                 "pairs_per_step_per_gpu": corpus.n_pairs}
         if index is not None:
             line["index"] = index
+        if gate is not None:
+            line["gate"] = gate
+        if latency is not None:
+            line["latency"] = latency
+        if api is not None:
+            line["e2e_python_api"] = api
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             v, secs, passes = cpu_baseline(corpus, cores, repeats=2, min_seconds=10.0)

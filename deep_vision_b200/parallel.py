@@ -164,3 +164,38 @@ def sharded_index_topk(index, queries_terms: Sequence[Sequence[str]], k: int, gr
     Local indexed top-k -> one all-gather of nq x k candidates -> merge (dvb_topk).  Identical on every rank."""
     li, ls, _ln = index.topk(queries_terms, k)
     return merge_topk(li, ls, k, group=group, ctx=index.ctx, topk_fn=topk_fn)
+
+
+def terms_to_device(queries_terms: Sequence[Sequence[str]], device=None):
+    """terms_to_symbols() of a query set, moved to the GPU once (reused by every sharded_index_topk_device call on it)."""
+    import torch
+    tsym, toff, qoff = rm.terms_to_symbols(queries_terms)
+    dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    return tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (tsym, toff, qoff))
+
+
+def sharded_index_topk_device(index, dev_terms, nq: int, k: int, group=None):
+    """Config 3/5 with the candidates kept on the device (web/server.py:32083-32099 over a sharded corpus): local indexed
+    top-k (dvb_chunk_index_topk, DVB_MEM_DEVICE) -> ONE all_gather_into_tensor of nq x k x 16 B (global index i64, score
+    widened to i64) over NCCL -> dvb_topk(DVB_MEM_DEVICE) on the gathered lists -> only the final [nq, k] crosses PCIe.
+    Returns numpy (idx, score, n_valid), identical on every rank."""
+    import torch
+    dist = _dist()
+    _rank, ws = world(group)
+    li, ls, ln = index.topk_device(dev_terms, nq, k)
+    if ws == 1 or nq == 0:
+        return li.cpu().numpy(), ls.cpu().numpy(), ln.cpu().numpy()
+    mine = torch.stack([li, ls.to(torch.int64)], dim=2).contiguous()              # [nq, k, 2] i64
+    allc = torch.empty((ws, nq, k, 2), dtype=torch.int64, device=mine.device)
+    dist.all_gather_into_tensor(allc, mine, group=group)
+    idx_all = allc[..., 0].permute(1, 0, 2).reshape(nq, ws * k).contiguous()
+    sc_all = allc[..., 1].permute(1, 0, 2).reshape(nq, ws * k).to(torch.int32).contiguous()
+    oi = torch.empty((nq, k), dtype=torch.int64, device=mine.device)
+    os_ = torch.empty((nq, k), dtype=torch.int32, device=mine.device)
+    on = torch.empty((nq,), dtype=torch.int32, device=mine.device)
+    ctx = index.ctx
+    torch.cuda.current_stream(mine.device).synchronize()                           # the library runs on its own stream
+    rc = ctx.lib.dvb_topk(ctx.handle, rm._lib.MEM_DEVICE, sc_all.data_ptr(), idx_all.data_ptr(), ws * k, nq, 0, k,
+                          oi.data_ptr(), os_.data_ptr(), on.data_ptr())
+    ctx.check(rc, "dvb_topk")
+    return oi.cpu().numpy(), os_.cpu().numpy(), on.cpu().numpy()

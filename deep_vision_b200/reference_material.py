@@ -463,6 +463,24 @@ class ChunkIndex:
             self.ctx.check(rc, "dvb_chunk_index_topk")
         return oi[:nq], os_[:nq], on[:nq]
 
+    def topk_device(self, dev_terms, nq: int, k: int):
+        """Same as topk() with everything resident: dev_terms = (term_sym u16, term_off i32, query_term_off i32) torch CUDA
+        tensors (terms_to_symbols() moved to the device once per query set); returns (idx[nq, k] i64, score[nq, k] i32,
+        n_valid[nq] i32) torch CUDA tensors — nothing crosses PCIe (config 3/5: the candidates go straight into the
+        all-gather, parallel.sharded_index_topk_device)."""
+        import torch
+        tsym, toff, qoff = dev_terms
+        dev = tsym.device
+        oi = torch.empty((max(nq, 1), k), dtype=torch.int64, device=dev)
+        os_ = torch.empty((max(nq, 1), k), dtype=torch.int32, device=dev)
+        on = torch.empty((max(nq, 1),), dtype=torch.int32, device=dev)
+        if nq:
+            torch.cuda.current_stream(dev).synchronize()         # the library runs on its own stream
+            rc = self.ctx.lib.dvb_chunk_index_topk(self.ctx.handle, self._h, _lib.MEM_DEVICE, tsym.data_ptr(), toff.data_ptr(), int(toff.numel()) - 1,
+                                                   qoff.data_ptr(), int(nq), self.index_base, int(k), oi.data_ptr(), os_.data_ptr(), on.data_ptr())
+            self.ctx.check(rc, "dvb_chunk_index_topk")
+        return oi[:nq], os_[:nq], on[:nq]
+
     def close(self):
         if self._h:
             self.ctx.lib.dvb_chunk_index_free(self._h)
