@@ -23,6 +23,7 @@ _SIGS = {
     "dvb_destroy": (None, [_vp]),
     "dvb_last_error": (C.c_char_p, [_vp]),
     "dvb_version": (C.c_int32, []),
+    "dvb_unicode_version": (C.c_char_p, []),
     "dvb_launch_count": (C.c_int64, [_vp]),
     "dvb_set_timing": (None, [_vp, C.c_int32]),
     "dvb_last_kernel_ms": (C.c_float, [_vp]),

@@ -1,7 +1,10 @@
 // api.cu — ctx lifecycle for libdvb200.so.  No CPU fallback: dvb_create fails without a CUDA device.
 #include "common.cuh"
 
-extern "C" int32_t dvb_version(void) { return 100; }
+#include "../../include/dv_unicode_tables.h"
+
+extern "C" int32_t dvb_version(void) { return 101; }
+extern "C" const char* dvb_unicode_version(void) { return DV_UNICODE_VERSION; }
 
 extern "C" int32_t dvb_create(int32_t device, dvb_ctx** out) {
     if (!out) return DVB_E_INVALID;

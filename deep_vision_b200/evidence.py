@@ -206,11 +206,25 @@ def bind_packed(ctx: "_lib.Context", claim_utf8, claim_off, fact_utf8, fact_off,
     return out
 
 
+def result_from_raw(field: str, min_score: Any, raw: Optional[Tuple[str, float, str]], evidence_pack: dict,
+                    config: WeakBindingConfig = DEFAULT_CONFIG) -> dict:
+    """The reference's last step (web/server.py:24848-24864) on a stored raw answer (q_id of the first best fact, unrounded
+    fp64 score, preferred dimension): the best fact and its score do not depend on min_score, only the bound decision does."""
+    if raw is None:
+        return {"refs": [], "score": 0.0}
+    qid, score, preferred = raw
+    threshold = binding_threshold(field, min_score, preferred, evidence_pack, config)
+    return {"refs": [qid] if not (score + 1e-9 < threshold) else [], "score": round(score, 3)}
+
+
 def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakBindingConfig = DEFAULT_CONFIG,
-               ctx: Optional["_lib.Context"] = None, dimension_resolver=None) -> List[dict]:
+               ctx: Optional["_lib.Context"] = None, dimension_resolver=None, raw: bool = False) -> List[Any]:
     """Batch form of infer_weak_evidence_refs_v3: one kernel launch for all (field, item, pack, min_score).
-    Requests that share an evidence_pack object share one device session."""
-    results: List[Optional[dict]] = [None] * len(requests)
+    Requests that share an evidence_pack object share one device session.
+    raw=True returns, per request, (q_id, unrounded score, preferred dimension) or None instead of the result dict
+    (see result_from_raw; the drop-in's a3 wrapper stores these for one repair pass)."""
+    results: List[Any] = [None] * len(requests)
+    prefs: Dict[int, str] = {}
     resolver = dimension_resolver or infer_item_dimension_key
     sessions: Dict[int, Tuple[_Session, List[Tuple[int, str, int, float]]]] = {}
     order: List[int] = []
@@ -230,6 +244,7 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
         sess, claims = sessions[key]
         claim_text = " ".join(_text(item.get(k, "")) for k in CLAIM_TEXT_FIELDS[field])
         preferred = resolver(field, item, pack)
+        prefs[i] = preferred
         pref_id = -1
         if preferred:
             pref_id = sess.dim_ids.get(preferred, 1 << 30)       # a dimension no fact carries never matches
@@ -265,12 +280,16 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
             sess, claims = sessions[k]
             for (i, _t, _p, _th) in claims:
                 bf = int(out["best_fact"][pos])
-                if bf < 0:
+                if raw:
+                    results[i] = (sess.qids[bf], float(out["best_score"][pos]), prefs[i]) if bf >= 0 else None
+                elif bf < 0:
                     results[i] = {"refs": [], "score": 0.0}
                 else:
                     sc = round(float(out["best_score"][pos]), 3)
                     results[i] = {"refs": [sess.qids[bf]] if out["bound"][pos] else [], "score": sc}
                 pos += 1
+    if raw:
+        return [r if isinstance(r, tuple) else None for r in results]
     return [r if r is not None else {"refs": [], "score": 0.0} for r in results]
 
 

@@ -53,6 +53,9 @@ int32_t     dvb_create(int32_t device, dvb_ctx** out);
 void        dvb_destroy(dvb_ctx* ctx);
 const char* dvb_last_error(dvb_ctx* ctx);           /* valid until the next call on ctx from this thread */
 int32_t     dvb_version(void);
+/* Unicode version of the case / class tables compiled into the library (CPython's unicodedata.unidata_version at
+ * generation time): str.lower() of web/server.py:24723, 32039, 20463 must agree with the host interpreter's. */
+const char* dvb_unicode_version(void);
 /* number of library kernels launched on this ctx since creation (bench.py's gpu_launches) */
 int64_t     dvb_launch_count(dvb_ctx* ctx);
 /* device time (ms) of the dominant kernel of the most recent call on this ctx, measured with CUDA

@@ -116,11 +116,13 @@ def load(extra_names: Iterable[str] = (), overrides: Optional[Dict[str, Any]] = 
             ns.update(overrides)
         names = HOT_PATH_NAMES + extra_names
         found = {}
+        nodes = []                                     # a constant may be assigned twice (value, then its clamp): keep every node
         for name, node in _toplevel_nodes(tree, names):
             found[name] = node
+            nodes.append((name, node))
         missing = [n for n in names if n not in found]
         # execute in source order so constants precede their users
-        for name, node in sorted(found.items(), key=lambda kv: kv[1].lineno):
+        for name, node in sorted(nodes, key=lambda kv: kv[1].lineno):
             mod = ast.Module(body=[node], type_ignores=[])
             code = compile(mod, filename=str(SERVER_PY), mode="exec")
             exec(code, ns)  # noqa: S102 - executing the read-only reference on purpose
