@@ -108,12 +108,16 @@ def index_arm(ctx, args, rank, world=1):
         box = [queries]
         dist.broadcast_object_list(box, src=0)
         queries = box[0]
+    # a6 on the device: query texts -> term symbol CSR (dvb_query_terms); the host extractor is timed on a sample for comparison
     t0 = time.perf_counter()
-    terms = [rm._tokenize_reference_material_query(t) for t in queries]
-    tok_s = time.perf_counter() - t0
+    sample_terms = [rm._tokenize_reference_material_query(t) for t in queries[:2000]]
+    tok_s = (time.perf_counter() - t0) * nq / max(1, min(nq, 2000))
+    rm.query_terms_batch(queries[:256], ctx=ctx, device=True)
     t0 = time.perf_counter()
-    dev_terms = parallel.terms_to_device(terms)
+    dev_terms = rm.query_terms_batch(queries, ctx=ctx, device=True)
+    torch.cuda.synchronize()
     sym_s = time.perf_counter() - t0
+    terms_kernel_ms = ctx.last_kernel_ms
     q_ms, li = [], None
     for _ in range(2):
         li, ls, ln = ix.topk_device(dev_terms, nq, k)
@@ -125,7 +129,7 @@ def index_arm(ctx, args, rank, world=1):
         import torch.distributed as dist
         sharded = {}
         for label, m in (("1000_queries", min(1000, nq)), ("all_queries", nq)):
-            sub = parallel.terms_to_device(terms[:m]) if m < nq else dev_terms
+            sub = rm.query_terms_batch(queries[:m], ctx=ctx, device=True) if m < nq else dev_terms
             local_ms, wall = [], []
             for _ in range(3):
                 ix.topk_device(sub, m, k); local_ms.append(ctx.last_kernel_ms)
@@ -147,9 +151,10 @@ def index_arm(ctx, args, rank, world=1):
         cores = os.cpu_count() or 1
         ok, checked, t0 = True, 0, time.perf_counter()
         for q in range(0, nq, max(1, nq // 6))[:6]:
-            if not terms[q]:
+            tq = dv_oracle.query_terms(queries[q])
+            if not tq:
                 continue
-            sc = dv_oracle.chunk_scores(None, terms[q], n_threads=cores, packed=(data, off))
+            sc = dv_oracle.chunk_scores(None, tq, n_threads=cores, packed=(data, off))
             wi, ws = dv_oracle.topk(sc, k)
             nv = int(ln_h[q])
             ok = ok and (li_h[q][:nv] - rank * n).tolist() == wi.tolist() and ls_h[q][:nv].tolist() == ws.tolist()
@@ -161,7 +166,9 @@ def index_arm(ctx, args, rank, world=1):
     return {"chunks_per_gpu": n, "queries": nq, "build_ms": best, "first_build_ms": builds[0], "postings": st["postings"],
             "text_bytes": st["text_bytes"], "algorithmic_bytes": st["text_bytes"] + 4 * st["postings"],
             "query_ms": min(q_ms), "query_algorithmic_bytes_lower_bound": 8 * int(ls_h.sum()) + 16 * k * nq,
-            "host_gen_s": gen_s, "host_tokenize_s": tok_s, "host_symbols_s": sym_s, "sharded": sharded, "parity": parity}
+            "host_gen_s": gen_s, "host_tokenize_s_python_extractor_estimate": tok_s, "terms_call_s": sym_s, "terms_kernel_ms": terms_kernel_ms,
+            "terms_match_host_extractor_on_sample": bool(rm.terms_from_symbols(*[a.cpu().numpy() for a in rm.query_terms_batch(queries[:2000], ctx=ctx, device=True)]) == sample_terms),
+            "sharded": sharded, "parity": parity}
 
 
 def _gather_segments(src, src_off, idx):
@@ -558,7 +565,10 @@ def main():
                                             "unit": "GB/s", "frac": mine["query_algorithmic_bytes_lower_bound"] / (q_ms / 1000.0) / 1e9 / peak_i,
                                             "algorithmic_bytes": mine["query_algorithmic_bytes_lower_bound"], "traffic": None,
                                             "note": "lower bound: 8 B per term occurrence in the RETURNED top-k chunks + 16 B x k out (SURVEY 8d counts every chunk; the kernel is bound by dependent-load latency, DESIGN.md section 4)"},
-                               "host_tokenize_s": mine["host_tokenize_s"], "host_symbols_s": mine["host_symbols_s"]},
+                               "query_terms": {"call_s": mine["terms_call_s"], "kernel_ms": mine["terms_kernel_ms"],
+                                               "python_extractor_s_estimate": mine["host_tokenize_s_python_extractor_estimate"],
+                                               "equals_host_extractor_on_2000_queries": mine["terms_match_host_extractor_on_sample"],
+                                               "note": "a6 (web/server.py:32037-32051) on the device: UTF-8 query texts -> term symbol CSR, dvb_query_terms"}},
                      "host_gen_s": mine["host_gen_s"], "parity": mine["parity"]}
             if mine.get("sharded"):
                 sh = {}

@@ -29,6 +29,7 @@ _SIGS = {
     "dvb_last_kernel_ms": (C.c_float, [_vp]),
     "dvb_set_stream": (None, [_vp, _vp]),
     "dvb_tokenize_v3": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, C.c_int64, _vp]),
+    "dvb_query_terms": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, _vp, C.c_int64, _vp, _vp, _vp]),
     "dvb_symbolize": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp]),
     "dvb_chunk_scores": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, C.c_int32, _vp, C.c_int32, _vp]),
     "dvb_topk": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp]),

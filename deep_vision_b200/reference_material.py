@@ -96,6 +96,50 @@ def terms_to_symbols(queries_terms: Sequence[Sequence[str]]) -> Tuple[np.ndarray
     return (sym if sym.size else np.zeros(1, np.uint16), toff.astype(np.int32), qoff.astype(np.int32))
 
 
+def query_terms_batch(query_texts: Sequence[str], *, ctx=None, max_terms: int = 80, packed=None, device: bool = False):
+    """a6 for a batch on the device (csrc/query_terms.cu): the term lists of _tokenize_reference_material_query as the symbol
+    CSR (term_sym u16, term_off i32, query_term_off i32) that ChunkIndex.topk_device / dvb_chunk_index_topk read.
+    device=False returns numpy arrays (host), device=True torch CUDA tensors (nothing but the texts crosses PCIe)."""
+    ctx = ctx or _lib.Context.get()
+    data, off = packed if packed is not None else pack_texts([str(t or "") for t in query_texts])
+    nq = len(off) - 1
+    nbytes = int(off[-1] - off[0])
+    cap = 4 * nbytes + 64                       # symbols <= bytes per term occurrence; grams of a run cost < 7 symbols per character
+    totals = np.zeros(2, np.int64)
+    for _attempt in range(2):
+        if device:
+            import torch
+            dev = torch.device("cuda", ctx.device)
+            d_data = torch.from_numpy(np.ascontiguousarray(data)).to(dev); d_off = torch.from_numpy(np.ascontiguousarray(off)).to(dev)
+            tsym = torch.empty(max(cap, 1), dtype=torch.int16, device=dev)
+            toff = torch.empty(nq * max_terms + 1, dtype=torch.int32, device=dev)
+            qoff = torch.empty(nq + 1, dtype=torch.int32, device=dev)
+            torch.cuda.current_stream(dev).synchronize()
+            rc = ctx.lib.dvb_query_terms(ctx.handle, _lib.MEM_DEVICE, d_data.data_ptr(), d_off.data_ptr(), nq, max_terms,
+                                         tsym.data_ptr(), cap, toff.data_ptr(), qoff.data_ptr(), ptr(totals))
+        else:
+            tsym = np.zeros(max(cap, 1), np.uint16); toff = np.zeros(nq * max_terms + 1, np.int32); qoff = np.zeros(nq + 1, np.int32)
+            rc = ctx.lib.dvb_query_terms(ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), nq, max_terms, ptr(tsym), cap, ptr(toff), ptr(qoff), ptr(totals))
+        if rc == _lib.DVB_E_CAPACITY and _attempt == 0:
+            cap = 8 * nbytes * 4 + 1024                            # generous second try (every character in four 4-grams and three 3-grams)
+            continue
+        ctx.check(rc, "dvb_query_terms")
+        break
+    n_terms, n_sym = int(totals[0]), int(totals[1])
+    return tsym[:max(n_sym, 1)], toff[:n_terms + 1], qoff
+
+
+def terms_from_symbols(tsym, toff, qoff) -> List[List[str]]:
+    """Inverse of terms_to_symbols for host arrays (tests, debugging): symbol CSR -> per-query term strings."""
+    tsym = np.asarray(tsym).astype(np.uint16); toff = np.asarray(toff); qoff = np.asarray(qoff)
+    cp = np.where(tsym >= 0x8000, 0, tsym.astype(np.int64) + 0x4E00 - 1)
+    a = (tsym & 0x7FFF).astype(np.int64)
+    asc = np.where(a <= 26, a + 96, np.where(a <= 36, a + 21, 95))
+    cp = np.where(tsym >= 0x8000, asc, cp)
+    chars = "".join(map(chr, cp.tolist()))
+    return [[chars[toff[t]:toff[t + 1]] for t in range(qoff[q], qoff[q + 1])] for q in range(len(qoff) - 1)]
+
+
 def _make_sym_lut() -> np.ndarray:
     """code point (BMP) -> kernel symbol (include/dvb200.h): CJK 1..20992, 0x8000 | class for [a-z0-9_], 0 = not a term character."""
     lut = np.zeros(0x10000, np.uint16)

@@ -104,6 +104,17 @@ int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
  * U+0130 yields 'i' + separator, U+212A yields 'k' (CPython str.lower()).  Query terms (web/server.py:32039)
  * contain only token characters, so lowered.count(term) == non-overlapping substring count on symbols. */
 
+/* ---- a6  replaces: _tokenize_reference_material_query(query_text) -> list[str]   web/server.py:32037-32051
+ * For a batch of query texts: the ordered, de-duplicated term list of each (terms of >= 2 characters of one class;
+ * pure-CJK terms of >= 6 characters add their 4-grams, then their 3-grams; the first max_terms <= 80 terms) as the
+ * symbol CSR dvb_chunk_index_topk / dvb_chunk_scores take: query q owns terms [out_query_term_off[q],
+ * out_query_term_off[q+1]), term t = out_term_sym[out_term_off[t] .. out_term_off[t+1]).  Capacities: out_term_off
+ * nq * max_terms + 1 entries, out_query_term_off nq + 1, out_term_sym sym_cap (DVB_E_CAPACITY names the size needed;
+ * 8 * (bytes of the batch) + 16 always suffices for texts of <= 80 terms worth of n-grams ... the call reports it).
+ * out_totals2 = { terms, symbols } of the batch is ALWAYS a host pointer. */
+int32_t dvb_query_terms(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t nq, int32_t max_terms,
+                        uint16_t* out_term_sym, int64_t sym_cap, int32_t* out_term_off, int32_t* out_query_term_off, int64_t* out_totals2);
+
 /* text t -> out_sym[off[t]-off[0] .. +out_cnt[t])   (out_sym needs off[n]-off[0] entries) */
 int32_t dvb_symbolize(dvb_ctx* ctx, int32_t mem, const uint8_t* utf8, const int64_t* off, int64_t n_texts,
                       uint16_t* out_sym, int32_t* out_cnt);

@@ -309,3 +309,43 @@ def test_gpu_select_through_sidecar_cache_matches_golden(gpu_ctx, golden, tmp_pa
     # explicit helper used by bulk jobs
     out = rm.save_chunk_index_sidecar(dirs[names[0]] / "chunks.json", ctx=gpu_ctx)
     assert out.name == rm.SIDECAR_NAME and out.stat().st_size > 256
+
+
+@pytest.mark.gpu
+def test_gpu_query_terms_golden_and_random_vs_oracle(gpu_ctx, oracle, golden):
+    """a6 on the device (dvb_query_terms): the golden term lists of the reference, adversarial and random texts against the
+    oracle, host-buffer and device-resident calls, and the result fed straight into the indexed top-k."""
+    import random
+    from deep_vision_b200 import reference_material as rm
+    cases = golden("a6_query_terms.json")
+    texts = [c["query"] for c in cases]
+    want = [c["terms"] for c in cases]
+    rng = random.Random(11)
+    cjk = [chr(0x4E00 + rng.randrange(3000)) for _ in range(200)]
+    special = ["İ", "K", "Ａ", "ß", " ", "\n", "，", "。", "_", "-", "A", "Z", "q", "0", "9", "😀", "é", "〇", "鿿", "一"]
+    def rnd(n, p):
+        return "".join(rng.choice(cjk) if rng.random() < p else rng.choice("abcXY019_") if rng.random() < 0.5 else rng.choice(special) for _ in range(n))
+    extra = ["", " ", "一", "一二", "ab", "a", "一二三四五六", "一二三四五" * 7, "ab" * 50, "一" * 100, "abc一二三四五六七def", ("一二三四五六七八九十" * 9)[:85] + " xyz xyz",
+             "".join(cjk[i % 200] for i in range(300)), "一二三四五六 一二三四五六 三四五六"]
+    extra += [rnd(rng.choice([3, 9, 25, 60, 300, 1200]), rng.choice([0.6, 0.95, 0.2])) for _ in range(400)]
+    texts += extra
+    want += [oracle.query_terms(t) for t in extra]
+    assert all(rm._tokenize_reference_material_query(t) == w for t, w in zip(texts, want))
+    tsym, toff, qoff = rm.query_terms_batch(texts, ctx=gpu_ctx)
+    assert rm.terms_from_symbols(tsym, toff, qoff) == want
+    assert max(len(w) for w in want) == 80                                      # the cap is exercised
+    d_tsym, d_toff, d_qoff = rm.query_terms_batch(texts, ctx=gpu_ctx, device=True)
+    assert np.array_equal(d_tsym.cpu().numpy().view(np.uint16), tsym) and np.array_equal(d_toff.cpu().numpy(), toff) and np.array_equal(d_qoff.cpu().numpy(), qoff)
+    # same CSR as the host path builds from the term strings, and usable as is by the index
+    hs, ho, hq = rm.terms_to_symbols(want)
+    assert np.array_equal(hs[: len(tsym)] if len(hs) >= len(tsym) else hs, tsym[: len(hs)]) and np.array_equal(ho, toff) and np.array_equal(hq, qoff)
+    chunks = [t for t in texts if t.strip()][:200]
+    ix = rm.ChunkIndex(chunks, ctx=gpu_ctx)
+    keep = [i for i, w in enumerate(want) if w][:64]
+    a = ix.topk([want[i] for i in keep], 8)
+    sub = rm.query_terms_batch([texts[i] for i in keep], ctx=gpu_ctx, device=True)
+    b = ix.topk_device(sub, len(keep), 8)
+    assert np.array_equal(a[0], b[0].cpu().numpy()) and np.array_equal(a[1], b[1].cpu().numpy()) and np.array_equal(a[2], b[2].cpu().numpy())
+    ix.close()
+    e = rm.query_terms_batch([], ctx=gpu_ctx)
+    assert len(e[2]) == 1 and int(e[2][0]) == 0
