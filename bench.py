@@ -279,6 +279,38 @@ def latency_arm(ctx):
     return out
 
 
+def annot_arm(ctx, args):
+    """Bulk re-index path (a11-a14): turns annotated/s through annotations.backfill_sessions on config-2-sized sessions (40
+    turns each) — three launches per batch (text features, option containment, decision stage) + Python dict extraction and
+    write-back — checked against the plain-Python restatement (oracle/dv_annot.py) on a sample, which is also the CPU row."""
+    import copy
+    import random
+    sys.path.insert(0, str(ROOT / "tools"))
+    from make_golden_annot import make_log
+    from deep_vision_b200 import annotations as an
+    rng = random.Random(5)
+    ns = 1000
+    sessions = [{"session_id": "s%d" % s_, "interview_log": [make_log(rng) for _ in range(args.turns)]} for s_ in range(ns)]
+    an.backfill_sessions(copy.deepcopy(sessions[:32]), ctx=ctx)
+    work = copy.deepcopy(sessions)
+    l0 = ctx.launches
+    t0 = time.perf_counter()
+    got = an.backfill_sessions(work, ctx=ctx)
+    dt = time.perf_counter() - t0
+    out = {"metric": "turns_annotated_per_s", "value": ns * args.turns / dt, "unit": "turns/s", "sessions": ns, "turns": ns * args.turns,
+           "seconds": dt, "kernel_launches": int(ctx.launches - l0),
+           "workload": "%d synthetic sessions x %d interview-log turns (question, answer, options) through backfill_sessions" % (ns, args.turns)}
+    if not args.no_cpu_baseline:
+        from oracle import dv_annot          # checker (allowed use): plain-Python restatement of web/server.py:21221-21584
+        sample = copy.deepcopy(sessions[:100])
+        t0 = time.perf_counter()
+        want = [dv_annot.backfill(s_) for s_ in sample]
+        cpu = time.perf_counter() - t0
+        out["parity"] = {"vs": "oracle/dv_annot.py on 100 sessions", "summaries_and_logs_identical": bool(got[:100] == want and work[:100] == sample)}
+        out["cpu_baseline"] = {"value": 100 * args.turns / cpu, "unit": "turns/s", "cores": 1, "kind": "port", "sample": "100 sessions, plain Python restatement"}
+    return out
+
+
 def python_api_arm(ctx, args):
     """What a drop-in caller pays: evidence.bind_batch from Python dicts (packing, pageable numpy buffers, H2D, kernel,
     D2H, result dicts) on a bounded config-2 sample."""
@@ -607,7 +639,7 @@ def main():
         else:
             gate = {"error": mine.get("error", "failed on another rank")}
 
-    latency = api = None
+    latency = api = annot = None
     if rank == 0 and not args.no_latency:
         try:
             latency = latency_arm(ctx)
@@ -617,6 +649,10 @@ def main():
             api = python_api_arm(ctx, args)
         except Exception as exc:
             api = {"error": repr(exc)[:300]}
+        try:
+            annot = annot_arm(ctx, args)
+        except Exception as exc:
+            annot = {"error": repr(exc)[:300]}
 
     pairs_all = corpus.n_pairs * world
     value = pairs_all * args.steps / (elapsed_ms / 1000.0)
@@ -650,6 +686,8 @@ def main():
             line["latency"] = latency
         if api is not None:
             line["e2e_python_api"] = api
+        if annot is not None:
+            line["annot"] = annot
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             v, secs, passes = cpu_baseline(corpus, cores, repeats=2, min_seconds=10.0)

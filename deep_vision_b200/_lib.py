@@ -41,6 +41,7 @@ _SIGS = {
                                       _vp, _vp, C.c_int32, C.c_double, _vp]),
     "dvb_solution_jaccard": (C.c_int32, [_vp, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp]),
     "dvb_text_features": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
+    "dvb_annotate_turns": (C.c_int32, [_vp, C.c_int32, C.c_int64] + [_vp] * 13 + [C.c_uint32, C.c_int32, _vp, _vp, _vp]),
     "dvb_contains": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, C.c_int64, _vp]),
     "dvb_chunk_index_build": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, C.POINTER(_vp)]),
     "dvb_chunk_index_free": (None, [_vp]),

@@ -421,80 +421,182 @@ def _log_texts(log: dict) -> Tuple[str, str, list]:
     return str(log.get("question", "") or ""), str(log.get("answer", "") or ""), options
 
 
-def _backfill_one(session: dict, feats: List[TurnFeatures], refresh_quality: bool, overwrite_contract: bool,
-                  sensitivity_table=None, hard_signals=None) -> dict:
-    interview_log = session.get("interview_log", [])
-    changed, logs_updated, field_updates, dim_history = False, 0, {}, {}
-    it = iter(feats)
-    for log in interview_log:
-        if not isinstance(log, dict):
-            continue
-        tf = next(it)
-        dimension = str(log.get("dimension", "") or "").strip()
-        prior = dim_history.setdefault(dimension, [])
-        inferred = _contract_from_features(log, prior, tf)
-        raw_mode = str(log.get("answer_mode", "") or "").strip().lower()
-        raw_intent = str(log.get("evidence_intent", "") or "").strip().lower()
-        current_mode = normalize_question_answer_mode(raw_mode, fallback=inferred["answer_mode"])
-        explicit = raw_mode in QUESTION_ANSWER_MODES and raw_intent in QUESTION_EVIDENCE_INTENTS
-        answer_mode = current_mode if (explicit and not overwrite_contract) else inferred["answer_mode"]
-        requires_rationale = bool(log.get("requires_rationale", False) or answer_mode == "pick_with_reason")
-        if overwrite_contract or not explicit:
-            requires_rationale = bool(inferred["requires_rationale"] or answer_mode == "pick_with_reason")
-        evidence_intent = normalize_question_evidence_intent(
-            log.get("evidence_intent", "") if (explicit and not overwrite_contract) else inferred["evidence_intent"],
-            fallback="high" if requires_rationale else ("medium" if answer_mode == "pick_with_reason" else "low"))
-        before = {k: (copy.deepcopy(log.get(k)) if k in ("follow_up_signals", "quality_signals") else log.get(k)) for k in _SNAPSHOT_KEYS}
-        log["answer_mode"] = answer_mode
-        log["requires_rationale"] = requires_rationale
-        log["evidence_intent"] = evidence_intent
-        _q, _a, options = _log_texts(log)
-        eval_result = depth_from_features(tf, dimension, options, bool(log.get("is_follow_up", False)),
-                                          bool(log.get("question_multi_select", log.get("multi_select", False))),
-                                          answer_mode, requires_rationale, evidence_intent, sensitivity_table, hard_signals)
-        quality = quality_from_features(eval_result, tf.a_len, tf.a_mask, bool(log.get("is_follow_up", False)),
-                                        int(log.get("follow_up_round", 0) or 0))
-        evidence_class = classify_answer_evidence_class_v3(eval_result.get("signals", []), quality.get("quality_score", 0.0), evidence_intent)
-        if refresh_quality or "follow_up_signals" not in log:
-            log["follow_up_signals"] = list(eval_result.get("signals", []) or [])
-            log["needs_follow_up"] = bool(eval_result.get("needs_follow_up", False))
-        if refresh_quality or "quality_score" not in log:
-            log["quality_score"] = quality.get("quality_score", 0.0)
-            log["quality_signals"] = list(quality.get("quality_signals", []) or [])
-            log["hard_triggered"] = bool(quality.get("hard_triggered", False))
-        log["answer_evidence_class"] = evidence_class
-        after = {k: log.get(k) for k in _SNAPSHOT_KEYS}
-        if before != after:
-            changed = True
-            logs_updated += 1
-            for key, value in after.items():
-                if before.get(key) != value:
-                    field_updates[key] = field_updates.get(key, 0) + 1
-        prior.append(log)
-    return {"changed": changed, "logs_total": len([log for log in interview_log if isinstance(log, dict)]),
-            "logs_updated": logs_updated, "field_updates": field_updates}
+SIGNAL_NAMES = ("too_short", "vague_expression", "generic_answer", "option_only", "rich_option_answer", "no_quantification",
+                "single_selection", "contradiction_detected")          # ids of dvb_annotate_turns = the order evaluate_answer_depth appends
+_MODE_NAMES = ("", "pick_only", "pick_with_reason")
+_INTENT_NAMES = ("", "low", "medium", "high")
+_CLASS_NAMES = ("explicit", "rich_option", "weak_inferred", "pending_follow_up")
+_MODE_IDS = {"pick_only": 1, "pick_with_reason": 2}
+_INTENT_IDS = {"low": 1, "medium": 2, "high": 3}
+_SIGNAL_LISTS = [[SIGNAL_NAMES[i] for i in range(8) if (m >> i) & 1] for m in range(256)]
+_TC_PC = ("tech_constraints", "project_constraints")
+
+
+_DECODED: Dict[int, tuple] = {}
+
+
+def _decode_turn_bits(b: int) -> tuple:
+    """out_bits of dvb_annotate_turns -> (answer_mode, requires_rationale, evidence_intent, class, signals, needs_follow_up,
+    quality_signals, hard_triggered); cached per distinct value (a few hundred occur)."""
+    sig = _SIGNAL_LISTS[b & 255]
+    qsig = []
+    if b & (1 << 21):
+        qsig.append("high_quality")
+    if b & 2048:
+        qsig.append("quantified")
+    if b & (1 << 22):
+        qsig.append("detailed")
+    if b & 16:
+        qsig.append("rich_option")
+    qsig.extend(sig)
+    return (_MODE_NAMES[(b >> 13) & 3], bool(b & 4096), _INTENT_NAMES[(b >> 15) & 3], _CLASS_NAMES[(b >> 17) & 7], sig, bool(b & 256), qsig, bool(b & 1024))
+
+
+def annotate_turns(q_mask, a_mask, a_len, a_flags, opt_off, opt_mask, opt_len, opt_flags, opt_bits, turn_flags, follow_up_round,
+                   formal_prior, sensitivity, hard_mask: int, overwrite_contract: bool, ctx=None):
+    """dvb_annotate_turns on host arrays: (bits u32[n], follow_up_score f64[n], quality_score f64[n]) — the whole decision
+    stage of a11/a12 for a batch of turns in one launch (csrc/annotate.cu, k_annotate_turns)."""
+    ctx = ctx or _lib.Context.get()
+    n = len(turn_flags)
+    bits = np.zeros(max(n, 1), np.uint32); fs = np.zeros(max(n, 1), np.float64); qs = np.zeros(max(n, 1), np.float64)
+    if n:
+        rc = ctx.lib.dvb_annotate_turns(ctx.handle, _lib.MEM_HOST, n, ptr(q_mask), ptr(a_mask), ptr(a_len), ptr(a_flags), ptr(opt_off),
+                                        ptr(opt_mask), ptr(opt_len), ptr(opt_flags), ptr(opt_bits), ptr(turn_flags), ptr(follow_up_round),
+                                        ptr(formal_prior), ptr(sensitivity), int(hard_mask), 1 if overwrite_contract else 0,
+                                        ptr(bits), ptr(fs), ptr(qs))
+        ctx.check(rc, "dvb_annotate_turns")
+    return bits[:n], fs[:n], qs[:n]
 
 
 def backfill_sessions(sessions: Sequence[Any], *, refresh_quality: bool = True, overwrite_contract: bool = False, ctx=None,
                       sensitivity_table=None, hard_signals=None) -> List[dict]:
-    """Batch form: the text features of every turn of every session come from two kernel launches; sessions are then
-    finished one after the other (each session dict is mutated in place, like the reference)."""
-    turns, spans = [], []
+    """Batch form of backfill_session_interview_log_evidence_annotations (web/server.py:21469-21584): three kernel launches
+    for every turn of every session — text features, option containment, and the decision stage (contract inference,
+    depth, quality, evidence class; dvb_annotate_turns).  Python only extracts the fields of each log and writes the nine
+    annotation fields back (each session dict is mutated in place, like the reference) with the reference's change counts."""
+    table = DIMENSION_FOLLOW_UP_SENSITIVITY if sensitivity_table is None else sensitivity_table
+    hard = HARD_FOLLOW_UP_SIGNALS if hard_signals is None else hard_signals
+    hard_mask = sum(1 << i for i, name in enumerate(SIGNAL_NAMES) if name in hard)
+    texts: List[str] = []                    # question, answer of every turn, then every option text
+    opt_texts: List[str] = []
+    opt_str: List[int] = []
+    needle_hay: List[int] = []
+    opt_off: List[int] = [0]
+    tflags: List[int] = []
+    fround: List[int] = []
+    formal: List[int] = []
+    sens: List[float] = []
+    spans: List[Optional[Tuple[int, int]]] = []
+    turn_logs: List[dict] = []
     for session in sessions:
         logs = session.get("interview_log", []) if isinstance(session, dict) else None
         if not isinstance(logs, list):
             spans.append(None)
             continue
-        start = len(turns)
-        turns.extend(_log_texts(log) for log in logs if isinstance(log, dict))
-        spans.append((start, len(turns)))
-    feats = extract_turn_features(turns, ctx=ctx) if turns else []
+        start = len(turn_logs)
+        prior_formal: Dict[str, int] = {}
+        for log in logs:
+            if not isinstance(log, dict):
+                continue
+            get = log.get
+            ti = len(turn_logs)
+            turn_logs.append(log)
+            texts.append(str(get("question", "") or ""))
+            texts.append(str(get("answer", "") or ""))
+            options = get("options", [])
+            if not isinstance(options, list):
+                options = []
+            for opt in options:
+                is_str = isinstance(opt, str)
+                opt_texts.append(opt if is_str else str(opt or ""))
+                opt_str.append(2 if is_str else 0)
+                needle_hay.append(ti)
+            opt_off.append(len(opt_texts))
+            dimension = str(get("dimension", "") or "").strip()
+            is_fu = bool(get("is_follow_up", False))
+            rnd = int(get("follow_up_round", 0) or 0)
+            raw_mode = str(get("answer_mode", "") or "").strip().lower()
+            raw_intent = str(get("evidence_intent", "") or "").strip().lower()
+            f = ((1 if options else 0) | (2 if get("question_multi_select", get("multi_select", False)) else 0) | (4 if is_fu else 0)
+                 | (8 if get("hard_triggered", False) else 0) | (16 if get("requires_rationale", False) else 0)
+                 | (32 if dimension in _TC_PC else 0) | (64 if dimension.lower() in _TC_PC else 0)
+                 | (_MODE_IDS.get(raw_mode, 0) << 8) | (_INTENT_IDS.get(raw_intent, 0) << 10) | (8192 if (is_fu or rnd > 0) else 0))
+            tflags.append(f)
+            fround.append(rnd)
+            formal.append(prior_formal.get(dimension, 0))
+            sens.append(table.get(dimension, 0.5))
+            if not is_fu:
+                prior_formal[dimension] = prior_formal.get(dimension, 0) + 1
+        spans.append((start, len(turn_logs)))
+    n = len(turn_logs)
+    if n:
+        mask, length, flags = text_features(texts + opt_texts, ctx=ctx)
+        cbits = contains(texts[1::2], opt_texts, needle_hay, ctx=ctx) if opt_texts else np.zeros(0, np.uint8)
+        n2 = 2 * n
+        no = len(opt_texts)
+        bits, fscore, qscore = annotate_turns(
+            np.ascontiguousarray(mask[0:n2:2]), np.ascontiguousarray(mask[1:n2:2]), np.ascontiguousarray(length[1:n2:2]), np.ascontiguousarray(flags[1:n2:2]),
+            np.asarray(opt_off, np.int32), np.ascontiguousarray(mask[n2:]) if no else np.zeros(1, np.uint64),
+            np.ascontiguousarray(length[n2:]) if no else np.zeros(1, np.int32),
+            ((flags[n2:] & 1) | np.asarray(opt_str, np.uint8)) if no else np.zeros(1, np.uint8),
+            np.ascontiguousarray(cbits) if no else np.zeros(1, np.uint8),
+            np.asarray(tflags, np.uint32), np.asarray(fround, np.int32), np.asarray(formal, np.int32), np.asarray(sens, np.float64),
+            hard_mask, overwrite_contract, ctx=ctx)
+        bits_l, q_l = bits.tolist(), qscore.tolist()
     out = []
     for session, span in zip(sessions, spans):
         if span is None:
             out.append(dict(_ZERO, field_updates={}))
-        else:
-            out.append(_backfill_one(session, feats[span[0]:span[1]], refresh_quality, overwrite_contract, sensitivity_table, hard_signals))
+            continue
+        logs_updated, field_updates = 0, {}
+        for ti in range(span[0], span[1]):
+            log = turn_logs[ti]
+            get = log.get
+            b = bits_l[ti]
+            if b & (1 << 20):
+                raise TypeError("'in <string>' requires string as left operand")      # what `opt in answer` raises in the reference
+            dec = _DECODED.get(b)
+            if dec is None:
+                dec = _DECODED[b] = _decode_turn_bits(b)
+            mode, rr, intent, cls, sig, needs, qsig, hard_t = dec
+            touched = False
+            # the nine fields in the reference's snapshot order (web/server.py:21549-21559); lists are fresh objects per log
+            if get("answer_mode") != mode:
+                field_updates["answer_mode"] = field_updates.get("answer_mode", 0) + 1; touched = True
+            log["answer_mode"] = mode
+            if get("requires_rationale") != rr:
+                field_updates["requires_rationale"] = field_updates.get("requires_rationale", 0) + 1; touched = True
+            log["requires_rationale"] = rr
+            if get("evidence_intent") != intent:
+                field_updates["evidence_intent"] = field_updates.get("evidence_intent", 0) + 1; touched = True
+            log["evidence_intent"] = intent
+            fresh_sig = refresh_quality or "follow_up_signals" not in log
+            fresh_q = refresh_quality or "quality_score" not in log
+            if fresh_sig:
+                if get("follow_up_signals") != sig:
+                    field_updates["follow_up_signals"] = field_updates.get("follow_up_signals", 0) + 1; touched = True
+                log["follow_up_signals"] = list(sig)
+            if fresh_q:
+                q = q_l[ti]
+                if get("quality_score") != q:
+                    field_updates["quality_score"] = field_updates.get("quality_score", 0) + 1; touched = True
+                log["quality_score"] = q
+                if get("quality_signals") != qsig:
+                    field_updates["quality_signals"] = field_updates.get("quality_signals", 0) + 1; touched = True
+                log["quality_signals"] = list(qsig)
+                if get("hard_triggered") != hard_t:
+                    field_updates["hard_triggered"] = field_updates.get("hard_triggered", 0) + 1; touched = True
+                log["hard_triggered"] = hard_t
+            if fresh_sig:
+                if get("needs_follow_up") != needs:
+                    field_updates["needs_follow_up"] = field_updates.get("needs_follow_up", 0) + 1; touched = True
+                log["needs_follow_up"] = needs
+            if get("answer_evidence_class") != cls:
+                field_updates["answer_evidence_class"] = field_updates.get("answer_evidence_class", 0) + 1; touched = True
+            log["answer_evidence_class"] = cls
+            if touched:
+                logs_updated += 1
+        out.append({"changed": logs_updated > 0, "logs_total": span[1] - span[0], "logs_updated": logs_updated, "field_updates": field_updates})
     return out
 
 

@@ -258,3 +258,207 @@ extern "C" int32_t dvb_contains(dvb_ctx* ctx, int32_t mem, const uint8_t* hay_ut
     ctx->launches += 1;
     return io.finish(ctx);
 }
+
+// ================================================================== a11 / a12 decision stage
+// replaces, per interview-log turn, the arithmetic and control flow of: _infer_legacy_log_capture_contract (reference
+//   web/server.py:21419-21466), the contract resolution of backfill_session_interview_log_evidence_annotations (21484-21520),
+//   _score_rich_option_answer (20318-20367), evaluate_answer_depth (21221-21401), evaluate_answer_quality (20370-20426) and
+//   classify_answer_evidence_class_v3 (22552-22565) — over the feature bits dvb_text_features / dvb_contains produced.
+// One thread per turn.  fp64 sums run in the reference's order (Python sum() left to right from 0), no FMA contraction;
+// round(x, 2) is exact decimal rounding (half to even on the exact value of the double), as CPython's float.__round__.
+// Pattern-group bit numbers are part of the ABI (include/dvb200.h, DVB_AN_G_*).
+#define AN_G_VAGUE 0
+#define AN_G_INFORMATIVE 1
+#define AN_G_SEMICOLON 2
+#define AN_G_CONTRA_L 3
+#define AN_G_CONTRA_R 9
+#define AN_G_SCENARIO 15
+#define AN_G_GENERIC 16
+#define AN_G_OPT_PUNCT 17
+#define AN_G_CAUSE 18
+#define AN_G_CONTEXT 19
+#define AN_G_ROLE 20
+#define AN_G_PROCESS 21
+#define AN_G_UNITS 22
+#define AN_G_Q_RICH 24
+#define AN_G_Q_EVIDENCE 25
+
+__device__ __forceinline__ bool an_bit(unsigned long long m, int g) { return ((m >> g) & 1ULL) != 0ULL; }
+
+// Python round(x, 2) for finite |x| < 2^40
+__device__ __forceinline__ double an_round2(double x) {
+    double k = floor(__dmul_rn(x, 100.0));
+    if (__fma_rn(x, 100.0, -k) < 0.0) k -= 1.0;                         // the product rounded up across an integer
+    else if (__fma_rn(x, 100.0, -(k + 1.0)) >= 0.0) k += 1.0;
+    const double e = __fma_rn(x, 100.0, -(k + 0.5));                    // sign of (exact x * 100) - (k + 1/2); zero only on an exact tie
+    const bool odd = fmod(fabs(k), 2.0) != 0.0;
+    if (e > 0.0 || (e == 0.0 && odd)) k += 1.0;
+    const double r = __ddiv_rn(k, 100.0);
+    return r == 0.0 ? copysign(0.0, x) : r;
+}
+
+struct AnTurnIn {
+    const unsigned long long* q_mask; const unsigned long long* a_mask; const int32_t* a_len; const uint8_t* a_flags;
+    const int32_t* opt_off; const unsigned long long* opt_mask; const int32_t* opt_len; const uint8_t* opt_flags; const uint8_t* opt_bits;
+    const uint32_t* turn_flags; const int32_t* follow_up_round; const int32_t* formal_prior; const double* sensitivity;
+};
+
+__global__ void __launch_bounds__(256) k_annotate_turns(AnTurnIn in, int64_t n, uint32_t hard_mask, int32_t overwrite_contract,
+                                                         uint32_t* __restrict__ out_bits, double* __restrict__ out_fscore, double* __restrict__ out_quality) {
+    const double W[8] = { 0.4, 0.5, 0.8, 0.3, 0.1, 0.2, 0.2, 0.6 };              // _SIGNAL_WEIGHTS.get(s, 0.1) by signal id
+    const double PEN[8] = { 0.2, 0.25, 0.3, 0.2, 0.05, 0.1, 0.1, 0.25 };          // negative_penalty.get(s, 0.05)
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long qm = in.q_mask[t], am = in.a_mask[t];
+        const int alen = in.a_len[t];
+        const bool adigit = (in.a_flags[t] & 1u) != 0u;
+        const uint32_t tf = in.turn_flags[t];
+        const bool options_truthy = tf & 1u, multi = tf & 2u, is_fu = tf & 4u, log_hard = tf & 8u, log_rr = tf & 16u,
+                   dim_exact = tf & 32u, dim_lower = tf & 64u, fu_contract = tf & (1u << 13);
+        const uint32_t raw_mode = (tf >> 8) & 3u, raw_intent = (tf >> 10) & 3u;
+        const int o0 = in.opt_off[t], o1 = in.opt_off[t + 1];
+        // ---- inferred contract (21419-21466; build_question_capture_contract 19669 with no missing aspects)
+        uint32_t imode, iintent; bool irr;
+        if (fu_contract || log_hard) { imode = 2; irr = true; iintent = 3; }
+        else if (in.formal_prior[t] >= 2 || dim_lower) { imode = 2; irr = true; iintent = 2; }
+        else { imode = 1; irr = false; iintent = 1; }
+        const bool asks = an_bit(qm, AN_G_Q_EVIDENCE);
+        const unsigned long long marker = (1ULL << AN_G_CAUSE) | (1ULL << AN_G_CONTEXT) | (1ULL << AN_G_ROLE) | (1ULL << AN_G_PROCESS);
+        bool opts_rich = false;
+        for (int j = o0; j < o1; j++) opts_rich = opts_rich || (in.opt_len[j] >= 10 && (in.opt_mask[j] & marker) != 0ULL);
+        if (asks || opts_rich) {
+            imode = 2; irr = true;
+            if (fu_contract || asks) iintent = 3; else if (iintent == 1) iintent = 2;
+        }
+        // ---- contract of the log (21484-21520)
+        const bool explicit_c = raw_mode != 0u && raw_intent != 0u;
+        const bool keep = explicit_c && !overwrite_contract;
+        const uint32_t mode = keep ? raw_mode : imode;
+        bool rr = log_rr || mode == 2u;
+        if (overwrite_contract || !explicit_c) rr = irr || mode == 2u;
+        const uint32_t intent = keep ? raw_intent : iintent;
+        // ---- rich option (20318-20367)
+        bool rich = false, exact = false;
+        {
+            bool any_cand = false, any_match = false;
+            int best_len = -1; unsigned long long best_mask = 0; bool best_digit = false;
+            for (int j = o0; j < o1; j++) {
+                if (in.opt_len[j] <= 0) continue;
+                any_cand = true;
+                const uint32_t b = in.opt_bits[j];
+                if (b & 4u) exact = true;
+                if ((b & 2u) && in.opt_len[j] > best_len) {                  // max(matched, key=len): the first of the longest
+                    any_match = true; best_len = in.opt_len[j]; best_mask = in.opt_mask[j]; best_digit = (in.opt_flags[j] & 1u) != 0u;
+                }
+            }
+            if (alen == 0 || !any_cand) exact = false;
+            else if (exact || any_match) {
+                int plen; unsigned long long pmask; bool pdigit;
+                if (exact) { plen = alen; pmask = am; pdigit = adigit; } else { plen = best_len; pmask = best_mask; pdigit = best_digit; }
+                int score = (exact ? 1 : 0) + (plen >= 10 ? 1 : 0) + (plen >= 16 ? 1 : 0)
+                          + (an_bit(pmask, AN_G_OPT_PUNCT) ? 1 : 0) + (an_bit(pmask, AN_G_CAUSE) ? 1 : 0) + (an_bit(pmask, AN_G_CONTEXT) ? 1 : 0)
+                          + (an_bit(pmask, AN_G_ROLE) ? 1 : 0) + (an_bit(pmask, AN_G_PROCESS) ? 1 : 0) + (pdigit ? 1 : 0) + (an_bit(qm, AN_G_Q_RICH) ? 1 : 0);
+                if (dim_lower && an_bit(pmask, AN_G_UNITS)) score += 1;
+                rich = score >= 4 || (exact && score >= 3 && plen >= 12);
+            }
+            if (alen == 0 || !any_cand || !(exact || any_match)) { rich = false; exact = false; }
+        }
+        // ---- depth (21221-21401)
+        const double sens = in.sensitivity[t];
+        const bool needs_rationale = rr || mode == 2u;
+        const bool pick_only = mode == 1u && !needs_rationale;
+        int short_thr = (int)__dadd_rn(20.0, __dmul_rn(sens, 20.0));
+        if (options_truthy) short_thr = min(short_thr, pick_only ? (multi ? 10 : 6) : (multi ? 18 : 12));
+        uint32_t sig = 0, err = 0;
+        if (alen < short_thr && !rich) sig |= 1u << 0;
+        if (an_bit(am, AN_G_VAGUE)) sig |= 1u << 1;
+        if (an_bit(am, AN_G_GENERIC)) sig |= 1u << 2;
+        if (options_truthy) {
+            const bool informative = alen >= 10 || rich || an_bit(am, AN_G_INFORMATIVE);
+            if (!pick_only && exact && alen < 16 && !informative) sig |= 1u << 3;
+            if (rich) sig |= 1u << 4;
+        }
+        if (dim_exact && !adigit && alen < 60) sig |= 1u << 5;
+        if (multi && options_truthy && !an_bit(am, AN_G_SEMICOLON) && (o1 - o0) >= 3 && !rich) {
+            int selected = 0;
+            for (int j = o0; j < o1; j++) {
+                if (!(in.opt_flags[j] & 2u)) err = 1u;                           // `opt in answer` with a non-str option raises in the reference
+                selected += (in.opt_bits[j] & 1u) ? 1 : 0;
+            }
+            if (selected <= 1 && alen < 30) sig |= 1u << 6;
+        }
+        bool contra = false;
+#pragma unroll
+        for (int i = 0; i < 6; i++) contra = contra || (an_bit(am, AN_G_CONTRA_L + i) && an_bit(am, AN_G_CONTRA_R + i));
+        if (contra) sig |= 1u << 7;
+        const bool s_detailed = alen > 80, s_multi = an_bit(am, AN_G_SEMICOLON) && alen > 40, s_quant = adigit && alen > 30;
+        double fs = 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) if (sig & (1u << i)) fs = __dadd_rn(fs, W[i]);
+        fs = __dmul_rn(fs, sens);
+        double suff = 0.0;
+        if (s_detailed) suff = __dadd_rn(suff, 0.5);
+        if (s_multi) suff = __dadd_rn(suff, 0.3);
+        if (s_quant) suff = __dadd_rn(suff, 0.2);
+        if (rich) suff = __dadd_rn(suff, intent == 3u ? 0.25 : 0.18);
+        fs = __dadd_rn(fs, -suff);
+        const bool any_suff = s_detailed || s_multi || s_quant || rich;
+        const bool hard = (sig & hard_mask) != 0u;
+        const bool needs = fs >= 0.4, suggest = !needs && fs >= 0.15 && !any_suff;
+        // ---- quality (20370-20426)
+        double q = 0.5;
+        if (alen >= 120) q = __dadd_rn(q, 0.2); else if (alen >= 80) q = __dadd_rn(q, 0.1);
+        if (adigit) q = __dadd_rn(q, 0.1);
+        if (an_bit(am, AN_G_SCENARIO)) q = __dadd_rn(q, 0.1);
+        if (sig & (1u << 4)) q = __dadd_rn(q, 0.12);
+        double pen = 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) if (sig & (1u << i)) pen = __dadd_rn(pen, PEN[i]);
+        q = __dadd_rn(q, -pen);
+        if (is_fu && in.follow_up_round[t] >= 1 && !hard) q = __dadd_rn(q, 0.05);
+        q = fmax(0.0, fmin(1.0, q));
+        const bool high_quality = q >= 0.75;
+        const double q2 = an_round2(q);
+        // ---- evidence class (22552-22565) on the ROUNDED quality, clamped again
+        const double qc = fmax(0.0, fmin(1.0, q2));
+        uint32_t cls;
+        if (sig & (1u << 4)) cls = 1;
+        else if (sig & ((1u << 1) | (1u << 2) | (1u << 7))) cls = (intent >= 2u) ? 3 : 2;
+        else if (sig & ((1u << 0) | (1u << 3) | (1u << 5) | (1u << 6))) cls = (intent == 3u) ? 3 : 2;
+        else if (qc < 0.35 && intent >= 2u) cls = 2;
+        else cls = 0;
+        out_bits[t] = sig | (needs ? 1u << 8 : 0u) | (suggest ? 1u << 9 : 0u) | (hard ? 1u << 10 : 0u) | (adigit ? 1u << 11 : 0u) | (rr ? 1u << 12 : 0u)
+                    | (mode << 13) | (intent << 15) | (cls << 17) | (err << 20) | (high_quality ? 1u << 21 : 0u) | (alen >= 80 ? 1u << 22 : 0u);
+        out_fscore[t] = an_round2(fs);
+        out_quality[t] = q2;
+    }
+}
+
+extern "C" int32_t dvb_annotate_turns(dvb_ctx* ctx, int32_t mem, int64_t n_turns,
+                                       const uint64_t* q_mask, const uint64_t* a_mask, const int32_t* a_len, const uint8_t* a_flags,
+                                       const int32_t* opt_off, const uint64_t* opt_mask, const int32_t* opt_len, const uint8_t* opt_flags, const uint8_t* opt_bits,
+                                       const uint32_t* turn_flags, const int32_t* follow_up_round, const int32_t* formal_prior, const double* sensitivity,
+                                       uint32_t hard_signal_mask, int32_t overwrite_contract,
+                                       uint32_t* out_bits, double* out_follow_up_score, double* out_quality_score) {
+    if (!ctx || n_turns < 0 || !q_mask || !a_mask || !a_len || !a_flags || !opt_off || !turn_flags || !follow_up_round || !formal_prior || !sensitivity ||
+        !out_bits || !out_follow_up_score || !out_quality_score) { dvb_set_err(ctx, "dvb_annotate_turns: invalid argument%s%s"); return DVB_E_INVALID; }
+    if (n_turns == 0) return DVB_OK;
+    dvb_scope sc(ctx); dvb_io io(sc, mem);
+    int32_t n_opt = 0;
+    if (mem == DVB_MEM_HOST) n_opt = opt_off[n_turns];
+    else { DVB_CUDA(ctx, cudaMemcpyAsync(&n_opt, opt_off + n_turns, 4, cudaMemcpyDeviceToHost, io.st)); DVB_CUDA(ctx, cudaStreamSynchronize(io.st)); }
+    if (n_opt < 0 || (n_opt > 0 && (!opt_mask || !opt_len || !opt_flags || !opt_bits))) { dvb_set_err(ctx, "dvb_annotate_turns: bad option arrays%s%s"); return DVB_E_INVALID; }
+    AnTurnIn in;
+    in.q_mask = (const unsigned long long*)io.in(q_mask, (size_t)n_turns); in.a_mask = (const unsigned long long*)io.in(a_mask, (size_t)n_turns);
+    in.a_len = io.in(a_len, (size_t)n_turns); in.a_flags = io.in(a_flags, (size_t)n_turns);
+    in.opt_off = io.in(opt_off, (size_t)n_turns + 1);
+    in.opt_mask = (const unsigned long long*)io.in(opt_mask, (size_t)n_opt); in.opt_len = io.in(opt_len, (size_t)n_opt);
+    in.opt_flags = io.in(opt_flags, (size_t)n_opt); in.opt_bits = io.in(opt_bits, (size_t)n_opt);
+    in.turn_flags = io.in(turn_flags, (size_t)n_turns); in.follow_up_round = io.in(follow_up_round, (size_t)n_turns);
+    in.formal_prior = io.in(formal_prior, (size_t)n_turns); in.sensitivity = io.in(sensitivity, (size_t)n_turns);
+    uint32_t* d_bits = io.out(out_bits, (size_t)n_turns); double* d_fs = io.out(out_follow_up_score, (size_t)n_turns); double* d_q = io.out(out_quality_score, (size_t)n_turns);
+    int32_t rc = io.check(ctx); if (rc) return rc;
+    const int grid = (int)std::min<int64_t>((n_turns + 255) / 256, (int64_t)ctx->num_sm * 8);
+    k_annotate_turns<<<grid, 256, 0, io.st>>>(in, n_turns, hard_signal_mask, overwrite_contract, d_bits, d_fs, d_q);
+    ctx->launches += 1;
+    return io.finish(ctx);
+}

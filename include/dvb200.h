@@ -214,6 +214,47 @@ int32_t dvb_contains(dvb_ctx* ctx, int32_t mem, const uint8_t* hay_utf8, const i
                      const uint8_t* needle_utf8, const int64_t* needle_off, const int32_t* needle_hay, int64_t n_needles,
                      uint8_t* out_bits);
 
+/* ---- a11 / a12 decision stage  replaces, per interview-log turn: _infer_legacy_log_capture_contract (web/server.py:
+ *      21419-21466), the contract resolution of backfill_session_interview_log_evidence_annotations (21484-21520),
+ *      _score_rich_option_answer (20318-20367), evaluate_answer_depth (21221-21401), evaluate_answer_quality (20370-20426) and
+ *      classify_answer_evidence_class_v3 (22552-22565), over the feature bits of dvb_text_features / dvb_contains.
+ * Inputs per turn: masks / stripped length / flags of the question and the answer; the options of turn t are entries
+ * [opt_off[t], opt_off[t+1]) of the option arrays (mask, stripped length, opt_flags bit 0 = has digit, bit 1 = the option is a
+ * str; opt_bits = dvb_contains bits against the turn's answer).  The masks use the group numbers DVB_AN_G_* below.
+ * turn_flags: bit 0 bool(options), 1 multi_select, 2 bool(is_follow_up), 3 bool(log hard_triggered), 4 bool(log requires_rationale),
+ *   5 dimension in ("tech_constraints", "project_constraints"), 6 the same test on str(dimension).strip().lower(),
+ *   8-9 answer_mode of the log (0 = none / invalid, 1 pick_only, 2 pick_with_reason), 10-11 evidence_intent of the log
+ *   (0 invalid, 1 low, 2 medium, 3 high), 13 is_follow_up or follow_up_round > 0.
+ * formal_prior = number of earlier logs of the session with the same dimension and is_follow_up false (21432);
+ * sensitivity = DIMENSION_FOLLOW_UP_SENSITIVITY.get(dimension, 0.5); hard_signal_mask = signals of HARD_FOLLOW_UP_SIGNALS.
+ * Signal ids (the order evaluate_answer_depth appends them): 0 too_short, 1 vague_expression, 2 generic_answer, 3 option_only,
+ *   4 rich_option_answer, 5 no_quantification, 6 single_selection, 7 contradiction_detected.
+ * out_bits: 0-7 signals, 8 needs_follow_up, 9 suggest_ai_eval, 10 hard_triggered, 11 has_numbers, 12 requires_rationale,
+ *   13-14 answer_mode, 15-16 evidence_intent, 17-19 evidence class (0 explicit, 1 rich_option, 2 weak_inferred, 3 pending_follow_up),
+ *   20 a non-str option reached `opt in answer` (the reference raises TypeError there), 21 quality >= 0.75 before rounding,
+ *   22 stripped answer >= 80 characters.  Scores are fp64 in the reference's operation order, rounded like Python round(x, 2). */
+#define DVB_AN_G_VAGUE 0
+#define DVB_AN_G_INFORMATIVE 1
+#define DVB_AN_G_SEMICOLON 2
+#define DVB_AN_G_CONTRA_L 3   /* six pairs: left words 3..8, right words 9..14 */
+#define DVB_AN_G_CONTRA_R 9
+#define DVB_AN_G_SCENARIO 15
+#define DVB_AN_G_GENERIC 16
+#define DVB_AN_G_OPT_PUNCT 17
+#define DVB_AN_G_CAUSE 18
+#define DVB_AN_G_CONTEXT 19
+#define DVB_AN_G_ROLE 20
+#define DVB_AN_G_PROCESS 21
+#define DVB_AN_G_UNITS 22
+#define DVB_AN_G_Q_RICH 24
+#define DVB_AN_G_Q_EVIDENCE 25
+int32_t dvb_annotate_turns(dvb_ctx* ctx, int32_t mem, int64_t n_turns,
+                           const uint64_t* q_mask, const uint64_t* a_mask, const int32_t* a_len, const uint8_t* a_flags,
+                           const int32_t* opt_off, const uint64_t* opt_mask, const int32_t* opt_len, const uint8_t* opt_flags, const uint8_t* opt_bits,
+                           const uint32_t* turn_flags, const int32_t* follow_up_round, const int32_t* formal_prior, const double* sensitivity,
+                           uint32_t hard_signal_mask, int32_t overwrite_contract,
+                           uint32_t* out_bits, double* out_follow_up_score, double* out_quality_score);
+
 /* ---- a7 at corpus scale (BASELINE configs 3/5)  replaces: the scoring loop + top-k of select_reference_material_context
  *      (web/server.py:32073-32087) for many queries over a resident chunk corpus.
  * dvb_chunk_index_build symbolises the chunks and builds a positional inverted index over adjacent same-class symbol

@@ -56,6 +56,48 @@ def py_contains(haystacks, needles, needle_hay, ctx=None):
     return out
 
 
+def py_annotate_turns(q_mask, a_mask, a_len, a_flags, opt_off, opt_mask, opt_len, opt_flags, opt_bits, turn_flags, follow_up_round,
+                      formal_prior, sensitivity, hard_mask, overwrite_contract, ctx=None):
+    """Stand-in for dvb_annotate_turns built from the package's reference-shaped decision functions (the ones the single-call
+    drop-ins use): lets the CPU suite run the extraction / write-back glue of backfill_sessions.  Tests only."""
+    from deep_vision_b200 import annotations as an
+    n = len(turn_flags)
+    bits = np.zeros(n, np.uint32); fs = np.zeros(n, np.float64); qs = np.zeros(n, np.float64)
+    hard = {an.SIGNAL_NAMES[i] for i in range(8) if (hard_mask >> i) & 1}
+    for t in range(n):
+        f = int(turn_flags[t])
+        opts = [an.OptionFeatures(is_str=bool(opt_flags[j] & 2), length=int(opt_len[j]), mask=int(opt_mask[j]), has_digit=bool(opt_flags[j] & 1),
+                                  raw_in_answer=bool(opt_bits[j] & 1), strip_in_answer=bool(opt_bits[j] & 2), equals_answer=bool(opt_bits[j] & 4))
+                for j in range(int(opt_off[t]), int(opt_off[t + 1]))]
+        tf = an.TurnFeatures(q_mask=int(q_mask[t]), a_mask=int(a_mask[t]), a_len=int(a_len[t]), a_digit=bool(a_flags[t] & 1), options=opts)
+        dim_exact = "tech_constraints" if f & 32 else ("Tech_Constraints" if f & 64 else "other")   # exact test / lower-cased test
+        log = {"dimension": dim_exact, "is_follow_up": bool(f & 8192), "follow_up_round": 0, "hard_triggered": bool(f & 8)}
+        inferred = an._contract_from_features(log, [{"is_follow_up": False}] * int(formal_prior[t]), tf)
+        raw_mode, raw_intent = an._MODE_NAMES[(f >> 8) & 3], an._INTENT_NAMES[(f >> 10) & 3]
+        explicit = bool(raw_mode) and bool(raw_intent)
+        keep = explicit and not overwrite_contract
+        mode = raw_mode if keep else inferred["answer_mode"]
+        rr = bool(f & 16) or mode == "pick_with_reason"
+        if overwrite_contract or not explicit:
+            rr = bool(inferred["requires_rationale"] or mode == "pick_with_reason")
+        intent = raw_intent if keep else inferred["evidence_intent"]
+        options = [0] * len(opts) if (f & 1) else []
+        err = 0
+        try:
+            ev = an.depth_from_features(tf, dim_exact, options, bool(f & 4), bool(f & 2), mode, rr, intent, {dim_exact: float(sensitivity[t])}, hard)
+        except TypeError:
+            err, ev = 1, {"signals": [], "needs_follow_up": False, "suggest_ai_eval": False, "hard_triggered": False, "has_numbers": False, "follow_up_score": 0.0}
+        ql = an.quality_from_features(ev, tf.a_len, tf.a_mask, bool(f & 4), int(follow_up_round[t]))
+        cls = an.classify_answer_evidence_class_v3(ev["signals"], ql["quality_score"], intent)
+        sig = sum(1 << an.SIGNAL_NAMES.index(s) for s in ev["signals"])
+        bits[t] = (sig | (256 if ev["needs_follow_up"] else 0) | (512 if ev["suggest_ai_eval"] else 0) | (1024 if ev["hard_triggered"] else 0)
+                   | (2048 if ev["has_numbers"] else 0) | (4096 if rr else 0) | (an._MODE_IDS[mode] << 13) | (an._INTENT_IDS[intent] << 15)
+                   | (an._CLASS_NAMES.index(cls) << 17) | (err << 20) | ((1 << 21) if "high_quality" in ql["quality_signals"] else 0)
+                   | ((1 << 22) if tf.a_len >= 80 else 0))
+        fs[t] = ev["follow_up_score"]; qs[t] = ql["quality_score"]
+    return bits, fs, qs
+
+
 def _check_product_against_golden(an, gold, ctx=None):
     for case in gold["backfill"]:
         work = copy.deepcopy(case["input"])
@@ -93,6 +135,7 @@ def test_host_decision_logic_with_standin_features(gold, monkeypatch):
     from deep_vision_b200 import annotations as an
     monkeypatch.setattr(an, "text_features", py_text_features)
     monkeypatch.setattr(an, "contains", py_contains)
+    monkeypatch.setattr(an, "annotate_turns", py_annotate_turns)
     _check_product_against_golden(an, gold)
     _check_packs(an, gold)
 
@@ -102,6 +145,7 @@ def test_script_body_dry_run_apply_and_shards(tmp_path, gold, monkeypatch):
     from deep_vision_b200 import annotations as an
     monkeypatch.setattr(an, "text_features", py_text_features)
     monkeypatch.setattr(an, "contains", py_contains)
+    monkeypatch.setattr(an, "annotate_turns", py_annotate_turns)
     sess_dir, bak = tmp_path / "sessions", tmp_path / "bak"
     sess_dir.mkdir(); bak.mkdir()
     cases = [c for c in gold["backfill"] if c["refresh_quality"] and isinstance(c["input"].get("interview_log"), list)][:12]
@@ -165,6 +209,28 @@ def test_gpu_annotations_golden(gpu_ctx, gold):
     from deep_vision_b200 import annotations as an
     _check_product_against_golden(an, gold, ctx=gpu_ctx)
     _check_packs(an, gold, ctx=gpu_ctx)
+
+
+@pytest.mark.gpu
+def test_gpu_decision_stage_rounds_like_python(gpu_ctx):
+    """round(x, 2) inside dvb_annotate_turns == Python's float.__round__ on every multiple of 0.005 in range, their
+    neighbouring doubles and random values: one vague_expression signal (weight 0.5) and sensitivity 2x make follow_up_score = x."""
+    import math
+    from deep_vision_b200 import annotations as an
+    xs = []
+    for k in range(-280, 281):
+        x = k * 0.005
+        xs += [x, math.nextafter(x, 2.0), math.nextafter(x, -2.0), k / 200.0]
+    rng = random.Random(3)
+    xs += [rng.uniform(-1.4, 1.4) for _ in range(20000)] + [0.0, -0.0, 1e-9, -1e-9, 0.004999999, -0.004999999]
+    n = len(xs)
+    sens = np.asarray([2.0 * x for x in xs], np.float64)
+    bits, fs, qs = an.annotate_turns(np.zeros(n, np.uint64), np.full(n, 1 << an.G_VAGUE, np.uint64), np.full(n, 79, np.int32), np.zeros(n, np.uint8),
+                                     np.zeros(n + 1, np.int32), np.zeros(1, np.uint64), np.zeros(1, np.int32), np.zeros(1, np.uint8), np.zeros(1, np.uint8),
+                                     np.zeros(n, np.uint32), np.zeros(n, np.int32), np.zeros(n, np.int32), sens, 0, False, ctx=gpu_ctx)
+    want = np.asarray([round(0.5 * float(s), 2) for s in sens], np.float64)
+    assert np.array_equal(fs.view(np.uint64), want.view(np.uint64))           # bit-identical, the sign of zero included
+    assert np.all((bits & 255) == 2) and np.all(qs == 0.25)                    # quality 0.5 - 0.25
 
 
 @pytest.mark.gpu
@@ -235,6 +301,7 @@ def test_saturation_host_logic_with_standin_features(golden, monkeypatch):
     from deep_vision_b200 import annotations as an
     monkeypatch.setattr(an, "text_features", py_text_features)
     monkeypatch.setattr(an, "contains", py_contains)
+    monkeypatch.setattr(an, "annotate_turns", py_annotate_turns)
     _check_saturation(an, golden("f2_saturation.json"))
 
 
@@ -245,6 +312,7 @@ def test_dropin_saturation_rebinding_and_stub_respect(golden, monkeypatch):
     from deep_vision_b200 import annotations as an, dropin
     monkeypatch.setattr(an, "text_features", py_text_features)
     monkeypatch.setattr(an, "contains", py_contains)
+    monkeypatch.setattr(an, "annotate_turns", py_annotate_turns)
     sat = golden("f2_saturation.json")
     base = _SatModule()
     mod = types.SimpleNamespace(**{k: getattr(base, k) for k in ("REPORT_TEMPLATE_CUSTOM_V1", "get_dimension_info_for_session",
