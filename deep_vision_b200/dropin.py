@@ -204,8 +204,33 @@ def check_unicode_tables(strict: bool = False) -> bool:
     return False
 
 
+def infer_reference_chunk_refs_v3_factory(mod, ctx=None):
+    """SURVEY §8(f)3 (no counterpart in the reference; opt-in): bind one report item to the chunks of an uploaded document
+    with a2's overlap score.  Same shape of call as infer_weak_evidence_refs_v3: (field, item, doc, top_k) ->
+    {"chunks": [{"chunk_id", "index", "start", "end", "score"}], "score": best score rounded to 3 places}."""
+    def infer_reference_chunk_refs_v3(field, item, doc, top_k=4):
+        empty = {"chunks": [], "score": 0.0}
+        try:
+            if field not in evidence.CLAIM_TEXT_FIELDS or not isinstance(item, dict):
+                return empty
+            loader = getattr(mod, "load_reference_material_chunks", None)
+            chunks = loader(doc) if loader is not None else []
+            if not chunks:
+                return empty
+            claim = " ".join(evidence._text(item.get(k, "")) for k in evidence.CLAIM_TEXT_FIELDS[field])
+            rows = evidence.bind_claims_to_chunks([claim], [str(c.get("text") or "") for c in chunks], top_k, ctx=ctx)[0]
+        except evidence._lib.DvbError:
+            raise
+        except Exception:
+            return empty
+        picked = [{"chunk_id": chunks[r["index"]].get("chunk_id"), "index": chunks[r["index"]].get("index"), "start": chunks[r["index"]].get("start"),
+                   "end": chunks[r["index"]].get("end"), "score": round(r["score"], 3)} for r in rows]
+        return {"chunks": picked, "score": picked[0]["score"] if picked else 0.0}
+    return infer_reference_chunk_refs_v3
+
+
 def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cache=None, saturation: bool = False,
-            strict_unicode: bool = False) -> Dict[str, Any]:
+            strict_unicode: bool = False, claim_chunk_binding: bool = False) -> Dict[str, Any]:
     """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent.
     sidecar_cache: a reference_material.ChunkIndexCache to serve select_reference_material_context from resident /
     persisted chunk indexes (off by default: the drop-in then writes nothing into the data directory)."""
@@ -225,9 +250,20 @@ def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cach
             saved[name] = current
         setattr(server_module, name, fn)
         done[name] = fn
+    if claim_chunk_binding:                                    # a NEW name: nothing of the reference is replaced by it
+        fn = infer_reference_chunk_refs_v3_factory(server_module, ctx)
+        saved.setdefault("infer_reference_chunk_refs_v3", getattr(server_module, "infer_reference_chunk_refs_v3", _MISSING))
+        setattr(server_module, "infer_reference_chunk_refs_v3", fn)
+        done["infer_reference_chunk_refs_v3"] = fn
     return done
 
 
 def uninstall(server_module) -> None:
     for name, fn in _SAVED.pop(id(server_module), {}).items():
-        setattr(server_module, name, fn)
+        if fn is _MISSING:
+            try:
+                delattr(server_module, name)
+            except AttributeError:
+                pass
+        else:
+            setattr(server_module, name, fn)

@@ -302,6 +302,85 @@ def infer_weak_evidence_refs_v3(field: str, item: dict, evidence_pack: dict, min
                       dimension_resolver=dimension_resolver)[0]
 
 
+# ----------------------------------------------------------------------------- claim -> uploaded-document chunk binding
+# Not in the reference: it binds claims to interview FACTS only (a2) and selects chunks by substring COUNTS only (a7).
+# This joins the two halves it does have — a2's overlap score over a7's chunks — and ships behind a flag
+# (dropin.install(..., claim_chunk_binding=True)).  Definition (oracle: oracle.dv_oracle.claim_chunk_topk):
+#   A = tokens(claim), B = tokens(chunk text)          (_tokenize_similarity_text_v3, web/server.py:24722-24732)
+#   ov = |A & B|; ov == 0 -> not a candidate
+#   score = 0.62 * ov / max(3, min(|A|, 14)) + 0.18 * ov / max(4, min(|B|, 18))      (web/server.py:24835-24843 with the
+#           quality, dimension and hard-trigger terms absent: a chunk carries none)
+#   order: min(floor(score * 2^20), 2^31 - 1) descending, chunk index ascending; the first k <= 32 with score > 0
+#          (the coverage term is not capped at 1 — ov may exceed 14 — so scores run into the hundreds for long claims)
+#   documents of more than `max_exhaustive` chunks: a claim is scored only against the <= 32 chunks the reference's own
+#   selector ranks first for it (a6 terms, a7 counts, (count desc, index asc); web/server.py:32073-32085).
+CLAIM_CHUNK_KEY_SCALE = float(1 << 20)
+
+
+def claim_chunk_scores(claim_texts: Sequence[str], chunk_texts: Sequence[str], ctx=None) -> np.ndarray:
+    """fp64 [n_claims, n_chunks] overlap scores (0 where the token sets are disjoint): ONE dvb_bind_claims launch — every
+    chunk is a session whose single fact is the chunk, so the per-claim best score IS the pair's score."""
+    ctx = ctx or _lib.Context.get()
+    nc, nk = len(claim_texts), len(chunk_texts)
+    if nc == 0 or nk == 0:
+        return np.zeros((nc, nk), np.float64)
+    cu, co = pack_texts([_text(t) for t in claim_texts])
+    nb = int(co[-1])
+    claim_utf8 = np.concatenate([np.tile(cu[:nb], nk), np.zeros(64, np.uint8)])
+    claim_off = (np.arange(nk, dtype=np.int64)[:, None] * nb + co[None, :-1]).reshape(-1)
+    claim_off = np.concatenate([claim_off, np.asarray([nk * nb], np.int64)])
+    fu, fo = pack_texts([_text(t) for t in chunk_texts])
+    out = bind_packed(ctx, claim_utf8, claim_off, fu, fo, np.arange(nk + 1, dtype=np.int64) * nc, np.arange(nk + 1, dtype=np.int64),
+                      np.zeros(nk, np.float64), np.zeros(nk, np.int32), np.zeros(nk, np.uint8), np.full(nk * nc, -1, np.int32),
+                      np.zeros(nk * nc, np.float64))
+    score = np.where(out["best_fact"] >= 0, out["best_score"], 0.0)
+    return np.ascontiguousarray(score.reshape(nk, nc).T)
+
+
+def bind_claims_to_chunks(claim_texts: Sequence[str], chunk_texts: Sequence[str], k: int = 4, *, ctx=None, max_exhaustive: int = 256,
+                          index=None) -> List[List[dict]]:
+    """Per claim the k best chunks of a document under a2's overlap score: [{"index": chunk position, "score": fp64}, ...].
+    `index`: a resident reference_material.ChunkIndex over exactly these chunks (candidate stage of large documents)."""
+    from . import reference_material as rm
+    ctx = ctx or _lib.Context.get()
+    nc, nk = len(claim_texts), len(chunk_texts)
+    k = max(1, min(int(k), 32))
+    if nc == 0 or nk == 0:
+        return [[] for _ in range(nc)]
+    subset = np.arange(nk, dtype=np.int64)
+    allowed = None
+    if nk > max_exhaustive:
+        own = index is None
+        ix = rm.ChunkIndex(chunk_texts, ctx=ctx) if own else index
+        try:
+            dev_terms = rm.query_terms_batch([_text(t) for t in claim_texts], ctx=ctx, device=True)
+            ci, _cs, cn = (a.cpu().numpy() for a in ix.topk_device(dev_terms, nc, 32))
+        finally:
+            if own:
+                ix.close()
+        ci = ci - ix.index_base
+        valid = np.arange(32)[None, :] < cn[:, None]
+        subset = np.unique(ci[valid])
+        allowed = np.zeros((nc, len(subset)), bool)
+        rows = np.repeat(np.arange(nc), cn)
+        allowed[rows, np.searchsorted(subset, ci[valid])] = True
+    if len(subset) == 0:
+        return [[] for _ in range(nc)]
+    scores = claim_chunk_scores(claim_texts, [chunk_texts[int(i)] for i in subset], ctx=ctx)
+    if allowed is not None:
+        scores = np.where(allowed, scores, 0.0)
+    keys = np.minimum(np.floor(scores * CLAIM_CHUNK_KEY_SCALE), 2147483647.0).astype(np.int32)
+    idx, _ks, nv = rm.topk(keys, k, index=np.ascontiguousarray(np.broadcast_to(subset, (nc, len(subset)))), ctx=ctx)
+    out = []
+    for c in range(nc):
+        row = []
+        for j in range(int(nv[c])):
+            g = int(idx[c, j])
+            row.append({"index": g, "score": float(scores[c, int(np.searchsorted(subset, g))])})
+        out.append(row)
+    return out
+
+
 # ----------------------------------------------------------------------------- a1: token keys
 
 def tokenize_similarity_keys(texts: Sequence[str], ctx=None) -> List[np.ndarray]:

@@ -268,3 +268,36 @@ def solution_jaccard(left_clean: str, right_clean: str, n: int = 2) -> Tuple[flo
     j = lib().dvo_solution_jaccard(_ptr(la, u8p), C.c_int64(len(lb)), _ptr(ra, u8p), C.c_int64(len(rb)), C.c_int32(n),
                                    C.byref(i), C.byref(u))
     return float(j), i.value, u.value
+
+
+def claim_chunk_topk(claims: Sequence[str], chunks: Sequence[str], k: int = 4, max_exhaustive: int = 256):
+    """SURVEY 8(f)3 (not in the reference; definition in deep_vision_b200/evidence.py): per claim the k best chunks under a2's
+    overlap score.  Independent route: ONE session holding every claim and every chunk as a fact, per-pair overlaps and set sizes
+    from the C tokenizer, the score formula in Python floats in the reference's operation order (web/server.py:24835-24843)."""
+    nc, nk = len(claims), len(chunks)
+    if nc == 0 or nk == 0:
+        return [[] for _ in range(nc)]
+    r = bind_claims(list(claims), list(chunks), [0, nc], [0, nk], np.zeros(nk), np.zeros(nk, np.int32), np.zeros(nk, np.uint8),
+                    np.full(nc, -1, np.int32), np.zeros(nc), want_overlap=True)
+    ov = r["overlap"][: nc * nk].reshape(nc, nk)
+    la, lb = r["len_claim"], r["len_fact"]
+    out = []
+    for c in range(nc):
+        cand = range(nk)
+        if nk > max_exhaustive:
+            s = chunk_scores(list(chunks), query_terms(claims[c]))
+            cand = sorted(topk(s, 32)[0].tolist())
+        rows = []
+        for j in cand:
+            o = int(ov[c, j])
+            if o <= 0:
+                continue
+            coverage = o / max(3, min(int(la[c]), 14))
+            precision = o / max(4, min(int(lb[j]), 18))
+            score = 0.62 * coverage + 0.18 * precision + 0.16 * 0.0 + 0.0 + 0.0
+            key = min(int(np.floor(score * float(1 << 20))), 2147483647)
+            if key > 0:
+                rows.append((-key, j, score))
+        rows.sort()
+        out.append([{"index": j, "score": sc} for (_k, j, sc) in rows[: max(1, min(int(k), 32))]])
+    return out

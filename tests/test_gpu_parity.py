@@ -235,3 +235,36 @@ def test_a2_degenerate_sessions(gpu_ctx, oracle):
     assert np.array_equal(got["bound"], ref["bound"])
     assert np.array_equal(got["len_claim"], np.minimum(ref["len_claim"], 14))
     assert got["best_fact"][:6].tolist() == [-1] * 6                   # no facts to bind to
+
+
+def _claim_chunk_case(n_chunks, seed):
+    import random
+    rng = random.Random(seed)
+    han = [chr(0x4E00 + rng.randrange(1200)) for _ in range(260)]
+    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
+    chunks = []
+    for c in range(n_chunks):
+        chunks.append("，".join(cjk(rng.randint(2, 30)) for _ in range(rng.randint(1, 12))) + rng.choice(["", " api_v2 sla 99", "\n\n预算有限 budget_2024"]))
+    claims = []
+    for i in range(23):
+        src = rng.choice(chunks)
+        a = rng.randrange(max(1, len(src) - 30))
+        claims.append(cjk(rng.randint(0, 12)) + src[a:a + rng.randint(3, 40)] + rng.choice(["", " sla", " budget_2024", cjk(5)]))
+    claims += ["", "   ", cjk(40), chunks[0], chunks[-1][:7]]
+    return claims, chunks
+
+
+@pytest.mark.gpu
+def test_claim_chunk_binding_vs_oracle(gpu_ctx, oracle):
+    """claims bound to document chunks with a2's overlap score — exhaustive for small documents, through the
+    count-selector candidate stage (resident index, device a6 terms) for large ones — indices and fp64 scores bit-identical."""
+    from deep_vision_b200 import evidence
+    for n_chunks, mx, k, seed in ((12, 256, 4, 1), (70, 256, 8, 2), (90, 16, 4, 3), (300, 64, 32, 4)):
+        claims, chunks = _claim_chunk_case(n_chunks, seed)
+        got = evidence.bind_claims_to_chunks(claims, chunks, k, ctx=gpu_ctx, max_exhaustive=mx)
+        want = oracle.claim_chunk_topk(claims, chunks, k, max_exhaustive=mx)
+        assert [[r["index"] for r in row] for row in got] == [[r["index"] for r in row] for row in want]
+        g = np.asarray([r["score"] for row in got for r in row]); w = np.asarray([r["score"] for row in want for r in row])
+        assert np.array_equal(g.view(np.uint64), w.view(np.uint64))
+        assert sum(len(r) for r in got) > len(claims)
+    assert evidence.bind_claims_to_chunks([], ["x"], 4, ctx=gpu_ctx) == [] and evidence.bind_claims_to_chunks(["一二三"], [], 4, ctx=gpu_ctx) == [[]]

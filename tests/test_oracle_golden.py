@@ -108,3 +108,29 @@ def test_a2_host_logic_with_oracle_scorer(oracle, golden, monkeypatch):
     reqs = [(c["field"], c["item"], g["packs"][c["pack"]] if isinstance(c["pack"], str) else c["pack"], c["min_score"])
             for c in g["cases"]]
     assert evidence.bind_batch(reqs, ctx=object()) == [c["result"] for c in g["cases"]]
+
+
+def test_f3_claim_chunk_host_logic_with_oracle_scorer(oracle, monkeypatch):
+    """SURVEY 8(f)3 host logic (session layout, key quantisation, top-k order, drop-in shape) with the oracle standing in
+    for the two kernels; the exhaustive path only (the candidate stage needs the resident index)."""
+    import types
+    import conftest
+    from deep_vision_b200 import dropin, evidence, reference_material as rm
+    from test_reference_material import _oracle_standins
+    monkeypatch.setattr(evidence, "bind_packed", conftest.oracle_bind_packed)
+    _oracle_standins(monkeypatch, oracle)
+    chunks = ["我们必须支持离线审批和断网补录，并保留审批链路证据。", "预算有限，budget_2024 已经确定。审批流程太慢需要优化", "开头普通说明。" * 5, "离线审批"]
+    claims = ["离线审批能力验证需要支持断网补录", "budget_2024 预算有限", "", "完全无关的内容", "离线审批"]
+    got = evidence.bind_claims_to_chunks(claims, chunks, 3, ctx=object())
+    assert got == oracle.claim_chunk_topk(claims, chunks, 3)
+    assert [r["index"] for r in got[0]][:1] == [0] and got[2] == [] and got[3] == []
+    mod = types.SimpleNamespace(load_reference_material_chunks=lambda doc: [{"chunk_id": "chunk-%04d" % i, "index": i, "start": 0, "end": len(t), "text": t}
+                                                                            for i, t in enumerate(chunks)])
+    done = dropin.install(mod, ctx=object(), claim_chunk_binding=True)
+    r = mod.infer_reference_chunk_refs_v3("risks", {"risk": claims[0]}, {"doc_id": "d"}, 2)
+    assert [c["index"] for c in r["chunks"]] == [x["index"] for x in got[0][:2]] and r["chunks"][0]["chunk_id"] == "chunk-0000"
+    assert r["score"] == round(got[0][0]["score"], 3)
+    assert mod.infer_reference_chunk_refs_v3("needs", {"title": "x"}, {}, 2) == {"chunks": [], "score": 0.0}
+    assert "infer_reference_chunk_refs_v3" in done
+    dropin.uninstall(mod)
+    assert not hasattr(mod, "infer_reference_chunk_refs_v3")
