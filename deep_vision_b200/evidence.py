@@ -305,7 +305,7 @@ def infer_weak_evidence_refs_v3(field: str, item: dict, evidence_pack: dict, min
 # ----------------------------------------------------------------------------- claim -> uploaded-document chunk binding
 # Not in the reference: it binds claims to interview FACTS only (a2) and selects chunks by substring COUNTS only (a7).
 # This joins the two halves it does have — a2's overlap score over a7's chunks — and ships behind a flag
-# (dropin.install(..., claim_chunk_binding=True)).  Definition (oracle: oracle.dv_oracle.claim_chunk_topk):
+# (dropin.install(..., claim_chunk_binding=True)).  Definition (restated independently by the test checker):
 #   A = tokens(claim), B = tokens(chunk text)          (_tokenize_similarity_text_v3, web/server.py:24722-24732)
 #   ov = |A & B|; ov == 0 -> not a candidate
 #   score = 0.62 * ov / max(3, min(|A|, 14)) + 0.18 * ov / max(4, min(|B|, 18))      (web/server.py:24835-24843 with the
