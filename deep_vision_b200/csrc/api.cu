@@ -53,8 +53,19 @@ extern "C" void dvb_destroy(dvb_ctx* c) {
     delete c;
 }
 
-extern "C" const char* dvb_last_error(dvb_ctx* c) { return c ? c->err : "null ctx"; }
+// ---- per-thread state (common.cuh)
+struct DvbTls { char err[512]; dvb_ctx* err_ctx; const dvb_ctx* stream_ctx; void* stream; };
+static thread_local DvbTls g_tls = { { 0 }, nullptr, nullptr, nullptr };
+char* dvb_tls_err(dvb_ctx* owner) { g_tls.err_ctx = owner; return g_tls.err; }
+void* dvb_tls_stream(const dvb_ctx* ctx) { return g_tls.stream_ctx == ctx ? g_tls.stream : nullptr; }
+
+// this thread's last message for c if it has one, else the last message any thread left on c
+extern "C" const char* dvb_last_error(dvb_ctx* c) {
+    if (!c) return "null ctx";
+    if (g_tls.err_ctx == c && g_tls.err[0]) return g_tls.err;
+    return c->err;
+}
 extern "C" int64_t dvb_launch_count(dvb_ctx* c) { return c ? c->launches.load() : 0; }
 extern "C" void dvb_set_timing(dvb_ctx* c, int32_t enabled) { if (c) c->timing.store(enabled ? 1 : 0); }
 extern "C" float dvb_last_kernel_ms(dvb_ctx* c) { return c ? c->last_ms : 0.f; }
-extern "C" void dvb_set_stream(dvb_ctx* c, void* stream) { if (c) c->user_stream.store(stream); }
+extern "C" void dvb_set_stream(dvb_ctx* c, void* stream) { if (c) { g_tls.stream_ctx = stream ? c : nullptr; g_tls.stream = stream; } }

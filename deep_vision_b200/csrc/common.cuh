@@ -43,19 +43,27 @@ struct dvb_ctx {
     dvb_lease leases[DVB_LEASES];
     std::atomic<int64_t> launches{0};
     std::atomic<int> timing{0};
-    std::atomic<void*> user_stream{nullptr};   // dvb_set_stream: run every call on the caller's stream
     float last_ms = 0.f;
     std::mutex unicode_mu;
     void* unicode_dev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // CPython case tables (gate.cu)
-    // per-thread error text would need TLS keyed by ctx; one buffer per ctx guarded by mu is enough here
+    // last error text of any thread (each thread also keeps its own: dvb_tls_err)
     char err[512] = {0};
 };
 
+// Error text: one buffer per THREAD (the header promises "valid until the next call on ctx from this thread": gunicorn gthread
+// workers share a ctx) plus a copy in the ctx for readers on another thread.  dvb_tls_err lives in api.cu.
+char* dvb_tls_err(dvb_ctx* owner);                           // this thread's 512-byte buffer, from now on speaking for `owner`
 static inline void dvb_set_err(dvb_ctx* ctx, const char* fmt, const char* a = "", const char* b = "") {
     if (!ctx) return;
+    char* buf = dvb_tls_err(ctx);
+    snprintf(buf, 512, fmt, a, b);
     std::lock_guard<std::mutex> g(ctx->mu);
-    snprintf(ctx->err, sizeof(ctx->err), fmt, a, b);
+    memcpy(ctx->err, buf, sizeof(ctx->err));
 }
+
+// dvb_set_stream is per (thread, ctx): a bench thread that brackets calls with its own events does not redirect the calls of
+// a worker thread on the same ctx.  Defined in api.cu.
+void* dvb_tls_stream(const dvb_ctx* ctx);
 
 #define DVB_CUDA(ctx, expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
     dvb_set_err(ctx, "CUDA error %s at %s", cudaGetErrorString(e__), #expr); return DVB_E_CUDA; } } while (0)
@@ -81,8 +89,20 @@ struct dvb_scope {
         if (l->high_water > l->arena.cap) reserve(l->high_water);
     }
     size_t call_bytes = 0;
-    ~dvb_scope() { std::lock_guard<std::mutex> g(ctx->mu); l->busy = false; }
-    cudaStream_t stream() const { void* u = ctx->user_stream.load(); return u ? (cudaStream_t)u : l->stream; }
+    ~dvb_scope() {
+        // a call that returned early (error path) may still have kernels in flight on the lease's stream: the next call on this
+        // lease resets the arena, so the stream is drained here (a no-op after a normal finish)
+        cudaStreamSynchronize(l->stream);
+        if (l->copy) cudaStreamSynchronize(l->copy);
+        // the workspace follows the recent calls instead of the largest call ever: the high-water mark decays by 1/8 per call and
+        // an arena more than 4x (and 256 MB) above it is given back
+        l->high_water = std::max(call_bytes, l->high_water - l->high_water / 8);
+        if (l->arena.base && l->arena.cap > (size_t(256) << 20) && l->arena.cap / 4 > l->high_water) {
+            cudaFree(l->arena.base); l->arena.base = nullptr; l->arena.cap = 0;
+        }
+        std::lock_guard<std::mutex> g(ctx->mu); l->busy = false;
+    }
+    cudaStream_t stream() const { void* u = dvb_tls_stream(ctx); return u ? (cudaStream_t)u : l->stream; }
     // reserve total workspace up front (grows the arena if needed; invalidates earlier allocs)
     int32_t reserve(size_t bytes) {
         bytes = (bytes + 255) & ~size_t(255);

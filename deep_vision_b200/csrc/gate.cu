@@ -234,7 +234,9 @@ __global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __r
         const int64_t c0 = cap_off[s];
         // code points (+1 for every 2-byte character: U+0130 lower-cases to two), times the synonym growth, bound the scratch use
         int64_t ncp = 2;
-        for (int64_t i = 0; i < nb && ncp <= GQ_CAP; i++) { const uint32_t c = t[i]; ncp += ((c & 0xC0u) != 0x80u) + ((c & 0xE0u) == 0xC0u); }
+        // stepped exactly like the decoder of gate_question (a stray continuation byte starts a 2-byte sequence there), so raw bytes
+        // that are not valid UTF-8 cannot produce more code points than counted here
+        for (int64_t i = 0; i < nb && ncp <= GQ_CAP; ) { const uint32_t c = t[i]; const int len = c < 0x80u ? 1 : (c < 0xE0u ? 2 : (c < 0xF0u ? 3 : 4)); ncp += 1 + (len == 2); i += len; }
         if (ncp * T.growth <= GQ_CAP) gate_question(t, nb, sa, sb, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, true);
         else gate_question(t, nb, GqGlobal{ bufA + c0 }, GqGlobal{ bufB + c0 }, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, false);
     }
@@ -649,7 +651,8 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     GateKeyTable KT{ nullptr, nullptr, nullptr, 0u };
     if (prefix) {
         d_nflag = io.tmp<int32_t>(1); d_flagged = io.tmp<int64_t>((size_t)n_cand);
-        uint32_t cap = 1024; while ((int64_t)cap < 2 * n_pairs) cap <<= 1;            // <= half full (distinct keys <= pairs)
+        if (n_pairs > (1LL << 30)) { dvb_set_err(ctx, "dvb_question_gate: history too large for the key table%s%s"); return DVB_E_CAPACITY; }
+        uint32_t cap = 1024; while ((int64_t)cap < 2 * n_pairs) cap <<= 1;            // <= half full (distinct keys <= pairs); n_pairs <= 2^30 keeps cap in 32 bits
         KT.mask = cap - 1;
         KT.key = io.tmp<unsigned long long>((size_t)cap); KT.lo = io.tmp<uint32_t>((size_t)cap); KT.df = io.tmp<uint32_t>((size_t)cap);
         rc = io.check(ctx); if (rc) return rc;

@@ -51,7 +51,7 @@ typedef struct dvb_ctx dvb_ctx;
 /* ---- handles ---- */
 int32_t     dvb_create(int32_t device, dvb_ctx** out);
 void        dvb_destroy(dvb_ctx* ctx);
-const char* dvb_last_error(dvb_ctx* ctx);           /* valid until the next call on ctx from this thread */
+const char* dvb_last_error(dvb_ctx* ctx);           /* per thread: valid until the next failing call of this thread */
 int32_t     dvb_version(void);
 /* Unicode version of the case / class tables compiled into the library (CPython's unicodedata.unidata_version at
  * generation time): str.lower() of web/server.py:24723, 32039, 20463 must agree with the host interpreter's. */
@@ -62,8 +62,8 @@ int64_t     dvb_launch_count(dvb_ctx* ctx);
  * events on the launching stream (0 if timing was not enabled with dvb_set_timing). */
 void        dvb_set_timing(dvb_ctx* ctx, int32_t enabled);
 float       dvb_last_kernel_ms(dvb_ctx* ctx);
-/* run all subsequent calls on the caller's CUDA stream (a cudaStream_t; NULL restores the internal
- * per-call streams).  Lets the caller bracket calls with its own CUDA events. */
+/* run the subsequent calls THIS THREAD makes on ctx on the caller's CUDA stream (a cudaStream_t; NULL restores the
+ * internal per-call streams).  Lets the caller bracket calls with its own CUDA events; other threads are not affected. */
 void        dvb_set_stream(dvb_ctx* ctx, void* stream);
 
 /* ---- a1  replaces: _tokenize_similarity_text_v3(text) -> set[str]   web/server.py:24722-24732

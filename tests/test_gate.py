@@ -140,3 +140,24 @@ def test_gpu_gate_config4_history_size_slice_vs_oracle(gpu_ctx, oracle):
     assert got[sl].tolist() == want.tolist()
     hit = [i for i, h in planted.items() if got[i] >= h]
     assert len(hit) >= 0.95 * len(planted), (len(hit), len(planted))
+
+
+@pytest.mark.gpu
+def test_gpu_question_keys_survive_raw_bytes_that_are_not_utf8(gpu_ctx):
+    """The C ABI accepts raw bytes: a question of continuation bytes only decodes (by the kernel's rule) to many more
+    code points than it has lead bytes; the shared-memory scratch must be chosen by what the decoder produces."""
+    from deep_vision_b200 import _lib, question_similarity as qs
+    from deep_vision_b200.packing import ptr
+    gate = qs.QuestionGate(ctx=gpu_ctx)
+    blobs = [bytes([0x80 + (i % 64) for i in range(n)]) for n in (256, 300, 2000, 63, 64, 65, 130)] + ["正常的问题文本？".encode("utf-8")]
+    data = np.frombuffer(b"".join(blobs) + b"\0" * 64, np.uint8).copy()
+    off = np.zeros(len(blobs) + 1, np.int64); off[1:] = np.cumsum([len(b) for b in blobs])
+    n = len(blobs)
+    cap = int(((off[1:] - off[:-1]) + 2).sum() * gate._growth)
+    cap_off = np.zeros(n + 1, np.int64); keys = np.zeros(cap, np.uint64); cnt = np.zeros(n, np.int32)
+    for _ in range(3):
+        rc = gpu_ctx.lib.dvb_question_keys(gpu_ctx.handle, _lib.MEM_HOST, ptr(data), ptr(off), n, *gate._table_args(),
+                                           ptr(cap_off), ptr(keys), ptr(cnt), None, None, cap)
+        gpu_ctx.check(rc, "dvb_question_keys")
+    assert int(cnt[-1]) == len(gate.keys(["正常的问题文本？"])[0]) > 0           # the context is still healthy and the valid text unaffected
+    assert all(int(c) >= 0 for c in cnt)
