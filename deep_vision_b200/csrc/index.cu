@@ -45,7 +45,8 @@ __global__ void __launch_bounds__(256) k_ix_count(const uint16_t* __restrict__ s
     }
 }
 __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
-                                                  int64_t n_chunks, const int64_t* __restrict__ post_off, unsigned long long* __restrict__ pk, uint32_t* __restrict__ pv) {
+                                                  int64_t n_chunks, const int64_t* __restrict__ post_off, unsigned long long* __restrict__ pk, uint32_t* __restrict__ pv,
+                                                  uint8_t* __restrict__ digit0) {
     const int lane = threadIdx.x & 31;
     for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_chunks; c += (int64_t)gridDim.x * 8) {
         const uint16_t* s = sym + sym_off[c]; const int32_t m = sym_cnt[c];
@@ -58,13 +59,82 @@ __global__ void __launch_bounds__(256) k_ix_emit(const uint16_t* __restrict__ sy
             const uint32_t bal = __ballot_sync(0xffffffffu, v);
             if (v) {
                 const int64_t o = w + __popc(bal & ((1u << lane) - 1u));
-                pk[o] = ((unsigned long long)c << 32) | (ix_pair_key(a, b) << IX_SUB_BITS) | (nx & IX_SUB_MASK);
+                const uint32_t k32 = (ix_pair_key(a, b) << IX_SUB_BITS) | (nx & IX_SUB_MASK);
+                pk[o] = ((unsigned long long)c << 32) | k32;
                 pv[o] = (uint32_t)i | (nx << 16);                  // position | the symbol AFTER the pair (0 = none / separator)
+                digit0[o] = (uint8_t)k32;                          // the first radix pass builds its histogram from these bytes, not from the keys
             }
             w += __popc(bal);
         }
     }
 }
+// ---- K2a + first radix pass fused: the postings are never written in emission order.
+// Block b owns the postings with emission index [b * RS_TILE, (b + 1) * RS_TILE): it finds the chunks that produce them
+// (binary search in the scanned per-chunk counts), re-walks their symbols — a chunk that straddles a block border is walked
+// by both neighbours, 16 steps for a 512-character chunk — and hands every posting of its range to `sink(tile position, key, value)`.
+template <typename Sink>
+__device__ __forceinline__ void ix_block_postings(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
+                                                  int64_t n_chunks, const int64_t* __restrict__ post_off, int64_t n_post, Sink sink) {
+    __shared__ int64_t s_c0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t P0 = (int64_t)blockIdx.x * RS_TILE, P1 = min(n_post, P0 + RS_TILE);
+    if (threadIdx.x == 0) {                                      // last chunk whose first posting index is <= P0
+        int64_t lo = 0, hi = n_chunks - 1;
+        while (lo < hi) { const int64_t mid = (lo + hi + 1) >> 1; if (post_off[mid] <= P0) lo = mid; else hi = mid - 1; }
+        s_c0 = lo;
+    }
+    __syncthreads();
+    for (int64_t c = s_c0 + warp; c < n_chunks; c += RS_WARPS) {
+        int64_t w = post_off[c];
+        if (w >= P1) break;
+        const int64_t wend = post_off[c + 1];
+        if (wend <= P0) continue;
+        const uint16_t* s = sym + sym_off[c]; const int32_t m = sym_cnt[c];
+        for (int32_t b0 = 0; b0 + 1 < m && w < P1; b0 += 32) {
+            const int32_t i = b0 + lane;
+            uint32_t a = 0, b = 0, nx = 0;
+            if (i + 1 < m) { a = s[i]; b = s[i + 1]; if (i + 2 < m) nx = s[i + 2]; }
+            const bool v = ix_same_class(a, b);
+            const uint32_t bal = __ballot_sync(0xffffffffu, v);
+            if (v) {
+                const int64_t o = w + __popc(bal & ((1u << lane) - 1u));
+                if (o >= P0 && o < P1)
+                    sink((int)(o - P0), ((unsigned long long)c << 32) | (ix_pair_key(a, b) << IX_SUB_BITS) | (nx & IX_SUB_MASK), (uint32_t)i | (nx << 16));
+            }
+            w += __popc(bal);
+        }
+    }
+}
+struct IxHistSink { uint32_t* h; __device__ __forceinline__ void operator()(int, unsigned long long key, uint32_t) const { atomicAdd(&h[(uint32_t)key & 255u], 1u); } };
+struct IxStageSink { unsigned long long* k; uint32_t* v; __device__ __forceinline__ void operator()(int pos, unsigned long long key, uint32_t val) const { k[pos] = key; v[pos] = val; } };
+
+static __global__ void __launch_bounds__(RS_THREADS) k_ix_hist1(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
+                                                                int64_t n_chunks, const int64_t* __restrict__ post_off, int64_t n_post,
+                                                                uint32_t* __restrict__ hist /*[256][nb]*/, int64_t nb) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    ix_block_postings(sym, sym_off, sym_cnt, n_chunks, post_off, n_post, IxHistSink{ h });
+    __syncthreads();
+    hist[(int64_t)threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
+}
+static __global__ void __launch_bounds__(RS_THREADS, 3) k_ix_scatter1(const uint16_t* __restrict__ sym, const int64_t* __restrict__ sym_off, const int32_t* __restrict__ sym_cnt,
+                                                                      int64_t n_chunks, const int64_t* __restrict__ post_off, int64_t n_post,
+                                                                      unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals,
+                                                                      const uint32_t* __restrict__ hist, int64_t nb, uint8_t* __restrict__ next_digit) {
+    extern __shared__ __align__(16) unsigned char rs_raw[];
+    RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
+    ix_block_postings(sym, sym_off, sym_cnt, n_chunks, post_off, n_post, IxStageSink{ sm.key, sm.val });       // emission order inside the tile
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cnt_tile = (int)min((int64_t)RS_TILE, n_post - (int64_t)blockIdx.x * RS_TILE);
+    unsigned long long k[RS_PER_LANE];
+    uint32_t v[RS_PER_LANE];
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) { const int t = warp * RS_ITEMS_PER_WARP + j * 32 + lane; k[j] = t < cnt_tile ? sm.key[t] : 0ULL; v[j] = t < cnt_tile ? sm.val[t] : 0u; }
+    rs_scatter_body(k, v, sm, okeys, ovals, n_post, 0, hist, nb, next_digit, 8);      // its first barrier orders these reads before the placement writes
+}
+
 // exclusive scan of int32 counts into int64 offsets (single CTA; n is the number of chunks / blocks)
 #define IX_SCAN_PER 8
 static __global__ void __launch_bounds__(1024) k_ix_scan(const int32_t* __restrict__ cnt, int64_t* __restrict__ off, int64_t n) {
@@ -506,11 +576,30 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
         IX_TRY(cudaMallocAsync((void**)&s_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&sg->pv, 4 * (size_t)n_post, st));
         IX_TRY(cudaMallocAsync((void**)&t_pk, 8 * (size_t)n_post, st)); IX_TRY(cudaMallocAsync((void**)&t_pv, 4 * (size_t)n_post, st));
         IX_TRY(cudaMallocAsync((void**)&d_hist, 4 * dv_radix_hist_words(n_post), st));
-        k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, s_pk, sg->pv);
-        ctx->launches += 1;
-        // K2b: stable sort by the 30 key bits + 2 sub-list bits (32 = 4 passes of 8)
+        // K2a + K2b: the first radix pass generates the postings from the symbols (no emission-order copy in HBM), the other
+        // three move 12-byte postings; stable, so postings of one key stay ordered by (chunk, position)
         int64_t l = 0;
-        const int which = dv_radix_sort_pairs(s_pk, sg->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l);
+        int which;
+        // Measured at 1 M chunks (profiles/README.md): generating the postings inside the first pass (DVB_IX_FUSED=1) costs more
+        // than it saves — 23.96 ms against 20.40 ms: the symbols are walked twice (histogram, scatter) by one warp per chunk
+        // with ~9 chunks per 8-warp block — so the default emits once and sorts; the fused kernels stay as the A/B arm.
+        static const bool fused = [] { const char* e = getenv("DVB_IX_FUSED"); return e && e[0] == '1'; }();
+        if (!fused) {
+            k_ix_emit<<<grid, 256, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, s_pk, sg->pv, dv_radix_digits_ptr(d_hist, n_post));
+            ctx->launches += 1;
+            which = dv_radix_sort_pairs(s_pk, sg->pv, t_pk, t_pv, n_post, 0, 32, d_hist, st, &l, /*first_digits_ready=*/true);
+        } else {
+            const int64_t nrb = (n_post + RS_TILE - 1) / RS_TILE;
+            cudaFuncSetAttribute(k_ix_scatter1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
+            k_ix_hist1<<<(unsigned)nrb, RS_THREADS, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, n_post, d_hist, nrb);
+            k_rs_scan<<<256, 1024, 0, st>>>(d_hist, nrb, dv_radix_totals_ptr(d_hist, n_post), 0);
+            k_rs_scan<<<256, 1024, 0, st>>>(d_hist, nrb, dv_radix_totals_ptr(d_hist, n_post), 1);
+            k_ix_scatter1<<<(unsigned)nrb, RS_THREADS, sizeof(RsSmem), st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, n_post, t_pk, t_pv,
+                                                                               d_hist, nrb, dv_radix_digits_ptr(d_hist, n_post));
+            ctx->launches += 4;
+            // passes 2..4 read t_*, so the ping-pong roles are swapped for the call: result 0 = t_*, 1 = s_*
+            which = 1 - dv_radix_sort_pairs(t_pk, t_pv, s_pk, sg->pv, n_post, 8, 32, d_hist, st, &l, /*first_digits_ready=*/true);
+        }
         ctx->launches += l;
         if (which) { std::swap(s_pk, t_pk); std::swap(sg->pv, t_pv); }
         cudaFreeAsync(t_pk, st); t_pk = nullptr; cudaFreeAsync(t_pv, st); t_pv = nullptr;      // the pool hands these bytes to pc below

@@ -93,20 +93,13 @@ struct RsSmem {
     uint32_t delta[256];             // global offset of the block's digit run minus its block-local start
     uint32_t wsum[RS_WARPS];
 };
-static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
-                                                               unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
-                                                               const uint32_t* __restrict__ hist, int64_t nb, uint8_t* __restrict__ next_digit, int next_shift) {
-    extern __shared__ __align__(16) unsigned char rs_raw[];
-    RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
+// The tile's items are in registers (item j of a lane = tile position warp * 512 + j * 32 + lane); everything after the load.
+static __device__ __forceinline__ void rs_scatter_body(unsigned long long (&k)[RS_PER_LANE], uint32_t (&v)[RS_PER_LANE], RsSmem& sm,
+                                                       unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
+                                                       const uint32_t* __restrict__ hist, int64_t nb, uint8_t* __restrict__ next_digit, int next_shift) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t bbase = (int64_t)blockIdx.x * RS_TILE;
     const int64_t wbase = bbase + (int64_t)warp * RS_ITEMS_PER_WARP;
-    unsigned long long k[RS_PER_LANE];
-    uint32_t v[RS_PER_LANE];
-#pragma unroll
-    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; k[j] = g < n ? keys[g] : 0ULL; }
-#pragma unroll
-    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; v[j] = g < n ? vals[g] : 0u; }
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&sm.cnt[0][0])[i] = 0;
     __syncthreads();
     // phase 1: per-warp digit counts
@@ -174,23 +167,45 @@ static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsig
         if (next_digit) next_digit[pos] = (uint8_t)(kk >> next_shift);       // the digit of the NEXT pass, for its histogram
     }
 }
+static __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_scatter(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                               unsigned long long* __restrict__ okeys, uint32_t* __restrict__ ovals, int64_t n, int shift,
+                                                               const uint32_t* __restrict__ hist, int64_t nb, uint8_t* __restrict__ next_digit, int next_shift) {
+    extern __shared__ __align__(16) unsigned char rs_raw[];
+    RsSmem& sm = *reinterpret_cast<RsSmem*>(rs_raw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t wbase = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * RS_ITEMS_PER_WARP;
+    unsigned long long k[RS_PER_LANE];
+    uint32_t v[RS_PER_LANE];
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; k[j] = g < n ? keys[g] : 0ULL; }
+#pragma unroll
+    for (int j = 0; j < RS_PER_LANE; j++) { const int64_t g = wbase + j * 32 + lane; v[j] = g < n ? vals[g] : 0u; }
+    rs_scatter_body(k, v, sm, okeys, ovals, n, shift, hist, nb, next_digit, next_shift);
+}
 
 // Sorts n pairs by bits [begin_bit, end_bit) of the key.  keys/vals and tkeys/tvals are ping-pong
 // buffers; returns which pair of buffers holds the result (0 = keys/vals, 1 = tkeys/tvals).
 // hist needs dv_radix_hist_words(n) uint32 and 16-byte alignment.
+static inline uint32_t* dv_radix_totals_ptr(uint32_t* hist, int64_t n) { return hist + 256 * ((n + RS_TILE - 1) / RS_TILE); }
+static inline uint8_t* dv_radix_digits_ptr(uint32_t* hist, int64_t n) {
+    const int64_t nb = (n + RS_TILE - 1) / RS_TILE;
+    return reinterpret_cast<uint8_t*>(hist + (((size_t)(256 * nb + 256) + 3) & ~size_t(3)));    // 16-byte aligned (hist is)
+}
+// first_digits_ready: an earlier pass (the caller's own) already wrote the digit bytes of the pass at begin_bit
 static inline int dv_radix_sort_pairs(unsigned long long* keys, uint32_t* vals, unsigned long long* tkeys, uint32_t* tvals,
-                                      int64_t n, int begin_bit, int end_bit, uint32_t* hist, cudaStream_t st, int64_t* launches) {
+                                      int64_t n, int begin_bit, int end_bit, uint32_t* hist, cudaStream_t st, int64_t* launches,
+                                      bool first_digits_ready = false) {
     if (n <= 1) return 0;
     cudaFuncSetAttribute(k_rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
     const int64_t nb = (n + RS_TILE - 1) / RS_TILE;
-    uint32_t* totals = hist + 256 * nb;
-    uint8_t* digits = reinterpret_cast<uint8_t*>(hist + (((size_t)(256 * nb + 256) + 3) & ~size_t(3)));    // 16-byte aligned (hist is)
+    uint32_t* totals = dv_radix_totals_ptr(hist, n);
+    uint8_t* digits = dv_radix_digits_ptr(hist, n);
     int cur = 0;
     for (int shift = begin_bit; shift < end_bit; shift += 8) {
         unsigned long long* ik = cur ? tkeys : keys; uint32_t* iv = cur ? tvals : vals;
         unsigned long long* ok = cur ? keys : tkeys; uint32_t* ov = cur ? vals : tvals;
         const bool more = shift + 8 < end_bit;
-        if (shift == begin_bit) k_rs_hist<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, n, shift, hist, nb);
+        if (shift == begin_bit && !first_digits_ready) k_rs_hist<<<(unsigned)nb, RS_THREADS, 0, st>>>(ik, n, shift, hist, nb);
         else k_rs_hist8<<<(unsigned)nb, RS_THREADS, 0, st>>>(digits, n, hist, nb);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 0);
         k_rs_scan<<<256, 1024, 0, st>>>(hist, nb, totals, 1);
