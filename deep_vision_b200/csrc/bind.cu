@@ -92,8 +92,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     int grid7 = 1;
     if (fast) {
         int occ7 = 1;
-        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
-        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_claims, BIND_THREADS, smem7));
+        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_facts, BIND_THREADS, smem7));
         if (occ7 < 1) occ7 = 1;
         grid7 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ7);
     }
@@ -106,7 +107,13 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     }
     need += dvb_pad((size_t)grid * (size_t)cap * 12);
     if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
-    if (fast) need += dvb_pad((size_t)grid7 * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4);
+    // fast kernels: one slab per claim group of a wave of sessions.  A session of n claims has ceil(n / 32) groups, so a
+    // range of sessions holds at most sessions + claims / 32 of them; ranges are cut so that a wave's slabs stay below 1 GB.
+    const int64_t slab_budget = std::max<int64_t>(((int64_t)1 << 30) / B7_BLOB_BYTES, 64);
+    const int64_t groups_bound = n_sessions + n_claims / BIND_CLAIMS;
+    const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
+    if (fast) need += dvb_pad((size_t)grid7 * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
+                    + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
@@ -162,18 +169,56 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         *(volatile int*)l->flag_h = 0;
         p7.gtable = sc.alloc<unsigned long long>((size_t)grid7 * bind7_ws_u64_per_cta());
         p7.sess_fallback = sc.alloc<uint8_t>((size_t)n_sessions);
-        if (!p7.gtable || !p7.sess_fallback) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        p7.sess_slab = sc.alloc<int32_t>((size_t)n_sessions);
+        p7.slab_cursor = sc.alloc<int>(16);
+        p7.slabs = sc.alloc<uint8_t>((size_t)n_slabs * B7_BLOB_BYTES);
+        if (!p7.gtable || !p7.sess_fallback || !p7.sess_slab || !p7.slab_cursor || !p7.slabs) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
         DVB_CUDA(ctx, cudaMemsetAsync(p7.sess_fallback, 0, (size_t)n_sessions, st));
         p7.overflow = l->flag_d;
     }
-    // one launch over sessions [s0, s1): fast kernel unless the call was routed to the general one
+    // sessions [s0, s1): the fast pair (claim tables, then facts; in waves whose claim groups fit the slabs) unless the call
+    // was routed to the general kernel
+    std::vector<int64_t> wave_sco;                            // session -> first claim, on the host, only when waves have to be cut
     auto launch = [&](bool use_fast, int64_t s0, int64_t s1) -> cudaError_t {
         BindParams q = use_fast ? p7 : p;
-        q.s_begin = s0; q.s_end = s1;
-        if (use_fast) k_bind_claims<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
-        else k_bind_claims_general<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(q);
-        ctx->launches += 1;
-        return cudaGetLastError();
+        if (!use_fast) {
+            q.s_begin = s0; q.s_end = s1;
+            k_bind_claims_general<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(q);
+            ctx->launches += 1;
+            return cudaGetLastError();
+        }
+        const int64_t* sco_h = mem == DVB_MEM_HOST ? sess_claim_off : nullptr;
+        if (groups_bound > n_slabs && !sco_h) {               // device offsets and more groups than slabs: fetch the offsets once
+            if (wave_sco.empty()) {
+                wave_sco.resize((size_t)n_sessions + 1);
+                cudaError_t e = cudaMemcpyAsync(wave_sco.data(), sess_claim_off, 8 * (size_t)(n_sessions + 1), cudaMemcpyDeviceToHost, st);
+                if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+                if (e != cudaSuccess) return e;
+            }
+            sco_h = wave_sco.data();
+        }
+        for (int64_t a = s0; a < s1;) {
+            int64_t b = s1;
+            if (groups_bound > n_slabs) {                     // longest prefix of sessions whose groups fit
+                int64_t g = 0; b = a;
+                while (b < s1) {
+                    const int64_t gs = (sco_h[b + 1] - sco_h[b] + BIND_CLAIMS - 1) / BIND_CLAIMS;
+                    if (g + gs > n_slabs) break;
+                    g += gs; b++;
+                }
+                if (b == a) return cudaErrorInvalidValue;     // one session with more groups than a wave holds (> 1 GB of tables)
+            }
+            q.s_begin = a; q.s_end = b;
+            cudaError_t e = cudaMemsetAsync(q.slab_cursor, 0, 4, st);
+            if (e != cudaSuccess) return e;
+            const int g7 = (int)std::min<int64_t>(b - a, (int64_t)grid7);
+            k_bind_claim_tables<<<g7, BIND_THREADS, smem7, st>>>(q);
+            k_bind_facts<<<g7, BIND_THREADS, smem7, st>>>(q);
+            ctx->launches += 2;
+            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            a = b;
+        }
+        return cudaSuccess;
     };
     const bool timing = ctx->timing.load() != 0;
     if (mem == DVB_MEM_DEVICE) {

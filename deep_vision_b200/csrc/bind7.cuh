@@ -1,4 +1,4 @@
-// bind7.cuh — k_bind_claims: the fused claim->fact binding kernel, cell tokenizer (included by bind.cu).
+// bind7.cuh — k_bind_claim_tables + k_bind_facts: the claim->fact binding kernels, cell tokenizer (included by bind.cu).
 // replaces: the scoring loop of infer_weak_evidence_refs_v3 (reference web/server.py:24813-24864) with the token
 //           semantics of _tokenize_similarity_text_v3 (web/server.py:24722-24732).
 //
@@ -31,6 +31,18 @@
 #ifndef B7_RUNG
 #define B7_RUNG 6
 #endif
+#ifndef B7_PSTS
+#define B7_PSTS 1
+#endif
+#ifndef B7_NI_INSERT
+#define B7_NI_INSERT 1
+#endif
+#ifndef B7_B_APFX
+#define B7_B_APFX 1
+#endif
+#ifndef B7_C_PPFX
+#define B7_C_PPFX 1
+#endif
 #define B7_NB 2048                   // bigram-table buckets of four 32-bit entries (32 KB)
 #define B7_HASH 0x9E3779B1u          // id -> h = id * B7_HASH: a bijection on the 30-bit ids (mod 2^30)
 #define B7_STASH 32                  // exact side list for the keys of buckets that are full
@@ -39,6 +51,8 @@
 #define B7_TCAP 3072                 // dense token indices per claim group = flag bytes per warp
 #define B7_HSTRIDE 4096              // per warp: B7_TCAP flag bytes, then the warp's scratch
 #define B7_FT_BITS 12                // signature filter in front of the ASCII-token probes
+#define B7_APFX_WORDS 48             // 38 * 38 = 1444 bits, padded to a multiple of 16 bytes
+#define B7_PPFX_BITS 12
 #define B7_CELL 12
 #define B7_STEP (32 * B7_CELL)
 #define B7_FULL 0xffffffffu
@@ -60,20 +74,43 @@ struct __align__(16) B7Scratch {     // per warp
     };
 };
 
+// What the claim kernel hands to the fact kernel besides the packed tables: copied as it stands (uint4s) between shared
+// memory and the group's slab.
+struct __align__(16) B7Head {
+    uint32_t n_tab, n_tok, n_sl, ttot;             // packed section sizes: table entries, token keys, shared-list entries; token indices used
+    uint16_t rbase[BIND_CLAIMS + 8];               // token-index range of claim c = [rbase[c], rbase[c + 1])
+    uint16_t ownc[BIND_CLAIMS], shc[BIND_CLAIMS];  // own / shared token counts of the claims
+    uint32_t ovb[B7_NB / 32];                      // bucket b has keys in the side list
+    uint32_t stash_id[B7_STASH], stash_e[B7_STASH];
+    uint32_t ft[1u << (B7_FT_BITS - 5)];
+    uint32_t apfx[B7_APFX_WORDS];                  // first two characters of the claims' ASCII tokens (38 x 38 bits)
+    uint32_t ppfx[1u << (B7_PPFX_BITS - 5)];       // (first two characters, length) of the claims' pieces, hashed
+};
+static_assert(sizeof(B7Head) % 16 == 0, "copied as uint4s");
+
 struct __align__(16) B7Shared {
     uint32_t tab[B7_NB * 4];
     uint8_t H[BIND_WARPS][B7_HSTRIDE];             // [0, B7_TCAP): facts: hit flags by token index; claims: "already listed" flags; then B7Scratch
     uint16_t tixT[B7_CAPT];                        // token-table slot -> t + 1
     uint16_t slist[B7_TCAP];                       // claim c's shared tokens at [rbase[c], rbase[c] + shc[c])
-    uint32_t ft[1u << (B7_FT_BITS - 5)];
-    uint32_t ovb[B7_NB / 32];                      // bucket b has keys in the side list
-    uint32_t stash_id[B7_STASH], stash_e[B7_STASH];
+    B7Head hd;
     unsigned long long ktab[DV_KTAB];
-    uint16_t rbase[BIND_CLAIMS + 1];
-    uint16_t ownc[BIND_CLAIMS], shc[BIND_CLAIMS];
     uint8_t lut[128];
     int next_item, ntok, ovf, exotic, wcnt[BIND_WARPS];
+    uint32_t wsum[BIND_WARPS], tsum[32];           // pack / unpack scans
+    int slab;
 };
+// Slab of one claim group in the workspace (bytes): head | table bitmap | token bitmap | packed shared lists | packed token
+// indices | packed token keys | packed table entries.  Sections are sized for the kernel's own limits (B7_TCAP token indices,
+// B7_TOK_LIMIT token keys), so a group that passes the claim kernel always fits.
+#define B7_BLOB_TABMAP 2048
+#define B7_BLOB_TOKMAP (B7_BLOB_TABMAP + B7_NB * 4 / 8)
+#define B7_BLOB_SLIST (B7_BLOB_TOKMAP + B7_CAPT / 8)
+#define B7_BLOB_TOKTIX (B7_BLOB_SLIST + 2 * B7_TCAP)
+#define B7_BLOB_TOKKEY (B7_BLOB_TOKTIX + 2 * B7_TOK_LIMIT)
+#define B7_BLOB_TABENT (B7_BLOB_TOKKEY + 8 * B7_TOK_LIMIT)
+#define B7_BLOB_BYTES (B7_BLOB_TABENT + 4 * B7_TCAP)
+static_assert(sizeof(B7Head) <= B7_BLOB_TABMAP && B7_BLOB_TOKKEY % 8 == 0 && B7_BLOB_TABENT % 16 == 0 && B7_BLOB_BYTES % 16 == 0, "slab layout");
 static_assert(sizeof(B7Scratch) <= B7_HSTRIDE - B7_TCAP, "the warp scratch lives behind the warp's flag bytes");
 static_assert(sizeof(B7Shared) <= 76800, "three CTAs per SM");
 
@@ -84,6 +121,7 @@ typedef uintptr_t b7_saddr;                         // the emulator has no share
 static inline b7_saddr b7_sa(const void* p) { return (uintptr_t)p; }
 static inline uint4 b7_lds128(b7_saddr a) { return *reinterpret_cast<const uint4*>(a); }
 static inline void b7_sts8(b7_saddr a, uint32_t v) { *reinterpret_cast<volatile uint8_t*>(a) = (uint8_t)v; }
+static inline void b7_sts8_if(bool c, b7_saddr a, uint32_t v) { if (c) *reinterpret_cast<volatile uint8_t*>(a) = (uint8_t)v; }
 #else
 #define B7_SH() (*reinterpret_cast<B7Shared*>(bind_smem))
 // 32-bit shared-window addresses kept in registers: the compiler otherwise rebuilds the window base (S2R + MOV + LEA) at
@@ -96,6 +134,11 @@ __device__ __forceinline__ uint4 b7_lds128(b7_saddr a) {
     return v;
 }
 __device__ __forceinline__ void b7_sts8(b7_saddr a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+// one predicated store: an `if` around the hit-flag store of the slot loop became a divergent region per slot (BSSY / BRA /
+// BSYNC / WARPSYNC: 13 instructions per slot, 52 of the 180 control instructions of a step)
+__device__ __forceinline__ void b7_sts8_if(bool c, b7_saddr a, uint32_t v) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p st.shared.u8 [%0], %1;\n\t}" :: "r"(a), "r"(v), "r"((uint32_t)c) : "memory");
+}
 #endif
 
 struct B7Tok {                       // per-warp tokenizer state (registers)
@@ -149,12 +192,12 @@ __device__ __forceinline__ bool b7_has_byte(uint32_t w, uint32_t b) {
 }
 __device__ __forceinline__ bool b7_ft_pass(const B7Shared& sh, uint32_t sig) {
     const uint32_t h = sig >> (32 - B7_FT_BITS);
-    return ((sh.ft[h >> 5] >> (h & 31)) & 1u) != 0u;
+    return ((sh.hd.ft[h >> 5] >> (h & 31)) & 1u) != 0u;
 }
 
 // ---------------------------------------------------------------- claim side: insert, token index, shared lists
 __device__ __forceinline__ uint32_t* b7_entry(B7Shared& sh, uint32_t slot) {       // bigram slots only
-    return (slot & B7_SLOT_STASH) ? &sh.stash_e[slot & (B7_SLOT_STASH - 1u)] : &sh.tab[slot];
+    return (slot & B7_SLOT_STASH) ? &sh.hd.stash_e[slot & (B7_SLOT_STASH - 1u)] : &sh.tab[slot];
 }
 // Convergent.  `act` lanes hold DISTINCT slots of tokens of the warp's claim; `created` = this lane made the entry.
 // A created token gets the next index of the claim's own range; a token another claim (or an earlier step of this
@@ -201,11 +244,11 @@ __device__ __forceinline__ int b7_bigram_slot(B7Shared& sh, uint32_t id, bool in
         if (prev == 0u) { created = insert; return insert ? (int)(b * 4u + j) : -1; }
         if (((prev ^ k) >> 13) == 0u) return (int)(b * 4u + j);
     }
-    if (insert) atomicOr(&sh.ovb[b >> 5], 1u << (b & 31u));
-    else if (!((sh.ovb[b >> 5] >> (b & 31u)) & 1u)) return -1;
+    if (insert) atomicOr(&sh.hd.ovb[b >> 5], 1u << (b & 31u));
+    else if (!((sh.hd.ovb[b >> 5] >> (b & 31u)) & 1u)) return -1;
     for (int j = 0; j < B7_STASH; j++) {
-        uint32_t prev = *(volatile uint32_t*)&sh.stash_id[j];
-        if (prev == 0u && insert) prev = atomicCAS(&sh.stash_id[j], 0u, id);
+        uint32_t prev = *(volatile uint32_t*)&sh.hd.stash_id[j];
+        if (prev == 0u && insert) prev = atomicCAS(&sh.hd.stash_id[j], 0u, id);
         if (prev == 0u) { created = insert; return insert ? (int)(B7_SLOT_STASH | (uint32_t)j) : -1; }
         if (prev == id) return (int)(B7_SLOT_STASH | (uint32_t)j);
     }
@@ -225,6 +268,20 @@ __device__ __forceinline__ void b7_bigram_insert(B7Tok& t, bool v, uint32_t id) 
     b7_claim_slot(t, slot >= 0, (uint32_t)slot, created);
 }
 
+// One out-of-line copy for the four slots of the claim walk (the inlined copies were 2 500 of the kernel's 8 600 instructions;
+// the fact walk shares the instruction cache with them).  vid = valid << 31 | id, own_shd = own | shared << 16.
+#ifdef DV_EMU
+#define B7_NOINLINE
+#else
+#define B7_NOINLINE __noinline__
+#endif
+__device__ B7_NOINLINE uint32_t b7_bigram_insert_ni(B7Shared* sh, uint8_t* H, int lane, uint32_t rb, uint32_t re, uint32_t own_shd, uint32_t vid) {
+    B7Tok t;
+    t.sh = sh; t.H = H; t.lane = lane; t.rb = rb; t.re = re; t.own = (int)(own_shd & 0xFFFFu); t.shd = (int)(own_shd >> 16);
+    b7_bigram_insert(t, (vid >> 31) != 0u, vid & 0x7FFFFFFFu);
+    return (uint32_t)t.own | ((uint32_t)t.shd << 16);
+}
+
 // Convergent: piece / ASCII tokens of the claim (64-bit keys) go to the open-addressing table in the workspace.
 __device__ __forceinline__ void b7_token_insert(B7Tok& t, bool v, uint64_t key, uint32_t sig) {
     B7Shared& sh = *t.sh;
@@ -236,7 +293,7 @@ __device__ __forceinline__ void b7_token_insert(B7Tok& t, bool v, uint64_t key, 
         if (*(volatile int*)&sh.ntok >= B7_TOK_LIMIT) sh.ovf = 1;
         else {
             const uint32_t h = sig >> (32 - B7_FT_BITS);
-            atomicOr(&sh.ft[h >> 5], 1u << (h & 31));
+            atomicOr(&sh.hd.ft[h >> 5], 1u << (h & 31));
             slot = bind_hash(key) & (B7_CAPT - 1);
             for (;;) {
                 const unsigned long long prev = atomicCAS(&t.tkeys[slot], 0ULL, (unsigned long long)key);
@@ -254,12 +311,12 @@ __device__ __forceinline__ void b7_token_insert(B7Tok& t, bool v, uint64_t key, 
 // piece << 12 | (t + 1) of id if it lives in the side list, else 0.  ~1 % of the probes get here; the loop stays rolled.
 __device__ __forceinline__ uint32_t b7_side_lookup(const B7Shared* sh, uint32_t h, uint32_t id) {
     const uint32_t bk = (h >> 19) & (B7_NB - 1u);
-    if (!((sh->ovb[bk >> 5] >> (bk & 31u)) & 1u)) return 0u;
+    if (!((sh->hd.ovb[bk >> 5] >> (bk & 31u)) & 1u)) return 0u;
 #pragma unroll 1
     for (int j = 0; j < B7_STASH; j++) {
-        const uint32_t sid = sh->stash_id[j];
+        const uint32_t sid = sh->hd.stash_id[j];
         if (sid == 0u) break;
-        if (sid == id) return sh->stash_e[j] & 0x1FFFu;
+        if (sid == id) return sh->hd.stash_e[j] & 0x1FFFu;
     }
     return 0u;
 }
@@ -302,24 +359,32 @@ __device__ __forceinline__ uint64_t b7_ascii_key(uint32_t h1, uint32_t h2, uint3
 }
 
 // Lanes [0, cnt) own one queued cell each: every ASCII token ([a-z0-9_]{2,} after lower-casing) that STARTS in the cell
-// is keyed by walking its bytes; a 0xC4 byte (lead of U+0130) hands the session back.
+// is keyed by walking its bytes; a 0xC4 byte (lead of U+0130) hands the session back.  Facts walk a token only when its
+// first two characters start an ASCII token of the claim group (apfx): most fact tokens end after two table reads.
 template <bool CLAIM>
 __device__ void b7_ascii_round(B7Tok& t, int head, int cnt) {
     B7Shared& sh = *t.sh;
     const bool act = t.lane < cnt;
     const int32_t o = act ? (int32_t)t.scr->aq[head + t.lane] : 0;
-    uint32_t starts = 0;
+    uint32_t starts = 0, w0 = 0, w1 = 0, w2 = 0, w3 = 0;
     if (act) {
-        const uint32_t wp = b7_ldw(t, o - 4), w0 = b7_ldw(t, o), w1 = b7_ldw(t, o + 4), w2 = b7_ldw(t, o + 8);
+        const uint32_t wp = b7_ldw(t, o - 4);
+        w0 = b7_ldw(t, o); w1 = b7_ldw(t, o + 4); w2 = b7_ldw(t, o + 8); w3 = b7_ldw(t, o + 12);
         if (b7_has_byte(w0, 0xC4u) || b7_has_byte(w1, 0xC4u) || b7_has_byte(w2, 0xC4u)) t.exotic = true;
-        const uint32_t al = b7_alnum4(w0) | (b7_alnum4(w1) << 4) | (b7_alnum4(w2) << 8);
+        const uint32_t al = b7_alnum4(w0) | (b7_alnum4(w1) << 4) | (b7_alnum4(w2) << 8) | (b7_alnum4(w3) << 12);
         const uint32_t pa = b7_alnum4(wp) >> 3;
-        starts = al & ~((al << 1) | pa) & 0xFFFu;
+        starts = al & ~((al << 1) | pa) & (al >> 1) & 0xFFFu;          // starts of tokens of >= 2 characters
     }
     while (__any_sync(B7_FULL, starts != 0u)) {
-        const bool has = starts != 0u;
+        bool has = starts != 0u;
         const int j = __ffs(starts) - 1;
         starts &= starts - 1u;
+        if (has) {
+            const uint32_t x = b7_fetch(w0, w1, w2, w3, (uint32_t)j);
+            const uint32_t pi = (uint32_t)sh.lut[x & 0x7Fu] * 38u + (uint32_t)sh.lut[(x >> 8) & 0x7Fu];
+            if (CLAIM) atomicOr(&sh.hd.apfx[pi >> 5], 1u << (pi & 31u));
+            else if (B7_B_APFX) has = ((sh.hd.apfx[pi >> 5] >> (pi & 31u)) & 1u) != 0u;
+        }
         uint32_t h1 = B7_AH1, h2 = B7_AH2, len = 0;
         if (has) {
             const uint8_t* bp = t.base + o + j;
@@ -334,11 +399,10 @@ __device__ void b7_ascii_round(B7Tok& t, int head, int cnt) {
                 len++;
             }
         }
-        const bool tk = has && len >= 2u;
         const uint64_t key = b7_ascii_key(h1, h2, len);
         const uint32_t sig = (h1 ^ (h2 >> 7)) * 0x85EBCA6Bu;
-        if (CLAIM) b7_token_insert(t, tk, key, sig);
-        else b7_token_probe(t, tk && b7_ft_pass(sh, sig), key);
+        if (CLAIM) b7_token_insert(t, has, key, sig);
+        else b7_token_probe(t, has && b7_ft_pass(sh, sig), key);
     }
 }
 
@@ -354,6 +418,17 @@ __device__ void b7_piece_round(B7Tok& t, int head, int cnt) {
     const uint32_t L = (e & 15u) + 1u;
     bool ok = act;
     if (ok && L < 12u && b7_code3(t, p + 3) != 0u) ok = false;
+    if (ok) {                                                       // (first two characters, length) of the piece: facts walk it only if a claim piece has them
+        const int32_t q = p - 3 * (int32_t)(L - 1u);                // bytes q .. q + 8 lie inside the text (L >= 3)
+        const uint32_t* wq = reinterpret_cast<const uint32_t*>(t.base + (q & ~3));
+        const uint32_t sft = ((uint32_t)q & 3u) * 8u;
+        const uint32_t q0 = wq[0], q1 = wq[1], q2 = wq[2];
+        const uint32_t x0 = __funnelshift_r(q0, q1, sft), x1 = __funnelshift_r(q1, q2, sft);
+        const uint32_t r0 = x0 & 0xFFFFFFu, r1 = ((x0 >> 24) | (x1 << 8)) & 0xFFFFFFu;
+        const uint32_t fi = ((r0 * 0x9E3779B1u) ^ (r1 * 0x85EBCA6Bu) ^ (L * 0xC2B2AE35u)) >> (32 - B7_PPFX_BITS);
+        if (CLAIM) atomicOr(&sh.hd.ppfx[fi >> 5], 1u << (fi & 31u));
+        else if (B7_C_PPFX) ok = ((sh.hd.ppfx[fi >> 5] >> (fi & 31u)) & 1u) != 0u;
+    }
     uint64_t mm = 0; uint32_t sp = 0, sl = 0;
     if (ok) {
         const uint8_t* bp = t.base + p - 3 * (int32_t)(L - 1u);
@@ -490,6 +565,10 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
         //      bigram hit an entry that ends a claim piece
         uint32_t candm = 0, candp = 0, vm = 0;
         uint32_t prev = pv >> 2;
+#if B7_PSTS
+        const int p_in = p;
+        bool side = false;
+#endif
         bool adn[4];                                 // the next character continues the run (last slot: possibly)
         adn[0] = ad[1]; adn[1] = ad[2]; adn[2] = ad[3]; adn[3] = ((x[3] >> 24) - 0xE5u) <= 4u;
 #pragma unroll
@@ -499,23 +578,54 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             const bool v = ad[i] && (p != 0 || (!CLAIM && B7_RUNG == 3));
             const uint32_t id = (prev << 15) | sy[i];
             bool pend = v && p >= 2 && (p == 11 || !adn[i]);
-            if (CLAIM) b7_bigram_insert(t, v, id);
-            else {
+            if (CLAIM) {
+#if B7_NI_INSERT
+                const uint32_t os = b7_bigram_insert_ni(t.sh, t.H, lane, t.rb, t.re, (uint32_t)t.own | ((uint32_t)t.shd << 16), (v ? 0x80000000u : 0u) | id);
+                t.own = (int)(os & 0xFFFFu); t.shd = (int)(os >> 16);
+#else
+                b7_bigram_insert(t, v, id);
+#endif
+            } else {
                 const uint32_t h = id * B7_HASH, k = h << 13;
                 const uint4 e = b7_lds128(tabS + ((h >> 15) & ((B7_NB - 1u) << 4)));
                 uint32_t m = min(min(e.x ^ k, e.y ^ k), min(e.z ^ k, e.w ^ k));
+#if B7_PSTS
+                const bool hit = v && (m - 1u) < 8191u;
+                side = side || (v && !hit && e.w != 0u);                                 // rare: full bucket, the key may be in the side list
+                b7_sts8_if(hit, hitS + (m & 0xFFFu), 1u);
+#else
                 bool hit = v && (m - 1u) < 8191u;
                 if (v && !hit && e.w != 0u) {                                            // rare: full bucket, the key may be in the side list
                     const uint32_t sm_ = b7_side_lookup(t.sh, h, id);
                     if (sm_) { m = sm_; hit = true; }
                 }
                 if (hit) b7_sts8(hitS + (m & 0xFFFu), 1u);
+#endif
                 pend = pend && hit && m >= 4096u;
                 vm |= (v ? 1u : 0u) << i;
             }
             if (pend) { candm |= 1u << i; candp |= (uint32_t)p << (4 * i); }
             prev = sy[i];
         }
+#if B7_PSTS
+        if (!CLAIM && side) {                        // ~1 % of the steps: the lane's valid bigrams again, against the side list only
+            int pp = p_in; uint32_t pr = pv >> 2;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                pp = ad[i] ? pp + 1 : 0;
+                if (pp == 12) pp = 0;
+                if (ad[i] && (pp != 0 || B7_RUNG == 3)) {
+                    const uint32_t id = (pr << 15) | sy[i];
+                    const uint32_t sm_ = b7_side_lookup(t.sh, id * B7_HASH, id);
+                    if (sm_) {
+                        b7_sts8(hitS + (sm_ & 0xFFFu), 1u);
+                        if (pp >= 2 && (pp == 11 || !adn[i]) && sm_ >= 4096u) { candm |= 1u << i; candp |= (uint32_t)pp << (4 * i); }
+                    }
+                }
+                pr = sy[i];
+            }
+        }
+#endif
         if (!CLAIM && B7_RUNG == 3) continue;
         carryP = __shfl_sync(B7_FULL, p, 31);
         if (!CLAIM && !t.cert) {                 // min(len(B), 18): >= 18 distinct valid bigrams in one slot round certify it
@@ -579,79 +689,236 @@ struct B7EmitCount {
     __device__ __forceinline__ void token(bool v, uint64_t key, uint32_t) { count(v, key); }
 };
 
+// out of line: short or repetitive facts only, and 500 instructions that would otherwise sit inside the fact loop
+__device__ B7_NOINLINE int b7_exact_count(B7Shared& sh, B7Scratch* scr, int* wcnt, const uint8_t* tx, int32_t n, int lane) {
+    scr->wset[lane] = 0ULL; scr->wset[lane + 32] = 0ULL;
+    if (lane == 0) *wcnt = 0;
+    __syncwarp();
+    B7EmitCount emit{ scr, wcnt, false };
+    dv_tokenize_serial(tx, n, scr, sh.ktab, emit);
+    __syncwarp();
+    const int wc = *(volatile int*)wcnt;
+    __syncwarp();
+    return wc < 18 ? wc : 18;
+}
+
 static inline size_t bind7_ws_u64_per_cta() { return (size_t)B7_CAPT; }
 static inline size_t bind7_smem_bytes() { return sizeof(B7Shared); }
 
-__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
-    B7Shared& sh = B7_SH();
+// ---------------------------------------------------------------- pack / unpack of a group's tables (all threads of the CTA)
+// Lane k of warp w owns word 32 w + k of a 256-word bitmap over the 8192 table slots; the slots of a word are read and
+// written by the 32 lanes side by side (no bank conflicts), the packed entries sit in slot order.
+__device__ __forceinline__ uint32_t b7_excl_scan32(uint32_t v, int lane, uint32_t& total) {
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(B7_FULL, x, d); if (lane >= d) x += y; }
+    total = __shfl_sync(B7_FULL, x, 31);
+    return x - v;
+}
+__device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* slab, int ncg) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t* tabmap = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TABMAP);
+    uint32_t* tokmap = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TOKMAP);
+    uint16_t* o_sl = reinterpret_cast<uint16_t*>(slab + B7_BLOB_SLIST);
+    uint16_t* o_tix = reinterpret_cast<uint16_t*>(slab + B7_BLOB_TOKTIX);
+    unsigned long long* o_key = reinterpret_cast<unsigned long long*>(slab + B7_BLOB_TOKKEY);
+    uint32_t* o_ent = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TABENT);
+    // ---- table: bitmap word per lane, then the entries
+    uint32_t myword = 0;
+#pragma unroll 4
+    for (int k = 0; k < 32; k++) {
+        const uint32_t wd = __ballot_sync(B7_FULL, sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane] != 0u);
+        if (lane == k) myword = wd;
+    }
+    uint32_t wtot;
+    const uint32_t ex = b7_excl_scan32((uint32_t)__popc(myword), lane, wtot);
+    if (lane == 0) sh.wsum[warp] = wtot;
+    // ---- token keys: warp w owns words 4 w .. 4 w + 3 of the 32-word bitmap over the 1024 key slots
+    uint32_t tw[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        tw[k] = __ballot_sync(B7_FULL, tkeys[(uint32_t)(4 * warp + k) * 32u + (uint32_t)lane] != 0ULL);
+        if (lane == 0) sh.tsum[4 * warp + k] = (uint32_t)__popc(tw[k]);
+    }
+    __syncthreads();
+    uint32_t wbase = 0, ntab = 0;
+    for (int w = 0; w < BIND_WARPS; w++) { if (w < warp) wbase += sh.wsum[w]; ntab += sh.wsum[w]; }
+    tabmap[32 * warp + lane] = myword;
+#pragma unroll 4
+    for (int k = 0; k < 32; k++) {
+        const uint32_t wd = __shfl_sync(B7_FULL, myword, k), base = wbase + __shfl_sync(B7_FULL, ex, k);
+        const uint32_t v = sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane];
+        if (v) o_ent[base + (uint32_t)__popc(wd & lt)] = v;
+    }
+    uint32_t tbase = 0, ntok = 0;
+    for (int j = 0; j < 32; j++) { if (j < 4 * warp) tbase += sh.tsum[j]; ntok += sh.tsum[j]; }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t slot = (uint32_t)(4 * warp + k) * 32u + (uint32_t)lane;
+        if (lane == 0) tokmap[4 * warp + k] = tw[k];
+        if ((tw[k] >> lane) & 1u) {
+            const uint32_t o = tbase + (uint32_t)__popc(tw[k] & lt);
+            o_key[o] = tkeys[slot]; o_tix[o] = sh.tixT[slot];
+        }
+        tbase += (uint32_t)__popc(tw[k]);
+    }
+    // ---- shared lists: claim c's entries follow those of the claims before it
+    uint32_t nsl = 0;
+    for (int c = 0; c < ncg; c++) { const uint32_t n = sh.hd.shc[c]; if (c == tid) for (uint32_t j = 0; j < n; j++) o_sl[nsl + j] = sh.slist[sh.hd.rbase[c] + j]; nsl += n; }
+    if (tid == 0) { sh.hd.n_tab = ntab; sh.hd.n_tok = ntok; sh.hd.n_sl = nsl; sh.hd.ttot = sh.hd.rbase[ncg]; }
+    __syncthreads();
+    for (uint32_t i = tid; i < sizeof(B7Head) / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(slab)[i] = reinterpret_cast<const uint4*>(&sh.hd)[i];
+}
+__device__ void b7_unpack(B7Shared& sh, unsigned long long* tkeys, const uint8_t* slab, int ncg) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t* tabmap = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TABMAP);
+    const uint32_t* tokmap = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TOKMAP);
+    const uint16_t* i_sl = reinterpret_cast<const uint16_t*>(slab + B7_BLOB_SLIST);
+    const uint16_t* i_tix = reinterpret_cast<const uint16_t*>(slab + B7_BLOB_TOKTIX);
+    const unsigned long long* i_key = reinterpret_cast<const unsigned long long*>(slab + B7_BLOB_TOKKEY);
+    const uint32_t* i_ent = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TABENT);
+    for (uint32_t i = tid; i < sizeof(B7Head) / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.hd)[i] = reinterpret_cast<const uint4*>(slab)[i];
+    const uint32_t myword = tabmap[32 * warp + lane];
+    uint32_t wtot;
+    const uint32_t ex = b7_excl_scan32((uint32_t)__popc(myword), lane, wtot);
+    if (lane == 0) sh.wsum[warp] = wtot;
+    const uint32_t tword = tokmap[lane];
+    uint32_t ttot_;
+    const uint32_t tex = b7_excl_scan32((uint32_t)__popc(tword), lane, ttot_);
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (int w = 0; w < warp; w++) wbase += sh.wsum[w];
+#pragma unroll 4
+    for (int k = 0; k < 32; k++) {
+        const uint32_t wd = __shfl_sync(B7_FULL, myword, k), base = wbase + __shfl_sync(B7_FULL, ex, k);
+        sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane] = ((wd >> lane) & 1u) ? i_ent[base + (uint32_t)__popc(wd & lt)] : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t wd = __shfl_sync(B7_FULL, tword, 4 * warp + k), base = __shfl_sync(B7_FULL, tex, 4 * warp + k);
+        const uint32_t slot = (uint32_t)(4 * warp + k) * 32u + (uint32_t)lane;
+        const bool on = ((wd >> lane) & 1u) != 0u;
+        const uint32_t o = base + (uint32_t)__popc(wd & lt);
+        tkeys[slot] = on ? i_key[o] : 0ULL;
+        sh.tixT[slot] = on ? i_tix[o] : (uint16_t)0;
+    }
+    uint32_t nsl = 0;
+    for (int c = 0; c < ncg; c++) { const uint32_t n = sh.hd.shc[c]; if (c == tid) for (uint32_t j = 0; j < n; j++) sh.slist[sh.hd.rbase[c] + j] = i_sl[nsl + j]; nsl += n; }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void b7_cta_init(B7Shared& sh, B7Tok& t, unsigned long long* tkeys) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     dv_fill_ktab(sh.ktab);
     for (int b = tid; b < 128; b += BIND_THREADS) sh.lut[b] = (uint8_t)(dv_ascii_sym((uint32_t)b) & 0xFFu);
     for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
-    B7Tok t;
     t.sh = &sh; t.tkeys = tkeys; t.H = sh.H[warp]; t.scr = reinterpret_cast<B7Scratch*>(sh.H[warp] + B7_TCAP); t.lane = lane;
     t.base = nullptr; t.a = 0; t.total = 0; t.aqn = 0; t.pqn = 0; t.rb = 0; t.re = 0; t.own = 0; t.shd = 0; t.cert = false; t.exotic = false;
+}
 
+// ---------------------------------------------------------------- kernel 1 of 2: the claims of every group -> tables -> slab
+// Two kernels instead of one fused kernel: the SM's instruction fetch is the limiter of this code (profiles/README.md,
+// experiments/icache/): 24 warps streaming more than ~12 KB of code run at 2 instructions per clock per SM instead of 4, and
+// one CTA's claim phase (insert paths, 60 KB of code) used to run next to the fact walk of its two neighbours.
+__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claim_tables(BindParams p) {
+    B7Shared& sh = B7_SH();
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
+    B7Tok t;
+    b7_cta_init(sh, t, tkeys);
     for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
-        const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
+        if (c1 <= c0) continue;
+        const int ngroups = (int)((c1 - c0 + BIND_CLAIMS - 1) / BIND_CLAIMS);
+        __syncthreads();
+        if (tid == 0) { sh.slab = atomicAdd(p.slab_cursor, ngroups); p.sess_slab[s] = sh.slab; }
+        __syncthreads();
+        const int slab0 = sh.slab;
         bool handback = false;
         for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
             // ---- clear tables, token-index ranges of the claims
             for (uint32_t i = tid; i < B7_NB; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
             for (uint32_t i = tid; i < B7_CAPT / 8; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tixT)[i] = make_uint4(0u, 0u, 0u, 0u);
-            if (tid < B7_NB / 32) sh.ovb[tid] = 0u;
-            if (tid < B7_STASH) { sh.stash_id[tid] = 0u; sh.stash_e[tid] = 0u; }
+            for (uint32_t i = tid; i < sizeof(B7Head) / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.hd)[i] = make_uint4(0u, 0u, 0u, 0u);
             for (uint32_t i = tid; i < B7_CAPT; i += BIND_THREADS) tkeys[i] = 0ULL;
-            for (uint32_t i = tid; i < (1u << (B7_FT_BITS - 5)); i += BIND_THREADS) sh.ft[i] = 0u;
+            __syncthreads();
             if (warp == 0) {
                 uint32_t bound = 0;
                 if (lane < ncg) {
                     const int64_t nb = p.claim_off[cg + lane + 1] - p.claim_off[cg + lane];
                     bound = (uint32_t)min((int64_t)65535, ((nb / 3 + 2) + 15) & ~(int64_t)15);       // distinct tokens <= bytes / 3 + 1
                 }
-                uint32_t incl = bound;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(B7_FULL, incl, d); if (lane >= d) incl += y; }
-                const uint32_t tot = __shfl_sync(B7_FULL, incl, 31);
-                if (tot <= B7_TCAP) { sh.rbase[lane + 1] = (uint16_t)incl; if (lane == 0) sh.rbase[0] = 0; }
+                uint32_t tot;
+                const uint32_t excl = b7_excl_scan32(bound, lane, tot);
+                if (tot <= B7_TCAP) { sh.hd.rbase[lane + 1] = (uint16_t)(excl + bound); if (lane == 0) sh.hd.rbase[0] = 0; }
                 if (lane == 0) { sh.next_item = 0; sh.ntok = 0; sh.ovf = tot > B7_TCAP ? 1 : 0; sh.exotic = 0; }
             }
             __syncthreads();
             const bool too_big = sh.ovf != 0;                         // uniform: written before the barrier, next writer is behind one
             __syncthreads();
             if (too_big) { handback = true; break; }
-            // ---- phase C: one warp per claim
+            // ---- one warp per claim
             for (;;) {
                 int c = 0;
                 if (lane == 0) c = atomicAdd(&sh.next_item, 1);
                 c = __shfl_sync(B7_FULL, c, 0);
                 if (c >= ncg) break;
                 const int64_t b = p.claim_off[cg + c], e = p.claim_off[cg + c + 1];
-                t.rb = sh.rbase[c]; t.re = sh.rbase[c + 1]; t.own = 0; t.shd = 0;
+                t.rb = sh.hd.rbase[c]; t.re = sh.hd.rbase[c + 1]; t.own = 0; t.shd = 0;
                 b7_text<true>(t, p.claim_utf8 + b, (int32_t)(e - b));
                 __syncwarp();
                 for (int j = lane; j < t.shd && t.rb + (uint32_t)j < t.re; j += 32) t.H[sh.slist[t.rb + j]] = 0;      // the "already listed" flags
-                if (lane == 0) { sh.ownc[c] = (uint16_t)t.own; sh.shc[c] = (uint16_t)t.shd; }
+                if (lane == 0) { sh.hd.ownc[c] = (uint16_t)t.own; sh.hd.shc[c] = (uint16_t)t.shd; }
                 __syncwarp();
             }
             if (__any_sync(B7_FULL, t.exotic)) sh.exotic = 1;
             __syncthreads();
-            const bool give_up = sh.ovf || sh.exotic;
-            if (tid == 0) sh.next_item = 0;
+            if (sh.ovf || sh.exotic) { handback = true; break; }      // uniform; the next writers are behind the barrier of the pack
+            b7_pack(sh, tkeys, p.slabs + (size_t)(slab0 + (int)((cg - c0) / BIND_CLAIMS)) * B7_BLOB_BYTES, ncg);
             __syncthreads();
-            if (give_up) { handback = true; break; }
-            // ---- phase F: one warp per fact
+        }
+        t.exotic = false;
+        if (handback) {
+            if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
+            // the H arrays may hold stale flags of an abandoned claim phase
+            __syncthreads();
+            for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+            __syncthreads();
+        }
+    }
+}
+
+// ---------------------------------------------------------------- kernel 2 of 2: the facts of every session against its groups' tables
+__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
+    B7Shared& sh = B7_SH();
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
+    B7Tok t;
+    b7_cta_init(sh, t, tkeys);
+    for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
+        const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
+        const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
+        if (c1 <= c0 || p.sess_fallback[s]) continue;                 // uniform
+        const int slab0 = p.sess_slab[s];
+        bool handback = false;
+        for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
+            const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
+            __syncthreads();
+            b7_unpack(sh, tkeys, p.slabs + (size_t)(slab0 + (int)((cg - c0) / BIND_CLAIMS)) * B7_BLOB_BYTES, ncg);
+            if (tid == 0) { sh.next_item = 0; sh.exotic = 0; }
+            __syncthreads();
+            // ---- one warp per fact
             double best = -1.0; int best_f = 0x7fffffff;              // lane c (< ncg) tracks claim c
-            const uint32_t rb = lane < ncg ? sh.rbase[lane] : 0u;
-            const int no = lane < ncg ? sh.ownc[lane] : 0, ns = lane < ncg ? sh.shc[lane] : 0;
+            const uint32_t rb = lane < ncg ? sh.hd.rbase[lane] : 0u;
+            const int no = lane < ncg ? sh.hd.ownc[lane] : 0, ns = lane < ncg ? sh.hd.shc[lane] : 0;
             const int la = no + ns;
             const int da = max(3, min(la, 14));
             const int pref = lane < ncg ? p.claim_pref_dim[cg + lane] : -1;
-            const uint32_t ttot = sh.rbase[ncg];
+            const uint32_t ttot = sh.hd.rbase[ncg];
             const int nf = (int)(f1 - f0);
             for (;;) {
                 int f = 0;
@@ -667,17 +934,7 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
                 const int fdim = p.fact_dim[f0 + f];
                 const uint32_t fhard = p.fact_hard[f0 + f];
                 int lb = 18;
-                if (!t.cert) {
-                    B7Scratch* scr = t.scr;
-                    scr->wset[lane] = 0ULL; scr->wset[lane + 32] = 0ULL;
-                    if (lane == 0) sh.wcnt[warp] = 0;
-                    __syncwarp();
-                    B7EmitCount emit{ scr, &sh.wcnt[warp], false };
-                    dv_tokenize_serial(p.fact_utf8 + b, (int32_t)(e - b), scr, sh.ktab, emit);
-                    __syncwarp();
-                    { const int wc = *(volatile int*)&sh.wcnt[warp]; lb = wc < 18 ? wc : 18; }
-                    __syncwarp();
-                }
+                if (!t.cert) lb = b7_exact_count(sh, t.scr, &sh.wcnt[warp], p.fact_utf8 + b, (int32_t)(e - b), lane);
                 // ---- overlap of claim `lane` with this fact: its own index range + its shared list
                 uint32_t ov = 0;
                 if (lane < ncg) {
@@ -711,7 +968,7 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
             t.scr->rbest[lane] = best; t.scr->ridx[lane] = best_f;
             __syncthreads();
             if (sh.exotic) handback = true;                          // uniform; no writer until the next barrier
-            // ---- phase R
+            // ---- per-claim reduction over the warps
             if (tid < ncg) {
                 double b = -1.0; int bf = 0x7fffffff;
                 for (int w = 0; w < BIND_WARPS; w++) {
@@ -724,17 +981,11 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claims(BindParams p) {
                 p.best_fact[c] = any ? bf : -1;
                 p.best_score[c] = any ? b : 0.0;
                 p.bound[c] = (any && !(__dadd_rn(b, 1e-9) < p.claim_threshold[c])) ? 1 : 0;
-                if (p.len_claim) p.len_claim[c] = min((int)sh.ownc[tid] + (int)sh.shc[tid], 14);
+                if (p.len_claim) p.len_claim[c] = min((int)sh.hd.ownc[tid] + (int)sh.hd.shc[tid], 14);
             }
             __syncthreads();
         }
         t.exotic = false;
-        if (handback) {
-            if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
-            // the H arrays may hold stale flags of an abandoned claim phase
-            __syncthreads();
-            for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
-            __syncthreads();
-        }
+        if (handback && tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
     }
 }

@@ -1,4 +1,4 @@
-// emu_bind.cpp — runs the PRODUCT source of k_bind_claims (bind7.cuh) and k_bind_claims_general (bind_general.cuh) on the
+// emu_bind.cpp — runs the PRODUCT source of k_bind_claim_tables + k_bind_facts (bind7.cuh) and k_bind_claims_general (bind_general.cuh) on the
 // CPU SIMT emulator, with the launch flow of dvb_bind_claims (fast kernel, then the general kernel over the sessions it
 // handed back).  TEST INFRASTRUCTURE: built by tests/emu/emu.py, called by tests/test_emu_bind.py.
 #include "simt_emu.h"
@@ -40,7 +40,14 @@ extern "C" int emu_bind_claims(const uint8_t* claim_utf8, const int64_t* claim_o
     if (mode != 2) {
         std::vector<unsigned long long> ws((size_t)grid * bind7_ws_u64_per_cta());
         p.gtable = ws.data();
-        emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_claims(p); });
+        int64_t n_groups = 0;
+        for (int64_t s = 0; s < n_sessions; s++) n_groups += (sess_claim_off[s + 1] - sess_claim_off[s] + BIND_CLAIMS - 1) / BIND_CLAIMS;
+        std::vector<unsigned long long> slabs(((size_t)n_groups * B7_BLOB_BYTES + 7) / 8 + 1);
+        std::vector<int32_t> sess_slab((size_t)n_sessions);
+        int cursor = 0;
+        p.slabs = reinterpret_cast<uint8_t*>(slabs.data()); p.slab_cursor = &cursor; p.sess_slab = sess_slab.data();
+        emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_claim_tables(p); });
+        emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_facts(p); });
     }
     if (mode == 2 || (mode == 0 && overflow)) {
         const uint32_t cap = emu_table_cap(mx);
