@@ -100,17 +100,17 @@ struct __align__(16) B7Shared {
     uint32_t wsum[BIND_WARPS], tsum[32];           // pack / unpack scans
     int slab;
 };
-// Slab of one claim group in the workspace (bytes): head | table bitmap | token bitmap | packed shared lists | packed token
-// indices | packed token keys | packed table entries.  Sections are sized for the kernel's own limits (B7_TCAP token indices,
+// Slab of one claim group in the workspace (bytes): head | token bitmap | packed shared lists | packed token indices |
+// packed token keys | table entries | their slots.  Sections are sized for the kernel's own limits (B7_TCAP token indices,
 // B7_TOK_LIMIT token keys), so a group that passes the claim kernel always fits.
-#define B7_BLOB_TABMAP 2048
-#define B7_BLOB_TOKMAP (B7_BLOB_TABMAP + B7_NB * 4 / 8)
+#define B7_BLOB_TOKMAP 2048
 #define B7_BLOB_SLIST (B7_BLOB_TOKMAP + B7_CAPT / 8)
 #define B7_BLOB_TOKTIX (B7_BLOB_SLIST + 2 * B7_TCAP)
 #define B7_BLOB_TOKKEY (B7_BLOB_TOKTIX + 2 * B7_TOK_LIMIT)
 #define B7_BLOB_TABENT (B7_BLOB_TOKKEY + 8 * B7_TOK_LIMIT)
-#define B7_BLOB_BYTES (B7_BLOB_TABENT + 4 * B7_TCAP)
-static_assert(sizeof(B7Head) <= B7_BLOB_TABMAP && B7_BLOB_TOKKEY % 8 == 0 && B7_BLOB_TABENT % 16 == 0 && B7_BLOB_BYTES % 16 == 0, "slab layout");
+#define B7_BLOB_TABSLOT (B7_BLOB_TABENT + 4 * B7_TCAP)
+#define B7_BLOB_BYTES (B7_BLOB_TABSLOT + 2 * B7_TCAP)
+static_assert(sizeof(B7Head) <= B7_BLOB_TOKMAP && B7_BLOB_TOKKEY % 8 == 0 && B7_BLOB_TABENT % 16 == 0 && B7_BLOB_BYTES % 16 == 0, "slab layout");
 static_assert(sizeof(B7Scratch) <= B7_HSTRIDE - B7_TCAP, "the warp scratch lives behind the warp's flag bytes");
 static_assert(sizeof(B7Shared) <= 76800, "three CTAs per SM");
 
@@ -567,7 +567,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
         uint32_t prev = pv >> 2;
 #if B7_PSTS
         const int p_in = p;
-        bool side = false;
+        uint32_t sidem = 0;                          // slots whose bigram missed in a FULL bucket (~1 % of the probes)
 #endif
         bool adn[4];                                 // the next character continues the run (last slot: possibly)
         adn[0] = ad[1]; adn[1] = ad[2]; adn[2] = ad[3]; adn[3] = ((x[3] >> 24) - 0xE5u) <= 4u;
@@ -591,7 +591,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
                 uint32_t m = min(min(e.x ^ k, e.y ^ k), min(e.z ^ k, e.w ^ k));
 #if B7_PSTS
                 const bool hit = v && (m - 1u) < 8191u;
-                side = side || (v && !hit && e.w != 0u);                                 // rare: full bucket, the key may be in the side list
+                if (v && !hit && e.w != 0u) sidem |= 1u << i;                            // rare: full bucket, the key may be in the side list
                 b7_sts8_if(hit, hitS + (m & 0xFFFu), 1u);
 #else
                 bool hit = v && (m - 1u) < 8191u;
@@ -608,13 +608,13 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             prev = sy[i];
         }
 #if B7_PSTS
-        if (!CLAIM && side) {                        // ~1 % of the steps: the lane's valid bigrams again, against the side list only
+        if (!CLAIM && sidem) {                       // most steps have one such lane: only its flagged slots look at the side list
             int pp = p_in; uint32_t pr = pv >> 2;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 pp = ad[i] ? pp + 1 : 0;
                 if (pp == 12) pp = 0;
-                if (ad[i] && (pp != 0 || B7_RUNG == 3)) {
+                if ((sidem >> i) & 1u) {
                     const uint32_t id = (pr << 15) | sy[i];
                     const uint32_t sm_ = b7_side_lookup(t.sh, id * B7_HASH, id);
                     if (sm_) {
@@ -718,8 +718,8 @@ __device__ __forceinline__ uint32_t b7_excl_scan32(uint32_t v, int lane, uint32_
 __device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* slab, int ncg) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t* tabmap = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TABMAP);
     uint32_t* tokmap = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TOKMAP);
+    uint16_t* o_slot = reinterpret_cast<uint16_t*>(slab + B7_BLOB_TABSLOT);
     uint16_t* o_sl = reinterpret_cast<uint16_t*>(slab + B7_BLOB_SLIST);
     uint16_t* o_tix = reinterpret_cast<uint16_t*>(slab + B7_BLOB_TOKTIX);
     unsigned long long* o_key = reinterpret_cast<unsigned long long*>(slab + B7_BLOB_TOKKEY);
@@ -744,12 +744,12 @@ __device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* 
     __syncthreads();
     uint32_t wbase = 0, ntab = 0;
     for (int w = 0; w < BIND_WARPS; w++) { if (w < warp) wbase += sh.wsum[w]; ntab += sh.wsum[w]; }
-    tabmap[32 * warp + lane] = myword;
 #pragma unroll 4
     for (int k = 0; k < 32; k++) {
         const uint32_t wd = __shfl_sync(B7_FULL, myword, k), base = wbase + __shfl_sync(B7_FULL, ex, k);
-        const uint32_t v = sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane];
-        if (v) o_ent[base + (uint32_t)__popc(wd & lt)] = v;
+        const uint32_t slot = (uint32_t)(32 * warp + k) * 32u + (uint32_t)lane;
+        const uint32_t v = sh.tab[slot];
+        if (v) { const uint32_t o = base + (uint32_t)__popc(wd & lt); o_ent[o] = v; o_slot[o] = (uint16_t)slot; }
     }
     uint32_t tbase = 0, ntok = 0;
     for (int j = 0; j < 32; j++) { if (j < 4 * warp) tbase += sh.tsum[j]; ntok += sh.tsum[j]; }
@@ -764,37 +764,30 @@ __device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* 
         tbase += (uint32_t)__popc(tw[k]);
     }
     // ---- shared lists: claim c's entries follow those of the claims before it
-    uint32_t nsl = 0;
-    for (int c = 0; c < ncg; c++) { const uint32_t n = sh.hd.shc[c]; if (c == tid) for (uint32_t j = 0; j < n; j++) o_sl[nsl + j] = sh.slist[sh.hd.rbase[c] + j]; nsl += n; }
-    if (tid == 0) { sh.hd.n_tab = ntab; sh.hd.n_tok = ntok; sh.hd.n_sl = nsl; sh.hd.ttot = sh.hd.rbase[ncg]; }
+    if (tid <= ncg) {                                              // thread c: claim c's list; thread ncg: the total
+        uint32_t before = 0;
+        for (int c = 0; c < tid; c++) before += sh.hd.shc[c];
+        if (tid < ncg) { const uint32_t n = sh.hd.shc[tid], rb = sh.hd.rbase[tid]; for (uint32_t j = 0; j < n; j++) o_sl[before + j] = sh.slist[rb + j]; }
+        else { sh.hd.n_tab = ntab; sh.hd.n_tok = ntok; sh.hd.n_sl = before; sh.hd.ttot = sh.hd.rbase[ncg]; }
+    }
     __syncthreads();
     for (uint32_t i = tid; i < sizeof(B7Head) / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(slab)[i] = reinterpret_cast<const uint4*>(&sh.hd)[i];
 }
 __device__ void b7_unpack(B7Shared& sh, unsigned long long* tkeys, const uint8_t* slab, int ncg) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    const uint32_t* tabmap = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TABMAP);
     const uint32_t* tokmap = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TOKMAP);
     const uint16_t* i_sl = reinterpret_cast<const uint16_t*>(slab + B7_BLOB_SLIST);
     const uint16_t* i_tix = reinterpret_cast<const uint16_t*>(slab + B7_BLOB_TOKTIX);
     const unsigned long long* i_key = reinterpret_cast<const unsigned long long*>(slab + B7_BLOB_TOKKEY);
     const uint32_t* i_ent = reinterpret_cast<const uint32_t*>(slab + B7_BLOB_TABENT);
+    const uint16_t* i_slot = reinterpret_cast<const uint16_t*>(slab + B7_BLOB_TABSLOT);
     for (uint32_t i = tid; i < sizeof(B7Head) / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.hd)[i] = reinterpret_cast<const uint4*>(slab)[i];
-    const uint32_t myword = tabmap[32 * warp + lane];
-    uint32_t wtot;
-    const uint32_t ex = b7_excl_scan32((uint32_t)__popc(myword), lane, wtot);
-    if (lane == 0) sh.wsum[warp] = wtot;
+    for (uint32_t i = tid; i < B7_NB; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
+    // token keys: every slot of the CTA's key table is rewritten (key or 0)
     const uint32_t tword = tokmap[lane];
     uint32_t ttot_;
     const uint32_t tex = b7_excl_scan32((uint32_t)__popc(tword), lane, ttot_);
-    __syncthreads();
-    uint32_t wbase = 0;
-    for (int w = 0; w < warp; w++) wbase += sh.wsum[w];
-#pragma unroll 4
-    for (int k = 0; k < 32; k++) {
-        const uint32_t wd = __shfl_sync(B7_FULL, myword, k), base = wbase + __shfl_sync(B7_FULL, ex, k);
-        sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane] = ((wd >> lane) & 1u) ? i_ent[base + (uint32_t)__popc(wd & lt)] : 0u;
-    }
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const uint32_t wd = __shfl_sync(B7_FULL, tword, 4 * warp + k), base = __shfl_sync(B7_FULL, tex, 4 * warp + k);
@@ -804,8 +797,15 @@ __device__ void b7_unpack(B7Shared& sh, unsigned long long* tkeys, const uint8_t
         tkeys[slot] = on ? i_key[o] : 0ULL;
         sh.tixT[slot] = on ? i_tix[o] : (uint16_t)0;
     }
-    uint32_t nsl = 0;
-    for (int c = 0; c < ncg; c++) { const uint32_t n = sh.hd.shc[c]; if (c == tid) for (uint32_t j = 0; j < n; j++) sh.slist[sh.hd.rbase[c] + j] = i_sl[nsl + j]; nsl += n; }
+    __syncthreads();
+    const uint32_t ntab = sh.hd.n_tab;
+    for (uint32_t i = tid; i < ntab; i += BIND_THREADS) sh.tab[i_slot[i]] = i_ent[i];
+    if (tid < ncg) {
+        uint32_t before = 0;
+        for (int c = 0; c < tid; c++) before += sh.hd.shc[c];
+        const uint32_t n = sh.hd.shc[tid], rb = sh.hd.rbase[tid];
+        for (uint32_t j = 0; j < n; j++) sh.slist[rb + j] = i_sl[before + j];
+    }
     __syncthreads();
 }
 

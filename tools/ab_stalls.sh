@@ -7,10 +7,5 @@ for lib in "$@"; do
   if [ "$lib" = default ]; then unset DVB_LIB; else export DVB_LIB=$PWD/$lib; fi
   timeout 300 ncu --metrics $M --clock-control none -k regex:k_bind_ -s 2 -c 2 --csv --log-file gpurun_out/st.csv python tools/prof_bind.py $n 2 > /dev/null 2>&1
   echo "== $lib"
-  grep -v "^==" gpurun_out/st.csv | python -c "
-import csv,sys
-rows=list(csv.reader(sys.stdin)); h=rows[0]
-for r in rows[1:]:
-    kn=r[h.index(chr(75)+"ernel Name")][:22]
-    n=r[h.index('Metric Name')].replace('smsp__average_warps_issue_stalled_','st_').replace('_per_issue_active.ratio',''); print("   %-22s %-58s %s" % (kn, n, r[h.index("Metric Value")]))"
+  python tools/ncu_metrics_table.py gpurun_out/st.csv
 done
