@@ -31,9 +31,6 @@
 #ifndef B7_RUNG
 #define B7_RUNG 6
 #endif
-#ifndef B7_PSTS
-#define B7_PSTS 1
-#endif
 #ifndef B7_NI_INSERT
 #define B7_NI_INSERT 1
 #endif
@@ -565,10 +562,8 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
         //      bigram hit an entry that ends a claim piece
         uint32_t candm = 0, candp = 0, vm = 0;
         uint32_t prev = pv >> 2;
-#if B7_PSTS
         const int p_in = p;
         uint32_t sidem = 0;                          // slots whose bigram missed in a FULL bucket (~1 % of the probes)
-#endif
         bool adn[4];                                 // the next character continues the run (last slot: possibly)
         adn[0] = ad[1]; adn[1] = ad[2]; adn[2] = ad[3]; adn[3] = ((x[3] >> 24) - 0xE5u) <= 4u;
 #pragma unroll
@@ -589,25 +584,15 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
                 const uint32_t h = id * B7_HASH, k = h << 13;
                 const uint4 e = b7_lds128(tabS + ((h >> 15) & ((B7_NB - 1u) << 4)));
                 uint32_t m = min(min(e.x ^ k, e.y ^ k), min(e.z ^ k, e.w ^ k));
-#if B7_PSTS
                 const bool hit = v && (m - 1u) < 8191u;
                 if (v && !hit && e.w != 0u) sidem |= 1u << i;                            // rare: full bucket, the key may be in the side list
                 b7_sts8_if(hit, hitS + (m & 0xFFFu), 1u);
-#else
-                bool hit = v && (m - 1u) < 8191u;
-                if (v && !hit && e.w != 0u) {                                            // rare: full bucket, the key may be in the side list
-                    const uint32_t sm_ = b7_side_lookup(t.sh, h, id);
-                    if (sm_) { m = sm_; hit = true; }
-                }
-                if (hit) b7_sts8(hitS + (m & 0xFFFu), 1u);
-#endif
                 pend = pend && hit && m >= 4096u;
                 vm |= (v ? 1u : 0u) << i;
             }
             if (pend) { candm |= 1u << i; candp |= (uint32_t)p << (4 * i); }
             prev = sy[i];
         }
-#if B7_PSTS
         if (!CLAIM && sidem) {                       // most steps have one such lane: only its flagged slots look at the side list
             int pp = p_in; uint32_t pr = pv >> 2;
 #pragma unroll
@@ -625,7 +610,6 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
                 pr = sy[i];
             }
         }
-#endif
         if (!CLAIM && B7_RUNG == 3) continue;
         carryP = __shfl_sync(B7_FULL, p, 31);
         if (!CLAIM && !t.cert) {                 // min(len(B), 18): >= 18 distinct valid bigrams in one slot round certify it
@@ -806,6 +790,7 @@ __device__ void b7_unpack(B7Shared& sh, unsigned long long* tkeys, const uint8_t
         const uint32_t n = sh.hd.shc[tid], rb = sh.hd.rbase[tid];
         for (uint32_t j = 0; j < n; j++) sh.slist[rb + j] = i_sl[before + j];
     }
+    if (tid == 0) { sh.next_item = 0; sh.exotic = 0; }               // every warp left the previous fact loop and read the flag before the barrier above
     __syncthreads();
 }
 
@@ -907,10 +892,9 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
         bool handback = false;
         for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
-            __syncthreads();
+            // no barrier here: behind the barrier that ends the previous fact phase only warp 0 still works (the reduction),
+            // on registers and the warps' scratch, which nothing writes before the two barriers of the unpack
             b7_unpack(sh, tkeys, p.slabs + (size_t)(slab0 + (int)((cg - c0) / BIND_CLAIMS)) * B7_BLOB_BYTES, ncg);
-            if (tid == 0) { sh.next_item = 0; sh.exotic = 0; }
-            __syncthreads();
             // ---- one warp per fact
             double best = -1.0; int best_f = 0x7fffffff;              // lane c (< ncg) tracks claim c
             const uint32_t rb = lane < ncg ? sh.hd.rbase[lane] : 0u;
@@ -981,9 +965,8 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
                 p.best_fact[c] = any ? bf : -1;
                 p.best_score[c] = any ? b : 0.0;
                 p.bound[c] = (any && !(__dadd_rn(b, 1e-9) < p.claim_threshold[c])) ? 1 : 0;
-                if (p.len_claim) p.len_claim[c] = min((int)sh.hd.ownc[tid] + (int)sh.hd.shc[tid], 14);
+                if (p.len_claim) p.len_claim[c] = min(la, 14);        // tid == lane in warp 0
             }
-            __syncthreads();
         }
         t.exotic = false;
         if (handback && tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
