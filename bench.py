@@ -399,7 +399,7 @@ def measured_peak():
 
 
 def ncu_traffic():
-    """dram bytes per launch of k_bind_claims from the committed ncu --set full capture, if any."""
+    """dram bytes per dvb_bind_claims call (k_bind_claim_tables + k_bind_facts) from the committed ncu --set full capture, if any."""
     p = ROOT / "profiles" / "bind_traffic.json"
     if p.exists():
         try:
@@ -670,12 +670,13 @@ def main():
                         "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": ncu_traffic(), "kernel": "k_bind_claims", "kernel_ms": k_ms,
+                             "traffic": ncu_traffic(), "kernel": "k_bind_claim_tables + k_bind_facts (one dvb_bind_claims call)", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": corpus.algorithmic_bytes,
                              "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src,
-                             "limiter": "instruction issue, not DRAM: 2.6 warp instructions per input byte at 22 of 32 lanes, 0.5 issued per scheduler "
-                                        "cycle with 5.8 resident warps, DRAM traffic 1.03 x algorithmic (profiles/r02_bind7_v2_ncu_full.json, "
-                                        "profiles/r02_bind_ladder.json; DESIGN.md section 5)"},
+                             "limiter": "instruction issue / ALU pipe, not DRAM: 2.6 warp instructions per input byte; the fused kernel was bound by "
+                                        "instruction FETCH (more than ~12 KB of hot code per SM halves the issue rate: experiments/icache), the split "
+                                        "pair issues 0.6 (facts) and 0.5 (claim tables) per scheduler cycle; DRAM traffic 1.2 x algorithmic "
+                                        "(profiles/r02_bind8_ncu_full.json, profiles/README.md; DESIGN.md section 5)"},
                 "clocks": clocks,
                 "pairs_per_step_per_gpu": corpus.n_pairs}
         if index is not None:

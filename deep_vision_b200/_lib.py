@@ -40,6 +40,7 @@ _SIGS = {
     "dvb_question_gate": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_int32,
                                       _vp, _vp, C.c_int32, C.c_double, _vp]),
     "dvb_solution_jaccard": (C.c_int32, [_vp, C.c_int32, _vp, _vp, _vp, _vp, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp]),
+    "dvb_slim_facts": (C.c_int32, [_vp, C.c_int32, C.c_int64] + [_vp] * 8 + [C.c_int32, C.c_double, C.c_int32, C.c_int32, _vp, _vp]),
     "dvb_text_features": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp, _vp]),
     "dvb_annotate_turns": (C.c_int32, [_vp, C.c_int32, C.c_int64] + [_vp] * 13 + [C.c_uint32, C.c_int32, _vp, _vp, _vp]),
     "dvb_contains": (C.c_int32, [_vp, C.c_int32, _vp, _vp, C.c_int64, _vp, _vp, _vp, C.c_int64, _vp]),

@@ -12,7 +12,7 @@ import json
 import threading
 from typing import Any, Dict, Optional
 
-from . import evidence, question_similarity as qs, reference_material as rm
+from . import evidence, prompt_facts, question_similarity as qs, reference_material as rm
 
 _SAVED: Dict[int, Dict[str, Any]] = {}
 _MISSING = object()
@@ -29,6 +29,10 @@ HOT_NAMES = (
 # 30566-30670), where two kernel launches per call cost more than the Python loop they replace, so they are re-bound
 # only on request (install(..., saturation=True)); build_report_evidence_pack uses the batched device pass either way.
 SATURATION_NAMES = ("calculate_dimension_saturation", "get_dimension_missing_aspects")
+# one evidence pack per call is ~10^2 facts — a launch costs more than the reference's Python loop, so the
+# single-call name is re-bound only on request (install(..., slim_facts=True)); prompt_facts.select_slimmed_facts_batch is the
+# batched entry (many packs, one launch).
+SLIM_NAMES = ("select_slimmed_facts_for_prompt",)
 
 
 # a3 (web/server.py:25241-25612): one repair pass scores all its candidate items in ONE launch; the per-item calls the
@@ -174,6 +178,15 @@ def build_bindings(mod, ctx=None, sidecar_cache: Optional["rm.ChunkIndexCache"] 
     def _solution_jaccard_similarity(left, right):
         return qs._solution_jaccard_similarity(left, right, int(getattr(mod, "SOLUTION_SIMILARITY_NGRAM_SIZE", 2)), ctx=ctx)
 
+    def select_slimmed_facts_for_prompt(evidence_pack, facts_limit):
+        return prompt_facts.select_slimmed_facts_for_prompt(
+            evidence_pack, facts_limit, ctx=ctx,
+            slim_enabled=bool(getattr(mod, "REPORT_V3_EVIDENCE_SLIM_ENABLED", True)),
+            dedup_enabled=bool(getattr(mod, "REPORT_V3_EVIDENCE_DEDUP_ENABLED", True)),
+            min_quality=getattr(mod, "REPORT_V3_EVIDENCE_MIN_QUALITY", 0.2),
+            dim_quota=getattr(mod, "REPORT_V3_EVIDENCE_DIM_QUOTA", 6),
+            keep_hard_triggered=bool(getattr(mod, "REPORT_V3_EVIDENCE_KEEP_HARD_TRIGGERED", True)))
+
     bindings = dict(locals())
     for k in ("mod", "ctx", "sidecar_cache", "_index_provider", "repairs_original"):
         bindings.pop(k, None)
@@ -184,7 +197,7 @@ def build_bindings(mod, ctx=None, sidecar_cache: Optional["rm.ChunkIndexCache"] 
         bindings.update(annotations.build_bindings(mod, ctx))
     except ImportError:
         pass
-    return {k: v for k, v in bindings.items() if k in HOT_NAMES or k in SATURATION_NAMES}
+    return {k: v for k, v in bindings.items() if k in HOT_NAMES or k in SATURATION_NAMES or k in SLIM_NAMES}
 
 
 def check_unicode_tables(strict: bool = False) -> bool:
@@ -230,7 +243,7 @@ def infer_reference_chunk_refs_v3_factory(mod, ctx=None):
 
 
 def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cache=None, saturation: bool = False,
-            strict_unicode: bool = False, claim_chunk_binding: bool = False) -> Dict[str, Any]:
+            strict_unicode: bool = False, claim_chunk_binding: bool = False, slim_facts: bool = False) -> Dict[str, Any]:
     """Rebind the hot-path names that exist on `server_module`; returns {name: replacement}.  Idempotent.
     sidecar_cache: a reference_material.ChunkIndexCache to serve select_reference_material_context from resident /
     persisted chunk indexes (off by default: the drop-in then writes nothing into the data directory)."""
@@ -242,6 +255,8 @@ def install(server_module, ctx=None, names: Optional[tuple] = None, sidecar_cach
         if names is not None and name not in names:
             continue
         if name in SATURATION_NAMES and not saturation and (names is None or name not in names):
+            continue
+        if name in SLIM_NAMES and not slim_facts and (names is None or name not in names):
             continue
         current = getattr(server_module, name, _MISSING)
         if current is _MISSING:

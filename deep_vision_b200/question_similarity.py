@@ -167,3 +167,19 @@ def _solution_jaccard_similarity(left: str, right: str, ngram: int = 2, ctx=None
     if nl[0] == 0 or nr[0] == 0:
         return 0.0
     return round(int(inter[0]) / max(1, int(union[0])), 3)
+
+
+def max_solution_similarity(signature: str, others: Sequence[Tuple[str, str]], ngram: int = 2, ctx=None) -> Tuple[float, str]:
+    """The similarity loop of build_solution_quality_signals (web/server.py:36970-36984) as ONE launch: `others` =
+    (report_name, similarity text) of the recent sidecars that passed the fingerprint check, in the reference's order.
+    -> (max score, name of the FIRST report that reaches it; (0.0, "") when no score is positive — the reference's strict '>')."""
+    if not others:
+        return 0.0, ""
+    left = clean_solution_text(signature)
+    inter, union, nl, nr = solution_jaccard_counts([(left, clean_solution_text(t)) for _n, t in others], ngram, ctx=ctx)
+    best, name = 0.0, ""
+    for i, (n, _t) in enumerate(others):
+        score = 0.0 if nl[i] == 0 or nr[i] == 0 else round(int(inter[i]) / max(1, int(union[i])), 3)
+        if score > best:
+            best, name = score, str(n or "")
+    return best, name

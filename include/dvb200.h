@@ -195,6 +195,23 @@ int32_t dvb_solution_jaccard(dvb_ctx* ctx, int32_t mem, const uint8_t* left_utf8
                              const uint8_t* right_utf8, const int64_t* right_off, int64_t n_pairs, int32_t ngram,
                              int32_t* out_inter, int32_t* out_union, int32_t* out_nleft, int32_t* out_nright);
 
+/* ---- SURVEY 8(f)4  replaces the scoring, ordering and the three greedy passes of: select_slimmed_facts_for_prompt
+ *               (web/server.py:22886-22993), for n_reports evidence packs per launch (one warp per pack).
+ * Facts of report r = [fact_off[r], fact_off[r+1]) (at most 1024).  Per fact, computed by the caller the way the reference does:
+ *   quality   max(0.0, min(1.0, _safe_float(quality_score)))                                  (server.py:22923)
+ *   flags     bit 0 hard_triggered, 1 q_id in the contradiction refs, 2 q_id in the unknown refs, 3 is_follow_up
+ *   sig_id    dense id in [0, n) of _fact_signature_for_prompt (equal ids <=> equal signatures)  (server.py:22876-22883)
+ *   dim_id    dense id in [0, n) of the lower-cased dimension ("__unknown__" included)
+ *   sort_key  _fact_sort_key_for_prompt                                                        (server.py:22867-22874)
+ * limit[r] = max(1, int(facts_limit or 1)); dim_quota / min_quality / keep_hard / dedup = REPORT_V3_EVIDENCE_DIM_QUOTA,
+ * _MIN_QUALITY, _KEEP_HARD_TRIGGERED, _DEDUP_ENABLED (server.py:992-998).
+ * out_sel[out_off[r] ..) receives the selected fact indices (0-based inside the report) in the reference's final order,
+ * out_cnt[r] their number; out_off[r+1] - out_off[r] >= min(limit[r], n) (3 n when dedup == 0: a fact may then be taken by
+ * more than one pass, as in the reference). */
+int32_t dvb_slim_facts(dvb_ctx* ctx, int32_t mem, int64_t n_reports, const int64_t* fact_off, const double* quality, const uint8_t* flags,
+                       const int32_t* sig_id, const int32_t* dim_id, const int64_t* sort_key, const int32_t* limit, const int64_t* out_off,
+                       int32_t dim_quota, double min_quality, int32_t keep_hard, int32_t dedup, int32_t* out_sel, int32_t* out_cnt);
+
 /* ---- a11-a13  replaces the string scans of: evaluate_answer_depth (web/server.py:21221-21401), _score_rich_option_answer
  *               (20318-20367), evaluate_answer_quality (20370-20426), _infer_legacy_log_capture_contract (21419-21466)
  * Per text: [b0, b1) = byte bounds of Python's text.strip(); out_len = len(text.strip()) in code points;

@@ -314,3 +314,26 @@ def test_unicode_table_version_is_checked_at_install(monkeypatch):
         assert dropin.check_unicode_tables() is False
     with pytest.raises(RuntimeError):
         dropin.check_unicode_tables(strict=True)
+
+
+def test_fuzz_f4_slim_facts_live(ref):
+    """the reference's select_slimmed_facts_for_prompt (loaded once per settings row) against the host
+    extraction of the package + the oracle restatement on fresh random evidence packs."""
+    import make_golden_slim as mg
+    from deep_vision_b200 import prompt_facts as pf
+    from oracle import dv_slim
+    rng = random.Random(99)
+    packs = [(mg.rand_pack(rng, rng.choice([1, 4, 9, 17, 40, 90])), rng.choice([1, 3, 8, 24, 60, None])) for _ in range(400)]
+    n = 0
+    for st in mg.SETTINGS[:3]:
+        fn = ref_loader.load(extra_names=mg.NAMES, overrides=st)["select_slimmed_facts_for_prompt"]
+        for pack, limit in packs:
+            facts = [f for f in pack.get("facts", []) if isinstance(f, dict)]
+            want = [next(i for i, f in enumerate(facts) if f is o) for o in fn(pack, limit)]
+            q, fl, sg, dm, ky = pf.extract_fact_arrays(pack, facts)
+            got = dv_slim.slim_select(q, fl, sg, dm, ky, max(1, int(limit or 1)), dim_quota=max(1, st["REPORT_V3_EVIDENCE_DIM_QUOTA"]),
+                                      min_quality=st["REPORT_V3_EVIDENCE_MIN_QUALITY"], keep_hard=st["REPORT_V3_EVIDENCE_KEEP_HARD_TRIGGERED"],
+                                      dedup=st["REPORT_V3_EVIDENCE_DEDUP_ENABLED"])
+            assert got == want
+            n += 1
+    assert n == 1200
