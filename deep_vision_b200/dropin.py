@@ -70,7 +70,9 @@ def _gate(mod, ctx) -> qs.QuestionGate:
     """Synonym dict and stop-word SET in the live process's iteration order (the set order is PYTHONHASHSEED dependent)."""
     syn = getattr(mod, "QUESTION_SIMILARITY_SYNONYMS", None)
     stop = getattr(mod, "QUESTION_SIMILARITY_STOPWORDS", None)
-    key = (id(syn), id(stop))
+    # keyed on CONTENT (and the set's iteration order), not on object identity: tests and hot-config change these objects in
+    # place, and the reference iterates the live objects on every call (web/server.py:20464-20468)
+    key = (tuple(syn.items()) if isinstance(syn, dict) else None, tuple(stop) if stop is not None else None)
     cached = getattr(mod, "_dvb200_gate_cache", None)
     if cached is not None and cached[0] == key:
         return cached[1]

@@ -134,3 +134,19 @@ def test_f3_claim_chunk_host_logic_with_oracle_scorer(oracle, monkeypatch):
     assert "infer_reference_chunk_refs_v3" in done
     dropin.uninstall(mod)
     assert not hasattr(mod, "infer_reference_chunk_refs_v3")
+
+
+def test_dropin_gate_tables_follow_in_place_changes():
+    """dropin._gate caches the device tables on the CONTENT of the module's synonym dict / stop-word set: an in-place change
+    (what tests and hot-config do; the reference iterates the live objects per call, web/server.py:20464-20468) rebuilds them."""
+    import types
+    from deep_vision_b200 import dropin
+    mod = types.SimpleNamespace(QUESTION_SIMILARITY_SYNONYMS={"痛点": "问题"}, QUESTION_SIMILARITY_STOPWORDS={"请", "你"})
+    g1 = dropin._gate(mod, ctx=object())
+    assert dropin._gate(mod, ctx=object()) is g1                      # unchanged content: cached
+    mod.QUESTION_SIMILARITY_STOPWORDS.add("们")                       # same object, new content
+    g2 = dropin._gate(mod, ctx=object())
+    assert g2 is not g1 and set(g2.stopwords) == {"请", "你", "们"}
+    mod.QUESTION_SIMILARITY_SYNONYMS["诉求"] = "需求"
+    g3 = dropin._gate(mod, ctx=object())
+    assert g3 is not g2 and ("诉求", "需求") in g3.synonyms
