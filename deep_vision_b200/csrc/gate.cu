@@ -13,6 +13,7 @@
 //                   shared-memory counters (one per history question), then one pass over the counters
 //                   evaluates  inter / max(1, |L|+|R|-inter) >= threshold  in fp64 exactly as the
 //                   reference and keeps the LARGEST matching history index (reversed(logs) scan).
+#include <type_traits>
 #include "common.cuh"
 #include "sort.cuh"
 #include "../../include/dv_unicode_tables.h"
@@ -47,15 +48,17 @@ __device__ __forceinline__ bool gate_is_punct(uint32_t c) {          // web/serv
     }
 }
 // CPython str.lower() of in[0..n) -> out; returns new length (<= n + #U+0130)
-// Scratch views.  Questions whose capacity fits GQ_CAP code points keep their two buffers in shared memory, element i of
-// thread t at word i * 128 + t (conflict-free when the lanes of a warp work on the same i); longer ones use the
-// per-question regions of the global scratch.  The helpers below are written once against operator[] / operator+.
+// Scratch views.  Questions whose capacity fits GQ_CAP code points and that stay inside the BMP (no 4-byte sequence in the
+// text, no astral character in a synonym replacement) keep their two buffers in shared memory as 16-BIT code points, element i
+// of thread t at half-word i * 128 + t; the others use the per-question regions of the global scratch (32-bit).  256 bytes per
+// thread instead of 512: the kernel is bound by the latency of its serial per-thread loops, and the shared scratch is what caps
+// the warps per SM (14 -> 28).  The helpers below are written once against operator[] / operator+.
 #define GQ_THREADS 128
 #define GQ_CAP 64
-#define GQ_SMEM_BYTES (2 * GQ_CAP * GQ_THREADS * 4)
+#define GQ_SMEM_BYTES (2 * GQ_CAP * GQ_THREADS * 2)
 struct GqShared {
-    uint32_t* p;
-    __device__ __forceinline__ uint32_t& operator[](int64_t i) const { return p[i * GQ_THREADS]; }
+    uint16_t* p;
+    __device__ __forceinline__ uint16_t& operator[](int64_t i) const { return p[i * GQ_THREADS]; }
     __device__ __forceinline__ GqShared operator+(int64_t k) const { return GqShared{ p + k * GQ_THREADS }; }
 };
 struct GqGlobal {
@@ -108,10 +111,10 @@ struct GqKeysGlobal {
     __device__ __forceinline__ unsigned long long get(int64_t i) const { return p[i]; }
     __device__ __forceinline__ void set(int64_t i, unsigned long long v) const { p[i] = v; }
 };
-struct GqKeysShared {
+struct GqKeysShared {            // key = first code point << 21 | second: one 16-bit code point per buffer
     GqShared hi, lo;
-    __device__ __forceinline__ unsigned long long get(int64_t i) const { return ((unsigned long long)hi[i] << 32) | lo[i]; }
-    __device__ __forceinline__ void set(int64_t i, unsigned long long v) const { hi[i] = (uint32_t)(v >> 32); lo[i] = (uint32_t)v; }
+    __device__ __forceinline__ unsigned long long get(int64_t i) const { return ((unsigned long long)hi[i] << 21) | lo[i]; }
+    __device__ __forceinline__ void set(int64_t i, unsigned long long v) const { hi[i] = (uint16_t)(v >> 21); lo[i] = (uint16_t)(v & 0x1FFFFFu); }
 };
 template <class K>
 __device__ void gate_heapsort_v(const K a, int64_t n) {
@@ -146,7 +149,7 @@ __device__ void gate_heapsort(unsigned long long* a, int64_t n) { gate_heapsort_
 // (optional) to norm[cap_off[s] ...] / norm_len[s].
 template <class Buf>
 __device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, const Buf a, const Buf b, const GateUnicode& U, const GateTablesDev& T,
-                                              unsigned long long* ks, int32_t* key_cnt_s, uint32_t* norm_s, int32_t* norm_len_s, bool keys_in_scratch) {
+                                              unsigned long long* ks, int32_t* key_cnt_s, uint32_t* norm_s, int32_t* norm_len_s, bool /*keys_in_scratch: implied by Buf*/) {
     // decode
     int64_t m = 0;
     for (int64_t i = 0; i < nb;) {
@@ -192,21 +195,15 @@ __device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, cons
     if (m == 1) { ks[0] = (1ULL << 42) | cur[0]; nk = 1; }
     else if (m > 1) {
         nk = m - 1;
-        if (keys_in_scratch) {
-            // key i = (cur[i] << 21) | cur[i + 1]: its high word replaces cur[i] (not needed any more), its low word goes to oth[i]
-            uint32_t c0 = cur[0];
-            for (int64_t i = 0; i + 1 < m; i++) {
-                const uint32_t c1 = cur[i + 1];
-                const unsigned long long k = ((unsigned long long)c0 << 21) | c1;
-                cur[i] = (uint32_t)(k >> 32); oth[i] = (uint32_t)k;
-                c0 = c1;
-            }
-            // (views over the same scratch; Buf is GqShared on this path)
-            gate_heapsort_v(GqKeysShared{ GqShared{ &cur[0] }, GqShared{ &oth[0] } }, nk);      // only taken with Buf = GqShared
-            unsigned long long prev = ((unsigned long long)cur[0] << 32) | oth[0];
+        if constexpr (std::is_same<Buf, GqShared>::value) {
+            // key i = (cur[i] << 21) | cur[i + 1]: its first code point stays in cur[i], the second goes to oth[i]; sorted in place
+            const GqKeysShared ksh{ GqShared{ &cur[0] }, GqShared{ &oth[0] } };
+            for (int64_t i = 0; i + 1 < m; i++) oth[i] = cur[i + 1];
+            gate_heapsort_v(ksh, nk);
+            unsigned long long prev = ksh.get(0);
             ks[0] = prev;
             int64_t u = 1;
-            for (int64_t i = 1; i < nk; i++) { const unsigned long long k = ((unsigned long long)cur[i] << 32) | oth[i]; if (k != prev) { ks[u++] = k; prev = k; } }
+            for (int64_t i = 1; i < nk; i++) { const unsigned long long k = ksh.get(i); if (k != prev) { ks[u++] = k; prev = k; } }
             nk = u;
         } else {
             for (int64_t i = 0; i + 1 < m; i++) ks[i] = ((unsigned long long)cur[i] << 21) | cur[i + 1];
@@ -221,13 +218,22 @@ __device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, cons
 // one thread per question.  Scratch: two code-point buffers of cap_off[s+1]-cap_off[s] entries each (shared memory when
 // that is <= GQ_CAP, else the question's region of bufA / bufB); keys of question s are written at keys[cap_off[s] ...],
 // their count to key_cnt[s]; the normalised text (optional) to norm[cap_off[s] ...] / norm_len[s].
-extern __shared__ uint32_t gq_smem[];
+extern __shared__ uint16_t gq_smem[];
 __global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
                                                         const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
                                                         GateUnicode U, GateTablesDev T,
                                                         unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
                                                         uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
     const GqShared sa{ gq_smem + threadIdx.x }, sb{ gq_smem + GQ_CAP * GQ_THREADS + threadIdx.x };
+    __shared__ int s_bmp;                                  // every synonym replacement writes BMP code points only
+    if (threadIdx.x == 0) {
+        int ok = 1;
+        const int32_t nd = T.n_syn > 0 ? T.syn_dst_off[T.n_syn] : 0;
+        for (int32_t j = 0; j < nd; j++) if (T.syn_dst[j] > 0xFFFFu) ok = 0;
+        s_bmp = ok;
+    }
+    __syncthreads();
+    const bool bmp_tables = s_bmp != 0;
     for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
         const uint8_t* t = utf8 + off[s];
         const int64_t nb = off[s + 1] - off[s];
@@ -236,8 +242,9 @@ __global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __r
         int64_t ncp = 2;
         // stepped exactly like the decoder of gate_question (a stray continuation byte starts a 2-byte sequence there), so raw bytes
         // that are not valid UTF-8 cannot produce more code points than counted here
-        for (int64_t i = 0; i < nb && ncp <= GQ_CAP; ) { const uint32_t c = t[i]; const int len = c < 0x80u ? 1 : (c < 0xE0u ? 2 : (c < 0xF0u ? 3 : 4)); ncp += 1 + (len == 2); i += len; }
-        if (ncp * T.growth <= GQ_CAP) gate_question(t, nb, sa, sb, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, true);
+        bool astral = false;                               // a 4-byte sequence: code points beyond 16 bits
+        for (int64_t i = 0; i < nb && ncp <= GQ_CAP; ) { const uint32_t c = t[i]; const int len = c < 0x80u ? 1 : (c < 0xE0u ? 2 : (c < 0xF0u ? 3 : 4)); ncp += 1 + (len == 2); astral |= len == 4; i += len; }
+        if (ncp * T.growth <= GQ_CAP && !astral && bmp_tables) gate_question(t, nb, sa, sb, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, true);
         else gate_question(t, nb, GqGlobal{ bufA + c0 }, GqGlobal{ bufB + c0 }, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, false);
     }
 }
@@ -575,7 +582,7 @@ extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* u
     if (mem == DVB_MEM_HOST) memcpy(out_cap_off, cap.data(), 8 * (size_t)(n + 1));
     else DVB_CUDA(ctx, cudaMemcpyAsync(out_cap_off, cap.data(), 8 * (size_t)(n + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
-    const int grid = (int)std::min<int64_t>((n + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
+    const int grid = (int)std::min<int64_t>((n + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<grid, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_utf8, d_off, n, d_cap, bufA, bufB, U, T, d_keys, d_cnt, d_norm, d_nl);
     ctx->launches += 1;
     return io.finish(ctx);          // synchronises: `cap` stays alive until here
@@ -615,9 +622,9 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     DVB_CUDA(ctx, cudaMemcpyAsync(d_ccap, ccap.data(), 8 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaMemcpyAsync(d_hcap, hcap.data(), 8 * (size_t)(n_hist + 1), cudaMemcpyHostToDevice, io.st));
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
-    const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
+    const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
-    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * (GQ_CAP <= 48 ? 4 : 3));
+    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
     k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
     int64_t n_pairs = 0;
