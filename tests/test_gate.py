@@ -64,6 +64,22 @@ def test_gpu_gate_vs_oracle_random(gpu_ctx, oracle):
 
 
 @pytest.mark.gpu
+def test_gpu_gate_astral_synonym_takes_32bit_scratch(gpu_ctx, oracle):
+    """k_question_keys keeps BMP questions as 16-bit code points in shared memory; a synonym that WRITES an astral character
+    (and any question holding one) must take the 32-bit global scratch — same keys and normalised text as the oracle."""
+    from deep_vision_b200 import question_similarity as qs
+    syn = [("痛点", "😀问题"), ("系统", "平台")]
+    gate = qs.QuestionGate(syn, ["请", "你"], ctx=gpu_ctx)
+    og = oracle.Gate(gate.synonyms, gate.stopwords)
+    cands = ["请问当前系统的痛点是什么", "痛点痛点", "没有替换的问题", "😀" * 3 + "系统", "", "A痛点b", "\U00010400大写𐐀"]
+    keys, norms = gate.keys(cands, want_norm=True)
+    for c, k, nm in zip(cands, keys, norms):
+        assert nm == og.normalize(c), repr(c)
+        assert k.tolist() == og.keys(c).tolist()
+    assert gate.match(cands, cands, 0.62).tolist() == og.gate(cands, cands, 0.62).tolist()
+
+
+@pytest.mark.gpu
 def test_gpu_gate_prefix_filter_equals_dense_counters(gpu_ctx, oracle, monkeypatch):
     """threshold > 0 runs k_gate_match_prefix (rarest-keys candidate generation + exact verification); DVB_GATE_KERNEL=dense
     forces the dense-counter kernel.  Same answers on near-duplicates, repeated history, very long questions
