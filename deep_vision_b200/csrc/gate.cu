@@ -14,6 +14,7 @@
 //                   evaluates  inter / max(1, |L|+|R|-inter) >= threshold  in fp64 exactly as the
 //                   reference and keeps the LARGEST matching history index (reversed(logs) scan).
 #include <type_traits>
+#include <chrono>
 #include "common.cuh"
 #include "sort.cuh"
 #include "../../include/dv_unicode_tables.h"
@@ -588,6 +589,34 @@ extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* u
     return io.finish(ctx);          // synchronises: `cap` stays alive until here
 }
 
+// capacity offsets on the device: cap[i] = (bytes before string i + 2 i) * growth — a closed form of the running sum gate_caps
+// builds on the host, so a 1 M-candidate call neither loops over the offsets on the host nor uploads 8 MB of capacities.
+// err: a string longer than 60000 bytes or decreasing offsets.
+__global__ void __launch_bounds__(256) k_gate_caps(const int64_t* __restrict__ off, int64_t n, int64_t growth, int64_t* __restrict__ cap, int32_t* __restrict__ err) {
+    const int64_t o0 = off[0];
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t oi = off[i];
+        cap[i] = (oi - o0 + 2 * i) * growth;
+        if (i < n) { const int64_t nb = off[i + 1] - oi; if (nb < 0 || nb > 60000) atomicExch(err, 1); }
+    }
+}
+// first and last offset of a CSR batch (host pointer or device pointer)
+static int32_t gate_span(dvb_ctx* ctx, dvb_io& io, const int64_t* off, int64_t n, int64_t* first, int64_t* last) {
+    if (io.mem == DVB_MEM_HOST) { *first = off[0]; *last = off[n]; return DVB_OK; }
+    DVB_CUDA(ctx, cudaMemcpyAsync(first, off, 8, cudaMemcpyDeviceToHost, io.st));
+    DVB_CUDA(ctx, cudaMemcpyAsync(last, off + n, 8, cudaMemcpyDeviceToHost, io.st));
+    DVB_CUDA(ctx, cudaStreamSynchronize(io.st));
+    return DVB_OK;
+}
+
+// DVB_GATE_TRACE=1: host-side checkpoints of a dvb_question_gate call on stderr (microseconds since entry)
+struct GateTrace {
+    bool on; std::chrono::steady_clock::time_point t0;
+    GateTrace() : on([] { const char* e = getenv("DVB_GATE_TRACE"); return e && e[0] == '1'; }()), t0(std::chrono::steady_clock::now()) {}
+    void at(const char* what) const {
+        if (on) fprintf(stderr, "[gate] %-28s %8.0f us\n", what, std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count());
+    }
+};
 extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* cand_utf8, const int64_t* cand_off, int64_t n_cand,
                                       const uint8_t* hist_utf8, const int64_t* hist_off, int64_t n_hist,
                                       const uint32_t* syn_src, const int32_t* syn_src_off, const uint32_t* syn_dst, const int32_t* syn_dst_off, int32_t n_syn,
@@ -595,7 +624,9 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
                                       double threshold, int64_t* out_match) {
     if (!ctx || n_cand < 0 || n_hist < 0 || !cand_off || !out_match || (n_hist > 0 && !hist_off)) { dvb_set_err(ctx, "dvb_question_gate: invalid argument%s%s"); return DVB_E_INVALID; }
     if (n_cand == 0) return DVB_OK;
+    GateTrace tr;
     dvb_scope sc(ctx); dvb_io io(sc, mem);
+    tr.at("scope");
     int64_t* d_out = io.out(out_match, (size_t)n_cand);
     if (n_hist == 0) {
         int32_t rc0 = io.check(ctx); if (rc0) return rc0;
@@ -605,31 +636,41 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     GateUnicode U; int32_t rc = gate_unicode(ctx, &U); if (rc) { dvb_set_err(ctx, "cannot upload unicode tables%s%s"); return rc; }
     GateTablesDev T; GateHostTables H;
     rc = gate_tables(ctx, io, syn_src, syn_src_off, syn_dst, syn_dst_off, n_syn, stop, stop_off, n_stop, &T, &H); if (rc) return rc;
-    std::vector<int64_t> coff, ccap, hoff, hcap;
-    rc = gate_caps(ctx, io, cand_off, n_cand, H.growth, &coff, &ccap); if (rc) return rc;
-    rc = gate_caps(ctx, io, hist_off, n_hist, H.growth, &hoff, &hcap); if (rc) return rc;
-    const int64_t ctotal = coff[n_cand] - coff[0], htotal = hoff[n_hist] - hoff[0];
-    const uint8_t* d_cu = mem == DVB_MEM_HOST ? io.in(cand_utf8 + coff[0], (size_t)ctotal + 16) - coff[0] : cand_utf8;
-    const uint8_t* d_hu = mem == DVB_MEM_HOST ? io.in(hist_utf8 + hoff[0], (size_t)htotal + 16) - hoff[0] : hist_utf8;
+    int64_t c_first = 0, c_last = 0, h_first = 0, h_last = 0;
+    rc = gate_span(ctx, io, cand_off, n_cand, &c_first, &c_last); if (rc) return rc;
+    rc = gate_span(ctx, io, hist_off, n_hist, &h_first, &h_last); if (rc) return rc;
+    const int64_t ctotal = c_last - c_first, htotal = h_last - h_first;
+    if (ctotal < 0 || htotal < 0) { dvb_set_err(ctx, "question gate: offsets must not decrease%s%s"); return DVB_E_INVALID; }
+    const int64_t ccap_n = (ctotal + 2 * n_cand) * H.growth, hcap_n = (htotal + 2 * n_hist) * H.growth;      // = cap[n] of k_gate_caps
+    tr.at("tables + spans");
+    const uint8_t* d_cu = mem == DVB_MEM_HOST ? io.in(cand_utf8 + c_first, (size_t)ctotal + 16) - c_first : cand_utf8;
+    const uint8_t* d_hu = mem == DVB_MEM_HOST ? io.in(hist_utf8 + h_first, (size_t)htotal + 16) - h_first : hist_utf8;
     const int64_t* d_co = io.in(cand_off, (size_t)n_cand + 1); const int64_t* d_ho = io.in(hist_off, (size_t)n_hist + 1);
     int64_t* d_ccap = io.tmp<int64_t>((size_t)n_cand + 1); int64_t* d_hcap = io.tmp<int64_t>((size_t)n_hist + 1);
-    const int64_t bufn = std::max(ccap[n_cand], hcap[n_hist]) + 1;
+    const int64_t bufn = std::max(ccap_n, hcap_n) + 1;
     uint32_t* bufA = io.tmp<uint32_t>((size_t)bufn); uint32_t* bufB = io.tmp<uint32_t>((size_t)bufn);
-    unsigned long long* d_ck = io.tmp<unsigned long long>((size_t)ccap[n_cand] + 1); int32_t* d_cc = io.tmp<int32_t>((size_t)n_cand);
-    unsigned long long* d_hk = io.tmp<unsigned long long>((size_t)hcap[n_hist] + 1); int32_t* d_hc = io.tmp<int32_t>((size_t)n_hist);
+    unsigned long long* d_ck = io.tmp<unsigned long long>((size_t)ccap_n + 1); int32_t* d_cc = io.tmp<int32_t>((size_t)n_cand);
+    unsigned long long* d_hk = io.tmp<unsigned long long>((size_t)hcap_n + 1); int32_t* d_hc = io.tmp<int32_t>((size_t)n_hist);
     int64_t* d_poff = io.tmp<int64_t>((size_t)n_hist + 1);
+    int32_t* d_err = io.tmp<int32_t>(1);
     rc = io.check(ctx); if (rc) return rc;
-    DVB_CUDA(ctx, cudaMemcpyAsync(d_ccap, ccap.data(), 8 * (size_t)(n_cand + 1), cudaMemcpyHostToDevice, io.st));
-    DVB_CUDA(ctx, cudaMemcpyAsync(d_hcap, hcap.data(), 8 * (size_t)(n_hist + 1), cudaMemcpyHostToDevice, io.st));
+    tr.at("inputs staged (H2D queued)");
+    DVB_CUDA(ctx, cudaMemsetAsync(d_err, 0, 4, io.st));
+    k_gate_caps<<<(int)std::min<int64_t>((n_cand + 256) / 256, (int64_t)ctx->num_sm * 8), 256, 0, io.st>>>(d_co, n_cand, H.growth, d_ccap, d_err);
+    k_gate_caps<<<(int)std::min<int64_t>((n_hist + 256) / 256, (int64_t)ctx->num_sm * 8), 256, 0, io.st>>>(d_ho, n_hist, H.growth, d_hcap, d_err);
+    ctx->launches += 2;
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
     const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
     const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
     k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
-    int64_t n_pairs = 0;
+    int64_t n_pairs = 0; int32_t bad_off = 0;
     DVB_CUDA(ctx, cudaMemcpyAsync(&n_pairs, d_poff + n_hist, 8, cudaMemcpyDeviceToHost, io.st));
+    DVB_CUDA(ctx, cudaMemcpyAsync(&bad_off, d_err, 4, cudaMemcpyDeviceToHost, io.st));
     DVB_CUDA(ctx, cudaStreamSynchronize(io.st));
+    tr.at("keys done (sync)");
+    if (bad_off) { dvb_set_err(ctx, "question gate: a question is limited to 60000 bytes%s%s"); return DVB_E_INVALID; }
     ctx->launches += 3;
     if (n_pairs >= 0x7FFFFFFFLL) { dvb_set_err(ctx, "dvb_question_gate: history too large%s%s"); return DVB_E_CAPACITY; }
     unsigned long long* pk = io.tmp<unsigned long long>((size_t)n_pairs + 1); unsigned long long* pk2 = io.tmp<unsigned long long>((size_t)n_pairs + 1);
@@ -678,7 +719,10 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     k_gate_match<<<grid, GATE_THREADS, smem, io.st>>>(d_ck, d_ccap, d_cc, n_cand, pk, pv, n_pairs, d_hc, n_hist, tile_h, threshold, d_out, d_nflag, d_flagged);
     if (timing) DVB_CUDA(ctx, cudaEventRecord(sc.l->ev1, io.st));
     ctx->launches += 1;
+    tr.at("match queued");
+    if (tr.on) { cudaStreamSynchronize(io.st); tr.at("match done (trace-only sync)"); }
     rc = io.finish(ctx);
+    tr.at("finish (D2H + sync)");
     if (rc == DVB_OK && timing) { float ms = 0.f; cudaEventElapsedTime(&ms, sc.l->ev0, sc.l->ev1); ctx->last_ms = ms; }
     return rc;
 }

@@ -64,6 +64,16 @@ def test_gpu_gate_vs_oracle_random(gpu_ctx, oracle):
 
 
 @pytest.mark.gpu
+def test_gpu_gate_rejects_overlong_question(gpu_ctx):
+    """the 60000-byte limit per question is checked on the device since the capacities are computed there (k_gate_caps)"""
+    from deep_vision_b200 import _lib, question_similarity as qs
+    gate = qs.QuestionGate(ctx=gpu_ctx)
+    with pytest.raises(_lib.DvbError):
+        gate.match(["短问题", "长" * 20001], ["历史问题"], 0.62)
+    assert gate.match(["历史问题？"], ["历史问题"], 0.62).tolist() == [0]          # the context is usable afterwards
+
+
+@pytest.mark.gpu
 def test_gpu_gate_astral_synonym_takes_32bit_scratch(gpu_ctx, oracle):
     """k_question_keys keeps BMP questions as 16-bit code points in shared memory; a synonym that WRITES an astral character
     (and any question holding one) must take the 32-bit global scratch — same keys and normalised text as the oracle."""
