@@ -55,6 +55,7 @@ __device__ __forceinline__ bool gate_is_punct(uint32_t c) {          // web/serv
 // thread instead of 512: the kernel is bound by the latency of its serial per-thread loops, and the shared scratch is what caps
 // the warps per SM (14 -> 28).  The helpers below are written once against operator[] / operator+.
 #define GQ_THREADS 128
+#define GATE_SLICES 4
 #define GQ_CAP 64
 #define GQ_SMEM_BYTES (2 * GQ_CAP * GQ_THREADS * 2)
 struct GqShared {
@@ -643,7 +644,11 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     if (ctotal < 0 || htotal < 0) { dvb_set_err(ctx, "question gate: offsets must not decrease%s%s"); return DVB_E_INVALID; }
     const int64_t ccap_n = (ctotal + 2 * n_cand) * H.growth, hcap_n = (htotal + 2 * n_hist) * H.growth;      // = cap[n] of k_gate_caps
     tr.at("tables + spans");
-    const uint8_t* d_cu = mem == DVB_MEM_HOST ? io.in(cand_utf8 + c_first, (size_t)ctotal + 16) - c_first : cand_utf8;
+    // Host buffers with >= 16 MB of candidate text: the text crosses PCIe in GATE_SLICES slices on the lease's copy stream while
+    // the key kernel works on the previous slice (the copy and the key kernel cost about the same, 3.4 ms each at config 4)
+    const int n_sl = (mem == DVB_MEM_HOST && ctotal >= ((int64_t)16 << 20) && n_cand >= 8 * GATE_SLICES) ? GATE_SLICES : 1;
+    uint8_t* d_cu_w = n_sl > 1 ? io.tmp<uint8_t>((size_t)ctotal + 16) : nullptr;
+    const uint8_t* d_cu = n_sl > 1 ? d_cu_w - c_first : (mem == DVB_MEM_HOST ? io.in(cand_utf8 + c_first, (size_t)ctotal + 16) - c_first : cand_utf8);
     const uint8_t* d_hu = mem == DVB_MEM_HOST ? io.in(hist_utf8 + h_first, (size_t)htotal + 16) - h_first : hist_utf8;
     const int64_t* d_co = io.in(cand_off, (size_t)n_cand + 1); const int64_t* d_ho = io.in(hist_off, (size_t)n_hist + 1);
     int64_t* d_ccap = io.tmp<int64_t>((size_t)n_cand + 1); int64_t* d_hcap = io.tmp<int64_t>((size_t)n_hist + 1);
@@ -662,8 +667,32 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
     const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
     k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
-    const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
-    k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
+    if (n_sl == 1) {
+        const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
+        k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
+    } else {
+        dvb_lease* l = sc.l;
+        if (!l->copy) DVB_CUDA(ctx, cudaStreamCreateWithFlags(&l->copy, cudaStreamNonBlocking));
+        while ((int)l->pipe_ev.size() < n_sl + 1) { cudaEvent_t e; DVB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); l->pipe_ev.push_back(e); }
+        DVB_CUDA(ctx, cudaEventRecord(l->pipe_ev[0], io.st));                  // the copy stream starts behind the allocations' last use
+        DVB_CUDA(ctx, cudaStreamWaitEvent(l->copy, l->pipe_ev[0], 0));
+        const bool pageable = dvb_is_pageable(cand_utf8);
+        cudaError_t pe = cudaSuccess;
+        for (int k = 0; k < n_sl && pe == cudaSuccess; k++) {
+            const int64_t s0 = n_cand * k / n_sl, s1 = n_cand * (k + 1) / n_sl;
+            const int64_t b0 = cand_off[s0], b1 = cand_off[s1];
+            if (b1 > b0) pe = (pageable && (size_t)(b1 - b0) >= DVB_H2D_MIN) ? dvb_h2d_staged(l, ctx->device, d_cu_w + (b0 - c_first), cand_utf8 + b0, (size_t)(b1 - b0), l->copy)
+                                                                              : cudaMemcpyAsync(d_cu_w + (b0 - c_first), cand_utf8 + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, l->copy);
+            if (pe == cudaSuccess) pe = cudaEventRecord(l->pipe_ev[k + 1], l->copy);
+            if (pe == cudaSuccess) pe = cudaStreamWaitEvent(io.st, l->pipe_ev[k + 1], 0);
+            if (pe != cudaSuccess) break;
+            const int gc = (int)std::min<int64_t>((s1 - s0 + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
+            k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co + s0, s1 - s0, d_ccap + s0, bufA, bufB, U, T, d_ck, d_cc + s0, nullptr, nullptr);
+            ctx->launches += 1;
+        }
+        if (pe != cudaSuccess) { cudaStreamSynchronize(l->copy); cudaStreamSynchronize(io.st); DVB_CUDA(ctx, pe); }
+        ctx->launches -= 1;                                                  // the += 3 below counts one candidate launch
+    }
     k_gate_scan_counts<<<1, 1024, 0, io.st>>>(d_hc, d_poff, n_hist);
     int64_t n_pairs = 0; int32_t bad_off = 0;
     DVB_CUDA(ctx, cudaMemcpyAsync(&n_pairs, d_poff + n_hist, 8, cudaMemcpyDeviceToHost, io.st));
