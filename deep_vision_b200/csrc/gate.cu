@@ -221,11 +221,12 @@ __device__ __forceinline__ void gate_question(const uint8_t* t, int64_t nb, cons
 // that is <= GQ_CAP, else the question's region of bufA / bufB); keys of question s are written at keys[cap_off[s] ...],
 // their count to key_cnt[s]; the normalised text (optional) to norm[cap_off[s] ...] / norm_len[s].
 extern __shared__ uint16_t gq_smem[];
-__global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
-                                                        const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
-                                                        GateUnicode U, GateTablesDev T,
-                                                        unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
-                                                        uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
+struct GqBatch {
+    const uint8_t* utf8; const int64_t* off; int64_t n; const int64_t* cap_off; uint32_t* bufA; uint32_t* bufB;
+    unsigned long long* keys; int32_t* key_cnt; uint32_t* norm; int32_t* norm_len;
+};
+// blocks [0, nblk) of a launch work through batch q, block `bid` of them
+__device__ __forceinline__ void gq_run(const GqBatch& q, int64_t bid, int64_t nblk, const GateUnicode& U, const GateTablesDev& T) {
     const GqShared sa{ gq_smem + threadIdx.x }, sb{ gq_smem + GQ_CAP * GQ_THREADS + threadIdx.x };
     __shared__ int s_bmp;                                  // every synonym replacement writes BMP code points only
     if (threadIdx.x == 0) {
@@ -236,19 +237,33 @@ __global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __r
     }
     __syncthreads();
     const bool bmp_tables = s_bmp != 0;
-    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < n; s += (int64_t)gridDim.x * blockDim.x) {
-        const uint8_t* t = utf8 + off[s];
-        const int64_t nb = off[s + 1] - off[s];
-        const int64_t c0 = cap_off[s];
+    for (int64_t s = bid * blockDim.x + threadIdx.x; s < q.n; s += nblk * blockDim.x) {
+        const uint8_t* t = q.utf8 + q.off[s];
+        const int64_t nb = q.off[s + 1] - q.off[s];
+        const int64_t c0 = q.cap_off[s];
         // code points (+1 for every 2-byte character: U+0130 lower-cases to two), times the synonym growth, bound the scratch use
         int64_t ncp = 2;
         // stepped exactly like the decoder of gate_question (a stray continuation byte starts a 2-byte sequence there), so raw bytes
         // that are not valid UTF-8 cannot produce more code points than counted here
         bool astral = false;                               // a 4-byte sequence: code points beyond 16 bits
         for (int64_t i = 0; i < nb && ncp <= GQ_CAP; ) { const uint32_t c = t[i]; const int len = c < 0x80u ? 1 : (c < 0xE0u ? 2 : (c < 0xF0u ? 3 : 4)); ncp += 1 + (len == 2); astral |= len == 4; i += len; }
-        if (ncp * T.growth <= GQ_CAP && !astral && bmp_tables) gate_question(t, nb, sa, sb, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, true);
-        else gate_question(t, nb, GqGlobal{ bufA + c0 }, GqGlobal{ bufB + c0 }, U, T, keys + c0, key_cnt + s, norm ? norm + c0 : nullptr, norm ? norm_len + s : nullptr, false);
+        if (ncp * T.growth <= GQ_CAP && !astral && bmp_tables) gate_question(t, nb, sa, sb, U, T, q.keys + c0, q.key_cnt + s, q.norm ? q.norm + c0 : nullptr, q.norm ? q.norm_len + s : nullptr, true);
+        else gate_question(t, nb, GqGlobal{ q.bufA + c0 }, GqGlobal{ q.bufB + c0 }, U, T, q.keys + c0, q.key_cnt + s, q.norm ? q.norm + c0 : nullptr, q.norm ? q.norm_len + s : nullptr, false);
     }
+}
+__global__ void __launch_bounds__(GQ_THREADS) k_question_keys(const uint8_t* __restrict__ utf8, const int64_t* __restrict__ off, int64_t n,
+                                                        const int64_t* __restrict__ cap_off, uint32_t* __restrict__ bufA, uint32_t* __restrict__ bufB,
+                                                        GateUnicode U, GateTablesDev T,
+                                                        unsigned long long* __restrict__ keys, int32_t* __restrict__ key_cnt,
+                                                        uint32_t* __restrict__ norm, int32_t* __restrict__ norm_len) {
+    const GqBatch q{ utf8, off, n, cap_off, bufA, bufB, keys, key_cnt, norm, norm_len };
+    gq_run(q, blockIdx.x, gridDim.x, U, T);
+}
+// history and candidates of one gate call in ONE launch (blocks [0, ga): batch a, the rest: batch b; separate scratch regions):
+// at config-1 sizes each of the two launches is a latency chain of ~60 us, not work
+__global__ void __launch_bounds__(GQ_THREADS) k_question_keys2(GqBatch a, int ga, GqBatch b, GateUnicode U, GateTablesDev T) {
+    if ((int)blockIdx.x < ga) gq_run(a, blockIdx.x, ga, U, T);
+    else gq_run(b, (int64_t)blockIdx.x - ga, (int64_t)gridDim.x - ga, U, T);
 }
 
 // (key, hid) pairs of the history questions, compacted at pair_off[h]
@@ -590,6 +605,32 @@ extern "C" int32_t dvb_question_keys(dvb_ctx* ctx, int32_t mem, const uint8_t* u
     return io.finish(ctx);          // synchronises: `cap` stays alive until here
 }
 
+// Small histories (config 1: 60 questions, ~1 200 pairs): ONE CTA sorts the (key, history id) pairs in shared memory instead
+// of the 24 launches of six radix passes, which cost more in launch latency than the whole rest of the call.  Bitonic network
+// over the next power of two, ordered by (key, id): the same order the stable radix sort leaves (ids ascend inside a key).
+#define GATE_SMALL_SORT 4096
+__global__ void __launch_bounds__(1024) k_gate_sort_small(unsigned long long* __restrict__ pk, uint32_t* __restrict__ pv, int n) {
+    extern __shared__ __align__(16) unsigned char gs_raw[];
+    unsigned long long* key = reinterpret_cast<unsigned long long*>(gs_raw);
+    uint32_t* val = reinterpret_cast<uint32_t*>(gs_raw + 8 * GATE_SMALL_SORT);
+    int m = 1; while (m < n) m <<= 1;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) { key[i] = i < n ? pk[i] : ~0ULL; val[i] = i < n ? pv[i] : 0xFFFFFFFFu; }
+    __syncthreads();
+    for (int k = 2; k <= m; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < m; i += blockDim.x) {
+                const int x = i ^ j;
+                if (x > i) {
+                    const unsigned long long ka = key[i], kb = key[x]; const uint32_t va = val[i], vb = val[x];
+                    const bool gt = ka > kb || (ka == kb && va > vb);
+                    if (gt == ((i & k) == 0)) { key[i] = kb; key[x] = ka; val[i] = vb; val[x] = va; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { pk[i] = key[i]; pv[i] = val[i]; }
+}
+
 // capacity offsets on the device: cap[i] = (bytes before string i + 2 i) * growth — a closed form of the running sum gate_caps
 // builds on the host, so a 1 M-candidate call neither loops over the offsets on the host nor uploads 8 MB of capacities.
 // err: a string longer than 60000 bytes or decreasing offsets.
@@ -652,7 +693,7 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     const uint8_t* d_hu = mem == DVB_MEM_HOST ? io.in(hist_utf8 + h_first, (size_t)htotal + 16) - h_first : hist_utf8;
     const int64_t* d_co = io.in(cand_off, (size_t)n_cand + 1); const int64_t* d_ho = io.in(hist_off, (size_t)n_hist + 1);
     int64_t* d_ccap = io.tmp<int64_t>((size_t)n_cand + 1); int64_t* d_hcap = io.tmp<int64_t>((size_t)n_hist + 1);
-    const int64_t bufn = std::max(ccap_n, hcap_n) + 1;
+    const int64_t bufn = (n_sl == 1 ? ccap_n + hcap_n : std::max(ccap_n, hcap_n)) + 2;     // one launch for both batches: separate regions
     uint32_t* bufA = io.tmp<uint32_t>((size_t)bufn); uint32_t* bufB = io.tmp<uint32_t>((size_t)bufn);
     unsigned long long* d_ck = io.tmp<unsigned long long>((size_t)ccap_n + 1); int32_t* d_cc = io.tmp<int32_t>((size_t)n_cand);
     unsigned long long* d_hk = io.tmp<unsigned long long>((size_t)hcap_n + 1); int32_t* d_hc = io.tmp<int32_t>((size_t)n_hist);
@@ -665,12 +706,16 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     k_gate_caps<<<(int)std::min<int64_t>((n_hist + 256) / 256, (int64_t)ctx->num_sm * 8), 256, 0, io.st>>>(d_ho, n_hist, H.growth, d_hcap, d_err);
     ctx->launches += 2;
     DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
+    DVB_CUDA(ctx, cudaFuncSetAttribute(k_question_keys2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GQ_SMEM_BYTES));
     const int gh = (int)std::min<int64_t>((n_hist + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
-    k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
     if (n_sl == 1) {
         const int gc = (int)std::min<int64_t>((n_cand + GQ_THREADS - 1) / GQ_THREADS, (int64_t)ctx->num_sm * 7);
-        k_question_keys<<<gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_cu, d_co, n_cand, d_ccap, bufA, bufB, U, T, d_ck, d_cc, nullptr, nullptr);
+        const GqBatch qh{ d_hu, d_ho, n_hist, d_hcap, bufA, bufB, d_hk, d_hc, nullptr, nullptr };
+        const GqBatch qc{ d_cu, d_co, n_cand, d_ccap, bufA + hcap_n + 1, bufB + hcap_n + 1, d_ck, d_cc, nullptr, nullptr };
+        k_question_keys2<<<gh + gc, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(qh, gh, qc, U, T);
+        ctx->launches -= 1;                                                  // the += 3 below counts two key launches
     } else {
+        k_question_keys<<<gh, GQ_THREADS, GQ_SMEM_BYTES, io.st>>>(d_hu, d_ho, n_hist, d_hcap, bufA, bufB, U, T, d_hk, d_hc, nullptr, nullptr);
         dvb_lease* l = sc.l;
         if (!l->copy) DVB_CUDA(ctx, cudaStreamCreateWithFlags(&l->copy, cudaStreamNonBlocking));
         while ((int)l->pipe_ev.size() < n_sl + 1) { cudaEvent_t e; DVB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); l->pipe_ev.push_back(e); }
@@ -709,10 +754,16 @@ extern "C" int32_t dvb_question_gate(dvb_ctx* ctx, int32_t mem, const uint8_t* c
     if (n_pairs > 0) {
         k_gate_pairs<<<(int)std::min<int64_t>(n_hist, (int64_t)ctx->num_sm * 8), 128, 0, io.st>>>(d_hk, d_hcap, d_hc, d_poff, n_hist, pk, pv);
         ctx->launches += 1;
-        int64_t l = 0;
-        const int which = dv_radix_sort_pairs(pk, pv, pk2, pv2, n_pairs, 0, 48, hist, io.st, &l);   // keys use 43 bits
-        ctx->launches += l;
-        if (which) { pk = pk2; pv = pv2; }
+        if (n_pairs <= GATE_SMALL_SORT) {
+            DVB_CUDA(ctx, cudaFuncSetAttribute(k_gate_sort_small, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * GATE_SMALL_SORT));
+            k_gate_sort_small<<<1, 1024, 12 * GATE_SMALL_SORT, io.st>>>(pk, pv, (int)n_pairs);
+            ctx->launches += 1;
+        } else {
+            int64_t l = 0;
+            const int which = dv_radix_sort_pairs(pk, pv, pk2, pv2, n_pairs, 0, 48, hist, io.st, &l);   // keys use 43 bits
+            ctx->launches += l;
+            if (which) { pk = pk2; pv = pv2; }
+        }
     }
     const int32_t tile_h = (int32_t)std::min<int64_t>(n_hist, 96 * 1024);
     const size_t smem = (size_t)((tile_h + 1) / 2) * 4;
