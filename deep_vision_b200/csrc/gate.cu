@@ -382,6 +382,9 @@ __global__ void k_gate_table_tails(const unsigned long long* __restrict__ pk, in
 }
 
 #define GP_MAXL 128
+#ifndef GP_BATCH
+#define GP_BATCH 8
+#endif
 #define GP_SET 256
 struct GpWarp {
     unsigned long long key[GP_MAXL];
@@ -460,10 +463,20 @@ __global__ void __launch_bounds__(256) k_gate_match_prefix(const unsigned long l
                     if (__ddiv_rn((double)mn, (double)un0) >= thr) {                          // size bound
                         const unsigned long long* hk = hkeys + hcap_off[h];
                         int32_t inter = 0;
-                        for (int32_t i = 0; i < hc; i++) {
-                            const unsigned long long key = hk[i];
-                            uint32_t sl = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 56);
-                            for (;;) { const unsigned long long v = W.set[sl]; if (v == key) { inter++; break; } if (v == ~0ULL) break; sl = (sl + 1) & (GP_SET - 1); }
+                        // GP_BATCH keys per round: their loads are issued together (the one-key loop waited for every load in turn:
+                        // long_scoreboard was 8 stall cycles per issue, profiles/README.md); a warp-cooperative verification of one
+                        // survivor at a time was measured too and is slower (7.1 vs 5.3 ms: the survivors' load chains no longer overlap)
+                        for (int32_t i = 0; i < hc; i += GP_BATCH) {
+                            unsigned long long kq[GP_BATCH];
+#pragma unroll
+                            for (int u = 0; u < GP_BATCH; u++) kq[u] = i + u < hc ? hk[i + u] : 0ULL;
+#pragma unroll
+                            for (int u = 0; u < GP_BATCH; u++) {
+                                if (i + u >= hc) break;
+                                const unsigned long long key = kq[u];
+                                uint32_t sl = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> 56);
+                                for (;;) { const unsigned long long v = W.set[sl]; if (v == key) { inter++; break; } if (v == ~0ULL) break; sl = (sl + 1) & (GP_SET - 1); }
+                            }
                         }
                         int32_t un = L + hc - inter; if (un < 1) un = 1;
                         if (inter > 0 && __ddiv_rn((double)inter, (double)un) >= thr) cand = h;
