@@ -15,6 +15,7 @@
 //            (score desc, fact index asc)  ==  the reference's strict '>' scan in index order.
 //   phase R  per-claim reduction of the warps' bests, outputs.
 // No intermediate key arrays ever reach HBM: algorithmic traffic = claim + fact bytes in, 16 B/claim out.
+#include <atomic>
 #include "common.cuh"
 #include "text.cuh"
 #include "bind_common.cuh"
@@ -80,22 +81,26 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     size_t smem = fixed + hit_bytes;
     const bool use_global = hit_bytes > 16384;          // huge claim groups: hit bitmaps move to global memory
     if (use_global) smem = fixed;
-    DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claims_general, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 1;
-    DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bind_claims_general, BIND_THREADS, smem));
-    if (occ < 1) occ = 1;
-    const int grid = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ);
+    // the general kernel runs only for handed-back sessions: its attribute and occupancy are queried when it is launched; the
+    // workspace is sized for the most CTAs an SM can hold (8 x 256 threads).  A config-1 sized call is ~25 driver calls long,
+    // so the ones that do not depend on the call are made once per device.
+    int grid = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * 8);
     // ---- fast kernel (bind7.cuh): per-session capacity checks happen on the device (sess_fallback)
     const char* force = getenv("DVB_BIND_KERNEL");
     const bool fast = !(force && !strcmp(force, "general"));
     const size_t smem7 = bind7_smem_bytes();
     int grid7 = 1;
     if (fast) {
-        int occ7 = 1;
-        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
-        DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
-        DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_facts, BIND_THREADS, smem7));
-        if (occ7 < 1) occ7 = 1;
+        static std::atomic<int> occ7_of[64];                       // per device: 0 = not asked yet
+        const int dslot = ctx->device & 63;
+        int occ7 = occ7_of[dslot].load();
+        if (occ7 <= 0) {
+            DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+            DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+            DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_facts, BIND_THREADS, smem7));
+            if (occ7 < 1) occ7 = 1;
+            occ7_of[dslot].store(occ7);
+        }
         grid7 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ7);
     }
     // ---- workspace
@@ -183,6 +188,11 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         BindParams q = use_fast ? p7 : p;
         if (!use_fast) {
             q.s_begin = s0; q.s_end = s1;
+            cudaError_t ge = cudaFuncSetAttribute(k_bind_claims_general, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            int occ = 1;
+            if (ge == cudaSuccess) ge = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_bind_claims_general, BIND_THREADS, smem);
+            if (ge != cudaSuccess) return ge;
+            grid = (int)std::min<int64_t>((int64_t)grid, (int64_t)ctx->num_sm * std::max(1, occ));      // never above the workspace's CTA count
             k_bind_claims_general<<<(int)std::min<int64_t>(s1 - s0, (int64_t)grid), BIND_THREADS, smem, st>>>(q);
             ctx->launches += 1;
             return cudaGetLastError();
