@@ -114,7 +114,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (use_global) need += dvb_pad((size_t)grid * hit_bytes);
     // fast kernels: one slab per claim group of a wave of sessions.  A session of n claims has ceil(n / 32) groups, so a
     // range of sessions holds at most sessions + claims / 32 of them; ranges are cut so that a wave's slabs stay below 1 GB.
-    const int64_t slab_budget = std::max<int64_t>(((int64_t)1 << 30) / B7_BLOB_BYTES, 64);
+    int64_t slab_budget = std::max<int64_t>(((int64_t)1 << 30) / B7_BLOB_BYTES, 64);
+    if (const char* e = getenv("DVB_BIND_SLAB_BUDGET")) { const long long v = atoll(e); if (v >= 1) slab_budget = v; }       // tests: force waves on small inputs
     const int64_t groups_bound = n_sessions + n_claims / BIND_CLAIMS;
     const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
     if (fast) need += dvb_pad((size_t)grid7 * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)

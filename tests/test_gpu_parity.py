@@ -85,6 +85,34 @@ def _bind_vs_oracle(gpu_ctx, oracle, a, check_len_fact=True):
     return got
 
 
+def test_a2_slab_waves_host_and_device_buffers(gpu_ctx, oracle, monkeypatch):
+    """dvb_bind_claims hands the claim tables from k_bind_claim_tables to k_bind_facts through one slab per claim group and
+    runs in waves of sessions when a call has more groups than slabs (1 GB of slabs in production; 64 slabs here): 150
+    sessions x 2 groups = 5 waves, host buffers (offsets on the host) and device buffers (offsets fetched once) — same
+    answers as the oracle and as the single-wave call."""
+    import torch
+    from deep_vision_b200 import _lib, evidence, synth
+    c = synth.make_sessions(150, turns=6, claims_per_session=40, seed=5)
+    a = (c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off,
+         c.fact_quality, c.fact_dim, c.fact_hard, c.claim_pref_dim, c.claim_threshold)
+    one = _bind_vs_oracle(gpu_ctx, oracle, a)
+    monkeypatch.setenv("DVB_BIND_SLAB_BUDGET", "64")
+    l0 = gpu_ctx.launches
+    waves = _bind_vs_oracle(gpu_ctx, oracle, a)
+    assert gpu_ctx.launches - l0 >= 2 * 5                           # five waves x two kernels
+    assert np.array_equal(one["best_score"].view(np.uint64), waves["best_score"].view(np.uint64))
+    dev = [torch.from_numpy(x).cuda() for x in a]
+    nc = int(c.sess_claim_off[-1])
+    ob = torch.empty(nc, dtype=torch.int32, device="cuda"); os_ = torch.empty(nc, dtype=torch.float64, device="cuda")
+    obd = torch.empty(nc, dtype=torch.uint8, device="cuda")
+    rc = gpu_ctx.lib.dvb_bind_claims(gpu_ctx.handle, _lib.MEM_DEVICE, *[t.data_ptr() for t in dev[:6]], c.n_sessions,
+                                     *[t.data_ptr() for t in dev[6:]], ob.data_ptr(), os_.data_ptr(), obd.data_ptr(), None, None, 0)
+    gpu_ctx.check(rc, "bind")
+    torch.cuda.synchronize()
+    assert np.array_equal(ob.cpu().numpy(), waves["best_fact"]) and np.array_equal(obd.cpu().numpy(), waves["bound"])
+    assert np.array_equal(os_.cpu().numpy().view(np.uint64), waves["best_score"].view(np.uint64))
+
+
 def test_a2_long_facts_chunk_parallel_tokenizer(gpu_ctx, oracle):
     """long facts (tests/bind_cases.py): cell/step boundaries, long runs, exotic case mappings (handed back to the general
     kernel), long ASCII tokens, 2-/4-byte characters — bit-exact against the oracle."""
