@@ -118,3 +118,33 @@ def test_gpu_max_solution_similarity_equals_pairwise_scan():
             best, name = s, n
     assert qs.max_solution_similarity(sig, others) == (best, name)
     assert qs.max_solution_similarity(sig, []) == (0.0, "")
+
+
+@pytest.mark.gpu
+def test_gpu_slim_facts_device_buffers_match_host_buffers():
+    """dvb_slim_facts with DVB_MEM_DEVICE (every array already on the GPU, outputs written in place) equals the host-buffer call."""
+    import torch
+    from deep_vision_b200 import _lib, prompt_facts as pf
+    from deep_vision_b200.packing import ptr
+    rng = random.Random(3)
+    packs = [{"facts": [{"q_id": "Q%d" % rng.randint(1, 50), "dimension": "d%d" % rng.randint(0, 3), "question": "q%d" % rng.randint(0, 20),
+                         "quality_score": rng.random(), "hard_triggered": rng.random() < 0.2} for _ in range(rng.choice([3, 40, 90]))]} for _ in range(64)]
+    limits = [rng.choice([2, 10, 30]) for _ in packs]
+    want = pf.select_slimmed_facts_batch(packs, limits)
+    ctx = _lib.Context.get()
+    fo, oo, q, fl, sg, dm, ky = [0], [0], [], [], [], [], []
+    for p, lim in zip(packs, limits):
+        a = pf.extract_fact_arrays(p, p["facts"])
+        q += a[0]; fl += a[1]; sg += a[2]; dm += a[3]; ky += a[4]
+        fo.append(len(q)); oo.append(oo[-1] + min(lim, len(p["facts"])))
+    host = [np.asarray(fo, np.int64), np.asarray(q, np.float64), np.asarray(fl, np.uint8), np.asarray(sg, np.int32), np.asarray(dm, np.int32),
+            np.asarray(ky, np.int64), np.asarray(limits, np.int32), np.asarray(oo, np.int64)]
+    dev = [torch.from_numpy(x).cuda() for x in host]
+    d_sel = torch.full((oo[-1],), -7, dtype=torch.int32, device="cuda"); d_cnt = torch.zeros(len(packs), dtype=torch.int32, device="cuda")
+    rc = ctx.lib.dvb_slim_facts(ctx.handle, _lib.MEM_DEVICE, len(packs), *[t.data_ptr() for t in dev], 6, 0.2, 1, 1, d_sel.data_ptr(), d_cnt.data_ptr())
+    ctx.check(rc, "dvb_slim_facts")
+    torch.cuda.synchronize()
+    sel, cnt = d_sel.cpu().numpy(), d_cnt.cpu().numpy()
+    for r, (p, w) in enumerate(zip(packs, want)):
+        got = [p["facts"][int(i)] for i in sel[oo[r]:oo[r] + int(cnt[r])]]
+        assert [id(x) for x in got] == [id(x) for x in w]
