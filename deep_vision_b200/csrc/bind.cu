@@ -88,19 +88,23 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     // ---- fast kernel (bind7.cuh): per-session capacity checks happen on the device (sess_fallback)
     const char* force = getenv("DVB_BIND_KERNEL");
     const bool fast = !(force && !strcmp(force, "general"));
-    const size_t smem7 = bind7_smem_bytes();
-    int grid7 = 1;
+    const size_t smem7 = bind7_smem_bytes(), smem7c = bind7_smem_bytes_claims();
+    int grid7 = 1, grid7c = 1;                                     // fact kernel (3 CTAs per SM), claim kernel (4)
     if (fast) {
-        static std::atomic<int> occ7_of[64];                       // per device: 0 = not asked yet
+        static std::atomic<int> occ7_of[64];                       // per device: 0 = not asked yet; fact occupancy | claim occupancy << 8
         const int dslot = ctx->device & 63;
         int occ7 = occ7_of[dslot].load();
         if (occ7 <= 0) {
-            DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+            int of = 1, oc = 1;
+            DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7c));
             DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
-            DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ7, k_bind_facts, BIND_THREADS, smem7));
-            if (occ7 < 1) occ7 = 1;
+            DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&of, k_bind_facts, BIND_THREADS, smem7));
+            DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&oc, k_bind_claim_tables, BIND_THREADS, smem7c));
+            occ7 = std::max(1, std::min(of, 255)) | (std::max(1, std::min(oc, 255)) << 8);
             occ7_of[dslot].store(occ7);
         }
+        grid7c = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * (occ7 >> 8));
+        occ7 &= 255;
         grid7 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ7);
     }
     // ---- workspace
@@ -118,7 +122,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (const char* e = getenv("DVB_BIND_SLAB_BUDGET")) { const long long v = atoll(e); if (v >= 1) slab_budget = v; }       // tests: force waves on small inputs
     const int64_t groups_bound = n_sessions + n_claims / BIND_CLAIMS;
     const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
-    if (fast) need += dvb_pad((size_t)grid7 * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
+    if (fast) need += dvb_pad((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
                     + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
@@ -173,7 +177,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             DVB_CUDA(ctx, cudaHostGetDevicePointer((void**)&l->flag_d, l->flag_h, 0));
         }
         *(volatile int*)l->flag_h = 0;
-        p7.gtable = sc.alloc<unsigned long long>((size_t)grid7 * bind7_ws_u64_per_cta());
+        p7.gtable = sc.alloc<unsigned long long>((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta());
         p7.sess_fallback = sc.alloc<uint8_t>((size_t)n_sessions);
         p7.sess_slab = sc.alloc<int32_t>((size_t)n_sessions);
         p7.slab_cursor = sc.alloc<int>(16);
@@ -222,9 +226,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             q.s_begin = a; q.s_end = b;
             cudaError_t e = cudaMemsetAsync(q.slab_cursor, 0, 4, st);
             if (e != cudaSuccess) return e;
-            const int g7 = (int)std::min<int64_t>(b - a, (int64_t)grid7);
-            k_bind_claim_tables<<<g7, BIND_THREADS, smem7, st>>>(q);
-            k_bind_facts<<<g7, BIND_THREADS, smem7, st>>>(q);
+            k_bind_claim_tables<<<(int)std::min<int64_t>(b - a, (int64_t)grid7c), BIND_THREADS, smem7c, st>>>(q);
+            k_bind_facts<<<(int)std::min<int64_t>(b - a, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
             ctx->launches += 2;
             if ((e = cudaGetLastError()) != cudaSuccess) return e;
             a = b;

@@ -21,6 +21,7 @@
 // Texts the cell walk cannot treat exactly (U+212A, a 0xC4 lead byte (U+0130), malformed UTF-8, tables too small)
 // raise sess_fallback[s]: the host re-runs exactly those sessions on k_bind_claims_general.
 #pragma once
+#include <stddef.h>
 #include "bind_common.cuh"
 #include "text.cuh"
 
@@ -87,7 +88,6 @@ static_assert(sizeof(B7Head) % 16 == 0, "copied as uint4s");
 
 struct __align__(16) B7Shared {
     uint32_t tab[B7_NB * 4];
-    uint8_t H[BIND_WARPS][B7_HSTRIDE];             // [0, B7_TCAP): facts: hit flags by token index; claims: "already listed" flags; then B7Scratch
     uint16_t tixT[B7_CAPT];                        // token-table slot -> t + 1
     uint16_t slist[B7_TCAP];                       // claim c's shared tokens at [rbase[c], rbase[c] + shc[c])
     B7Head hd;
@@ -95,8 +95,14 @@ struct __align__(16) B7Shared {
     uint8_t lut[128];
     int next_item, ntok, ovf, exotic, wcnt[BIND_WARPS];
     uint32_t wsum[BIND_WARPS], tsum[32];           // pack / unpack scans
-    int slab;
+    int slab, pad_[3];
+    // LAST member: the fact kernel uses all of it (per warp [0, B7_TCAP) hit flags by token index, then its B7Scratch); the claim
+    // kernel allocates only BIND_WARPS * B7_HSTRIDE_C bytes of it (per warp its B7Scratch, then B7_TCAP "already listed" BITS),
+    // which takes its CTA from 70.7 to 53.8 KB: four CTAs per SM instead of three (it needs 64 registers, no spills)
+    uint8_t H[BIND_WARPS][B7_HSTRIDE];
 };
+#define B7_HSTRIDE_C (1024 + B7_TCAP / 8)
+static_assert(offsetof(B7Shared, H) % 16 == 0 && B7_HSTRIDE_C % 16 == 0, "uint4 clears");
 // Slab of one claim group in the workspace (bytes): head | token bitmap | packed shared lists | packed token indices |
 // packed token keys | table entries | their slots.  Sections are sized for the kernel's own limits (B7_TCAP token indices,
 // B7_TOK_LIMIT token keys), so a group that passes the claim kernel always fits.
@@ -108,7 +114,7 @@ struct __align__(16) B7Shared {
 #define B7_BLOB_TABSLOT (B7_BLOB_TABENT + 4 * B7_TCAP)
 #define B7_BLOB_BYTES (B7_BLOB_TABSLOT + 2 * B7_TCAP)
 static_assert(sizeof(B7Head) <= B7_BLOB_TOKMAP && B7_BLOB_TOKKEY % 8 == 0 && B7_BLOB_TABENT % 16 == 0 && B7_BLOB_BYTES % 16 == 0, "slab layout");
-static_assert(sizeof(B7Scratch) <= B7_HSTRIDE - B7_TCAP, "the warp scratch lives behind the warp's flag bytes");
+static_assert(sizeof(B7Scratch) <= B7_HSTRIDE - B7_TCAP && sizeof(B7Scratch) <= 1024, "the warp scratch lives behind the warp's flag bytes");
 static_assert(sizeof(B7Shared) <= 76800, "three CTAs per SM");
 
 #ifdef DV_EMU
@@ -139,7 +145,7 @@ __device__ __forceinline__ void b7_sts8_if(bool c, b7_saddr a, uint32_t v) {
 #endif
 
 struct B7Tok {                       // per-warp tokenizer state (registers)
-    B7Shared* sh; unsigned long long* tkeys; uint8_t* H; B7Scratch* scr;
+    B7Shared* sh; unsigned long long* tkeys; uint8_t* H; uint32_t* hbits; B7Scratch* scr;   // H: fact kernel (flag bytes); hbits: claim kernel (flag bits)
     const uint8_t* base; int32_t a, total;          // text = bytes [a, total) from the 4-byte aligned base
     int lane, aqn, pqn;
     uint32_t rb, re; int own, shd;                  // claims: own token range [rb, re), counts
@@ -219,7 +225,10 @@ __device__ __forceinline__ void b7_claim_slot(B7Tok& t, bool act, uint32_t slot,
             DV_SPIN_PAUSE();
         }
         tt = (v & 0xFFFu) - 1u;
-        if ((tt < t.rb || tt >= t.re) && !t.H[tt]) { t.H[tt] = 1; isnew = true; }
+        if (tt < t.rb || tt >= t.re) {                             // another claim's token: listed once (test-and-set of its bit)
+            const uint32_t bit = 1u << (tt & 31u);
+            isnew = (atomicOr(&t.hbits[tt >> 5], bit) & bit) == 0u;
+        }
     }
     const uint32_t sm = __ballot_sync(B7_FULL, isnew);
     if (isnew) {
@@ -272,9 +281,9 @@ __device__ __forceinline__ void b7_bigram_insert(B7Tok& t, bool v, uint32_t id) 
 #else
 #define B7_NOINLINE __noinline__
 #endif
-__device__ B7_NOINLINE uint32_t b7_bigram_insert_ni(B7Shared* sh, uint8_t* H, int lane, uint32_t rb, uint32_t re, uint32_t own_shd, uint32_t vid) {
+__device__ B7_NOINLINE uint32_t b7_bigram_insert_ni(B7Shared* sh, uint32_t* hbits, int lane, uint32_t rb, uint32_t re, uint32_t own_shd, uint32_t vid) {
     B7Tok t;
-    t.sh = sh; t.H = H; t.lane = lane; t.rb = rb; t.re = re; t.own = (int)(own_shd & 0xFFFFu); t.shd = (int)(own_shd >> 16);
+    t.sh = sh; t.hbits = hbits; t.lane = lane; t.rb = rb; t.re = re; t.own = (int)(own_shd & 0xFFFFu); t.shd = (int)(own_shd >> 16);
     b7_bigram_insert(t, (vid >> 31) != 0u, vid & 0x7FFFFFFFu);
     return (uint32_t)t.own | ((uint32_t)t.shd << 16);
 }
@@ -575,7 +584,7 @@ __device__ void b7_text(B7Tok& t, const uint8_t* tx, int32_t n) {
             bool pend = v && p >= 2 && (p == 11 || !adn[i]);
             if (CLAIM) {
 #if B7_NI_INSERT
-                const uint32_t os = b7_bigram_insert_ni(t.sh, t.H, lane, t.rb, t.re, (uint32_t)t.own | ((uint32_t)t.shd << 16), (v ? 0x80000000u : 0u) | id);
+                const uint32_t os = b7_bigram_insert_ni(t.sh, t.hbits, lane, t.rb, t.re, (uint32_t)t.own | ((uint32_t)t.shd << 16), (v ? 0x80000000u : 0u) | id);
                 t.own = (int)(os & 0xFFFFu); t.shd = (int)(os >> 16);
 #else
                 b7_bigram_insert(t, v, id);
@@ -688,6 +697,7 @@ __device__ B7_NOINLINE int b7_exact_count(B7Shared& sh, B7Scratch* scr, int* wcn
 
 static inline size_t bind7_ws_u64_per_cta() { return (size_t)B7_CAPT; }
 static inline size_t bind7_smem_bytes() { return sizeof(B7Shared); }
+static inline size_t bind7_smem_bytes_claims() { return offsetof(B7Shared, H) + (size_t)BIND_WARPS * B7_HSTRIDE_C; }
 
 // ---------------------------------------------------------------- pack / unpack of a group's tables (all threads of the CTA)
 // Lane k of warp w owns word 32 w + k of a 256-word bitmap over the 8192 table slots; the slots of a word are read and
@@ -794,13 +804,18 @@ __device__ void b7_unpack(B7Shared& sh, unsigned long long* tkeys, const uint8_t
     __syncthreads();
 }
 
+template <bool CLAIMS>
 __device__ __forceinline__ void b7_cta_init(B7Shared& sh, B7Tok& t, unsigned long long* tkeys) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     dv_fill_ktab(sh.ktab);
     for (int b = tid; b < 128; b += BIND_THREADS) sh.lut[b] = (uint8_t)(dv_ascii_sym((uint32_t)b) & 0xFFu);
-    for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+    uint8_t* hbase = &sh.H[0][0];
+    const uint32_t hbytes = BIND_WARPS * (CLAIMS ? B7_HSTRIDE_C : B7_HSTRIDE);
+    for (uint32_t i = tid; i < hbytes / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(hbase)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
-    t.sh = &sh; t.tkeys = tkeys; t.H = sh.H[warp]; t.scr = reinterpret_cast<B7Scratch*>(sh.H[warp] + B7_TCAP); t.lane = lane;
+    t.sh = &sh; t.tkeys = tkeys; t.lane = lane;
+    if (CLAIMS) { t.H = nullptr; t.scr = reinterpret_cast<B7Scratch*>(hbase + warp * B7_HSTRIDE_C); t.hbits = reinterpret_cast<uint32_t*>(hbase + warp * B7_HSTRIDE_C + 1024); }
+    else { t.H = sh.H[warp]; t.hbits = nullptr; t.scr = reinterpret_cast<B7Scratch*>(sh.H[warp] + B7_TCAP); }
     t.base = nullptr; t.a = 0; t.total = 0; t.aqn = 0; t.pqn = 0; t.rb = 0; t.re = 0; t.own = 0; t.shd = 0; t.cert = false; t.exotic = false;
 }
 
@@ -808,12 +823,12 @@ __device__ __forceinline__ void b7_cta_init(B7Shared& sh, B7Tok& t, unsigned lon
 // Two kernels instead of one fused kernel: the SM's instruction fetch is the limiter of this code (profiles/README.md,
 // experiments/icache/): 24 warps streaming more than ~12 KB of code run at 2 instructions per clock per SM instead of 4, and
 // one CTA's claim phase (insert paths, 60 KB of code) used to run next to the fact walk of its two neighbours.
-__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claim_tables(BindParams p) {
+__global__ void __launch_bounds__(BIND_THREADS, 4) k_bind_claim_tables(BindParams p) {
     B7Shared& sh = B7_SH();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     B7Tok t;
-    b7_cta_init(sh, t, tkeys);
+    b7_cta_init<true>(sh, t, tkeys);
     for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
         if (c1 <= c0) continue;
@@ -856,7 +871,10 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claim_tables(BindParam
                 t.rb = sh.hd.rbase[c]; t.re = sh.hd.rbase[c + 1]; t.own = 0; t.shd = 0;
                 b7_text<true>(t, p.claim_utf8 + b, (int32_t)(e - b));
                 __syncwarp();
-                for (int j = lane; j < t.shd && t.rb + (uint32_t)j < t.re; j += 32) t.H[sh.slist[t.rb + j]] = 0;      // the "already listed" flags
+                for (int j = lane; j < t.shd && t.rb + (uint32_t)j < t.re; j += 32) {                                     // the "already listed" bits
+                    const uint32_t tt = sh.slist[t.rb + j];
+                    atomicAnd(&t.hbits[tt >> 5], ~(1u << (tt & 31u)));
+                }
                 if (lane == 0) { sh.hd.ownc[c] = (uint16_t)t.own; sh.hd.shc[c] = (uint16_t)t.shd; }
                 __syncwarp();
             }
@@ -869,9 +887,9 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_claim_tables(BindParam
         t.exotic = false;
         if (handback) {
             if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
-            // the H arrays may hold stale flags of an abandoned claim phase
+            // the "already listed" bits may be stale after an abandoned claim phase
             __syncthreads();
-            for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE_C / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
             __syncthreads();
         }
     }
@@ -883,7 +901,7 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     B7Tok t;
-    b7_cta_init(sh, t, tkeys);
+    b7_cta_init<false>(sh, t, tkeys);
     for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
         const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
