@@ -6,7 +6,7 @@ for lib in "$@"; do
   if [ "$lib" = default ]; then unset DVB_LIB; else export DVB_LIB=$PWD/$lib; fi
   echo "== $lib"
   timeout 120 python tools/prof_bind.py $n 3 2>&1 | tail -3
-  timeout 300 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,launch__registers_per_thread,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none -k regex:k_bind -s 1 -c 1 --csv --log-file gpurun_out/ab.csv python tools/prof_bind.py $n 2 > /dev/null 2>&1
+  timeout 300 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,launch__registers_per_thread,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none -k regex:k_bind_ -s 2 -c 2 --csv --log-file gpurun_out/ab.csv python tools/prof_bind.py $n 2 > /dev/null 2>&1
   grep -v "^==" gpurun_out/ab.csv | python -c "
 import csv,sys
 for r in list(csv.reader(sys.stdin))[1:]: print('   ', r[-3], r[-1])"

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Cost-ladder builds of the bind kernel: _ab/rung<n>.so = libdvb200 with bind.cu compiled -DB7_RUNG=n (bind7.cuh).
-# Only the fact side of k_bind_claims differs; rung 6 is the product.  Run tools/ladder_run.sh on the GPU box afterwards.
+# Only k_bind_facts differs (rungs stop its fact walk early); rung 6 is the product.  Run tools/ladder_run.sh on the GPU box afterwards.
 set -e
 cd "$(dirname "$0")/.."
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --fmad=true -Xcompiler -fPIC -Xcompiler -O2"
