@@ -592,8 +592,8 @@ static int32_t ix_build_segment(dvb_ctx* ctx, dvb_scope& sc, cudaStream_t st, in
             const int64_t nrb = (n_post + RS_TILE - 1) / RS_TILE;
             cudaFuncSetAttribute(k_ix_scatter1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
             k_ix_hist1<<<(unsigned)nrb, RS_THREADS, 0, st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, n_post, d_hist, nrb);
-            k_rs_scan<<<256, 1024, 0, st>>>(d_hist, nrb, dv_radix_totals_ptr(d_hist, n_post), 0);
-            k_rs_scan<<<256, 1024, 0, st>>>(d_hist, nrb, dv_radix_totals_ptr(d_hist, n_post), 1);
+            k_rs_scan<<<256, 1024, 0, st>>>(d_hist, nrb, dv_radix_totals_ptr(d_hist, n_post));
+            k_rs_base<<<1, 256, 0, st>>>(dv_radix_totals_ptr(d_hist, n_post), dv_radix_dbase_ptr(d_hist, n_post));
             k_ix_scatter1<<<(unsigned)nrb, RS_THREADS, sizeof(RsSmem), st>>>(sg->sym, sg->sym_off, sg->sym_cnt, n_chunks, d_po, n_post, t_pk, t_pv,
                                                                                d_hist, nrb, dv_radix_digits_ptr(d_hist, n_post));
             ctx->launches += 4;
