@@ -103,9 +103,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             occ7 = std::max(1, std::min(of, 255)) | (std::max(1, std::min(oc, 255)) << 8);
             occ7_of[dslot].store(occ7);
         }
-        grid7c = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * (occ7 >> 8));
+        grid7c = (int)std::min<int64_t>(n_sessions + n_claims / BIND_CLAIMS, (int64_t)ctx->num_sm * (occ7 >> 8));   // CTAs take claim groups
         occ7 &= 255;
-        grid7 = (int)std::min<int64_t>(n_sessions, (int64_t)ctx->num_sm * occ7);
+        grid7 = (int)std::min<int64_t>(n_sessions + n_claims / BIND_CLAIMS, (int64_t)ctx->num_sm * occ7);
     }
     // ---- workspace
     size_t need = 8192;
@@ -123,7 +123,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     const int64_t groups_bound = n_sessions + n_claims / BIND_CLAIMS;
     const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
     if (fast) need += dvb_pad((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
-                    + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
+                    + dvb_pad(4 * (size_t)n_slabs) + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
@@ -181,8 +181,9 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         p7.sess_fallback = sc.alloc<uint8_t>((size_t)n_sessions);
         p7.sess_slab = sc.alloc<int32_t>((size_t)n_sessions);
         p7.slab_cursor = sc.alloc<int>(16);
+        p7.slab_sess = sc.alloc<int32_t>((size_t)n_slabs);
         p7.slabs = sc.alloc<uint8_t>((size_t)n_slabs * B7_BLOB_BYTES);
-        if (!p7.gtable || !p7.sess_fallback || !p7.sess_slab || !p7.slab_cursor || !p7.slabs) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        if (!p7.gtable || !p7.sess_fallback || !p7.sess_slab || !p7.slab_cursor || !p7.slab_sess || !p7.slabs) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
         DVB_CUDA(ctx, cudaMemsetAsync(p7.sess_fallback, 0, (size_t)n_sessions, st));
         p7.overflow = l->flag_d;
     }
@@ -214,6 +215,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         }
         for (int64_t a = s0; a < s1;) {
             int64_t b = s1;
+            int64_t units = std::min<int64_t>(groups_bound, n_slabs);   // claim groups of [a, b): exact with host offsets, else the bound
             if (groups_bound > n_slabs) {                     // longest prefix of sessions whose groups fit
                 int64_t g = 0; b = a;
                 while (b < s1) {
@@ -222,14 +224,20 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
                     g += gs; b++;
                 }
                 if (b == a) return cudaErrorInvalidValue;     // one session with more groups than a wave holds (> 1 GB of tables)
+                units = g;
+            } else if (sco_h) {
+                units = 0;
+                for (int64_t x = a; x < b; x++) units += (sco_h[x + 1] - sco_h[x] + BIND_CLAIMS - 1) / BIND_CLAIMS;
             }
             q.s_begin = a; q.s_end = b;
-            cudaError_t e = cudaMemsetAsync(q.slab_cursor, 0, 4, st);
-            if (e != cudaSuccess) return e;
-            k_bind_claim_tables<<<(int)std::min<int64_t>(b - a, (int64_t)grid7c), BIND_THREADS, smem7c, st>>>(q);
-            k_bind_facts<<<(int)std::min<int64_t>(b - a, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
-            ctx->launches += 2;
-            if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            if (units > 0) {
+                k_bind_groups<<<1, B7_GROUPS_THREADS, 0, st>>>(q);
+                k_bind_claim_tables<<<(int)std::min<int64_t>(units, (int64_t)grid7c), BIND_THREADS, smem7c, st>>>(q);
+                k_bind_facts<<<(int)std::min<int64_t>(units, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
+                ctx->launches += 3;
+                const cudaError_t e = cudaGetLastError();
+                if (e != cudaSuccess) return e;
+            }
             a = b;
         }
         return cudaSuccess;

@@ -819,6 +819,51 @@ __device__ __forceinline__ void b7_cta_init(B7Shared& sh, B7Tok& t, unsigned lon
     t.base = nullptr; t.a = 0; t.total = 0; t.aqn = 0; t.pqn = 0; t.rb = 0; t.re = 0; t.own = 0; t.shd = 0; t.cert = false; t.exotic = false;
 }
 
+// ---------------------------------------------------------------- kernel 0: numbering of the claim groups
+// One CTA.  The unit of work of the two kernels below is a claim GROUP (<= 32 claims of one session), not a session: 2000
+// sessions over 592 resident CTAs are 3.4 rounds of which the slowest CTA runs 4; their 8000 groups are 13.5 of which it runs 14.
+// sess_slab[s] = groups in front of session s (in [s_begin, s_end)), slab_sess[u] = session of group u, *slab_cursor = groups.
+#define B7_GROUPS_THREADS 1024
+#define B7_GROUPS_PER_THREAD 4
+__global__ void __launch_bounds__(B7_GROUPS_THREADS) k_bind_groups(BindParams p) {
+    __shared__ uint32_t wtot[B7_GROUPS_THREADS / 32];
+    __shared__ uint32_t carry;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int64_t s0 = p.s_begin; s0 < p.s_end; s0 += B7_GROUPS_THREADS * B7_GROUPS_PER_THREAD) {
+        const int64_t sa = s0 + (int64_t)tid * B7_GROUPS_PER_THREAD;          // this thread: sessions sa .. sa + 3
+        uint32_t ng[B7_GROUPS_PER_THREAD], mine = 0;
+#pragma unroll
+        for (int k = 0; k < B7_GROUPS_PER_THREAD; k++) {
+            ng[k] = 0;
+            if (sa + k < p.s_end) {
+                const int64_t nc = p.sess_claim_off[sa + k + 1] - p.sess_claim_off[sa + k];
+                ng[k] = nc > 0 ? (uint32_t)((nc + BIND_CLAIMS - 1) / BIND_CLAIMS) : 0u;
+            }
+            mine += ng[k];
+        }
+        uint32_t tot;
+        const uint32_t excl = b7_excl_scan32(mine, lane, tot);
+        if (lane == 0) wtot[warp] = tot;
+        __syncthreads();
+        uint32_t base = carry + excl;
+        for (int w = 0; w < warp; w++) base += wtot[w];
+#pragma unroll
+        for (int k = 0; k < B7_GROUPS_PER_THREAD; k++) {
+            if (sa + k < p.s_end) {
+                p.sess_slab[sa + k] = (int32_t)base;
+                for (uint32_t g = 0; g < ng[k]; g++) p.slab_sess[base + g] = (int32_t)(sa + k);
+            }
+            base += ng[k];
+        }
+        __syncthreads();
+        if (tid == B7_GROUPS_THREADS - 1) carry = base;
+        __syncthreads();
+    }
+    if (tid == 0) *p.slab_cursor = (int)carry;
+}
+
 // ---------------------------------------------------------------- kernel 1 of 2: the claims of every group -> tables -> slab
 // Two kernels instead of one fused kernel: the SM's instruction fetch is the limiter of this code (profiles/README.md,
 // experiments/icache/): 24 warps streaming more than ~12 KB of code run at 2 instructions per clock per SM instead of 4, and
@@ -829,16 +874,13 @@ __global__ void __launch_bounds__(BIND_THREADS, 4) k_bind_claim_tables(BindParam
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     B7Tok t;
     b7_cta_init<true>(sh, t, tkeys);
-    for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
+    const int n_units = *p.slab_cursor;
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+        const int64_t s = p.slab_sess[u];
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
-        if (c1 <= c0) continue;
-        const int ngroups = (int)((c1 - c0 + BIND_CLAIMS - 1) / BIND_CLAIMS);
-        __syncthreads();
-        if (tid == 0) { sh.slab = atomicAdd(p.slab_cursor, ngroups); p.sess_slab[s] = sh.slab; }
-        __syncthreads();
-        const int slab0 = sh.slab;
         bool handback = false;
-        for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
+        do {
+            const int64_t cg = c0 + (int64_t)(u - p.sess_slab[s]) * BIND_CLAIMS;
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
             // ---- clear tables, token-index ranges of the claims
             for (uint32_t i = tid; i < B7_NB; i += BIND_THREADS) reinterpret_cast<uint4*>(sh.tab)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -881,12 +923,12 @@ __global__ void __launch_bounds__(BIND_THREADS, 4) k_bind_claim_tables(BindParam
             if (__any_sync(B7_FULL, t.exotic)) sh.exotic = 1;
             __syncthreads();
             if (sh.ovf || sh.exotic) { handback = true; break; }      // uniform; the next writers are behind the barrier of the pack
-            b7_pack(sh, tkeys, p.slabs + (size_t)(slab0 + (int)((cg - c0) / BIND_CLAIMS)) * B7_BLOB_BYTES, ncg);
+            b7_pack(sh, tkeys, p.slabs + (size_t)u * B7_BLOB_BYTES, ncg);
             __syncthreads();
-        }
+        } while (0);
         t.exotic = false;
         if (handback) {
-            if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
+            if (tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; p.slab_sess[u] = (int32_t)(-1 - s); }     // every thread read slab_sess[u] before the barriers above
             // the "already listed" bits may be stale after an abandoned claim phase
             __syncthreads();
             for (uint32_t i = tid; i < BIND_WARPS * B7_HSTRIDE_C / 16; i += BIND_THREADS) reinterpret_cast<uint4*>(&sh.H[0][0])[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -902,17 +944,21 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     B7Tok t;
     b7_cta_init<false>(sh, t, tkeys);
-    for (int64_t s = p.s_begin + blockIdx.x; s < p.s_end; s += gridDim.x) {
+    const int n_units = *p.slab_cursor;
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+        // a group the claim kernel handed back has no tables (its session number is stored negated); nothing writes slab_sess
+        // in this kernel, so the branch is uniform.  The other groups of such a session are scored here and again by the general kernel
+        if (p.slab_sess[u] < 0) continue;
+        const int64_t s = p.slab_sess[u];
         const int64_t c0 = p.sess_claim_off[s], c1 = p.sess_claim_off[s + 1];
         const int64_t f0 = p.sess_fact_off[s], f1 = p.sess_fact_off[s + 1];
-        if (c1 <= c0 || p.sess_fallback[s]) continue;                 // uniform
-        const int slab0 = p.sess_slab[s];
         bool handback = false;
-        for (int64_t cg = c0; cg < c1 && !handback; cg += BIND_CLAIMS) {
+        {
+            const int64_t cg = c0 + (int64_t)(u - p.sess_slab[s]) * BIND_CLAIMS;
             const int ncg = (int)min((int64_t)BIND_CLAIMS, c1 - cg);
             // no barrier here: behind the barrier that ends the previous fact phase only warp 0 still works (the reduction),
             // on registers and the warps' scratch, which nothing writes before the two barriers of the unpack
-            b7_unpack(sh, tkeys, p.slabs + (size_t)(slab0 + (int)((cg - c0) / BIND_CLAIMS)) * B7_BLOB_BYTES, ncg);
+            b7_unpack(sh, tkeys, p.slabs + (size_t)u * B7_BLOB_BYTES, ncg);
             // ---- one warp per fact
             double best = -1.0; int best_f = 0x7fffffff;              // lane c (< ncg) tracks claim c
             const uint32_t rb = lane < ncg ? sh.hd.rbase[lane] : 0u;

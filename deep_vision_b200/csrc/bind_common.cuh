@@ -32,8 +32,9 @@ struct BindParams {
     uint8_t* sess_fallback;               // fast kernel: sess_fallback[s] = 1 -> session s must be scored by the general kernel
     const uint8_t* only_flagged;          // general kernel: when non-null, score only sessions with only_flagged[s] != 0
     uint8_t* slabs;                       // fast kernels: one slab of B7_BLOB_BYTES per claim group (claim kernel -> fact kernel)
-    int* slab_cursor;                     // fast kernels: next free slab of this launch pair
+    int* slab_cursor;                     // fast kernels: claim groups (= slabs in use) of this launch
     int32_t* sess_slab;                   // fast kernels: first slab of session s
+    int32_t* slab_sess;                   // fast kernels: session of slab u (-1 - s once the claim kernel handed the group back)
 };
 
 __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {

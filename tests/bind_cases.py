@@ -103,6 +103,29 @@ def token_table_overflow():
                  np.zeros(len(facts)), np.full(len(claims), -1), np.full(len(claims), 0.46))
 
 
+def handback_in_one_group():
+    """Sessions of several claim groups (the unit of work of the fast kernels) in which ONE group is handed back: session 0 by
+    the claim kernel (U+0130 in a claim of its third group), session 1 by the fact kernel (U+212A in a fact), session 2 not at
+    all.  The whole session goes to the general kernel; the groups the fast kernels did score are rewritten by it."""
+    import random
+    rng = random.Random(77)
+    han = [chr(0x4E00 + rng.randrange(2000)) for _ in range(300)]
+    def cjk(n): return "".join(rng.choice(han) for _ in range(n))
+    claims, facts, sco, sfo = [], [], [0], [0]
+    for s_ in range(3):
+        fs = [cjk(rng.randint(20, 200)) + " abc" + str(rng.randrange(50)) for _ in range(30)]
+        cs = []
+        for _ in range(100):                               # four groups: 32 + 32 + 32 + 4
+            f = rng.choice(fs); i = rng.randrange(len(f) - 12)
+            cs.append(f[i:i + rng.randint(4, 12)] + cjk(3))
+        if s_ == 0: cs[70] = cs[70] + "\u0130"
+        if s_ == 1: fs[11] = fs[11][:9] + "\u212a" + fs[11][9:]
+        claims += cs; facts += fs; sco.append(len(claims)); sfo.append(len(facts))
+    nf, nc = len(facts), len(claims)
+    return _pack(claims, facts, sco, sfo, np.linspace(0.05, 0.95, nf), np.arange(nf) % 4, np.arange(nf) % 3 == 0,
+                 np.arange(nc) % 5 - 1, np.full(nc, 0.3))
+
+
 def degenerate():
     """sessions without claims / without facts; empty and white-space-only claim and fact texts"""
     claims = ["", "   ", "\u9884\u7b97\u6709\u9650 budget_2024", "\uff0c\u3002\uff1b", "a", "\u5ba1\u6279\u6d41\u7a0b\u592a\u6162\u9700\u8981\u4f18\u5316"]

@@ -43,9 +43,10 @@ extern "C" int emu_bind_claims(const uint8_t* claim_utf8, const int64_t* claim_o
         int64_t n_groups = 0;
         for (int64_t s = 0; s < n_sessions; s++) n_groups += (sess_claim_off[s + 1] - sess_claim_off[s] + BIND_CLAIMS - 1) / BIND_CLAIMS;
         std::vector<unsigned long long> slabs(((size_t)n_groups * B7_BLOB_BYTES + 7) / 8 + 1);
-        std::vector<int32_t> sess_slab((size_t)n_sessions);
+        std::vector<int32_t> sess_slab((size_t)n_sessions), slab_sess((size_t)n_groups + 1);
         int cursor = 0;
-        p.slabs = reinterpret_cast<uint8_t*>(slabs.data()); p.slab_cursor = &cursor; p.sess_slab = sess_slab.data();
+        p.slabs = reinterpret_cast<uint8_t*>(slabs.data()); p.slab_cursor = &cursor; p.sess_slab = sess_slab.data(); p.slab_sess = slab_sess.data();
+        emu::launch(1u, B7_GROUPS_THREADS, [&] { k_bind_groups(p); });
         emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_claim_tables(p); });
         emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_facts(p); });
     }

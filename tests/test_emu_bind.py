@@ -54,6 +54,7 @@ def test_emu_handbacks(emu, oracle):
     _check(emu, oracle, bc.token_table_overflow(), expect_handback=1)        # > 704 ASCII tokens in a claim group
     _check(emu, oracle, bc.big_claim_groups(), expect_handback=2)            # token ranges beyond the flag array
     _check(emu, oracle, bc.long_facts(1), expect_handback=1)                 # U+0130 / U+212A inside
+    _check(emu, oracle, bc.handback_in_one_group(), expect_handback=2, grid=3)   # one group of four, from the claim and from the fact side
 
 
 def test_emu_crowded_bucket_side_list(emu, oracle):

@@ -151,6 +151,15 @@ def test_a2_general_kernel_same_results(gpu_ctx, oracle, monkeypatch):
     assert np.array_equal(gen["best_score"].view(np.uint64), ref["best_score"].view(np.uint64))
 
 
+def test_a2_one_group_of_a_session_handed_back(gpu_ctx, oracle):
+    """The fast kernels take claim GROUPS as their unit of work (k_bind_groups numbers them): sessions of four groups where
+    one group is handed back by the claim kernel, or the session by the fact kernel, come out as the oracle has them."""
+    import bind_cases as bc
+    l0 = gpu_ctx.launches
+    _bind_vs_oracle(gpu_ctx, oracle, bc.handback_in_one_group())
+    assert gpu_ctx.launches - l0 == 4                               # groups, claim tables, facts, general kernel for the two sessions
+
+
 def test_a2_token_table_overflow_reruns_general(gpu_ctx, oracle):
     """> 704 distinct ASCII tokens in one claim group: the fast kernel raises `overflow`, the call re-runs exactly."""
     from deep_vision_b200 import packing

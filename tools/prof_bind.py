@@ -8,7 +8,10 @@ from deep_vision_b200 import _lib, synth
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-c = synth.make_sessions(n, seed=synth.SEED)
+kw = {}
+if len(sys.argv) > 3: kw["claims_per_session"] = int(sys.argv[3])          # > 32: several claim groups per session
+if len(sys.argv) > 4: kw["turns"] = int(sys.argv[4])
+c = synth.make_sessions(n, seed=synth.SEED, **kw)
 ctx = _lib.Context.get(0)
 host = [c.claim_utf8, c.claim_off, c.fact_utf8, c.fact_off, c.sess_claim_off, c.sess_fact_off, c.fact_quality, c.fact_dim,
         c.fact_hard, c.claim_pref_dim, c.claim_threshold]
