@@ -45,6 +45,7 @@ extern "C" void dvb_destroy(dvb_ctx* c) {
         if (c->leases[i].copy) { cudaStreamSynchronize(c->leases[i].copy); cudaStreamDestroy(c->leases[i].copy); }
         for (cudaEvent_t e : c->leases[i].pipe_ev) cudaEventDestroy(e);
         if (c->leases[i].flag_h) cudaFreeHost(c->leases[i].flag_h);
+        if (c->leases[i].small_h) cudaFreeHost(c->leases[i].small_h);
         if (c->leases[i].bounce) { cudaFreeHost(c->leases[i].bounce); for (cudaEvent_t e : c->leases[i].bounce_ev) if (e) cudaEventDestroy(e); }
         if (c->leases[i].arena.base) cudaFree(c->leases[i].arena.base);
         for (void* b : c->leases[i].overflow) cudaFree(b);

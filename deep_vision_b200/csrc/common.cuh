@@ -30,6 +30,7 @@ struct dvb_lease {
     std::vector<cudaEvent_t> pipe_ev;    // one per in-flight input slice
     int* flag_h = nullptr;               // pinned + mapped word a kernel can raise (read by the host after the stream sync)
     int* flag_d = nullptr;
+    uint8_t* small_h = nullptr;          // pinned 2 x DVB_SMALL_STAGE bytes: all inputs / all outputs of a small host-buffer call in ONE copy each
     uint8_t* bounce = nullptr;           // pinned staging of large PAGEABLE inputs: DVB_H2D_THREADS x DVB_H2D_CHUNK bytes (first use)
     cudaEvent_t bounce_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool busy = false;
@@ -144,6 +145,7 @@ static inline size_t dvb_pad(size_t bytes) { return (bytes + 255 + 64) & ~size_t
 // Here DVB_H2D_THREADS host threads copy alternate 2 MB chunks into pinned buffers of the lease and queue the DMA of each
 // chunk on the call's stream, so the host memcpy of one chunk overlaps the DMA of the others.  Returns after every chunk
 // has left its bounce buffer (the stream still orders later kernels behind the copies).
+#define DVB_SMALL_STAGE (size_t(256) << 10)
 #define DVB_H2D_THREADS 8
 #define DVB_H2D_CHUNK (size_t(2) << 20)
 #define DVB_H2D_MIN (size_t(8) << 20)
