@@ -154,7 +154,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         const size_t in_span = (size_t)(reinterpret_cast<uint8_t*>(d_ct + n_claims) - d_cu);
         const size_t out_span = (size_t)(reinterpret_cast<uint8_t*>(d_lf + n_facts) - reinterpret_cast<uint8_t*>(d_best));
         if (reinterpret_cast<uint8_t*>(d_ct) > d_cu && reinterpret_cast<uint8_t*>(d_lf) > reinterpret_cast<uint8_t*>(d_best)
-            && in_span <= DVB_SMALL_STAGE && out_span <= DVB_SMALL_STAGE && !getenv("DVB_NO_SMALL_STAGE")) {
+            && in_span <= DVB_SMALL_STAGE && out_span <= DVB_SMALL_STAGE && sc.in_arena(d_cu, in_span) && sc.in_arena(d_best, out_span)
+            && !getenv("DVB_NO_SMALL_STAGE")) {
             dvb_lease* l = sc.l;
             if (!l->small_h && cudaHostAlloc((void**)&l->small_h, 2 * DVB_SMALL_STAGE, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); l->small_h = nullptr; }
             small_h = l->small_h;

@@ -122,6 +122,11 @@ struct dvb_scope {
         l->arena.cap = want;
         return DVB_OK;
     }
+    // [p, p + bytes) lies in the arena block (not in a one-off overflow block): ranges between two such pointers are one allocation
+    bool in_arena(const void* p, size_t bytes) const {
+        const uint8_t* a = reinterpret_cast<const uint8_t*>(p); const uint8_t* base = reinterpret_cast<const uint8_t*>(l->arena.base);
+        return base && a >= base && a + bytes <= base + l->arena.cap;
+    }
     template <typename T> T* alloc(size_t n) {
         size_t bytes = (n * sizeof(T) + 255 + 64) & ~size_t(255);
         call_bytes += bytes;
@@ -199,13 +204,32 @@ struct dvb_io {
     dvb_scope& sc; int mem; cudaStream_t st; cudaError_t err = cudaSuccess; bool oom = false;
     struct Out { void* host; void* dev; size_t bytes; };
     std::vector<Out> outs;
-    dvb_io(dvb_scope& s, int m) : sc(s), mem(m), st(s.stream()) {}
+    // Small host arrays (a one-report call is a handful of arrays of a few hundred bytes) are gathered in the lease's pinned block
+    // at the offsets their device copies have in the workspace and cross PCIe as ONE copy at check(); the outputs come back the
+    // same way in finish().  A driver copy from pageable memory costs ~6 us whatever its size.  `coalesce` = false: every array
+    // is copied where in() is called (entry points that launch between their in() calls).
+    bool coalesce; uint8_t* stage = nullptr; uint8_t* first = nullptr; size_t span = 0;
+    dvb_io(dvb_scope& s, int m, bool coalesce_small = true) : sc(s), mem(m), st(s.stream()), coalesce(coalesce_small && m == DVB_MEM_HOST) {}
+    uint8_t* stage_block() {
+        dvb_lease* l = sc.l;
+        if (!l->small_h && cudaHostAlloc((void**)&l->small_h, 2 * DVB_SMALL_STAGE, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); l->small_h = nullptr; }
+        return l->small_h;
+    }
     template <typename T> const T* in(const T* p, size_t n) {
         if (mem == DVB_MEM_DEVICE || !p) return p;
         T* d = sc.alloc<T>(n ? n : 1);
         if (!d) { oom = true; return nullptr; }
         if (n) {
             const size_t bytes = n * sizeof(T);
+            if (coalesce && bytes <= DVB_SMALL_STAGE && sc.in_arena(d, bytes) && (stage || (stage = stage_block()))) {
+                if (!first) first = reinterpret_cast<uint8_t*>(d);
+                const ptrdiff_t o = reinterpret_cast<uint8_t*>(d) - first;
+                if (o >= 0 && (size_t)o + bytes <= DVB_SMALL_STAGE) {
+                    memcpy(stage + o, p, bytes);
+                    span = std::max(span, (size_t)o + bytes);
+                    return d;
+                }
+            }
             cudaError_t e = (bytes >= DVB_H2D_MIN && dvb_is_pageable(p)) ? dvb_h2d_staged(sc.l, sc.ctx->device, d, p, bytes, st)
                                                                          : cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, st);
             if (e != cudaSuccess) err = e;
@@ -220,16 +244,34 @@ struct dvb_io {
         return d;
     }
     template <typename T> T* tmp(size_t n) { T* d = sc.alloc<T>(n ? n : 1); if (!d) oom = true; return d; }
+    // the gathered inputs go out; from here on in() copies directly (the pinned block is in flight until the stream is synchronised)
+    void flush() {
+        if (span) { const cudaError_t e = cudaMemcpyAsync(first, stage, span, cudaMemcpyHostToDevice, st); if (e != cudaSuccess) err = e; }
+        span = 0; coalesce = false;
+    }
     int32_t check(dvb_ctx* ctx) {
+        flush();
         if (oom) { dvb_set_err(ctx, "out of device memory%s%s"); return DVB_E_NOMEM; }
         if (err != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s while staging arguments%s", cudaGetErrorString(err)); return DVB_E_CUDA; }
         return DVB_OK;
     }
     int32_t finish(dvb_ctx* ctx) {
         cudaError_t e = cudaGetLastError();
-        for (auto& o : outs) if (o.bytes && e == cudaSuccess) e = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, st);
+        // outputs that lie within DVB_SMALL_STAGE bytes of each other in the workspace: one copy into the pinned block
+        uint8_t *lo = nullptr, *hi = nullptr; bool arena_only = true;
+        for (auto& o : outs) if (o.bytes) {
+            uint8_t* a = reinterpret_cast<uint8_t*>(o.dev);
+            arena_only = arena_only && sc.in_arena(a, o.bytes);
+            if (!lo || a < lo) lo = a;
+            if (!hi || a + o.bytes > hi) hi = a + o.bytes;
+        }
+        if (!stage && mem == DVB_MEM_HOST && outs.size() > 1) stage = stage_block();
+        const bool one = stage && lo && arena_only && outs.size() > 1 && (size_t)(hi - lo) <= DVB_SMALL_STAGE;
+        if (one) { if (e == cudaSuccess) e = cudaMemcpyAsync(stage + DVB_SMALL_STAGE, lo, (size_t)(hi - lo), cudaMemcpyDeviceToHost, st); }
+        else for (auto& o : outs) if (o.bytes && e == cudaSuccess) e = cudaMemcpyAsync(o.host, o.dev, o.bytes, cudaMemcpyDeviceToHost, st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s at finish%s", cudaGetErrorString(e)); return DVB_E_CUDA; }
+        if (one) for (auto& o : outs) if (o.bytes) memcpy(o.host, stage + DVB_SMALL_STAGE + (reinterpret_cast<uint8_t*>(o.dev) - lo), o.bytes);
         return DVB_OK;
     }
 };
