@@ -399,7 +399,7 @@ def measured_peak():
 
 
 def ncu_traffic():
-    """dram bytes per dvb_bind_claims call (k_bind_claim_tables + k_bind_facts) from the committed ncu --set full capture, if any."""
+    """dram bytes per dvb_bind_claims call (k_bind_groups + k_bind_claim_tables + k_bind_facts) from the committed ncu --set full capture, if any."""
     p = ROOT / "profiles" / "bind_traffic.json"
     if p.exists():
         try:
@@ -670,7 +670,7 @@ def main():
                         "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": ncu_traffic(), "kernel": "k_bind_claim_tables + k_bind_facts (one dvb_bind_claims call)", "kernel_ms": k_ms,
+                             "traffic": ncu_traffic(), "kernel": "k_bind_groups + k_bind_claim_tables + k_bind_facts (one dvb_bind_claims call)", "kernel_ms": k_ms,
                              "algorithmic_bytes_per_launch": corpus.algorithmic_bytes,
                              "bytes_per_pair": corpus.algorithmic_bytes / corpus.n_pairs, "peak_source": peak_src,
                              "limiter": "instruction issue / ALU pipe, not DRAM: 2.6 warp instructions per input byte; the fused kernel was bound by "
