@@ -452,11 +452,36 @@ def run_reference(args, rank, world):
             "config": workload_config(args, world),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
+
+
+_LINE_FD = None
+
+
+def quiet_stdout():
+    """stdout carries ONE line, the JSON line of rank 0: anything a library prints meanwhile (NCCL announces its version on
+    stdout when the box sets NCCL_DEBUG) goes to stderr.  File descriptor 1 is pointed at stderr for the run; emit_line()
+    writes to the saved descriptor."""
+    global _LINE_FD
+    if _LINE_FD is None:
+        sys.stdout.flush()
+        _LINE_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _LINE_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+        return
+    sys.stdout.flush()
+    while data:
+        data = data[os.write(_LINE_FD, data):]
 
 
 def main():
     args = parse_args()
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -702,7 +727,7 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": "all %d sessions (%d pairs) x %d passes, %.1f s wall, oracle C port of web/server.py:24780-24864, %d threads"
                                               % (corpus.n_sessions, corpus.n_pairs, passes, secs, cores)}
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
