@@ -126,6 +126,25 @@ def handback_in_one_group():
                  np.arange(nc) % 5 - 1, np.full(nc, 0.3))
 
 
+def many_tiny_sessions(n=4300):
+    """More sessions than one step of k_bind_groups numbers (4096): sessions of one short claim and one fact, every 97th
+    without claims, every 211th with 33 claims (two groups), so the running group count is carried across the steps."""
+    import random
+    rng = random.Random(1)
+    han = [chr(0x4E00 + rng.randrange(500)) for _ in range(100)]
+    def cjk(k): return "".join(rng.choice(han) for _ in range(k))
+    claims, facts, sco, sfo = [], [], [0], [0]
+    for s_ in range(n):
+        nc = 0 if s_ % 97 == 5 else (33 if s_ % 211 == 0 else 1)
+        f = cjk(8)
+        for _ in range(nc):
+            claims.append(f[rng.randrange(4):][:5] + cjk(1))
+        facts.append(f); sco.append(len(claims)); sfo.append(len(facts))
+    nf, nc = len(facts), len(claims)
+    return _pack(claims, facts, sco, sfo, np.linspace(0.05, 0.95, nf), np.arange(nf) % 4, np.arange(nf) % 3 == 0,
+                 np.arange(nc) % 5 - 1, np.full(nc, 0.3))
+
+
 def degenerate():
     """sessions without claims / without facts; empty and white-space-only claim and fact texts"""
     claims = ["", "   ", "\u9884\u7b97\u6709\u9650 budget_2024", "\uff0c\u3002\uff1b", "a", "\u5ba1\u6279\u6d41\u7a0b\u592a\u6162\u9700\u8981\u4f18\u5316"]

@@ -57,6 +57,10 @@ def test_emu_handbacks(emu, oracle):
     _check(emu, oracle, bc.handback_in_one_group(), expect_handback=2, grid=3)   # one group of four, from the claim and from the fact side
 
 
+def test_emu_group_numbering_across_steps(emu, oracle):
+    _check(emu, oracle, bc.many_tiny_sessions(), expect_handback=0, grid=7)  # k_bind_groups: 4300 sessions > one 4096-session step
+
+
 def test_emu_crowded_bucket_side_list(emu, oracle):
     _check(emu, oracle, bc.crowded_bucket(5), expect_handback=0)             # one key in the side list
     _check(emu, oracle, bc.crowded_bucket(30), expect_handback=0)            # 26 keys in the side list

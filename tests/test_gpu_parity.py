@@ -160,6 +160,12 @@ def test_a2_one_group_of_a_session_handed_back(gpu_ctx, oracle):
     assert gpu_ctx.launches - l0 == 4                               # groups, claim tables, facts, general kernel for the two sessions
 
 
+def test_a2_group_numbering_across_steps(gpu_ctx, oracle):
+    """4300 sessions (> one 4096-session step of k_bind_groups), some without claims, some of two groups."""
+    import bind_cases as bc
+    _bind_vs_oracle(gpu_ctx, oracle, bc.many_tiny_sessions())
+
+
 def test_a2_token_table_overflow_reruns_general(gpu_ctx, oracle):
     """> 704 distinct ASCII tokens in one claim group: the fast kernel raises `overflow`, the call re-runs exactly."""
     from deep_vision_b200 import packing
