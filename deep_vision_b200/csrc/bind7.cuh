@@ -94,8 +94,9 @@ struct __align__(16) B7Shared {
     unsigned long long ktab[DV_KTAB];
     uint8_t lut[128];
     int next_item, ntok, ovf, exotic, wcnt[BIND_WARPS];
-    uint32_t wsum[BIND_WARPS], tsum[32];           // pack / unpack scans
-    int slab, pad_[3];
+    uint32_t tsum[32];                             // pack: token keys per 32-slot word
+    uint32_t nent, pad_;                           // claim kernel: bigram-table entries created so far in this group
+    uint16_t* oslot;                               // claim kernel: their slots, appended to the group's slab as they are created
     // LAST member: the fact kernel uses all of it (per warp [0, B7_TCAP) hit flags by token index, then its B7Scratch); the claim
     // kernel allocates only BIND_WARPS * B7_HSTRIDE_C bytes of it (per warp its B7Scratch, then B7_TCAP "already listed" BITS),
     // which takes its CTA from 70.7 to 53.8 KB: four CTAs per SM instead of three (it needs 64 registers, no spills)
@@ -270,6 +271,10 @@ __device__ __forceinline__ void b7_bigram_insert(B7Tok& t, bool v, uint32_t id) 
     if (leader) {
         slot = b7_bigram_slot(sh, id, true, created);
         if (slot < 0) sh.ovf = 1;
+        else if (created && !((uint32_t)slot & B7_SLOT_STASH)) {      // b7_pack walks this list instead of scanning the 8192 slots
+            const uint32_t n = atomicAdd(&sh.nent, 1u);
+            if (n < B7_TCAP) sh.oslot[n] = (uint16_t)slot; else sh.ovf = 1;      // cannot happen: every created entry takes a token index
+        }
     }
     b7_claim_slot(t, slot >= 0, (uint32_t)slot, created);
 }
@@ -718,16 +723,10 @@ __device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* 
     uint16_t* o_tix = reinterpret_cast<uint16_t*>(slab + B7_BLOB_TOKTIX);
     unsigned long long* o_key = reinterpret_cast<unsigned long long*>(slab + B7_BLOB_TOKKEY);
     uint32_t* o_ent = reinterpret_cast<uint32_t*>(slab + B7_BLOB_TABENT);
-    // ---- table: bitmap word per lane, then the entries
-    uint32_t myword = 0;
-#pragma unroll 4
-    for (int k = 0; k < 32; k++) {
-        const uint32_t wd = __ballot_sync(B7_FULL, sh.tab[(uint32_t)(32 * warp + k) * 32u + (uint32_t)lane] != 0u);
-        if (lane == k) myword = wd;
-    }
-    uint32_t wtot;
-    const uint32_t ex = b7_excl_scan32((uint32_t)__popc(myword), lane, wtot);
-    if (lane == 0) sh.wsum[warp] = wtot;
+    // ---- table: the slots of the entries are in the slab already (appended by their creators, in no particular order; the
+    // barrier in front of this call made them visible); their entries go next to them
+    const uint32_t ntab = min(sh.nent, (uint32_t)B7_TCAP);
+    for (uint32_t i = tid; i < ntab; i += BIND_THREADS) o_ent[i] = sh.tab[o_slot[i]];
     // ---- token keys: warp w owns words 4 w .. 4 w + 3 of the 32-word bitmap over the 1024 key slots
     uint32_t tw[4];
 #pragma unroll
@@ -736,15 +735,6 @@ __device__ void b7_pack(B7Shared& sh, const unsigned long long* tkeys, uint8_t* 
         if (lane == 0) sh.tsum[4 * warp + k] = (uint32_t)__popc(tw[k]);
     }
     __syncthreads();
-    uint32_t wbase = 0, ntab = 0;
-    for (int w = 0; w < BIND_WARPS; w++) { if (w < warp) wbase += sh.wsum[w]; ntab += sh.wsum[w]; }
-#pragma unroll 4
-    for (int k = 0; k < 32; k++) {
-        const uint32_t wd = __shfl_sync(B7_FULL, myword, k), base = wbase + __shfl_sync(B7_FULL, ex, k);
-        const uint32_t slot = (uint32_t)(32 * warp + k) * 32u + (uint32_t)lane;
-        const uint32_t v = sh.tab[slot];
-        if (v) { const uint32_t o = base + (uint32_t)__popc(wd & lt); o_ent[o] = v; o_slot[o] = (uint16_t)slot; }
-    }
     uint32_t tbase = 0, ntok = 0;
     for (int j = 0; j < 32; j++) { if (j < 4 * warp) tbase += sh.tsum[j]; ntok += sh.tsum[j]; }
 #pragma unroll
@@ -897,7 +887,10 @@ __global__ void __launch_bounds__(BIND_THREADS, 4) k_bind_claim_tables(BindParam
                 uint32_t tot;
                 const uint32_t excl = b7_excl_scan32(bound, lane, tot);
                 if (tot <= B7_TCAP) { sh.hd.rbase[lane + 1] = (uint16_t)(excl + bound); if (lane == 0) sh.hd.rbase[0] = 0; }
-                if (lane == 0) { sh.next_item = 0; sh.ntok = 0; sh.ovf = tot > B7_TCAP ? 1 : 0; sh.exotic = 0; }
+                if (lane == 0) {
+                    sh.next_item = 0; sh.ntok = 0; sh.ovf = tot > B7_TCAP ? 1 : 0; sh.exotic = 0;
+                    sh.nent = 0; sh.oslot = reinterpret_cast<uint16_t*>(p.slabs + (size_t)u * B7_BLOB_BYTES + B7_BLOB_TABSLOT);
+                }
             }
             __syncthreads();
             const bool too_big = sh.ovf != 0;                         // uniform: written before the barrier, next writer is behind one
