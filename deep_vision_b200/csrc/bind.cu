@@ -41,8 +41,10 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (!ctx || n_sessions < 0 || !claim_off || !fact_off || !sess_claim_off || !sess_fact_off ||
         !out_best_fact || !out_best_score || !out_bound) { dvb_set_err(ctx, "dvb_bind_claims: invalid argument%s%s"); return DVB_E_INVALID; }
     if (n_sessions == 0) return DVB_OK;
+    dvb_trace tr("DVB_BIND_TRACE", "bind");
     dvb_scope sc(ctx);
     cudaStream_t st = sc.stream();
+    tr.at("scope");
     // ---- host view of the session/claim offsets (sizes; table capacity)
     std::vector<int64_t> h_sco, h_sfo, h_co, h_fo;
     int64_t n_claims = 0, n_facts = 0, claim_bytes = 0, fact_bytes = 0, co0 = 0, fo0 = 0;
@@ -124,6 +126,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
     if (fast) need += dvb_pad((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
                     + dvb_pad(4 * (size_t)n_slabs) + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
+    tr.at("sizes, occupancy");
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
     p.s_begin = 0; p.s_end = n_sessions; p.cap = cap;
@@ -190,6 +193,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         p.claim_pref_dim = claim_pref_dim; p.claim_threshold = claim_threshold;
         p.best_fact = out_best_fact; p.best_score = out_best_score; p.bound = out_bound; p.len_claim = out_len_claim; p.len_fact = out_len_fact;
     }
+    tr.at("inputs staged (H2D queued)");
     if (p.len_fact && n_facts) DVB_CUDA(ctx, cudaMemsetAsync(p.len_fact, 0, 4 * (size_t)n_facts, st));
     p.gtable = sc.alloc<unsigned long long>(((size_t)grid * (size_t)cap * 12 + 7) / 8);
     if (!p.gtable) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
@@ -327,8 +331,11 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         if (out_len_fact && n_facts && (e = cudaMemcpyAsync(out_len_fact, d_lf, 4 * (size_t)n_facts, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return e;
         return e;
     };
+    tr.at("kernels queued");
     DVB_CUDA(ctx, queue_host_out());
+    tr.at("D2H queued");
     DVB_CUDA(ctx, cudaStreamSynchronize(st));
+    tr.at("stream synchronised");
     if (fast && *(volatile int*)sc.l->flag_h) {               // sessions the cell walk handed back: exact re-run of exactly those
         p.only_flagged = p7.sess_fallback;
         DVB_CUDA(ctx, launch(false, 0, n_sessions));

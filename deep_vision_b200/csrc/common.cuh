@@ -1,5 +1,6 @@
 // common.cuh — ctx, stream/workspace leases and error plumbing for libdvb200.so (sm_100a).
 #pragma once
+#include <chrono>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -273,6 +274,16 @@ struct dvb_io {
         if (e != cudaSuccess) { dvb_set_err(ctx, "CUDA error %s at finish%s", cudaGetErrorString(e)); return DVB_E_CUDA; }
         if (one) for (auto& o : outs) if (o.bytes) memcpy(o.host, stage + DVB_SMALL_STAGE + (reinterpret_cast<uint8_t*>(o.dev) - lo), o.bytes);
         return DVB_OK;
+    }
+};
+
+// Host-side trace of one call (where the microseconds of a small call go): DVB_<NAME>_TRACE=1 prints the time since the call began
+// at every at().  Costs one getenv per call when off.
+struct dvb_trace {
+    bool on; const char* tag; std::chrono::steady_clock::time_point t0;
+    dvb_trace(const char* env, const char* tag_) : on([env] { const char* e = getenv(env); return e && e[0] == '1'; }()), tag(tag_), t0(std::chrono::steady_clock::now()) {}
+    void at(const char* what) const {
+        if (on) fprintf(stderr, "[%s] %-32s %8.0f us\n", tag, what, std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count());
     }
 };
 
