@@ -91,7 +91,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     const char* force = getenv("DVB_BIND_KERNEL");
     const bool fast = !(force && !strcmp(force, "general"));
     const size_t smem7 = bind7_smem_bytes(), smem7c = bind7_smem_bytes_claims();
-    int grid7 = 1, grid7c = 1;                                     // fact kernel (3 CTAs per SM), claim kernel (4)
+    int grid7 = 1, grid7c = 1, grid7_max = 1;                      // fact kernel (3 CTAs per SM), claim kernel (4); resident fact CTAs of the device
     if (fast) {
         static std::atomic<int> occ7_of[64];                       // per device: 0 = not asked yet; fact occupancy | claim occupancy << 8
         const int dslot = ctx->device & 63;
@@ -100,6 +100,7 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             int of = 1, oc = 1;
             DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_claim_tables, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7c));
             DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
+            DVB_CUDA(ctx, cudaFuncSetAttribute(k_bind_facts_split, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem7));
             DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&of, k_bind_facts, BIND_THREADS, smem7));
             DVB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&oc, k_bind_claim_tables, BIND_THREADS, smem7c));
             occ7 = std::max(1, std::min(of, 255)) | (std::max(1, std::min(oc, 255)) << 8);
@@ -107,7 +108,8 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
         }
         grid7c = (int)std::min<int64_t>(n_sessions + n_claims / BIND_CLAIMS, (int64_t)ctx->num_sm * (occ7 >> 8));   // CTAs take claim groups
         occ7 &= 255;
-        grid7 = (int)std::min<int64_t>(n_sessions + n_claims / BIND_CLAIMS, (int64_t)ctx->num_sm * occ7);
+        grid7_max = ctx->num_sm * occ7;
+        grid7 = (int)std::min<int64_t>(n_sessions + n_claims / BIND_CLAIMS, (int64_t)grid7_max);
     }
     // ---- workspace
     size_t need = 8192;
@@ -124,8 +126,10 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
     if (const char* e = getenv("DVB_BIND_SLAB_BUDGET")) { const long long v = atoll(e); if (v >= 1) slab_budget = v; }       // tests: force waves on small inputs
     const int64_t groups_bound = n_sessions + n_claims / BIND_CLAIMS;
     const int64_t n_slabs = fast ? std::min(groups_bound, slab_budget) : 0;
-    if (fast) need += dvb_pad((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
-                    + dvb_pad(4 * (size_t)n_slabs) + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
+    const int ws_ctas = std::max(std::max(grid7, grid7c), (int)std::min<int64_t>(grid7_max, (n_sessions + n_claims / BIND_CLAIMS) * BIND_MAX_PARTS));   // split fact kernel: groups x parts CTAs
+    if (fast) need += dvb_pad((size_t)ws_ctas * bind7_ws_u64_per_cta() * 8) + dvb_pad((size_t)n_sessions) + dvb_pad(4 * (size_t)n_sessions) + dvb_pad(64)
+                    + dvb_pad(4 * (size_t)n_slabs) * 2 + dvb_pad((size_t)grid7_max * BIND_CLAIMS * 8) + dvb_pad((size_t)grid7_max * BIND_CLAIMS * 4)
+                    + dvb_pad((size_t)n_slabs * B7_BLOB_BYTES);
     tr.at("sizes, occupancy");
     int32_t rc = sc.reserve(need); if (rc) return rc;
     BindParams p; memset(&p, 0, sizeof(p));
@@ -206,13 +210,16 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             DVB_CUDA(ctx, cudaHostGetDevicePointer((void**)&l->flag_d, l->flag_h, 0));
         }
         *(volatile int*)l->flag_h = 0;
-        p7.gtable = sc.alloc<unsigned long long>((size_t)std::max(grid7, grid7c) * bind7_ws_u64_per_cta());
+        p7.gtable = sc.alloc<unsigned long long>((size_t)ws_ctas * bind7_ws_u64_per_cta());
         p7.sess_fallback = sc.alloc<uint8_t>((size_t)n_sessions);
         p7.sess_slab = sc.alloc<int32_t>((size_t)n_sessions);
         p7.slab_cursor = sc.alloc<int>(16);
         p7.slab_sess = sc.alloc<int32_t>((size_t)n_slabs);
+        p7.part_cnt = sc.alloc<int>((size_t)n_slabs);
+        p7.part_score = sc.alloc<double>((size_t)grid7_max * BIND_CLAIMS);          // groups x parts <= the fact kernel's resident CTAs when it splits
+        p7.part_idx = sc.alloc<int>((size_t)grid7_max * BIND_CLAIMS);
         p7.slabs = sc.alloc<uint8_t>((size_t)n_slabs * B7_BLOB_BYTES);
-        if (!p7.gtable || !p7.sess_fallback || !p7.sess_slab || !p7.slab_cursor || !p7.slab_sess || !p7.slabs) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
+        if (!p7.gtable || !p7.sess_fallback || !p7.sess_slab || !p7.slab_cursor || !p7.slab_sess || !p7.part_cnt || !p7.part_score || !p7.part_idx || !p7.slabs) { dvb_set_err(ctx, "workspace layout error%s%s"); return DVB_E_NOMEM; }
         DVB_CUDA(ctx, cudaMemsetAsync(p7.sess_fallback, 0, (size_t)n_sessions, st));
         p7.overflow = l->flag_d;
     }
@@ -262,7 +269,12 @@ extern "C" int32_t dvb_bind_claims(dvb_ctx* ctx, int32_t mem,
             if (units > 0) {
                 k_bind_groups<<<1, B7_GROUPS_THREADS, 0, st>>>(q);
                 k_bind_claim_tables<<<(int)std::min<int64_t>(units, (int64_t)grid7c), BIND_THREADS, smem7c, st>>>(q);
-                k_bind_facts<<<(int)std::min<int64_t>(units, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
+                // fewer groups than half the resident CTAs (one report per call): the facts of every group are cut into `parts` ranges
+                const int parts = (int)std::min<int64_t>(BIND_MAX_PARTS, (int64_t)grid7_max / units);
+                if (parts >= 2 && !getenv("DVB_BIND_NO_SPLIT")) {
+                    q.parts = parts;
+                    k_bind_facts_split<<<(int)(units * parts), BIND_THREADS, smem7, st>>>(q);
+                } else k_bind_facts<<<(int)std::min<int64_t>(units, (int64_t)grid7), BIND_THREADS, smem7, st>>>(q);
                 ctx->launches += 3;
                 const cudaError_t e = cudaGetLastError();
                 if (e != cudaSuccess) return e;

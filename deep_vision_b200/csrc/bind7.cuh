@@ -95,7 +95,7 @@ struct __align__(16) B7Shared {
     uint8_t lut[128];
     int next_item, ntok, ovf, exotic, wcnt[BIND_WARPS];
     uint32_t tsum[32];                             // pack: token keys per 32-slot word
-    uint32_t nent, pad_;                           // claim kernel: bigram-table entries created so far in this group
+    uint32_t nent, last;                           // claim kernel: bigram-table entries created so far in this group | split fact kernel: this CTA reduces
     uint16_t* oslot;                               // claim kernel: their slots, appended to the group's slab as they are created
     // LAST member: the fact kernel uses all of it (per warp [0, B7_TCAP) hit flags by token index, then its B7Scratch); the claim
     // kernel allocates only BIND_WARPS * B7_HSTRIDE_C bytes of it (per warp its B7Scratch, then B7_TCAP "already listed" BITS),
@@ -843,7 +843,7 @@ __global__ void __launch_bounds__(B7_GROUPS_THREADS) k_bind_groups(BindParams p)
         for (int k = 0; k < B7_GROUPS_PER_THREAD; k++) {
             if (sa + k < p.s_end) {
                 p.sess_slab[sa + k] = (int32_t)base;
-                for (uint32_t g = 0; g < ng[k]; g++) p.slab_sess[base + g] = (int32_t)(sa + k);
+                for (uint32_t g = 0; g < ng[k]; g++) { p.slab_sess[base + g] = (int32_t)(sa + k); p.part_cnt[base + g] = 0; }
             }
             base += ng[k];
         }
@@ -931,14 +931,20 @@ __global__ void __launch_bounds__(BIND_THREADS, 4) k_bind_claim_tables(BindParam
 }
 
 // ---------------------------------------------------------------- kernel 2 of 2: the facts of every session against its groups' tables
-__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
+// SPLIT: a launch with fewer groups than SMs (one report per call) cuts the facts of every group into p.parts ranges, one CTA
+// each; a part leaves its best (score, fact) per claim in scratch and the LAST part of a group to finish (ticket counter,
+// no waiting) reduces them under the same order and writes the outputs.  The plain kernel is the same code with one part.
+template <bool SPLIT>
+__device__ __forceinline__ void b7_facts_body(const BindParams& p) {
     B7Shared& sh = B7_SH();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     unsigned long long* tkeys = p.gtable + (size_t)blockIdx.x * (size_t)B7_CAPT;
     B7Tok t;
     b7_cta_init<false>(sh, t, tkeys);
     const int n_units = *p.slab_cursor;
-    for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+    const int parts = SPLIT ? p.parts : 1;
+    for (int w = blockIdx.x; w < n_units * parts; w += gridDim.x) {
+        const int u = SPLIT ? w / parts : w, part = SPLIT ? w % parts : 0;
         // a group the claim kernel handed back has no tables (its session number is stored negated); nothing writes slab_sess
         // in this kernel, so the branch is uniform.  The other groups of such a session are scored here and again by the general kernel
         if (p.slab_sess[u] < 0) continue;
@@ -961,11 +967,12 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
             const int pref = lane < ncg ? p.claim_pref_dim[cg + lane] : -1;
             const uint32_t ttot = sh.hd.rbase[ncg];
             const int nf = (int)(f1 - f0);
+            const int fa = SPLIT ? (int)((int64_t)nf * part / parts) : 0, fb = SPLIT ? (int)((int64_t)nf * (part + 1) / parts) : nf;   // this CTA's facts
             for (;;) {
                 int f = 0;
-                if (lane == 0) f = atomicAdd(&sh.next_item, 1);
+                if (lane == 0) f = fa + atomicAdd(&sh.next_item, 1);
                 f = __shfl_sync(B7_FULL, f, 0);
-                if (f >= nf) break;
+                if (f >= fb) break;
                 const int64_t b = p.fact_off[f0 + f], e = p.fact_off[f0 + f + 1];
                 t.cert = false;
                 if (B7_RUNG >= 1) b7_text<false>(t, p.fact_utf8 + b, (int32_t)(e - b));
@@ -1010,13 +1017,34 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
             __syncthreads();
             if (sh.exotic) handback = true;                          // uniform; no writer until the next barrier
             // ---- per-claim reduction over the warps
+            double b = -1.0; int bf = 0x7fffffff;
             if (tid < ncg) {
-                double b = -1.0; int bf = 0x7fffffff;
-                for (int w = 0; w < BIND_WARPS; w++) {
-                    const B7Scratch* ws = reinterpret_cast<const B7Scratch*>(sh.H[w] + B7_TCAP);
+                for (int wi = 0; wi < BIND_WARPS; wi++) {
+                    const B7Scratch* ws = reinterpret_cast<const B7Scratch*>(sh.H[wi] + B7_TCAP);
                     const double sc = ws->rbest[tid]; const int fi = ws->ridx[tid];
                     if (sc > b || (sc == b && fi < bf)) { b = sc; bf = fi; }
                 }
+            }
+            bool writer = true;                                       // this CTA writes the group's outputs
+            if (SPLIT) {
+                const size_t slot0 = ((size_t)u * (size_t)parts) * BIND_CLAIMS;
+                if (tid < ncg) { p.part_score[slot0 + (size_t)part * BIND_CLAIMS + tid] = b; p.part_idx[slot0 + (size_t)part * BIND_CLAIMS + tid] = bf; }
+                __threadfence();
+                __syncthreads();
+                if (tid == 0) sh.last = (atomicAdd(&p.part_cnt[u], 1) == parts - 1) ? 1u : 0u;
+                __syncthreads();
+                writer = sh.last != 0u;                               // uniform; the next writer of sh.last is behind the barriers of the unpack
+                if (writer && tid < ncg) {
+                    __threadfence();
+                    b = -1.0; bf = 0x7fffffff;
+                    for (int q = 0; q < parts; q++) {
+                        const double sc = *(volatile const double*)&p.part_score[slot0 + (size_t)q * BIND_CLAIMS + tid];
+                        const int fi = *(volatile const int*)&p.part_idx[slot0 + (size_t)q * BIND_CLAIMS + tid];
+                        if (sc > b || (sc == b && fi < bf)) { b = sc; bf = fi; }
+                    }
+                }
+            }
+            if (writer && tid < ncg) {
                 const int64_t c = cg + tid;
                 const bool any = b >= 0.0;
                 p.best_fact[c] = any ? bf : -1;
@@ -1029,3 +1057,5 @@ __global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) {
         if (handback && tid == 0) { p.sess_fallback[s] = 1; *p.overflow = 1; }
     }
 }
+__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts(BindParams p) { b7_facts_body<false>(p); }
+__global__ void __launch_bounds__(BIND_THREADS, 3) k_bind_facts_split(BindParams p) { b7_facts_body<true>(p); }

@@ -10,6 +10,7 @@
 #define BIND_FB_BITS 16         // bigram filter: 2^16 bits = 8 KB
 #define BIND_FT_BITS 13         // token filter: 2^13 bits = 1 KB
 #define BIND_QCAP 64
+#define BIND_MAX_PARTS 8        // split fact kernel: at most this many CTAs per claim group
 
 // a lane that polls memory another lane (possibly of its own warp) is about to write: the GPU schedules diverged lanes
 // independently; the CPU emulator of the tests runs lanes as cooperative fibers and has to be told to switch
@@ -35,6 +36,9 @@ struct BindParams {
     int* slab_cursor;                     // fast kernels: claim groups (= slabs in use) of this launch
     int32_t* sess_slab;                   // fast kernels: first slab of session s
     int32_t* slab_sess;                   // fast kernels: session of slab u (-1 - s once the claim kernel handed the group back)
+    int parts;                            // split fact kernel: CTAs per claim group (each walks 1 / parts of the session's facts)
+    int* part_cnt;                        // fast kernels: per group, parts that have finished (zeroed by k_bind_groups)
+    double* part_score; int* part_idx;    // split fact kernel: [group * parts + part][32] best score / fact per claim
 };
 
 __device__ __forceinline__ uint32_t bind_hash(uint64_t key) {

@@ -46,9 +46,17 @@ extern "C" int emu_bind_claims(const uint8_t* claim_utf8, const int64_t* claim_o
         std::vector<int32_t> sess_slab((size_t)n_sessions), slab_sess((size_t)n_groups + 1);
         int cursor = 0;
         p.slabs = reinterpret_cast<uint8_t*>(slabs.data()); p.slab_cursor = &cursor; p.sess_slab = sess_slab.data(); p.slab_sess = slab_sess.data();
+        // EMU_BIND_PARTS=n: the split fact kernel with n CTAs per claim group (dvb_bind_claims takes it for launches of few groups)
+        const char* pe = getenv("EMU_BIND_PARTS");
+        const int parts = pe ? std::max(1, std::min(atoi(pe), BIND_MAX_PARTS)) : 1;
+        std::vector<int> part_cnt((size_t)n_groups + 1), part_idx((size_t)(n_groups + 1) * parts * BIND_CLAIMS);
+        std::vector<double> part_score((size_t)(n_groups + 1) * parts * BIND_CLAIMS);
+        p.part_cnt = part_cnt.data(); p.part_score = part_score.data(); p.part_idx = part_idx.data(); p.parts = parts;
         emu::launch(1u, B7_GROUPS_THREADS, [&] { k_bind_groups(p); });
         emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_claim_tables(p); });
-        emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_facts(p); });
+        if (getenv("EMU_BIND_VERBOSE")) fprintf(stderr, "emu_bind: %d part(s) per claim group\n", parts);
+        if (parts >= 2) emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_facts_split(p); });
+        else emu::launch((unsigned)grid, BIND_THREADS, [&] { k_bind_facts(p); });
     }
     if (mode == 2 || (mode == 0 && overflow)) {
         const uint32_t cap = emu_table_cap(mx);
