@@ -61,6 +61,18 @@ def test_emu_group_numbering_across_steps(emu, oracle):
     _check(emu, oracle, bc.many_tiny_sessions(), expect_handback=0, grid=7)  # k_bind_groups: 4300 sessions > one 4096-session step
 
 
+@pytest.mark.parametrize("parts", [2, 3, 8])
+def test_emu_split_fact_kernel(emu, oracle, monkeypatch, parts):
+    """k_bind_facts_split (what dvb_bind_claims launches when a call has few claim groups): the facts of every group over
+    `parts` CTAs, the last one to finish reduces the per-part bests — same answers, ties on the lower fact index included."""
+    monkeypatch.setenv("EMU_BIND_PARTS", str(parts))
+    _check(emu, oracle, bc.degenerate(), expect_handback=0)                  # sessions with fewer facts than parts, without facts, without claims
+    _check(emu, oracle, bc.mixed_real_text(), expect_handback=0)
+    _check(emu, oracle, bc.synthetic(4, 7, 33), expect_handback=0)
+    _check(emu, oracle, bc.handback_in_one_group(), expect_handback=2, grid=5)
+    _check(emu, oracle, bc.long_facts(1), expect_handback=1)
+
+
 def test_emu_crowded_bucket_side_list(emu, oracle):
     _check(emu, oracle, bc.crowded_bucket(5), expect_handback=0)             # one key in the side list
     _check(emu, oracle, bc.crowded_bucket(30), expect_handback=0)            # 26 keys in the side list

@@ -166,6 +166,19 @@ def test_a2_group_numbering_across_steps(gpu_ctx, oracle):
     _bind_vs_oracle(gpu_ctx, oracle, bc.many_tiny_sessions())
 
 
+def test_a2_split_and_plain_fact_kernels_agree(gpu_ctx, oracle, monkeypatch):
+    """A call of few claim groups runs k_bind_facts_split (facts of a group over several CTAs); DVB_BIND_NO_SPLIT=1 forces the
+    plain kernel: both equal the oracle, bit for bit."""
+    import bind_cases as bc
+    for a in (bc.synthetic(3, 12, 40), bc.synthetic(40, 7, 33), bc.mixed_real_text()):
+        split = _bind_vs_oracle(gpu_ctx, oracle, a)
+        monkeypatch.setenv("DVB_BIND_NO_SPLIT", "1")
+        plain = _bind_vs_oracle(gpu_ctx, oracle, a)
+        monkeypatch.delenv("DVB_BIND_NO_SPLIT")
+        assert np.array_equal(split["best_score"].view(np.uint64), plain["best_score"].view(np.uint64))
+        assert np.array_equal(split["best_fact"], plain["best_fact"])
+
+
 def test_a2_token_table_overflow_reruns_general(gpu_ctx, oracle):
     """> 704 distinct ASCII tokens in one claim group: the fast kernel raises `overflow`, the call re-runs exactly."""
     from deep_vision_b200 import packing
