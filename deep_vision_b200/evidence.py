@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import re
+from operator import is_ as _is
 from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
@@ -157,7 +158,7 @@ def binding_threshold(field: str, min_score: Any, preferred_dimension: str, evid
 class _Session:
     """Facts of one evidence_pack in device order (only facts whose q_id matches Q\\d+, 24817-24819)."""
 
-    __slots__ = ("qids", "texts", "quality", "dims", "hard", "dim_ids")
+    __slots__ = ("qids", "texts", "quality", "dims", "hard", "dim_ids", "_packed")
 
     def __init__(self, evidence_pack: dict):
         self.qids: List[str] = []
@@ -166,6 +167,7 @@ class _Session:
         self.dims: List[int] = []
         self.hard: List[int] = []
         self.dim_ids: Dict[str, int] = {}
+        self._packed = None
         facts = evidence_pack.get("facts", [])
         for fact in facts if isinstance(facts, list) else []:
             if not isinstance(fact, dict):
@@ -180,6 +182,46 @@ class _Session:
             self.quality.append(max(0.0, min(1.0, _as_float(fact.get("quality_score", 0.0), 0.0))))
             self.dims.append(self.dim_ids.setdefault(dim, len(self.dim_ids)))
             self.hard.append(1 if bool(fact.get("hard_triggered", False)) else 0)
+
+    def packed(self):
+        """The five fact arrays of dvb_bind_claims for a call on this session alone (built once per session object)."""
+        if self._packed is None:
+            fu, fo = pack_texts(self.texts)
+            self._packed = (fu, fo, np.asarray(self.quality, np.float64), np.asarray(self.dims, np.int32), np.asarray(self.hard, np.uint8))
+        return self._packed
+
+
+# The reference calls infer_weak_evidence_refs_v3 once per draft item against the SAME evidence pack (web/server.py:24871-24935):
+# packing its facts (join, encode, numpy) is ~100 us of a ~200 us call.  A session is kept per pack object and reused while
+# every value _Session reads from every fact is still the very same object (identity, not equality: `1`, `1.0` and `True`
+# compare equal and print differently).  The entry holds references to those values, so an id cannot be recycled under it; only
+# immutable value types are cached — a fact holding a list or a dict is packed afresh every call.
+_FACT_KEYS = ("q_id", "question", "answer", "dimension_name", "dimension", "quality_score", "hard_triggered")
+_IMMUTABLE = (str, int, float, bool, type(None))
+_SESSION_CACHE: Dict[int, Tuple[list, _Session]] = {}
+SESSION_CACHE_ENTRIES = 16          # 0 switches the cache off
+
+
+def _session_for(pack: dict) -> _Session:
+    if SESSION_CACHE_ENTRIES <= 0:
+        return _Session(pack)
+    facts = pack.get("facts", [])
+    vals: list = []
+    for fact in facts if isinstance(facts, list) else []:
+        if type(fact) is not dict:                       # the reference skips non-dicts; dict subclasses may compute values
+            return _Session(pack)
+        vals.extend(map(fact.get, _FACT_KEYS))
+    hit = _SESSION_CACHE.get(id(pack))
+    if hit is not None and len(hit[0]) == len(vals) and all(map(_is, hit[0], vals)):
+        return hit[1]
+    sess = _Session(pack)
+    if all(type(v) in _IMMUTABLE for v in vals):
+        if len(_SESSION_CACHE) >= SESSION_CACHE_ENTRIES:
+            _SESSION_CACHE.clear()
+        _SESSION_CACHE[id(pack)] = (vals, sess)
+    else:
+        _SESSION_CACHE.pop(id(pack), None)
+    return sess
 
 
 def bind_packed(ctx: "_lib.Context", claim_utf8, claim_off, fact_utf8, fact_off, sess_claim_off, sess_fact_off,
@@ -239,7 +281,7 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
             continue
         key = id(pack)
         if key not in sessions:
-            sessions[key] = (_Session(pack), [])
+            sessions[key] = (_session_for(pack), [])
             order.append(key)
         sess, claims = sessions[key]
         claim_text = " ".join(_text(item.get(k, "")) for k in CLAIM_TEXT_FIELDS[field])
@@ -259,7 +301,17 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
         ctx = ctx or _lib.Context.get()
         claim_texts, fact_texts, sco, sfo = [], [], [0], [0]
         fq, fd, fh, cp, ct = [], [], [], [], []
-        for k in order:
+        if len(order) == 1:                               # one pack (the reference's call shape): its packed fact arrays are kept with the session
+            sess, claims = sessions[order[0]]
+            fu, fo, a_fq, a_fd, a_fh = sess.packed()
+            cu, co = pack_texts([t for (_i, t, _p, _th) in claims])
+            out = bind_packed(ctx, cu, co, fu, fo, np.asarray([0, len(claims)], np.int64), np.asarray([0, len(sess.texts)], np.int64),
+                              a_fq, a_fd, a_fh, np.asarray([p for (_i, _t, p, _th) in claims], np.int32),
+                              np.asarray([th for (_i, _t, _p, th) in claims], np.float64))
+            order_multi = []
+        else:
+            order_multi = order
+        for k in order_multi:
             sess, claims = sessions[k]
             claim_texts.extend(t for (_i, t, _p, _th) in claims)
             cp.extend(p for (_i, _t, p, _th) in claims)
@@ -270,11 +322,12 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
             fh.extend(sess.hard)
             sco.append(len(claim_texts))
             sfo.append(len(fact_texts))
-        cu, co = pack_texts(claim_texts)
-        fu, fo = pack_texts(fact_texts)
-        out = bind_packed(ctx, cu, co, fu, fo, np.asarray(sco, np.int64), np.asarray(sfo, np.int64),
-                          np.asarray(fq, np.float64), np.asarray(fd, np.int32), np.asarray(fh, np.uint8),
-                          np.asarray(cp, np.int32), np.asarray(ct, np.float64))
+        if order_multi:
+            cu, co = pack_texts(claim_texts)
+            fu, fo = pack_texts(fact_texts)
+            out = bind_packed(ctx, cu, co, fu, fo, np.asarray(sco, np.int64), np.asarray(sfo, np.int64),
+                              np.asarray(fq, np.float64), np.asarray(fd, np.int32), np.asarray(fh, np.uint8),
+                              np.asarray(cp, np.int32), np.asarray(ct, np.float64))
         pos = 0
         for k in order:
             sess, claims = sessions[k]

@@ -337,3 +337,70 @@ def test_fuzz_f4_slim_facts_live(ref):
             assert got == want
             n += 1
     assert n == 1200
+
+
+def test_a2_session_cache_follows_in_place_changes(ref, oracle, monkeypatch):
+    """evidence._session_for keeps the packed facts of an evidence pack between calls (the reference calls
+    infer_weak_evidence_refs_v3 once per draft item on the same pack).  Every way of changing the pack in place — a fact's
+    text, quality, q_id, dimension, a fact replaced, appended, removed, a value swapped for an equal one of another type —
+    must show in the next call exactly as it does in the reference."""
+    import conftest
+    from deep_vision_b200 import evidence
+    monkeypatch.setattr(evidence, "bind_packed", conftest.oracle_bind_packed)
+    evidence._SESSION_CACHE.clear()
+    built = []
+    real_session = evidence._Session
+    class Counting(real_session):
+        __slots__ = ()
+        def __init__(self, pack):
+            built.append(1)
+            real_session.__init__(self, pack)
+    monkeypatch.setattr(evidence, "_Session", Counting)
+    rng = random.Random(11)
+    pack = _random_pack(rng, 12)
+    items = [(f, _random_item(rng, f, pack)) for f in ("risks", "actions", "open_questions") for _ in range(4)]
+
+    def check():
+        for field, item in items:
+            want = ref["infer_weak_evidence_refs_v3"](field, item, pack)
+            got = evidence.infer_weak_evidence_refs_v3(field, item, pack, ctx=object())
+            assert got == want, (field, item)
+
+    check()
+    assert len(built) == 1                                           # twelve calls, one packing
+    check()
+    assert len(built) == 1
+    facts = pack["facts"]
+    edits = [
+        lambda: facts[0].__setitem__("answer", facts[0]["answer"] + " 离线审批 断网补录"),
+        lambda: facts[1].__setitem__("quality_score", 0.99),
+        lambda: facts[2].__setitem__("q_id", "nope"),
+        lambda: facts[3].__setitem__("dimension", "customer_needs" if facts[3].get("dimension") != "customer_needs" else "tech_constraints"),
+        lambda: facts[4].__setitem__("hard_triggered", not bool(facts[4].get("hard_triggered"))),
+        lambda: facts.__setitem__(5, dict(facts[5], question="预算 审批 流程 " + str(facts[5].get("question", "")))),
+        lambda: facts.append(dict(facts[0], q_id="Q99")),
+        lambda: facts.pop(1),
+        lambda: facts[0].__setitem__("quality_score", 1),              # int 1, then True: equal values, different objects
+        lambda: facts[0].__setitem__("quality_score", True),
+        lambda: facts[0].pop("dimension_name", None),
+    ]
+    for n, edit in enumerate(edits, start=2):
+        edit()
+        check()
+        assert len(built) == n, n                                      # repacked once per edit, not per call
+    # a value that can change without changing identity is never cached
+    facts[0]["answer"] = ["列表", "答案"]
+    before = len(built)
+    check()
+    assert len(built) == before + len(items)
+    facts[0]["answer"].append("预算有限 需要 审批")
+    check()
+    assert id(pack) not in evidence._SESSION_CACHE
+    # a new pack object at a recycled address cannot hit the old entry: the entry is validated by the identity of its values
+    evidence._SESSION_CACHE.clear()
+    other = _random_pack(rng, 7)
+    evidence.infer_weak_evidence_refs_v3("risks", items[0][1], other, ctx=object())
+    ent = evidence._SESSION_CACHE[id(other)]
+    evidence._SESSION_CACHE[id(pack)] = ent                            # as if `pack` had been allocated where `other` was
+    facts[0]["answer"] = "普通答案"
+    check()
