@@ -270,6 +270,9 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
     resolver = dimension_resolver or infer_item_dimension_key
     sessions: Dict[int, Tuple[_Session, List[Tuple[int, str, int, float]]]] = {}
     order: List[int] = []
+    # the kept sessions serve the reference's call shape (a few packs, many calls); a bulk batch of more packs than the cache
+    # holds would only evict itself
+    few_packs = len(requests) <= SESSION_CACHE_ENTRIES or len({id(r[2]) for r in requests}) <= SESSION_CACHE_ENTRIES
     for i, (field, item, pack, min_score) in enumerate(requests):
         empty = {"refs": [], "score": 0.0}
         if not config.enabled or field not in CLAIM_TEXT_FIELDS or not isinstance(item, dict) or not isinstance(pack, dict):
@@ -281,7 +284,7 @@ def bind_batch(requests: Sequence[Tuple[str, dict, dict, Any]], *, config: WeakB
             continue
         key = id(pack)
         if key not in sessions:
-            sessions[key] = (_session_for(pack), [])
+            sessions[key] = (_session_for(pack) if few_packs else _Session(pack), [])
             order.append(key)
         sess, claims = sessions[key]
         claim_text = " ".join(_text(item.get(k, "")) for k in CLAIM_TEXT_FIELDS[field])
